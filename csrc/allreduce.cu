@@ -1,0 +1,206 @@
+// Stand-alone peer-memory all-reduce of a flat fp32 vector, optionally fused with
+// the 1/W scale and the SGD-momentum update.
+//
+// Used (a) by the layer-at-a-time / autograd path, where gradients already sit in
+// Network._flat_grad, launched per bucket on a side stream; (b) in the
+// reference-parity "epoch-average" and "replication" modes, where the vector is
+// the PARAMETER buffer and the op is a plain mean (reference:
+// data_parallelism_train.py:238-240, model_replication_train.py:134-136 -- R1);
+// (c) by the latency benchmark that picks the variant per message size.
+//
+// Variants
+//   one-shot : every rank pushes its slice to every peer, then sums locally.
+//              (W-1) x bytes out per rank, ONE flag round trip. Wins while the
+//              message is latency-bound (248 KB gradient of this CNN).
+//   two-shot : slice s is owned by the (s mod n)-th configured rank; others push
+//              only to the owner, the owner reduces and pushes the result back.
+//              2(W-1)/W x bytes, TWO flag round trips. Wins for large vectors.
+//              Ownership needs a static membership, so ranks must not leave
+//              between the host's membership updates while this variant is used.
+//
+// The fused step path (fused_step.cu: update_kernel) embeds the one-shot variant
+// directly behind its wgrad tiles.
+#include <cuda_runtime.h>
+
+#include "common.cuh"
+#include "exchange.cuh"
+#include "layout.h"
+#include "step_types.h"
+
+namespace dnnb200 {
+
+constexpr int kArThreads = kSlice / 4;  // 128 threads, one float4 each
+
+enum ArMode : int {
+  kArMean = 0,  // out = mean(in)
+  kArSgd = 1,   // g = mean(in); momentum = mu*momentum + g; params -= lr*momentum   (out optional: g)
+};
+
+struct ArParams {
+  const float* in[kMaxWorld];  // per virtual rank
+  float* out[kMaxWorld];
+  int n;         // elements (multiple of 4, <= kFlatNumel)
+  int mode;      // ArMode
+  int two_shot;  // 0/1
+};
+
+__device__ __forceinline__ void finish(const RankCtx& cx, const ArParams& prm, int vr, int i, const float (&v)[4],
+                                       int n) {
+  const float inv = 1.f / (float)n;
+  const float4 g = make_float4(v[0] * inv, v[1] * inv, v[2] * inv, v[3] * inv);
+  if (prm.mode == kArSgd) {
+    const float lr = cx.ctl->lr, mu = cx.ctl->mu;
+    float4 m = *reinterpret_cast<float4*>(cx.momentum + i);
+    float4 p = *reinterpret_cast<float4*>(cx.params + i);
+    m.x = mu * m.x + g.x; m.y = mu * m.y + g.y; m.z = mu * m.z + g.z; m.w = mu * m.w + g.w;
+    p.x -= lr * m.x; p.y -= lr * m.y; p.z -= lr * m.z; p.w -= lr * m.w;
+    *reinterpret_cast<float4*>(cx.momentum + i) = m;
+    *reinterpret_cast<float4*>(cx.params + i) = p;
+  }
+  if (prm.out[vr]) *reinterpret_cast<float4*>(prm.out[vr] + i) = g;
+}
+
+__global__ void __launch_bounds__(kArThreads)
+allreduce_kernel(const RankCtx* __restrict__ ctxs, const ArParams prm) {
+  __shared__ ExchangeShared xsh;
+  __shared__ unsigned int s_ok;
+  const int vr = blockIdx.y;
+  const RankCtx& cx = ctxs[vr];
+  StepCtl* ctl = cx.ctl;
+  const int slice = blockIdx.x, tid = threadIdx.x;
+  const int i = slice * kSlice + 4 * tid;
+  const bool in_range = i < prm.n;
+  const unsigned long long step = *reinterpret_cast<volatile unsigned long long*>(&ctl->step);
+  const unsigned int seq = (unsigned int)(step + 1ull);
+  const int world = cx.world, rank = cx.rank;
+
+  float v[4] = {0.f, 0.f, 0.f, 0.f};
+  if (in_range) {
+    const float4 t = *reinterpret_cast<const float4*>(prm.in[vr] + i);
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
+  int n = 1;
+  if (world > 1 && !prm.two_shot) {
+    exchange_slice<4>(cx, &xsh, slice, seq, i, in_range, v, &n);
+    if (in_range) finish(cx, prm, vr, i, v, n);
+  } else if (world > 1) {
+    // ---------------- two-shot ----------------
+    const unsigned int configured = ctl->active_mask;
+    const int n_cfg = __popc(configured);
+    // owner = the (slice mod n_cfg)-th set bit of the configured mask
+    int owner = 0;
+    {
+      int k = slice % n_cfg;
+      for (int p = 0; p < world; ++p)
+        if ((configured >> p) & 1u) { if (k == 0) { owner = p; break; } --k; }
+    }
+    const unsigned int parity = seq & 1u;
+    unsigned int* my_flags = cx.flags[rank];
+    const unsigned long long tmo = ctl->timeout_ns;
+    float* my_recv = cx.recv[rank];
+    if (rank != owner) {
+      // phase 1: push to the owner only
+      if (in_range)
+        *reinterpret_cast<float4*>(cx.recv[owner] + ((size_t)(parity * world + rank) * kFlatNumel + i)) =
+            make_float4(v[0], v[1], v[2], v[3]);
+      __syncthreads();
+      if (tid == 0) {
+        __threadfence_system();
+        st_release_sys(cx.flags[owner] + rank * kFlagRow + slice, seq);
+        // phase 2: wait for the owner's result (second flag bank)
+        const unsigned int* f = my_flags + (kMaxWorld + owner) * kFlagRow + slice;
+        unsigned long long t0 = 0; unsigned int spins = 0; unsigned int ok = 1u;
+        while (!seq_reached(ld_acquire_sys(f), seq)) {
+          if (tmo != 0ull && (++spins & 0x3ffu) == 0u) {
+            const unsigned long long now = globaltimer_ns();
+            if (t0 == 0ull) t0 = now;
+            else if (now - t0 > tmo) { atomicOr(&ctl->status, kStatusTimeout | (1u << (8 + owner))); ok = 0u; break; }
+          }
+        }
+        s_ok = ok;
+      }
+      __syncthreads();
+      if (in_range && s_ok) {
+        const float4 t = ld_cg_f4(reinterpret_cast<const float4*>(
+            my_recv + ((size_t)(parity * world + owner) * kFlatNumel + i)));
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+        finish(cx, prm, vr, i, v, 1);  // the owner already divided
+      }
+    } else {
+      // owner: wait for every configured peer, reduce in rank order, broadcast the mean
+      if (tid == 0) s_ok = 1u;
+      __syncthreads();
+      if (tid < world && tid != rank && ((configured >> tid) & 1u)) {
+        const unsigned int* f = my_flags + tid * kFlagRow + slice;
+        unsigned long long t0 = 0; unsigned int spins = 0;
+        while (!seq_reached(ld_acquire_sys(f), seq)) {
+          if (tmo != 0ull && (++spins & 0x3ffu) == 0u) {
+            const unsigned long long now = globaltimer_ns();
+            if (t0 == 0ull) t0 = now;
+            else if (now - t0 > tmo) { atomicOr(&ctl->status, kStatusTimeout | (1u << (8 + tid))); atomicAnd(&s_ok, 0u); break; }
+          }
+        }
+      }
+      __syncthreads();
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      if (in_range) {
+        for (int p = 0; p < world; ++p) {
+          if (!((configured >> p) & 1u)) continue;
+          if (p == rank) { acc[0] += v[0]; acc[1] += v[1]; acc[2] += v[2]; acc[3] += v[3]; }
+          else {
+            const float4 t = ld_cg_f4(reinterpret_cast<const float4*>(
+                my_recv + ((size_t)(parity * world + p) * kFlatNumel + i)));
+            acc[0] += t.x; acc[1] += t.y; acc[2] += t.z; acc[3] += t.w;
+          }
+        }
+        const float inv = 1.f / (float)n_cfg;
+        const float4 mean = make_float4(acc[0] * inv, acc[1] * inv, acc[2] * inv, acc[3] * inv);
+        for (int p = 0; p < world; ++p) {
+          if (p == rank || !((configured >> p) & 1u)) continue;
+          *reinterpret_cast<float4*>(cx.recv[p] + ((size_t)(parity * world + rank) * kFlatNumel + i)) = mean;
+        }
+        v[0] = mean.x; v[1] = mean.y; v[2] = mean.z; v[3] = mean.w;
+      }
+      __syncthreads();
+      if (tid < world && tid != rank && ((configured >> tid) & 1u)) {
+        __threadfence_system();
+        st_release_sys(cx.flags[tid] + (kMaxWorld + rank) * kFlagRow + slice, seq);
+      }
+      if (in_range) finish(cx, prm, vr, i, v, 1);
+    }
+  } else {
+    if (in_range) finish(cx, prm, vr, i, v, 1);
+  }
+
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    const unsigned int done = atomicAdd(&ctl->ctas_done, 1u);
+    if (done == gridDim.x - 1) {
+      ctl->ctas_done = 0u;
+      __threadfence();
+      *reinterpret_cast<volatile unsigned long long*>(&ctl->step) = step + 1ull;
+    }
+  }
+}
+
+int launch_allreduce(const RankCtx* d_ctxs, int n_virtual_ranks, const float* const* in, float* const* out,
+                     int n, int mode, int two_shot, cudaStream_t stream) {
+  DNN_ARG_CHECK(n > 0 && n <= kFlatNumel && (n % 4) == 0, "allreduce: n must be a multiple of 4 and <= %d", kFlatNumel);
+  DNN_ARG_CHECK(n_virtual_ranks >= 1 && n_virtual_ranks <= kMaxWorld, "allreduce: bad virtual rank count");
+  ArParams prm;
+  for (int r = 0; r < kMaxWorld; ++r) { prm.in[r] = nullptr; prm.out[r] = nullptr; }
+  for (int r = 0; r < n_virtual_ranks; ++r) { prm.in[r] = in[r]; prm.out[r] = out[r]; }
+  prm.n = n; prm.mode = mode; prm.two_shot = two_shot;
+  dim3 grid((n + kSlice - 1) / kSlice, n_virtual_ranks);
+  if (n_virtual_ranks > 1) {
+    void* args[] = {(void*)&d_ctxs, (void*)&prm};
+    DNN_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)allreduce_kernel, grid, dim3(kArThreads), args, 0, stream));
+  } else {
+    allreduce_kernel<<<grid, kArThreads, 0, stream>>>(d_ctxs, prm);
+    DNN_CUDA_CHECK(cudaGetLastError());
+  }
+  return kOk;
+}
+
+}  // namespace dnnb200

@@ -1,0 +1,77 @@
+// Small device/host helpers shared by all translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+namespace dnnb200 {
+
+// Error codes returned by every extern "C" entry point (0 = ok).
+enum : int {
+  kOk = 0,
+  kErrCuda = 1,      // a CUDA runtime call failed (message via dnnb200_last_error)
+  kErrArg = 2,       // invalid argument / unsupported shape
+  kErrState = 3,     // object not in the right state
+  kErrTimeout = 4,   // a peer did not show up in time
+};
+
+void set_last_error(const char* fmt, ...);
+
+#define DNN_CUDA_CHECK(expr)                                                         \
+  do {                                                                               \
+    cudaError_t _e = (expr);                                                         \
+    if (_e != cudaSuccess) {                                                         \
+      ::dnnb200::set_last_error("%s failed at %s:%d: %s", #expr, __FILE__, __LINE__, \
+                                cudaGetErrorString(_e));                             \
+      return ::dnnb200::kErrCuda;                                                    \
+    }                                                                                \
+  } while (0)
+
+#define DNN_ARG_CHECK(cond, ...)               \
+  do {                                         \
+    if (!(cond)) {                             \
+      ::dnnb200::set_last_error(__VA_ARGS__);  \
+      return ::dnnb200::kErrArg;               \
+    }                                          \
+  } while (0)
+
+#ifdef __CUDACC__
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// ---- system-scope flag traffic for the peer-memory exchange -------------------
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned int ld_relaxed_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// L2-coherent loads (skip the non-coherent L1) for data a peer GPU wrote.
+__device__ __forceinline__ float4 ld_cg_f4(const float4* p) { return __ldcg(p); }
+__device__ __forceinline__ float ld_cg_f(const float* p) { return __ldcg(p); }
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+#endif  // __CUDACC__
+
+}  // namespace dnnb200

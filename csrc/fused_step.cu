@@ -1,0 +1,694 @@
+// The training step as two kernels.
+//
+//   fwd_bwd_kernel  one CTA per image: the whole forward pass, the loss, the data
+//                   gradients of every layer and the two conv weight gradients,
+//                   with every activation of the image resident in shared memory.
+//                   (reference: models/model.py:20-27 + autograd of
+//                   data_parallelism_train.py:195-198; kernels K1-K17 of SURVEY §2.7.)
+//   update_kernel   one CTA per 512-float slice of the flat parameter vector: the
+//                   batch reduction of the weight gradient for that slice (FC
+//                   layers: outer products over the batch; conv: sum of the
+//                   per-image partials), the peer-memory all-reduce of the slice,
+//                   the 1/W scale and the SGD-momentum update, all in registers.
+//                   (reference: data_parallelism_train.py:187,199 SGD; :210,226-244
+//                   the parameter exchange; K13/K18/K19/K22.)
+//
+// Exploited structure: after max-pooling, only one of the four conv outputs in a
+// window carries gradient, so the conv weight gradients run over the pooled grid
+// with the 2-bit argmax as an address offset (4x fewer MACs than the dense form),
+// and ReLU'/pool' cost nothing (K14/K15 fused away).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "common.cuh"
+#include "exchange.cuh"
+#include "layout.h"
+#include "step_types.h"
+
+namespace dnnb200 {
+
+// ============================================================================
+// fwd_bwd_kernel
+// ============================================================================
+constexpr int kFBThreads = 512;
+constexpr int kRedFloats = 6144;
+
+struct __align__(16) FBSmem {
+  float x[kImgNumel];          // input image, CHW (bulk-copied by the TMA engine)
+  float w1t[75 * 8];           // conv1 weights [(c,kh,kw)][half*4 + j]   (j<3: out channel half*3+j)
+  float b1[8];
+  float p1[1176 + 8];          // pooled relu(conv1)  [6][14][14]
+  float w2t[150 * 16];         // conv2 weights [(c,kh,kw)][o]   (forward)
+  float w2d[16 * 25 * 8];      // conv2 weights [(o,kh,kw)][c8]  (data gradient)
+  float b2[16];
+  float p2[400];               // pooled relu(conv2)  [16][5][5] == fc1 input
+  float h1[120];
+  float h2[88];
+  float logits[16];
+  float d3[16];
+  float d2[88];
+  float d1[120];
+  float g2[400];               // dL/d p2, masked by p2 > 0
+  float g1[1176 + 8];          // dL/d p1, masked by p1 > 0
+  float dc2p[16 * 18 * 18];    // dL/d conv2-out, dense, zero border of 4
+  float red[kRedFloats];       // scratch for split reductions
+  unsigned long long mbar;     // mbarrier for the bulk copy
+  unsigned char idx1[1176 + 8];
+  unsigned char idx2[400];
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t phase) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(phase)
+      : "memory");
+}
+// 1-D bulk copy global -> shared through the TMA engine (SASS: UBLKCP)
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes,
+                                         unsigned long long* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          smem_u32(dst)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+
+// y[m] = act(b[m] + W[m,:] . in), W row-major [M][K] in global, K % 4 == 0, in/out in smem.
+// One warp per row, four rows in flight per warp to cover the L2 latency.
+template <int M, int K, bool kRelu>
+__device__ __forceinline__ void fc_forward(const float* __restrict__ W, const float* __restrict__ b,
+                                           const float* in, float* out) {
+  constexpr int K4 = K / 4;
+  constexpr int kWarps = kFBThreads / 32;
+  constexpr int kIter = (K4 + 31) / 32;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float4* in4 = reinterpret_cast<const float4*>(in);
+  for (int r0 = warp; r0 < M; r0 += 4 * kWarps) {
+    float4 w[4][kIter];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int r = r0 + q * kWarps;
+#pragma unroll
+      for (int it = 0; it < kIter; ++it) {
+        const int k4 = lane + it * 32;
+        w[q][it] = (r < M && k4 < K4) ? __ldg(reinterpret_cast<const float4*>(W + (size_t)r * K) + k4)
+                                      : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int r = r0 + q * kWarps;
+      float acc = 0.f;
+#pragma unroll
+      for (int it = 0; it < kIter; ++it) {
+        const int k4 = lane + it * 32;
+        if (k4 < K4) {
+          const float4 v = in4[k4];
+          acc += w[q][it].x * v.x + w[q][it].y * v.y + w[q][it].z * v.z + w[q][it].w * v.w;
+        }
+      }
+      acc = warp_sum(acc);
+      if (lane == 0 && r < M) {
+        acc += __ldg(b + r);
+        out[r] = kRelu ? fmaxf(acc, 0.f) : acc;
+      }
+    }
+  }
+}
+
+// dx[k] = [act[k] > 0] * sum_m W[m,k] * dy[m];  W row-major [M][K] global, dy/act/dx in smem.
+// Threads are (row group g, float4 column k4); the groups' partial sums meet in `red`.
+template <int M, int K>
+__device__ __forceinline__ void fc_backward_dx(const float* __restrict__ W, const float* dy,
+                                               const float* act, float* dx, float* red) {
+  constexpr int K4 = K / 4;
+  constexpr int G0 = kFBThreads / K4;
+  constexpr int G = G0 < M ? G0 : M;
+  constexpr int kRows = (M + G - 1) / G;
+  static_assert(G * K <= kRedFloats, "reduction scratch too small");
+  const int tid = threadIdx.x;
+  if (tid < G * K4) {
+    const int g = tid / K4, k4 = tid - g * K4;
+    const int m0 = g * kRows;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 12
+    for (int q = 0; q < kRows; ++q) {
+      const int m = m0 + q;
+      if (m < M) {
+        const float4 w = __ldg(reinterpret_cast<const float4*>(W + (size_t)m * K) + k4);
+        const float d = dy[m];
+        acc.x += w.x * d; acc.y += w.y * d; acc.z += w.z * d; acc.w += w.w * d;
+      }
+    }
+    reinterpret_cast<float4*>(red)[g * K4 + k4] = acc;
+  }
+  __syncthreads();
+  if (tid < K) {
+    float s = 0.f;
+#pragma unroll
+    for (int g = 0; g < G; ++g) s += red[g * K + tid];
+    dx[tid] = act[tid] > 0.f ? s : 0.f;
+  }
+  __syncthreads();
+}
+
+template <bool kTrain>
+__global__ void __launch_bounds__(kFBThreads, 1)
+fwd_bwd_kernel(const float* __restrict__ params, const float* __restrict__ x,
+               const long long* __restrict__ labels, float* __restrict__ saved,
+               float* __restrict__ partials, float* __restrict__ img_loss,
+               int* __restrict__ img_correct, float* __restrict__ logits_out, int B,
+               float inv_batch) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  FBSmem& s = *reinterpret_cast<FBSmem*>(smem_raw);
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+
+  if (tid == 0) {
+    mbar_init(&s.mbar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  uint32_t phase = 0;
+  int img = blockIdx.x;
+  if (tid == 0 && img < B) {
+    mbar_expect_tx(&s.mbar, kImgNumel * 4);
+    bulk_g2s(s.x, x + (size_t)img * kImgNumel, kImgNumel * 4, &s.mbar);
+  }
+
+  // ---- conv weights into shared memory, re-laid out for broadcast vector loads ----
+  for (int i = tid; i < 75 * 8; i += kFBThreads) {
+    const int t = i >> 3, q = i & 7, half = q >> 2, j = q & 3;
+    s.w1t[i] = j < 3 ? __ldg(params + kOffW1 + (half * 3 + j) * 75 + t) : 0.f;
+  }
+  if (tid < 8) s.b1[tid] = tid < 6 ? __ldg(params + kOffB1 + tid) : 0.f;
+  for (int i = tid; i < 150 * 16; i += kFBThreads) {
+    const int t = i >> 4, o = i & 15;
+    s.w2t[i] = __ldg(params + kOffW2 + o * 150 + t);
+  }
+  if (kTrain) {
+    for (int i = tid; i < 16 * 25 * 8; i += kFBThreads) {
+      const int c = i & 7, ot = i >> 3, o = ot / 25, t = ot - o * 25;
+      s.w2d[i] = c < 6 ? __ldg(params + kOffW2 + o * 150 + c * 25 + t) : 0.f;
+    }
+  }
+  if (tid < 16) s.b2[tid] = __ldg(params + kOffB2 + tid);
+
+  for (; img < B; img += gridDim.x) {
+    mbar_wait(&s.mbar, phase);
+    phase ^= 1u;
+    __syncthreads();  // weights (first round) and image are visible to everyone
+
+    // ================= conv1 + bias + ReLU + maxpool (K1-K3) =================
+    // thread = (pooled pixel, half of the output channels); 12 accumulators
+    {
+      const int half = tid / 224, pp = tid - half * 224;
+      if (tid < 448 && pp < 196) {
+        const int ph = pp / 14, pw = pp - ph * 14;
+        float acc[3][4];
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+#pragma unroll
+          for (int q = 0; q < 4; ++q) acc[j][q] = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < 3; ++c) {
+          const float* xb = s.x + c * 1024 + (2 * ph) * 32 + 2 * pw;
+          float patch[6][6];
+#pragma unroll
+          for (int r = 0; r < 6; ++r)
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+              const float2 v = *reinterpret_cast<const float2*>(xb + r * 32 + 2 * q);
+              patch[r][2 * q] = v.x;
+              patch[r][2 * q + 1] = v.y;
+            }
+          const float* wb = s.w1t + (c * 25) * 8 + half * 4;
+#pragma unroll
+          for (int kh = 0; kh < 5; ++kh)
+#pragma unroll
+            for (int kw = 0; kw < 5; ++kw) {
+              const float4 w = *reinterpret_cast<const float4*>(wb + (kh * 5 + kw) * 8);
+              const float a00 = patch[kh][kw], a01 = patch[kh][kw + 1];
+              const float a10 = patch[kh + 1][kw], a11 = patch[kh + 1][kw + 1];
+              acc[0][0] += w.x * a00; acc[0][1] += w.x * a01; acc[0][2] += w.x * a10; acc[0][3] += w.x * a11;
+              acc[1][0] += w.y * a00; acc[1][1] += w.y * a01; acc[1][2] += w.y * a10; acc[1][3] += w.y * a11;
+              acc[2][0] += w.z * a00; acc[2][1] += w.z * a01; acc[2][2] += w.z * a10; acc[2][3] += w.z * a11;
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          const int o = half * 3 + j;
+          const float bias = s.b1[o];
+          float best = fmaxf(acc[j][0] + bias, 0.f);
+          int bi = 0;
+#pragma unroll
+          for (int q = 1; q < 4; ++q) {
+            const float v = fmaxf(acc[j][q] + bias, 0.f);
+            if (v > best) { best = v; bi = q; }  // strict: first maximum wins, as ATen does
+          }
+          s.p1[o * 196 + pp] = best;
+          s.idx1[o * 196 + pp] = (unsigned char)bi;
+        }
+      }
+    }
+    __syncthreads();
+
+    // ================= conv2 + bias + ReLU + maxpool (K4-K6) =================
+    // thread = (pair of input channels, quad of output channels, pooled pixel)
+    if (tid < 384) {
+      const int grp = tid >> 5, pp = tid & 31;
+      const int cp = grp >> 2, oq = grp & 3;
+      if (pp < 25) {
+        const int ph = pp / 5, pw = pp - ph * 5;
+        float acc[4][4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+          for (int q = 0; q < 4; ++q) acc[j][q] = 0.f;
+#pragma unroll 1
+        for (int cc = 0; cc < 2; ++cc) {
+          const int c = cp * 2 + cc;
+          const float* xb = s.p1 + c * 196 + (2 * ph) * 14 + 2 * pw;
+          float patch[6][6];
+#pragma unroll
+          for (int r = 0; r < 6; ++r)
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+              const float2 v = *reinterpret_cast<const float2*>(xb + r * 14 + 2 * q);
+              patch[r][2 * q] = v.x;
+              patch[r][2 * q + 1] = v.y;
+            }
+          const float* wb = s.w2t + (c * 25) * 16 + oq * 4;
+#pragma unroll
+          for (int kh = 0; kh < 5; ++kh)
+#pragma unroll
+            for (int kw = 0; kw < 5; ++kw) {
+              const float4 w = *reinterpret_cast<const float4*>(wb + (kh * 5 + kw) * 16);
+              const float a00 = patch[kh][kw], a01 = patch[kh][kw + 1];
+              const float a10 = patch[kh + 1][kw], a11 = patch[kh + 1][kw + 1];
+              acc[0][0] += w.x * a00; acc[0][1] += w.x * a01; acc[0][2] += w.x * a10; acc[0][3] += w.x * a11;
+              acc[1][0] += w.y * a00; acc[1][1] += w.y * a01; acc[1][2] += w.y * a10; acc[1][3] += w.y * a11;
+              acc[2][0] += w.z * a00; acc[2][1] += w.z * a01; acc[2][2] += w.z * a10; acc[2][3] += w.z * a11;
+              acc[3][0] += w.w * a00; acc[3][1] += w.w * a01; acc[3][2] += w.w * a10; acc[3][3] += w.w * a11;
+            }
+        }
+        float4* dst = reinterpret_cast<float4*>(s.red + (grp * 32 + pp) * 16);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) dst[j] = make_float4(acc[j][0], acc[j][1], acc[j][2], acc[j][3]);
+      }
+    }
+    __syncthreads();
+    if (tid < 400) {
+      const int o = tid / 25, pp = tid - o * 25;
+      const int oq = o >> 2, j = o & 3;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int cp = 0; cp < 3; ++cp) {
+        const float4 t = *reinterpret_cast<const float4*>(s.red + ((cp * 4 + oq) * 32 + pp) * 16 + j * 4);
+        v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+      }
+      const float bias = s.b2[o];
+      float best = fmaxf(v.x + bias, 0.f);
+      int bi = 0;
+      float t = fmaxf(v.y + bias, 0.f);
+      if (t > best) { best = t; bi = 1; }
+      t = fmaxf(v.z + bias, 0.f);
+      if (t > best) { best = t; bi = 2; }
+      t = fmaxf(v.w + bias, 0.f);
+      if (t > best) { best = t; bi = 3; }
+      s.p2[tid] = best;  // (C,H,W) flatten order: o*25 + ph*5 + pw
+      s.idx2[tid] = (unsigned char)bi;
+    }
+    __syncthreads();
+
+    // the image buffer is free only in eval mode (training re-reads it for conv1 wgrad)
+    if (!kTrain && tid == 0 && img + gridDim.x < B) {
+      mbar_expect_tx(&s.mbar, kImgNumel * 4);
+      bulk_g2s(s.x, x + (size_t)(img + gridDim.x) * kImgNumel, kImgNumel * 4, &s.mbar);
+    }
+
+    // ================= fc1, fc2, fc3 (K8-K10) =================
+    fc_forward<kF1, kFlat, true>(params + kOffF1W, params + kOffF1B, s.p2, s.h1);
+    __syncthreads();
+    fc_forward<kF2, kF1, true>(params + kOffF2W, params + kOffF2B, s.h1, s.h2);
+    __syncthreads();
+    fc_forward<kF3, kF2, false>(params + kOffF3W, params + kOffF3B, s.h2, s.logits);
+    __syncthreads();
+
+    // ================= softmax cross-entropy, forward and backward (K11/K12) =================
+    if (warp == 0) {
+      const int label = (int)__ldg(labels + img);
+      const float z = lane < 10 ? s.logits[lane] : -INFINITY;
+      const float m = warp_max(z);
+      const float e = lane < 10 ? __expf(z - m) : 0.f;
+      const float sum = warp_sum(e);
+      const float lse = m + __logf(sum);
+      const float zl = __shfl_sync(0xffffffffu, z, label & 31);
+      // first index attaining the maximum, as torch.argmax
+      const unsigned int hit = __ballot_sync(0xffffffffu, lane < 10 && z == m);
+      const int pred = __ffs(hit) - 1;
+      if (lane < 10) {
+        s.d3[lane] = (e / sum - (lane == label ? 1.f : 0.f)) * inv_batch;
+        if (logits_out) logits_out[(size_t)img * 10 + lane] = z;
+      }
+      if (lane == 0) {
+        img_loss[img] = lse - zl;
+        if (img_correct) img_correct[img] = (pred == label) ? 1 : 0;
+      }
+    }
+    if (!kTrain) {
+      __syncthreads();
+      continue;
+    }
+    __syncthreads();
+
+    // ================= FC data gradients (K13 dX, K14) =================
+    fc_backward_dx<kF3, kF2>(params + kOffF3W, s.d3, s.h2, s.d2, s.red);
+    fc_backward_dx<kF2, kF1>(params + kOffF2W, s.d2, s.h1, s.d1, s.red);
+    fc_backward_dx<kF1, kFlat>(params + kOffF1W, s.d1, s.p2, s.g2, s.red);
+
+    // record for the update kernel: FC inputs and deltas of this image
+    {
+      float* sv = saved + (size_t)img * kSavStride;
+      if (tid < 400) sv[kSavP2 + tid] = s.p2[tid];
+      if (tid < 120) { sv[kSavH1 + tid] = s.h1[tid]; sv[kSavD1 + tid] = s.d1[tid]; }
+      if (tid < 84) { sv[kSavH2 + tid] = s.h2[tid]; sv[kSavD2 + tid] = s.d2[tid]; }
+      if (tid < 10) sv[kSavD3 + tid] = s.d3[tid];
+    }
+    float* part = partials + (size_t)img * kConvPrefix;
+
+    // ================= conv2 weight gradient over the pooled grid (K16 wgrad, K15) =================
+    // zero the dense padded gradient plane for the data gradient in the same pass
+    for (int i = tid; i < 16 * 18 * 18; i += kFBThreads) s.dc2p[i] = 0.f;
+    if (tid < 480) {
+      const int o = tid / 30, rem = tid - o * 30, c = rem / 5, kh = rem - c * 5;
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+#pragma unroll 5
+      for (int pp = 0; pp < 25; ++pp) {
+        const float g = s.g2[o * 25 + pp];
+        const int id = s.idx2[o * 25 + pp];
+        const int ph = pp / 5, pw = pp - ph * 5;
+        const float* row = s.p1 + c * 196 + (2 * ph + (id >> 1) + kh) * 14 + 2 * pw + (id & 1);
+        a0 += g * row[0]; a1 += g * row[1]; a2 += g * row[2]; a3 += g * row[3]; a4 += g * row[4];
+      }
+      float* dst = part + kOffW2 + o * 150 + c * 25 + kh * 5;
+      dst[0] = a0; dst[1] = a1; dst[2] = a2; dst[3] = a3; dst[4] = a4;
+    } else if (tid < 496) {
+      const int o = tid - 480;
+      float a = 0.f;
+      for (int pp = 0; pp < 25; ++pp) a += s.g2[o * 25 + pp];
+      part[kOffB2 + o] = a;
+    }
+    __syncthreads();
+    if (tid < 400) {  // scatter pooled gradient to its argmax position (K15)
+      const int o = tid / 25, pp = tid - o * 25, ph = pp / 5, pw = pp - ph * 5;
+      const int id = s.idx2[tid];
+      s.dc2p[o * 324 + (2 * ph + (id >> 1) + 4) * 18 + (2 * pw + (id & 1) + 4)] = s.g2[tid];
+    }
+    __syncthreads();
+
+    // ================= conv2 data gradient (K16 dgrad), then ReLU'/pool' of conv1 =================
+    {
+      const int half = tid / 224, pix = tid - half * 224;
+      if (tid < 448 && pix < 196) {
+        const int ih = pix / 14, iw = pix - ih * 14;
+        float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll 1
+        for (int oo = 0; oo < 8; ++oo) {
+          const int o = half * 8 + oo;
+#pragma unroll
+          for (int kh = 0; kh < 5; ++kh) {
+            const int r = ih + 4 - kh;
+            if (r < 4 || r > 13) continue;  // rows of the zero border
+            const float* row = s.dc2p + o * 324 + r * 18 + iw + 4;
+            const float* wb = s.w2d + (o * 25 + kh * 5) * 8;
+#pragma unroll
+            for (int kw = 0; kw < 5; ++kw) {
+              const float v = row[-kw];
+              const float4 wa = *reinterpret_cast<const float4*>(wb + kw * 8);
+              const float2 wc = *reinterpret_cast<const float2*>(wb + kw * 8 + 4);
+              acc[0] += v * wa.x; acc[1] += v * wa.y; acc[2] += v * wa.z; acc[3] += v * wa.w;
+              acc[4] += v * wc.x; acc[5] += v * wc.y;
+            }
+          }
+        }
+#pragma unroll
+        for (int c = 0; c < 6; ++c) s.red[half * 1176 + c * 196 + pix] = acc[c];
+      }
+    }
+    __syncthreads();
+    for (int i = tid; i < 1176; i += kFBThreads) {
+      const float v = s.red[i] + s.red[1176 + i];
+      s.g1[i] = s.p1[i] > 0.f ? v : 0.f;
+    }
+    __syncthreads();
+
+    // ================= conv1 weight gradient over the pooled grid (K17, K15) =================
+    if (tid < 450) {
+      const int pg = tid / 90, rem = tid - pg * 90;
+      const int o = rem / 15, r2 = rem - o * 15, c = r2 / 5, kh = r2 - c * 5;
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+#pragma unroll 4
+      for (int pp = pg; pp < 196; pp += 5) {
+        const float g = s.g1[o * 196 + pp];
+        const int id = s.idx1[o * 196 + pp];
+        const int ph = pp / 14, pw = pp - ph * 14;
+        const float* row = s.x + c * 1024 + (2 * ph + (id >> 1) + kh) * 32 + 2 * pw + (id & 1);
+        a0 += g * row[0]; a1 += g * row[1]; a2 += g * row[2]; a3 += g * row[3]; a4 += g * row[4];
+      }
+      float* dst = s.red + pg * 450 + o * 75 + c * 25 + kh * 5;  // red was consumed above
+      dst[0] = a0; dst[1] = a1; dst[2] = a2; dst[3] = a3; dst[4] = a4;
+    } else if (warp >= 15) {
+      // warp 15 (threads 480..511): conv1 bias gradient
+      for (int o = 0; o < 6; ++o) {
+        float a = 0.f;
+        for (int pp = lane; pp < 196; pp += 32) a += s.g1[o * 196 + pp];
+        a = warp_sum(a);
+        if (lane == 0) part[kOffB1 + o] = a;
+      }
+    }
+    __syncthreads();
+    if (tid < 450) {
+      float a = 0.f;
+#pragma unroll
+      for (int pg = 0; pg < 5; ++pg) a += s.red[pg * 450 + tid];
+      part[kOffW1 + tid] = a;
+    }
+    __syncthreads();  // s.x may be overwritten now
+    if (tid == 0 && img + gridDim.x < B) {
+      mbar_expect_tx(&s.mbar, kImgNumel * 4);
+      bulk_g2s(s.x, x + (size_t)(img + gridDim.x) * kImgNumel, kImgNumel * 4, &s.mbar);
+    }
+  }
+}
+
+// ============================================================================
+// update_kernel
+// ============================================================================
+constexpr int kUpdThreads = kSlice / 2;  // 256 threads, two consecutive floats each
+
+// d(loss)/d(param[i]) and param[i+1] summed over the local batch. i is even and both
+// elements lie in the same tensor row (all row lengths are even).
+__device__ __forceinline__ float2 local_grad2(const RankCtx& cx, int i, int B) {
+  float2 g = make_float2(0.f, 0.f);
+  if (i < kConvPrefix) {
+    const float* p = cx.partials + i;
+#pragma unroll 8
+    for (int b = 0; b < B; ++b) {
+      const float2 t = __ldg(reinterpret_cast<const float2*>(p + (size_t)b * kConvPrefix));
+      g.x += t.x; g.y += t.y;
+    }
+    return g;
+  }
+  int off_d, off_a, j, k;
+  bool is_bias = false;
+  if (i < kOffF1B) {
+    const int e = i - kOffF1W; j = e / kFlat; k = e - j * kFlat; off_d = kSavD1; off_a = kSavP2;
+  } else if (i < kOffF2W) {
+    j = i - kOffF1B; k = 0; off_d = kSavD1; off_a = 0; is_bias = true;
+    if (j >= kF1) return g;
+  } else if (i < kOffF2B) {
+    const int e = i - kOffF2W; j = e / kF1; k = e - j * kF1; off_d = kSavD2; off_a = kSavH1;
+  } else if (i < kOffF3W) {
+    j = i - kOffF2B; k = 0; off_d = kSavD2; off_a = 0; is_bias = true;
+    if (j >= kF2) return g;
+  } else if (i < kOffF3B) {
+    const int e = i - kOffF3W; j = e / kF2; k = e - j * kF2; off_d = kSavD3; off_a = kSavH2;
+    if (e >= kF3 * kF2) return g;
+  } else {
+    j = i - kOffF3B; k = 0; off_d = kSavD3; off_a = 0; is_bias = true;
+    if (j >= kF3) return g;
+  }
+  const float* sv = cx.saved;
+  if (is_bias) {
+    // j even, j+1 in range for all three biases (120, 84, 10 are even)
+#pragma unroll 8
+    for (int b = 0; b < B; ++b) {
+      const float2 d = __ldg(reinterpret_cast<const float2*>(sv + (size_t)b * kSavStride + off_d + j));
+      g.x += d.x; g.y += d.y;
+    }
+  } else {
+#pragma unroll 8
+    for (int b = 0; b < B; ++b) {
+      const float d = __ldg(sv + (size_t)b * kSavStride + off_d + j);
+      const float2 a = __ldg(reinterpret_cast<const float2*>(sv + (size_t)b * kSavStride + off_a + k));
+      g.x += d * a.x; g.y += d * a.y;
+    }
+  }
+  return g;
+}
+
+__global__ void __launch_bounds__(kUpdThreads)
+update_kernel(const RankCtx* __restrict__ ctxs, int B, int loss_slot, int flags) {
+  __shared__ ExchangeShared xsh;
+  const RankCtx& cx = ctxs[blockIdx.y];
+  StepCtl* ctl = cx.ctl;
+  const int slice = blockIdx.x, tid = threadIdx.x;
+  const int i = slice * kSlice + 2 * tid;
+  const bool in_range = i < kFlatNumel;
+  const unsigned long long step = *reinterpret_cast<volatile unsigned long long*>(&ctl->step);
+  const unsigned int seq = (unsigned int)(step + 1ull);
+
+  float v[2] = {0.f, 0.f};
+  if (in_range) {
+    const float2 g = local_grad2(cx, i, B);
+    v[0] = g.x; v[1] = g.y;
+  }
+  const bool grad_only = (flags & 1) != 0;  // tests: leave the local batch gradient in cx.grads, touch nothing else
+  int n = 1;
+  if (cx.world > 1 && !grad_only) exchange_slice<2>(cx, &xsh, slice, seq, i, in_range, v, &n);
+
+  if (in_range && grad_only) {
+    if (cx.grads) *reinterpret_cast<float2*>(cx.grads + i) = make_float2(v[0], v[1]);
+  } else if (in_range) {
+    const float inv_n = 1.f / (float)n;
+    const float lr = ctl->lr, mu = ctl->mu;
+    const float g0 = v[0] * inv_n, g1 = v[1] * inv_n;
+    float2 m = *reinterpret_cast<float2*>(cx.momentum + i);
+    float2 p = *reinterpret_cast<float2*>(cx.params + i);
+    m.x = mu * m.x + g0;  // zeroed momentum makes the first step buf = g, as torch.optim.SGD
+    m.y = mu * m.y + g1;
+    p.x -= lr * m.x;
+    p.y -= lr * m.y;
+    *reinterpret_cast<float2*>(cx.momentum + i) = m;
+    *reinterpret_cast<float2*>(cx.params + i) = p;
+    if (cx.grads) *reinterpret_cast<float2*>(cx.grads + i) = make_float2(g0, g1);
+  }
+
+  if (slice == 0 && tid < 32) {  // per-step mean loss, fixed summation order
+    float a = 0.f;
+    for (int b = tid; b < B; b += 32) a += cx.img_loss[b];
+    a = warp_sum(a);
+    if (tid == 0) {
+      const float mean = a / (float)B;
+      cx.loss_ring[loss_slot & cx.loss_ring_mask] = mean;
+      if (!grad_only) {
+        ctl->loss_sum += mean;
+        ctl->loss_steps += 1u;
+      }
+    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    const unsigned int done = atomicAdd(&ctl->ctas_done, 1u);
+    if (done == gridDim.x - 1) {  // last CTA of this rank: everyone has read `step`
+      ctl->ctas_done = 0u;
+      __threadfence();
+      if (!grad_only) *reinterpret_cast<volatile unsigned long long*>(&ctl->step) = step + 1ull;
+    }
+  }
+}
+
+// ============================================================================
+// eval reduction: mean over batches of the batch-mean loss, and the hit count
+// (reference: data_parallelism_train.py:157-183 -- np.mean(losses), 100*corrects/total)
+// ============================================================================
+__global__ void eval_reduce_kernel(const float* __restrict__ img_loss, const int* __restrict__ img_correct,
+                                   int N, int bs, double* __restrict__ out /* [2] */) {
+  __shared__ double s_loss[32];
+  __shared__ long long s_hit[32];
+  const int nb = (N + bs - 1) / bs;
+  double acc = 0.0;
+  long long hit = 0;
+  for (int b = threadIdx.x; b < nb; b += blockDim.x) {
+    const int lo = b * bs, hi = min(N, lo + bs);
+    float t = 0.f;
+    for (int k = lo; k < hi; ++k) { t += img_loss[k]; hit += img_correct[k]; }
+    acc += (double)(t / (float)(hi - lo));
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    hit += __shfl_xor_sync(0xffffffffu, hit, o);
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) { s_loss[warp] = acc; s_hit[warp] = hit; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double a = 0.0; long long h = 0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { a += s_loss[w]; h += s_hit[w]; }
+    out[0] = a / (double)nb;
+    out[1] = (double)h;
+  }
+}
+
+// ============================================================================
+// host launchers (used by engine.cpp and by the C ABI in api.cpp)
+// ============================================================================
+int launch_fwd_bwd(bool train, const float* params, const float* x, const long long* labels,
+                   float* saved, float* partials, float* img_loss, int* img_correct,
+                   float* logits_out, int B, int max_ctas, cudaStream_t stream) {
+  static bool attr_set[2] = {false, false};
+  const size_t smem = sizeof(FBSmem);
+  auto kern = train ? fwd_bwd_kernel<true> : fwd_bwd_kernel<false>;
+  if (!attr_set[train ? 1 : 0]) {
+    DNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set[train ? 1 : 0] = true;
+  }
+  const int grid = B < max_ctas ? B : max_ctas;
+  kern<<<grid, kFBThreads, smem, stream>>>(params, x, labels, saved, partials, img_loss, img_correct,
+                                           logits_out, B, 1.f / (float)B);
+  DNN_CUDA_CHECK(cudaGetLastError());
+  return kOk;
+}
+
+int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int loss_slot, int flags, cudaStream_t stream) {
+  dim3 grid(kNumSlices, n_virtual_ranks);
+  if (n_virtual_ranks > 1) {
+    // ranks emulated on ONE device wait on each other: every CTA must be resident
+    void* args[] = {(void*)&d_ctxs, (void*)&B, (void*)&loss_slot, (void*)&flags};
+    DNN_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)update_kernel, grid, dim3(kUpdThreads), args, 0, stream));
+  } else {
+    update_kernel<<<grid, kUpdThreads, 0, stream>>>(d_ctxs, B, loss_slot, flags);
+    DNN_CUDA_CHECK(cudaGetLastError());
+  }
+  return kOk;
+}
+
+int launch_eval_reduce(const float* img_loss, const int* img_correct, int N, int bs, double* out,
+                       cudaStream_t stream) {
+  eval_reduce_kernel<<<1, 256, 0, stream>>>(img_loss, img_correct, N, bs, out);
+  DNN_CUDA_CHECK(cudaGetLastError());
+  return kOk;
+}
+
+size_t fwd_bwd_smem_bytes() { return sizeof(FBSmem); }
+
+}  // namespace dnnb200

@@ -1,0 +1,599 @@
+// Host runtime: peer group (CUDA IPC symmetric buffers), fused step engine
+// (buffers, launch sequencing, host-fed input ring) and the extern "C" surface
+// declared in include/dnnb200.h.
+//
+// Reference counterparts: the mpi4py bootstrap + send/recv star
+// (data_parallelism_train.py:60-62,118,135,210,227), the child training loop
+// (:185-213) and eval (:157-183). The reference has no native code;
+// everything here is new.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <new>
+#include <vector>
+
+#include "../include/dnnb200.h"
+#include "common.cuh"
+#include "layout.h"
+#include "step_types.h"
+
+namespace dnnb200 {
+
+// ---- error plumbing ---------------------------------------------------------
+static thread_local char g_err[512] = "";
+void set_last_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+// ---- launchers implemented in the .cu files -----------------------------------
+int launch_fwd_bwd(bool train, const float* params, const float* x, const long long* labels, float* saved,
+                   float* partials, float* img_loss, int* img_correct, float* logits_out, int B, int max_ctas,
+                   cudaStream_t stream);
+int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int loss_slot, int flags, cudaStream_t stream);
+int launch_eval_reduce(const float* img_loss, const int* img_correct, int N, int bs, double* out, cudaStream_t stream);
+int launch_allreduce(const RankCtx* d_ctxs, int n_virtual_ranks, const float* const* in, float* const* out, int n,
+                     int mode, int two_shot, cudaStream_t stream);
+int launch_conv_relu_pool_fwd(const float*, const float*, const float*, float*, unsigned char*, int, int, int, int,
+                              int, cudaStream_t);
+int launch_conv_relu_pool_bwd(const float*, const float*, const float*, const unsigned char*, const float*, float*,
+                              float*, float*, int, int, int, int, int, cudaStream_t);
+int launch_linear_fwd(const float*, const float*, const float*, float*, int, int, int, int, cudaStream_t);
+int launch_linear_bwd(const float*, const float*, const float*, const float*, float*, float*, float*, int, int, int,
+                      int, cudaStream_t);
+int launch_softmax_xent(const float*, const long long*, float*, float*, int, int, cudaStream_t);
+int launch_sgd_momentum(float*, const float*, float*, int, float, float, int, float, cudaStream_t);
+
+// ---- tiny control kernels ---------------------------------------------------
+__global__ void ctl_set_hparams_kernel(StepCtl* c, float lr, float mu) { c->lr = lr; c->mu = mu; }
+__global__ void ctl_set_membership_kernel(StepCtl* c, unsigned int mask, unsigned long long tmo) {
+  c->active_mask = mask;
+  c->timeout_ns = tmo;
+  c->status = 0u;
+}
+__global__ void ctl_reset_loss_kernel(StepCtl* c) { c->loss_sum = 0.f; c->loss_steps = 0u; }
+__global__ void ctl_set_step_kernel(StepCtl* c, unsigned long long step) { c->step = step; c->ctas_done = 0u; }
+// leave marker = first sequence number this rank will not take part in
+__global__ void leave_kernel(const RankCtx* cx, int clear) {
+  const int p = threadIdx.x;
+  if (p >= cx->world || p == cx->rank) return;
+  const unsigned int marker = clear ? 0u : (unsigned int)(cx->ctl->step + 1ull);
+  __threadfence_system();
+  st_release_sys(cx->flags[p] + cx->rank * kFlagRow + kLeaveSlot, marker);
+}
+
+// ============================================================================
+// Peer group
+// ============================================================================
+constexpr size_t kFlagBytes = (size_t)2 * kMaxWorld * kFlagRow * sizeof(unsigned int);  // two banks
+
+}  // namespace dnnb200
+
+struct dnnb200_group {
+  int rank = 0, world = 1, device = 0;
+  void* base = nullptr;  // [flags | recv]
+  size_t bytes = 0;
+  void* peer_base[dnnb200::kMaxWorld] = {};
+  bool ipc_opened[dnnb200::kMaxWorld] = {};
+  bool connected = false;
+};
+
+struct dnnb200_engine {
+  int device = 0, max_batch = 0;
+  float *params = nullptr, *momentum = nullptr, *grads = nullptr;
+  float *saved = nullptr, *partials = nullptr, *img_loss = nullptr;
+  int* img_correct = nullptr;
+  float* eval_loss = nullptr;
+  int* eval_correct = nullptr;
+  int eval_cap = 0;
+  double* d_eval_out = nullptr;
+  dnnb200::StepCtl* ctl = nullptr;
+  float* loss_ring = nullptr;
+  int loss_ring_mask = 1023;
+  dnnb200::RankCtx h_ctx;
+  dnnb200::RankCtx* d_ctx = nullptr;
+  dnnb200::RankCtx* h_ctx_pinned = nullptr;
+  dnnb200_group* group = nullptr;
+  unsigned long long launches = 0;
+  unsigned long long steps_launched = 0;  // host mirror: update launches (loss ring slot)
+  int num_sms = 148;
+  // host-fed ring
+  static constexpr int kRing = 4;
+  cudaStream_t copy_stream = nullptr, d2h_stream = nullptr;
+  cudaEvent_t slot_ready[kRing] = {}, slot_free[kRing] = {}, step_done[kRing] = {};
+  float* d_x[kRing] = {};
+  long long* d_y[kRing] = {};
+  bool ring_ready = false;
+  unsigned long long ring_uses = 0;
+};
+
+namespace dnnb200 {
+
+static int push_ctx(dnnb200_engine* e, cudaStream_t s) {
+  // RankCtx lives in device memory; stage through pinned memory so the copy is truly async
+  *e->h_ctx_pinned = e->h_ctx;
+  DNN_CUDA_CHECK(cudaMemcpyAsync(e->d_ctx, e->h_ctx_pinned, sizeof(RankCtx), cudaMemcpyHostToDevice, s));
+  // the pinned staging copy is reused: make sure it is consumed before anyone rewrites it
+  DNN_CUDA_CHECK(cudaStreamSynchronize(s));
+  return kOk;
+}
+
+static int group_create(int rank, int world, dnnb200_group** out, void* h_handle64) {
+  DNN_ARG_CHECK(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world, "group: bad rank/world %d/%d", rank,
+                world);
+  dnnb200_group* g = new (std::nothrow) dnnb200_group();
+  DNN_ARG_CHECK(g != nullptr, "group: out of host memory");
+  g->rank = rank;
+  g->world = world;
+  DNN_CUDA_CHECK(cudaGetDevice(&g->device));
+  g->bytes = kFlagBytes + (size_t)2 * world * kFlatNumel * sizeof(float);
+  DNN_CUDA_CHECK(cudaMalloc(&g->base, g->bytes));
+  DNN_CUDA_CHECK(cudaMemset(g->base, 0, g->bytes));
+  DNN_CUDA_CHECK(cudaDeviceSynchronize());
+  g->peer_base[rank] = g->base;
+  if (h_handle64) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == DNNB200_IPC_HANDLE_BYTES, "IPC handle size");
+    cudaIpcMemHandle_t h;
+    DNN_CUDA_CHECK(cudaIpcGetMemHandle(&h, g->base));
+    memcpy(h_handle64, &h, sizeof(h));
+  }
+  *out = g;
+  return kOk;
+}
+
+static int engine_refresh_peers(dnnb200_engine* e, cudaStream_t s) {
+  dnnb200_group* g = e->group;
+  for (int p = 0; p < kMaxWorld; ++p) { e->h_ctx.recv[p] = nullptr; e->h_ctx.flags[p] = nullptr; }
+  if (g) {
+    for (int p = 0; p < g->world; ++p) {
+      unsigned char* b = static_cast<unsigned char*>(g->peer_base[p]);
+      e->h_ctx.flags[p] = reinterpret_cast<unsigned int*>(b);
+      e->h_ctx.recv[p] = reinterpret_cast<float*>(b + kFlagBytes);
+    }
+    e->h_ctx.rank = g->rank;
+    e->h_ctx.world = g->world;
+  } else {
+    e->h_ctx.rank = 0;
+    e->h_ctx.world = 1;
+  }
+  return push_ctx(e, s);
+}
+
+static int ensure_ring(dnnb200_engine* e) {
+  if (e->ring_ready) return kOk;
+  DNN_CUDA_CHECK(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+  DNN_CUDA_CHECK(cudaStreamCreateWithFlags(&e->d2h_stream, cudaStreamNonBlocking));
+  for (int i = 0; i < dnnb200_engine::kRing; ++i) {
+    DNN_CUDA_CHECK(cudaEventCreateWithFlags(&e->slot_ready[i], cudaEventDisableTiming));
+    DNN_CUDA_CHECK(cudaEventCreateWithFlags(&e->slot_free[i], cudaEventDisableTiming));
+    DNN_CUDA_CHECK(cudaEventCreateWithFlags(&e->step_done[i], cudaEventDisableTiming));
+    DNN_CUDA_CHECK(cudaMalloc(&e->d_x[i], (size_t)e->max_batch * kImgNumel * sizeof(float)));
+    DNN_CUDA_CHECK(cudaMalloc(&e->d_y[i], (size_t)e->max_batch * sizeof(long long)));
+  }
+  e->ring_ready = true;
+  return kOk;
+}
+
+static int step_kernels(dnnb200_engine* e, const float* x, const long long* y, int B, int flags, cudaStream_t s) {
+  int rc = launch_fwd_bwd(true, e->params, x, y, e->saved, e->partials, e->img_loss, e->img_correct, nullptr, B,
+                          e->num_sms * 2, s);
+  if (rc) return rc;
+  rc = launch_update(e->d_ctx, 1, B, (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask), flags, s);
+  if (rc) return rc;
+  e->launches += 2;
+  return kOk;
+}
+
+}  // namespace dnnb200
+
+using namespace dnnb200;
+
+extern "C" {
+
+const char* dnnb200_last_error(void) { return g_err; }
+int dnnb200_version(void) { return 100; }
+
+int dnnb200_layout(int* offsets10, int* flat_numel, int* slice, int* num_slices) {
+  const int offs[10] = {kOffW1, kOffB1, kOffW2, kOffB2, kOffF1W, kOffF1B, kOffF2W, kOffF2B, kOffF3W, kOffF3B};
+  if (offsets10) memcpy(offsets10, offs, sizeof(offs));
+  if (flat_numel) *flat_numel = kFlatNumel;
+  if (slice) *slice = kSlice;
+  if (num_slices) *num_slices = kNumSlices;
+  return kOk;
+}
+
+// ---- layer kernels ------------------------------------------------------------
+int dnnb200_conv_relu_pool_fwd(const float* x, const float* w, const float* b, float* y, uint8_t* idx, int N, int Ci,
+                               int H, int W, int Co, void* stream) {
+  DNN_ARG_CHECK(N > 0 && Ci > 0 && Co > 0 && Ci * 25 * 4 <= 48 * 1024, "conv_relu_pool_fwd: bad shape");
+  return launch_conv_relu_pool_fwd(x, w, b, y, idx, N, Ci, H, W, Co, (cudaStream_t)stream);
+}
+int dnnb200_conv_relu_pool_bwd(const float* x, const float* w, const float* y, const uint8_t* idx, const float* dy,
+                               float* dx, float* dw, float* db, int N, int Ci, int H, int W, int Co, void* stream) {
+  DNN_ARG_CHECK(N > 0 && Ci > 0 && Co > 0, "conv_relu_pool_bwd: bad shape");
+  return launch_conv_relu_pool_bwd(x, w, y, idx, dy, dx, dw, db, N, Ci, H, W, Co, (cudaStream_t)stream);
+}
+int dnnb200_linear_fwd(const float* x, const float* w, const float* b, float* y, int N, int M, int K, int relu,
+                       void* stream) {
+  DNN_ARG_CHECK(N > 0 && M > 0 && K > 0, "linear_fwd: bad shape");
+  return launch_linear_fwd(x, w, b, y, N, M, K, relu, (cudaStream_t)stream);
+}
+int dnnb200_linear_bwd(const float* x, const float* w, const float* y, const float* dy, float* dx, float* dw,
+                       float* db, int N, int M, int K, int relu, void* stream) {
+  DNN_ARG_CHECK(N > 0 && M > 0 && K > 0, "linear_bwd: bad shape");
+  return launch_linear_bwd(x, w, y, dy, dx, dw, db, N, M, K, relu, (cudaStream_t)stream);
+}
+int dnnb200_softmax_xent(const float* logits, const int64_t* target, float* loss, float* dlogits, int N, int C,
+                         void* stream) {
+  DNN_ARG_CHECK(N > 0 && C > 0, "softmax_xent: bad shape");
+  return launch_softmax_xent(logits, (const long long*)target, loss, dlogits, N, C, (cudaStream_t)stream);
+}
+int dnnb200_sgd_momentum(float* p, const float* g, float* buf, int n, float lr, float mu, int first_step, float scale,
+                         void* stream) {
+  DNN_ARG_CHECK(n > 0, "sgd_momentum: n must be positive");
+  return launch_sgd_momentum(p, g, buf, n, lr, mu, first_step, scale, (cudaStream_t)stream);
+}
+
+// ---- peer group -----------------------------------------------------------------
+int dnnb200_group_create(int rank, int world, dnnb200_group** out, void* h_handle64) {
+  return group_create(rank, world, out, h_handle64);
+}
+
+int dnnb200_group_connect(dnnb200_group* g, const void* h_all_handles) {
+  DNN_ARG_CHECK(g && h_all_handles, "group_connect: null argument");
+  const unsigned char* hs = static_cast<const unsigned char*>(h_all_handles);
+  for (int p = 0; p < g->world; ++p) {
+    if (p == g->rank) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, hs + (size_t)p * DNNB200_IPC_HANDLE_BYTES, sizeof(h));
+    void* ptr = nullptr;
+    DNN_CUDA_CHECK(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    g->peer_base[p] = ptr;
+    g->ipc_opened[p] = true;
+  }
+  g->connected = true;
+  return kOk;
+}
+
+int dnnb200_group_connect_local(dnnb200_group** groups, int n) {
+  DNN_ARG_CHECK(groups && n >= 1 && n <= kMaxWorld, "group_connect_local: bad arguments");
+  for (int a = 0; a < n; ++a) {
+    DNN_ARG_CHECK(groups[a] && groups[a]->world == n && groups[a]->rank == a,
+                  "group_connect_local: group %d must have rank %d of world %d", a, a, n);
+    for (int b = 0; b < n; ++b) {
+      if (groups[a]->device != groups[b]->device) {
+        int can = 0;
+        DNN_CUDA_CHECK(cudaDeviceCanAccessPeer(&can, groups[a]->device, groups[b]->device));
+        DNN_ARG_CHECK(can, "group_connect_local: device %d cannot access device %d", groups[a]->device,
+                      groups[b]->device);
+      }
+      groups[a]->peer_base[b] = groups[b]->base;
+    }
+    groups[a]->connected = true;
+  }
+  return kOk;
+}
+
+int dnnb200_group_destroy(dnnb200_group* g) {
+  if (!g) return kOk;
+  for (int p = 0; p < g->world; ++p)
+    if (g->ipc_opened[p] && g->peer_base[p]) cudaIpcCloseMemHandle(g->peer_base[p]);
+  if (g->base) cudaFree(g->base);
+  delete g;
+  return kOk;
+}
+
+// ---- engine ---------------------------------------------------------------------
+int dnnb200_engine_create(float* params, float* momentum, float* grads, int max_batch, float lr, float mu,
+                          dnnb200_engine** out) {
+  DNN_ARG_CHECK(params && momentum && out, "engine_create: null argument");
+  DNN_ARG_CHECK(max_batch >= 1 && max_batch <= 65536, "engine_create: max_batch out of range");
+  dnnb200_engine* e = new (std::nothrow) dnnb200_engine();
+  DNN_ARG_CHECK(e != nullptr, "engine_create: out of host memory");
+  DNN_CUDA_CHECK(cudaGetDevice(&e->device));
+  cudaDeviceProp prop;
+  DNN_CUDA_CHECK(cudaGetDeviceProperties(&prop, e->device));
+  e->num_sms = prop.multiProcessorCount;
+  e->max_batch = max_batch;
+  e->params = params;
+  e->momentum = momentum;
+  e->grads = grads;
+  DNN_CUDA_CHECK(cudaMalloc(&e->saved, (size_t)max_batch * kSavStride * sizeof(float)));
+  DNN_CUDA_CHECK(cudaMalloc(&e->partials, (size_t)max_batch * kConvPrefix * sizeof(float)));
+  DNN_CUDA_CHECK(cudaMemset(e->partials, 0, (size_t)max_batch * kConvPrefix * sizeof(float)));
+  DNN_CUDA_CHECK(cudaMemset(e->saved, 0, (size_t)max_batch * kSavStride * sizeof(float)));
+  DNN_CUDA_CHECK(cudaMalloc(&e->img_loss, (size_t)max_batch * sizeof(float)));
+  DNN_CUDA_CHECK(cudaMalloc(&e->img_correct, (size_t)max_batch * sizeof(int)));
+  DNN_CUDA_CHECK(cudaMalloc(&e->ctl, sizeof(StepCtl)));
+  DNN_CUDA_CHECK(cudaMalloc(&e->loss_ring, (size_t)(e->loss_ring_mask + 1) * sizeof(float)));
+  DNN_CUDA_CHECK(cudaMemset(e->loss_ring, 0, (size_t)(e->loss_ring_mask + 1) * sizeof(float)));
+  DNN_CUDA_CHECK(cudaMalloc(&e->d_ctx, sizeof(RankCtx)));
+  DNN_CUDA_CHECK(cudaMalloc(&e->d_eval_out, 2 * sizeof(double)));
+  DNN_CUDA_CHECK(cudaMallocHost(&e->h_ctx_pinned, sizeof(RankCtx)));
+  StepCtl c;
+  memset(&c, 0, sizeof(c));
+  c.lr = lr;
+  c.mu = mu;
+  c.active_mask = 1u;
+  c.timeout_ns = 0ull;
+  DNN_CUDA_CHECK(cudaMemcpy(e->ctl, &c, sizeof(c), cudaMemcpyHostToDevice));
+  memset(&e->h_ctx, 0, sizeof(e->h_ctx));
+  e->h_ctx.params = params;
+  e->h_ctx.momentum = momentum;
+  e->h_ctx.grads = grads;
+  e->h_ctx.saved = e->saved;
+  e->h_ctx.partials = e->partials;
+  e->h_ctx.img_loss = e->img_loss;
+  e->h_ctx.loss_ring = e->loss_ring;
+  e->h_ctx.loss_ring_mask = e->loss_ring_mask;
+  e->h_ctx.ctl = e->ctl;
+  int rc = engine_refresh_peers(e, nullptr);
+  if (rc) return rc;
+  *out = e;
+  return kOk;
+}
+
+int dnnb200_engine_destroy(dnnb200_engine* e) {
+  if (!e) return kOk;
+  cudaDeviceSynchronize();
+  cudaFree(e->saved); cudaFree(e->partials); cudaFree(e->img_loss); cudaFree(e->img_correct);
+  cudaFree(e->eval_loss); cudaFree(e->eval_correct); cudaFree(e->d_eval_out);
+  cudaFree(e->ctl); cudaFree(e->loss_ring); cudaFree(e->d_ctx);
+  cudaFreeHost(e->h_ctx_pinned);
+  if (e->ring_ready) {
+    for (int i = 0; i < dnnb200_engine::kRing; ++i) {
+      cudaEventDestroy(e->slot_ready[i]); cudaEventDestroy(e->slot_free[i]); cudaEventDestroy(e->step_done[i]);
+      cudaFree(e->d_x[i]); cudaFree(e->d_y[i]);
+    }
+    cudaStreamDestroy(e->copy_stream); cudaStreamDestroy(e->d2h_stream);
+  }
+  delete e;
+  return kOk;
+}
+
+int dnnb200_engine_attach_group(dnnb200_engine* e, dnnb200_group* g) {
+  DNN_ARG_CHECK(e, "engine_attach_group: null engine");
+  if (g) {
+    DNN_ARG_CHECK(g->connected || g->world == 1, "engine_attach_group: group is not connected yet");
+  }
+  e->group = g;
+  int rc = engine_refresh_peers(e, nullptr);
+  if (rc) return rc;
+  const unsigned int mask = g ? ((g->world >= 32) ? 0xffffffffu : ((1u << g->world) - 1u)) : 1u;
+  ctl_set_membership_kernel<<<1, 1>>>(e->ctl, mask, 0ull);
+  DNN_CUDA_CHECK(cudaGetLastError());
+  DNN_CUDA_CHECK(cudaDeviceSynchronize());
+  return kOk;
+}
+
+int dnnb200_engine_set_hparams(dnnb200_engine* e, float lr, float mu, void* stream) {
+  DNN_ARG_CHECK(e, "null engine");
+  ctl_set_hparams_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(e->ctl, lr, mu);
+  DNN_CUDA_CHECK(cudaGetLastError());
+  return kOk;
+}
+
+int dnnb200_engine_set_membership(dnnb200_engine* e, unsigned int active_mask, unsigned long long timeout_ns,
+                                  void* stream) {
+  DNN_ARG_CHECK(e, "null engine");
+  ctl_set_membership_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(e->ctl, active_mask, timeout_ns);
+  DNN_CUDA_CHECK(cudaGetLastError());
+  return kOk;
+}
+
+int dnnb200_engine_zero_momentum(dnnb200_engine* e, void* stream) {
+  DNN_ARG_CHECK(e, "null engine");
+  DNN_CUDA_CHECK(cudaMemsetAsync(e->momentum, 0, kFlatNumel * sizeof(float), (cudaStream_t)stream));
+  return kOk;
+}
+
+int dnnb200_engine_reset_loss(dnnb200_engine* e, void* stream) {
+  DNN_ARG_CHECK(e, "null engine");
+  ctl_reset_loss_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(e->ctl);
+  DNN_CUDA_CHECK(cudaGetLastError());
+  return kOk;
+}
+
+int dnnb200_engine_read_ctl(dnnb200_engine* e, dnnb200_ctl* h_out, void* stream) {
+  DNN_ARG_CHECK(e && h_out, "null argument");
+  static_assert(sizeof(dnnb200_ctl) == sizeof(StepCtl), "dnnb200_ctl must mirror StepCtl");
+  DNN_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
+  DNN_CUDA_CHECK(cudaMemcpy(h_out, e->ctl, sizeof(StepCtl), cudaMemcpyDeviceToHost));
+  return kOk;
+}
+
+unsigned long long dnnb200_engine_launches(const dnnb200_engine* e) { return e ? e->launches : 0ull; }
+
+int dnnb200_engine_step(dnnb200_engine* e, const float* x, const int64_t* y, int B, void* stream) {
+  DNN_ARG_CHECK(e && x && y, "engine_step: null argument");
+  DNN_ARG_CHECK(B >= 1 && B <= e->max_batch, "engine_step: batch %d exceeds max_batch %d", B, e->max_batch);
+  int rc = step_kernels(e, x, (const long long*)y, B, 0, (cudaStream_t)stream);
+  if (rc) return rc;
+  e->steps_launched += 1;
+  return kOk;
+}
+
+int dnnb200_engine_grad_only(dnnb200_engine* e, const float* x, const int64_t* y, int B, float* grads_out,
+                             float* h_loss, void* stream) {
+  DNN_ARG_CHECK(e && x && y && grads_out, "engine_grad_only: null argument");
+  DNN_ARG_CHECK(B >= 1 && B <= e->max_batch, "engine_grad_only: batch %d exceeds max_batch %d", B, e->max_batch);
+  cudaStream_t s = (cudaStream_t)stream;
+  float* keep = e->h_ctx.grads;
+  e->h_ctx.grads = grads_out;
+  int rc = push_ctx(e, s);
+  if (rc) return rc;
+  rc = step_kernels(e, x, (const long long*)y, B, /*grad_only=*/1, s);
+  if (rc) return rc;
+  const int slot = (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask);
+  DNN_CUDA_CHECK(cudaStreamSynchronize(s));
+  if (h_loss) DNN_CUDA_CHECK(cudaMemcpy(h_loss, e->loss_ring + slot, sizeof(float), cudaMemcpyDeviceToHost));
+  e->h_ctx.grads = keep;
+  return push_ctx(e, s);
+}
+
+int dnnb200_engine_train_host(dnnb200_engine* e, const float* h_x, const int64_t* h_y, int B, int nsteps,
+                              float* h_losses, void* stream) {
+  DNN_ARG_CHECK(e && h_x && h_y, "engine_train_host: null argument");
+  DNN_ARG_CHECK(B >= 1 && B <= e->max_batch, "engine_train_host: batch %d exceeds max_batch %d", B, e->max_batch);
+  DNN_ARG_CHECK(nsteps >= 1, "engine_train_host: nsteps must be positive");
+  int rc = ensure_ring(e);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  constexpr int R = dnnb200_engine::kRing;
+  const size_t xb = (size_t)B * kImgNumel * sizeof(float), yb = (size_t)B * sizeof(long long);
+  for (int t = 0; t < nsteps; ++t) {
+    const int slot = (int)(e->ring_uses % R);
+    // copy stream: wait until the fwd/bwd kernel that last read this slot has finished
+    if (e->ring_uses >= (unsigned long long)R) DNN_CUDA_CHECK(cudaStreamWaitEvent(e->copy_stream, e->slot_free[slot], 0));
+    DNN_CUDA_CHECK(cudaMemcpyAsync(e->d_x[slot], h_x + (size_t)t * B * kImgNumel, xb, cudaMemcpyHostToDevice, e->copy_stream));
+    DNN_CUDA_CHECK(cudaMemcpyAsync(e->d_y[slot], h_y + (size_t)t * B, yb, cudaMemcpyHostToDevice, e->copy_stream));
+    DNN_CUDA_CHECK(cudaEventRecord(e->slot_ready[slot], e->copy_stream));
+    DNN_CUDA_CHECK(cudaStreamWaitEvent(s, e->slot_ready[slot], 0));
+    rc = launch_fwd_bwd(true, e->params, e->d_x[slot], e->d_y[slot], e->saved, e->partials, e->img_loss,
+                        e->img_correct, nullptr, B, e->num_sms * 2, s);
+    if (rc) return rc;
+    DNN_CUDA_CHECK(cudaEventRecord(e->slot_free[slot], s));
+    const int lslot = (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask);
+    rc = launch_update(e->d_ctx, 1, B, lslot, 0, s);
+    if (rc) return rc;
+    e->launches += 2;
+    e->steps_launched += 1;
+    e->ring_uses += 1;
+    if (h_losses) {
+      DNN_CUDA_CHECK(cudaEventRecord(e->step_done[slot], s));
+      DNN_CUDA_CHECK(cudaStreamWaitEvent(e->d2h_stream, e->step_done[slot], 0));
+      DNN_CUDA_CHECK(cudaMemcpyAsync(h_losses + t, e->loss_ring + lslot, sizeof(float), cudaMemcpyDeviceToHost, e->d2h_stream));
+    }
+  }
+  if (h_losses) {
+    // make `stream` the single thing the caller has to synchronise
+    DNN_CUDA_CHECK(cudaEventRecord(e->step_done[0], e->d2h_stream));
+    DNN_CUDA_CHECK(cudaStreamWaitEvent(s, e->step_done[0], 0));
+  }
+  return kOk;
+}
+
+int dnnb200_engine_eval(dnnb200_engine* e, const float* x, const int64_t* y, int N, int bs, float* logits,
+                        double* h_out2, void* stream) {
+  DNN_ARG_CHECK(e && x && y && h_out2, "engine_eval: null argument");
+  DNN_ARG_CHECK(N >= 1 && bs >= 1, "engine_eval: N and bs must be positive");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (N > e->eval_cap) {
+    DNN_CUDA_CHECK(cudaStreamSynchronize(s));
+    cudaFree(e->eval_loss); cudaFree(e->eval_correct);
+    e->eval_loss = nullptr; e->eval_correct = nullptr; e->eval_cap = 0;
+    DNN_CUDA_CHECK(cudaMalloc(&e->eval_loss, (size_t)N * sizeof(float)));
+    DNN_CUDA_CHECK(cudaMalloc(&e->eval_correct, (size_t)N * sizeof(int)));
+    e->eval_cap = N;
+  }
+  int rc = launch_fwd_bwd(false, e->params, x, (const long long*)y, nullptr, nullptr, e->eval_loss, e->eval_correct,
+                          logits, N, e->num_sms * 2, s);
+  if (rc) return rc;
+  rc = launch_eval_reduce(e->eval_loss, e->eval_correct, N, bs, e->d_eval_out, s);
+  if (rc) return rc;
+  e->launches += 2;
+  DNN_CUDA_CHECK(cudaMemcpyAsync(h_out2, e->d_eval_out, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  DNN_CUDA_CHECK(cudaStreamSynchronize(s));
+  return kOk;
+}
+
+int dnnb200_engine_allreduce(dnnb200_engine* e, const float* in, float* out, int n, int mode, int two_shot,
+                             void* stream) {
+  DNN_ARG_CHECK(e && in, "engine_allreduce: null argument");
+  const float* ins[1] = {in};
+  float* outs[1] = {out};
+  int rc = launch_allreduce(e->d_ctx, 1, ins, outs, n, mode, two_shot, (cudaStream_t)stream);
+  if (rc) return rc;
+  e->launches += 1;
+  return kOk;
+}
+
+int dnnb200_engine_leave(dnnb200_engine* e, void* stream) {
+  DNN_ARG_CHECK(e, "null engine");
+  if (!e->group || e->group->world == 1) return kOk;
+  leave_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(e->d_ctx, 0);
+  DNN_CUDA_CHECK(cudaGetLastError());
+  e->launches += 1;
+  return kOk;
+}
+
+int dnnb200_engine_rejoin(dnnb200_engine* e, unsigned long long step, void* stream) {
+  DNN_ARG_CHECK(e, "null engine");
+  cudaStream_t s = (cudaStream_t)stream;
+  ctl_set_step_kernel<<<1, 1, 0, s>>>(e->ctl, step);
+  DNN_CUDA_CHECK(cudaGetLastError());
+  if (e->group && e->group->world > 1) {
+    leave_kernel<<<1, 32, 0, s>>>(e->d_ctx, 1);
+    DNN_CUDA_CHECK(cudaGetLastError());
+  }
+  e->launches += 2;
+  return kOk;
+}
+
+// ---- ranks emulated on one device -----------------------------------------------
+static int gather_ctxs(dnnb200_engine** engines, int n, RankCtx** d_out) {
+  std::vector<RankCtx> h((size_t)n);
+  for (int r = 0; r < n; ++r) h[(size_t)r] = engines[r]->h_ctx;
+  RankCtx* d = nullptr;
+  DNN_CUDA_CHECK(cudaMalloc(&d, sizeof(RankCtx) * (size_t)n));
+  DNN_CUDA_CHECK(cudaMemcpy(d, h.data(), sizeof(RankCtx) * (size_t)n, cudaMemcpyHostToDevice));
+  *d_out = d;
+  return kOk;
+}
+
+int dnnb200_vr_step(dnnb200_engine** engines, int n, const float* const* xs, const int64_t* const* ys, int B,
+                    void* stream) {
+  DNN_ARG_CHECK(engines && xs && ys && n >= 1 && n <= kMaxWorld, "vr_step: bad arguments");
+  cudaStream_t s = (cudaStream_t)stream;
+  for (int r = 0; r < n; ++r) {
+    dnnb200_engine* e = engines[r];
+    if (!xs[r]) continue;  // this virtual rank sits the step out (it has left)
+    DNN_ARG_CHECK(B >= 1 && B <= e->max_batch, "vr_step: batch exceeds max_batch");
+    int rc = launch_fwd_bwd(true, e->params, xs[r], (const long long*)ys[r], e->saved, e->partials, e->img_loss,
+                            e->img_correct, nullptr, B, e->num_sms * 2, s);
+    if (rc) return rc;
+    e->launches += 1;
+  }
+  // compact the participating ranks into one cooperative launch
+  std::vector<dnnb200_engine*> live;
+  for (int r = 0; r < n; ++r) if (xs[r]) live.push_back(engines[r]);
+  if (live.empty()) return kOk;
+  RankCtx* d = nullptr;
+  int rc = gather_ctxs(live.data(), (int)live.size(), &d);
+  if (rc) return rc;
+  const int lslot = (int)(live[0]->steps_launched & (unsigned long long)live[0]->loss_ring_mask);
+  rc = launch_update(d, (int)live.size(), B, lslot, 0, s);
+  cudaStreamSynchronize(s);
+  cudaFree(d);
+  if (rc) return rc;
+  for (auto* e : live) { e->launches += 1; e->steps_launched += 1; }
+  return kOk;
+}
+
+int dnnb200_vr_allreduce(dnnb200_engine** engines, int n, const float* const* in, float* const* out, int count,
+                         int mode, int two_shot, void* stream) {
+  DNN_ARG_CHECK(engines && in && out && n >= 1 && n <= kMaxWorld, "vr_allreduce: bad arguments");
+  cudaStream_t s = (cudaStream_t)stream;
+  std::vector<dnnb200_engine*> live;
+  std::vector<const float*> lin;
+  std::vector<float*> lout;
+  for (int r = 0; r < n; ++r)
+    if (in[r]) { live.push_back(engines[r]); lin.push_back(in[r]); lout.push_back(out[r]); }
+  if (live.empty()) return kOk;
+  RankCtx* d = nullptr;
+  int rc = gather_ctxs(live.data(), (int)live.size(), &d);
+  if (rc) return rc;
+  rc = launch_allreduce(d, (int)live.size(), lin.data(), lout.data(), count, mode, two_shot, s);
+  cudaStreamSynchronize(s);
+  cudaFree(d);
+  if (rc) return rc;
+  for (auto* e : live) e->launches += 1;
+  return kOk;
+}
+
+}  // extern "C"

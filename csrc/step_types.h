@@ -1,0 +1,55 @@
+// Device-visible structs shared by the fused step kernels, the stand-alone
+// all-reduce kernel and the host runtime (engine.cpp / peer_group.cpp).
+#pragma once
+#include <stdint.h>
+#include "layout.h"
+
+namespace dnnb200 {
+
+// Flags area of one rank: one row per source rank, kFlagRow words per row.
+//   [src][0 .. kNumSlices)  sequence number of the newest slice src has pushed here
+//   [src][kLeaveSlot]       "leave marker": first sequence number src will NOT take part in (0 = present)
+constexpr int kFlagRow = 128;
+constexpr int kLeaveSlot = kNumSlices;  // 122
+static_assert(kLeaveSlot < kFlagRow, "flag row too small");
+
+// Receive area of one rank: [2 parities][world][kFlatNumel] floats. Parity = seq & 1,
+// so the pushes of step t+1 never land on data a slow reader still sums for step t.
+
+enum StepStatus : unsigned int {
+  kStatusOk = 0,
+  kStatusTimeout = 1u,  // bit 0: some peer was waited for longer than timeout_ns
+  // bits 8..23: bitmask of the ranks that timed out
+};
+
+struct StepCtl {
+  unsigned long long step;        // optimizer steps completed; exchange sequence of the next step = step + 1
+  unsigned long long timeout_ns;  // spin bound while waiting for a peer's slice (0 = wait forever)
+  float lr;
+  float mu;
+  float loss_sum;           // sum of per-step mean losses since the host last cleared it
+  unsigned int loss_steps;  // number of steps in loss_sum
+  unsigned int ctas_done;   // last-CTA-out counter of the update kernel
+  unsigned int status;      // StepStatus bits, sticky until the host clears them
+  unsigned int active_mask; // ranks configured into the exchange (bit r = rank r)
+  unsigned int average_only;  // 1: out = mean(in) with no optimizer (epoch-average / replication modes)
+};
+
+struct RankCtx {
+  float* params;          // [kFlatNumel] master weights
+  float* momentum;        // [kFlatNumel]
+  float* grads;           // [kFlatNumel] optional: averaged gradient written back (nullptr = skip)
+  const float* saved;     // [B][kSavStride]   per-image FC inputs/deltas from the fwd/bwd kernel
+  const float* partials;  // [B][kConvPrefix]  per-image conv weight/bias gradients
+  const float* img_loss;  // [B]
+  float* loss_ring;       // [loss_ring_mask + 1] per-step mean loss, indexed by step & mask
+  StepCtl* ctl;
+  int loss_ring_mask;
+  int rank;
+  int world;
+  int pad_;
+  float* recv[kMaxWorld];          // recv[p]  = rank p's receive area as mapped in THIS process
+  unsigned int* flags[kMaxWorld];  // flags[p] = rank p's flag area as mapped in THIS process
+};
+
+}  // namespace dnnb200

@@ -1,0 +1,302 @@
+"""ctypes binding of the in-tree native runtime (``_native/libdnnb200.so``).
+
+The library is built by ``build.py`` / ``__graft_entry__.build()`` with
+``nvcc -gencode arch=compute_100a,code=sm_100a`` and exposes the C ABI declared
+in ``include/dnnb200.h``. Tensors are passed as raw device pointers and the
+kernels are enqueued on PyTorch's current CUDA stream, so they compose with
+torch ops, events and CUDA graphs.
+
+There is deliberately no fallback here: on a CUDA tensor a missing library is
+an error (``require()``), so a GPU run can never silently measure eager PyTorch.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+from typing import Optional, Sequence
+
+import torch
+
+_LIB_PATH = Path(__file__).resolve().parent.parent / "_native" / "libdnnb200.so"
+_lib: Optional[C.CDLL] = None
+_load_error: Optional[str] = None
+
+FLAT_NUMEL = 62144
+IPC_HANDLE_BYTES = 64
+
+
+class Ctl(C.Structure):
+    """Mirror of ``dnnb200_ctl`` / ``StepCtl`` (csrc/step_types.h)."""
+
+    _fields_ = [
+        ("step", C.c_ulonglong),
+        ("timeout_ns", C.c_ulonglong),
+        ("lr", C.c_float),
+        ("mu", C.c_float),
+        ("loss_sum", C.c_float),
+        ("loss_steps", C.c_uint),
+        ("ctas_done", C.c_uint),
+        ("status", C.c_uint),
+        ("active_mask", C.c_uint),
+        ("average_only", C.c_uint),
+    ]
+
+
+def lib_path() -> Path:
+    return _LIB_PATH
+
+
+def _load() -> Optional[C.CDLL]:
+    global _lib, _load_error
+    if _lib is not None or _load_error is not None:
+        return _lib
+    if not _LIB_PATH.exists():
+        _load_error = f"{_LIB_PATH} not found -- run `python build.py`"
+        return None
+    try:
+        lib = C.CDLL(str(_LIB_PATH))
+    except OSError as e:  # e.g. libcudart missing on a CPU-only box
+        _load_error = f"cannot load {_LIB_PATH}: {e}"
+        return None
+    lib.dnnb200_last_error.restype = C.c_char_p
+    lib.dnnb200_engine_launches.restype = C.c_ulonglong
+    lib.dnnb200_engine_launches.argtypes = [C.c_void_p]
+    _lib = lib
+    return lib
+
+
+def available() -> bool:
+    return _load() is not None
+
+
+def require() -> C.CDLL:
+    lib = _load()
+    if lib is None:
+        raise RuntimeError(
+            "native sm_100a runtime is not available: " + str(_load_error) +
+            " (CUDA tensors are never routed to an eager fallback)")
+    return lib
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        msg = require().dnnb200_last_error().decode(errors="replace")
+        raise RuntimeError(f"dnnb200 native call failed (code {rc}): {msg}")
+
+
+def _p(t: Optional[torch.Tensor]) -> C.c_void_p:
+    if t is None:
+        return C.c_void_p(0)
+    return C.c_void_p(t.data_ptr())
+
+
+def _stream() -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _f32(t: torch.Tensor, name: str) -> torch.Tensor:
+    if t.dtype != torch.float32 or not t.is_contiguous() or not t.is_cuda:
+        raise TypeError(f"{name}: expected a contiguous CUDA float32 tensor, got {t.dtype} "
+                        f"contiguous={t.is_contiguous()} device={t.device}")
+    return t
+
+
+def layout():
+    lib = require()
+    offs = (C.c_int * 10)()
+    flat, sl, ns = C.c_int(), C.c_int(), C.c_int()
+    _check(lib.dnnb200_layout(offs, C.byref(flat), C.byref(sl), C.byref(ns)))
+    return list(offs), flat.value, sl.value, ns.value
+
+
+# ---------------------------------------------------------------------------
+# layer kernels
+# ---------------------------------------------------------------------------
+def conv_relu_pool_fwd(x, w, b, y, idx) -> None:
+    lib = require()
+    N, Ci, H, W = x.shape
+    _check(lib.dnnb200_conv_relu_pool_fwd(_p(_f32(x, "x")), _p(_f32(w, "w")), _p(_f32(b, "b")), _p(_f32(y, "y")),
+                                          _p(idx), N, Ci, H, W, w.shape[0], _stream()))
+
+
+def conv_relu_pool_bwd(x, w, y, idx, dy, dx, dw, db) -> None:
+    lib = require()
+    N, Ci, H, W = x.shape
+    _check(lib.dnnb200_conv_relu_pool_bwd(_p(_f32(x, "x")), _p(_f32(w, "w")), _p(_f32(y, "y")), _p(idx),
+                                          _p(_f32(dy, "dy")), _p(dx), _p(_f32(dw, "dw")), _p(_f32(db, "db")),
+                                          N, Ci, H, W, w.shape[0], _stream()))
+
+
+def linear_fwd(x, w, b, y, relu: bool) -> None:
+    lib = require()
+    N, K = x.shape
+    _check(lib.dnnb200_linear_fwd(_p(_f32(x, "x")), _p(_f32(w, "w")), _p(_f32(b, "b")), _p(_f32(y, "y")),
+                                  N, w.shape[0], K, int(relu), _stream()))
+
+
+def linear_bwd(x, w, y, dy, dx, dw, db, relu: bool) -> None:
+    lib = require()
+    N, K = x.shape
+    _check(lib.dnnb200_linear_bwd(_p(_f32(x, "x")), _p(_f32(w, "w")), _p(_f32(y, "y")), _p(_f32(dy, "dy")), _p(dx),
+                                  _p(_f32(dw, "dw")), _p(_f32(db, "db")), N, w.shape[0], K, int(relu), _stream()))
+
+
+def softmax_xent(logits, target, loss, dlogits) -> None:
+    lib = require()
+    if target.dtype != torch.int64:
+        raise TypeError("target must be int64")
+    N, Cn = logits.shape
+    _check(lib.dnnb200_softmax_xent(_p(_f32(logits, "logits")), _p(target), _p(loss), _p(_f32(dlogits, "dlogits")),
+                                    N, Cn, _stream()))
+
+
+def sgd_momentum(p, g, buf, lr: float, mu: float, first_step: bool, scale: float = 1.0) -> None:
+    lib = require()
+    _check(lib.dnnb200_sgd_momentum(_p(_f32(p, "p")), _p(_f32(g, "g")), _p(_f32(buf, "buf")), p.numel(),
+                                    C.c_float(lr), C.c_float(mu), int(first_step), C.c_float(scale), _stream()))
+
+
+# ---------------------------------------------------------------------------
+# peer group
+# ---------------------------------------------------------------------------
+class Group:
+    """This rank's receive/flag area plus the mapped areas of its peers."""
+
+    def __init__(self, rank: int, world: int):
+        lib = require()
+        self.rank, self.world = rank, world
+        self._h = C.c_void_p()
+        buf = (C.c_ubyte * IPC_HANDLE_BYTES)()
+        _check(lib.dnnb200_group_create(rank, world, C.byref(self._h), buf))
+        self.handle: bytes = bytes(buf)
+
+    def connect(self, all_handles: Sequence[bytes]) -> None:
+        assert len(all_handles) == self.world
+        blob = b"".join(all_handles)
+        assert len(blob) == self.world * IPC_HANDLE_BYTES
+        _check(require().dnnb200_group_connect(self._h, blob))
+
+    @staticmethod
+    def connect_local(groups: Sequence["Group"]) -> None:
+        arr = (C.c_void_p * len(groups))(*[g._h for g in groups])
+        _check(require().dnnb200_group_connect_local(arr, len(groups)))
+
+    def close(self) -> None:
+        if self._h:
+            require().dnnb200_group_destroy(self._h)
+            self._h = C.c_void_p()
+
+
+# ---------------------------------------------------------------------------
+# fused step engine
+# ---------------------------------------------------------------------------
+class Engine:
+    """Owns the step buffers; updates ``params``/``momentum`` (flat CUDA tensors) in place."""
+
+    def __init__(self, params: torch.Tensor, momentum: torch.Tensor, grads: Optional[torch.Tensor],
+                 max_batch: int, lr: float, mu: float):
+        lib = require()
+        for name, t in (("params", params), ("momentum", momentum)):
+            _f32(t, name)
+            if t.numel() != FLAT_NUMEL:
+                raise ValueError(f"{name} must have {FLAT_NUMEL} elements")
+        self.params, self.momentum, self.grads = params, momentum, grads  # keep alive
+        self.max_batch = max_batch
+        self._h = C.c_void_p()
+        self.group: Optional[Group] = None
+        with torch.cuda.device(params.device):
+            _check(lib.dnnb200_engine_create(_p(params), _p(momentum), _p(grads), max_batch, C.c_float(lr),
+                                             C.c_float(mu), C.byref(self._h)))
+
+    # -- configuration
+    def attach_group(self, group: Optional[Group]) -> None:
+        self.group = group
+        _check(require().dnnb200_engine_attach_group(self._h, group._h if group else None))
+
+    def set_hparams(self, lr: float, mu: float) -> None:
+        _check(require().dnnb200_engine_set_hparams(self._h, C.c_float(lr), C.c_float(mu), _stream()))
+
+    def set_membership(self, active_mask: int, timeout_ns: int = 0) -> None:
+        _check(require().dnnb200_engine_set_membership(self._h, C.c_uint(active_mask), C.c_ulonglong(timeout_ns),
+                                                       _stream()))
+
+    def zero_momentum(self) -> None:
+        _check(require().dnnb200_engine_zero_momentum(self._h, _stream()))
+
+    def reset_loss(self) -> None:
+        _check(require().dnnb200_engine_reset_loss(self._h, _stream()))
+
+    def read_ctl(self) -> Ctl:
+        c = Ctl()
+        _check(require().dnnb200_engine_read_ctl(self._h, C.byref(c), _stream()))
+        return c
+
+    @property
+    def launches(self) -> int:
+        return int(require().dnnb200_engine_launches(self._h))
+
+    # -- work
+    def step(self, x: torch.Tensor, y: torch.Tensor) -> None:
+        _f32(x, "x")
+        if y.dtype != torch.int64 or not y.is_cuda:
+            raise TypeError("y must be a CUDA int64 tensor")
+        _check(require().dnnb200_engine_step(self._h, _p(x), _p(y), x.shape[0], _stream()))
+
+    def grad_only(self, x: torch.Tensor, y: torch.Tensor, grads_out: torch.Tensor) -> float:
+        _f32(x, "x"); _f32(grads_out, "grads_out")
+        loss = C.c_float()
+        _check(require().dnnb200_engine_grad_only(self._h, _p(x), _p(y), x.shape[0], _p(grads_out), C.byref(loss),
+                                                  _stream()))
+        return float(loss.value)
+
+    def train_host(self, h_x: torch.Tensor, h_y: torch.Tensor, h_losses: Optional[torch.Tensor]) -> None:
+        """h_x [steps,B,3,32,32] fp32 and h_y [steps,B] int64 in PINNED host memory."""
+        if not (h_x.is_pinned() and h_y.is_pinned()):
+            raise ValueError("train_host needs pinned host tensors")
+        if h_losses is not None and not h_losses.is_pinned():
+            raise ValueError("h_losses must be pinned")
+        steps, B = h_y.shape
+        assert h_x.shape[0] == steps and h_x.shape[1] == B and h_x.is_contiguous() and h_y.is_contiguous()
+        _check(require().dnnb200_engine_train_host(self._h, _p(h_x), _p(h_y), B, steps, _p(h_losses), _stream()))
+
+    def evaluate(self, x: torch.Tensor, y: torch.Tensor, bs: int, logits: Optional[torch.Tensor] = None):
+        _f32(x, "x")
+        out = (C.c_double * 2)()
+        _check(require().dnnb200_engine_eval(self._h, _p(x), _p(y), x.shape[0], bs, _p(logits), out, _stream()))
+        return float(out[0]), int(out[1])
+
+    def allreduce(self, inp: torch.Tensor, out: Optional[torch.Tensor], mode: int = 0, two_shot: bool = False) -> None:
+        _f32(inp, "in")
+        _check(require().dnnb200_engine_allreduce(self._h, _p(inp), _p(out), inp.numel(), mode, int(two_shot),
+                                                  _stream()))
+
+    def leave(self) -> None:
+        _check(require().dnnb200_engine_leave(self._h, _stream()))
+
+    def rejoin(self, step: int) -> None:
+        _check(require().dnnb200_engine_rejoin(self._h, C.c_ulonglong(step), _stream()))
+
+    def close(self) -> None:
+        if self._h:
+            require().dnnb200_engine_destroy(self._h)
+            self._h = C.c_void_p()
+
+
+def vr_step(engines: Sequence[Engine], xs: Sequence[Optional[torch.Tensor]], ys: Sequence[Optional[torch.Tensor]],
+            B: int) -> None:
+    """One step of ``len(engines)`` ranks emulated on ONE device (cooperative launch)."""
+    n = len(engines)
+    eh = (C.c_void_p * n)(*[e._h for e in engines])
+    xp = (C.c_void_p * n)(*[(x.data_ptr() if x is not None else 0) for x in xs])
+    yp = (C.c_void_p * n)(*[(y.data_ptr() if y is not None else 0) for y in ys])
+    _check(require().dnnb200_vr_step(eh, n, xp, yp, B, _stream()))
+
+
+def vr_allreduce(engines: Sequence[Engine], ins: Sequence[Optional[torch.Tensor]],
+                 outs: Sequence[Optional[torch.Tensor]], count: int, mode: int = 0, two_shot: bool = False) -> None:
+    n = len(engines)
+    eh = (C.c_void_p * n)(*[e._h for e in engines])
+    ip = (C.c_void_p * n)(*[(t.data_ptr() if t is not None else 0) for t in ins])
+    op = (C.c_void_p * n)(*[(t.data_ptr() if t is not None else 0) for t in outs])
+    _check(require().dnnb200_vr_allreduce(eh, n, ip, op, count, mode, int(two_shot), _stream()))

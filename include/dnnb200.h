@@ -1,0 +1,142 @@
+/* C ABI of the native runtime (libdnnb200.so), loaded from Python with ctypes
+ * (distributed_neural_network_b200/ops/native.py) and usable from C/C++.
+ *
+ * Conventions: every function returns 0 on success or a DNNB200_ERR_* code;
+ * dnnb200_last_error() gives the message of the last failure on the calling
+ * thread. Pointers are device pointers unless the name starts with h_ (host,
+ * pinned where noted). All work is enqueued on the given cudaStream_t (passed as
+ * void*; NULL = legacy default stream) and nothing synchronises unless stated.
+ * Tensors are fp32, contiguous, NCHW; labels are int64.
+ */
+#ifndef DNNB200_H_
+#define DNNB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DNNB200_OK 0
+#define DNNB200_ERR_CUDA 1
+#define DNNB200_ERR_ARG 2
+#define DNNB200_ERR_STATE 3
+#define DNNB200_ERR_TIMEOUT 4
+
+#define DNNB200_FLAT_NUMEL 62144 /* floats in the flat parameter vector (62006 real + alignment gaps) */
+#define DNNB200_IPC_HANDLE_BYTES 64
+
+const char* dnnb200_last_error(void);
+int dnnb200_version(void);
+/* layout constants, so Python can assert it agrees with csrc/layout.h */
+int dnnb200_layout(int* offsets10, int* flat_numel, int* slice, int* num_slices);
+
+/* ---- layer kernels (reference: models/model.py:20-27) ---------------- */
+/* y = maxpool2x2(relu(conv5x5_valid(x, w) + b)); idx = 2-bit argmax per pooled pixel (K1-K6) */
+int dnnb200_conv_relu_pool_fwd(const float* x, const float* w, const float* b, float* y, uint8_t* idx,
+                               int N, int Ci, int H, int W, int Co, void* stream);
+/* backward of the above; dx may be NULL (first layer). ReLU'/pool' are folded in (K14-K17) */
+int dnnb200_conv_relu_pool_bwd(const float* x, const float* w, const float* y, const uint8_t* idx,
+                               const float* dy, float* dx, float* dw, float* db,
+                               int N, int Ci, int H, int W, int Co, void* stream);
+/* y[N,M] = act(x[N,K] w[M,K]^T + b[M]) (K8-K10) */
+int dnnb200_linear_fwd(const float* x, const float* w, const float* b, float* y, int N, int M, int K,
+                       int relu, void* stream);
+/* dx may be NULL; y is the layer OUTPUT (its sign gives ReLU') (K13, K14) */
+int dnnb200_linear_bwd(const float* x, const float* w, const float* y, const float* dy, float* dx,
+                       float* dw, float* db, int N, int M, int K, int relu, void* stream);
+/* mean cross-entropy of logits[N,C] and d(loss)/d(logits) in one pass (K11, K12;
+ * reference: data_parallelism_train.py:29,197) */
+int dnnb200_softmax_xent(const float* logits, const int64_t* target, float* loss, float* dlogits,
+                         int N, int C, void* stream);
+/* buf = mu*buf + g*scale (buf = g*scale if first_step); p -= lr*buf (K19;
+ * reference: data_parallelism_train.py:187,199) */
+int dnnb200_sgd_momentum(float* p, const float* g, float* buf, int n, float lr, float mu,
+                         int first_step, float scale, void* stream);
+
+/* ---- peer group: symmetric receive/flag buffers over CUDA IPC (reference: the mpi4py
+ *      send/recv star of data_parallelism_train.py:118,135,210,227 -- SURVEY 2.5) ---------- */
+typedef struct dnnb200_group dnnb200_group;
+/* allocates this rank's receive + flag area on the current device and exports its IPC handle */
+int dnnb200_group_create(int rank, int world, dnnb200_group** out, void* h_handle64);
+/* h_all_handles: world x 64 bytes, gathered by the bootstrap (mpi4py / torch.distributed / file) */
+int dnnb200_group_connect(dnnb200_group* g, const void* h_all_handles);
+/* single-process variant: the n groups live in this process (tests; ranks emulated on one GPU) */
+int dnnb200_group_connect_local(dnnb200_group** groups, int n);
+int dnnb200_group_destroy(dnnb200_group* g);
+
+/* ---- fused step engine ------------------------------------------------------------------- */
+typedef struct dnnb200_engine dnnb200_engine;
+typedef struct dnnb200_ctl {
+  unsigned long long step;
+  unsigned long long timeout_ns;
+  float lr, mu;
+  float loss_sum;
+  unsigned int loss_steps;
+  unsigned int ctas_done;
+  unsigned int status;
+  unsigned int active_mask;
+  unsigned int average_only;
+} dnnb200_ctl;
+
+/* params/momentum (and optional grads, may be NULL) are caller-owned flat buffers of
+ * DNNB200_FLAT_NUMEL floats, e.g. Network._flat: the engine updates them in place */
+int dnnb200_engine_create(float* params, float* momentum, float* grads, int max_batch, float lr, float mu,
+                          dnnb200_engine** out);
+int dnnb200_engine_destroy(dnnb200_engine* e);
+int dnnb200_engine_attach_group(dnnb200_engine* e, dnnb200_group* g);
+int dnnb200_engine_set_hparams(dnnb200_engine* e, float lr, float mu, void* stream);
+int dnnb200_engine_set_membership(dnnb200_engine* e, unsigned int active_mask, unsigned long long timeout_ns,
+                                  void* stream);
+/* zero the momentum buffer (the reference re-creates its optimizer every epoch:
+ * data_parallelism_train.py:187) */
+int dnnb200_engine_zero_momentum(dnnb200_engine* e, void* stream);
+int dnnb200_engine_reset_loss(dnnb200_engine* e, void* stream);
+/* synchronises the stream and copies the control block to the host */
+int dnnb200_engine_read_ctl(dnnb200_engine* e, dnnb200_ctl* h_out, void* stream);
+/* number of kernels this engine has launched so far */
+unsigned long long dnnb200_engine_launches(const dnnb200_engine* e);
+
+/* one optimizer step on a device-resident batch: fwd/bwd kernel + update kernel
+ * (reference: the loop body data_parallelism_train.py:195-203) */
+int dnnb200_engine_step(dnnb200_engine* e, const float* x, const int64_t* y, int B, void* stream);
+/* nsteps steps fed from PINNED host memory: per step an async H2D copy of that step's
+ * inputs (4-slot device ring on a copy stream), the two kernels, and an async D2H copy of
+ * the step's mean loss into h_losses[t] (pinned). Returns after everything is enqueued;
+ * the caller synchronises `stream` before reading h_losses. */
+int dnnb200_engine_train_host(dnnb200_engine* e, const float* h_x, const int64_t* h_y, int B, int nsteps,
+                              float* h_losses, void* stream);
+/* forward only over N device-resident images; h_out2 = {mean over batches of the batch-mean
+ * loss, number of correct predictions}; logits may be NULL. Synchronises.
+ * (reference: data_parallelism_train.py:157-183) */
+int dnnb200_engine_eval(dnnb200_engine* e, const float* x, const int64_t* y, int N, int bs, float* logits,
+                        double* h_out2, void* stream);
+/* forward + backward only (no update): fills the per-image records; grads of the local batch
+ * are written to `grads_out` (flat, summed over the batch, already scaled by 1/B). For tests. */
+int dnnb200_engine_grad_only(dnnb200_engine* e, const float* x, const int64_t* y, int B, float* grads_out,
+                             float* h_loss, void* stream);
+
+/* peer-memory all-reduce of a flat vector (n % 4 == 0, n <= FLAT_NUMEL).
+ * mode 0: out = mean(in); mode 1: fused SGD-momentum on the engine's params with g = mean(in)
+ * (out may be NULL). two_shot selects the reduce-scatter/all-gather variant. */
+int dnnb200_engine_allreduce(dnnb200_engine* e, const float* in, float* out, int n, int mode, int two_shot,
+                             void* stream);
+
+/* membership epoch: announce that this rank stops taking part after the steps
+ * already enqueued; peers divide by the survivors from then on */
+int dnnb200_engine_leave(dnnb200_engine* e, void* stream);
+/* come back: clear the marker on every peer and adopt the group's sequence number */
+int dnnb200_engine_rejoin(dnnb200_engine* e, unsigned long long step, void* stream);
+
+/* ranks emulated on ONE device (tests, and boxes with fewer GPUs than ranks): one cooperative
+ * launch runs the update (or all-reduce) of all n engines so that they can wait on each other */
+int dnnb200_vr_step(dnnb200_engine** engines, int n, const float* const* xs, const int64_t* const* ys, int B,
+                    void* stream);
+int dnnb200_vr_allreduce(dnnb200_engine** engines, int n, const float* const* in, float* const* out, int count,
+                         int mode, int two_shot, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DNNB200_H_ */
