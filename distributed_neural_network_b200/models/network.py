@@ -94,6 +94,17 @@ class Network(nn.Module):
         self._rebind()
         return self
 
+    def __deepcopy__(self, memo):
+        # nn.Parameter.__deepcopy__ clones each view into private storage, which would silently
+        # detach the copy's parameters from its flat buffer; rebuild the aliasing instead.
+        new = type(self)()
+        new._buffers["_flat"] = self._flat.detach().clone()
+        new._buffers["_flat_grad"] = self._flat_grad.detach().clone()
+        new._rebind()
+        new.train(self.training)
+        memo[id(self)] = new
+        return new
+
     @property
     def flat_params(self) -> torch.Tensor:
         return self._flat
