@@ -37,6 +37,12 @@ def main():
         us = time_steps(lambda: eng.step(x, y), 500)
         out[f"fused_step_us_B{B}"] = round(us, 2)
         out[f"fused_img_per_s_B{B}"] = round(B / us * 1e6)
+        out[f"cluster_B{B}"] = str(eng.cluster_info(B))
+        if B in (16, 64):
+            for cs in (1, 2, 4, 8):
+                eng.set_cluster_size(cs)
+                out[f"fused_step_us_B{B}_cs{cs}"] = round(time_steps(lambda: eng.step(x, y), 300), 2)
+            eng.set_cluster_size(0)
         if B == 16:
             steps = 512
             hx = torch.randn(steps, B, 3, 32, 32).pin_memory()

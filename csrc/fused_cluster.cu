@@ -1,0 +1,600 @@
+// fwd_bwd_cluster_kernel: the forward/backward half of the training step with each
+// IMAGE spread over a thread-block cluster of CS CTAs (CS = 1, 2, 4 or 8).
+//
+// Why: at the reference's batch sizes (1..64 per rank, data_parallelism_train.py:263,
+// run_training.sh) one CTA per image leaves most of the 148 SMs idle and makes the step a
+// long serial chain on a few SMs. A cluster splits every layer of one image CS ways and
+// re-assembles the small activations with distributed-shared-memory stores:
+//
+//   conv1+ReLU+pool   split by pooled rows      -> p1 pushed to every CTA of the cluster
+//   conv2+ReLU+pool   split by output channel   -> p2 pushed
+//   fc1 / fc2         split by output row       -> h1 / h2 pushed   (also splits the 192 KB weight stream)
+//   fc3, softmax-CE, fc3 dX                      redundantly in every CTA (tiny)
+//   fc2 dX / fc1 dX   split by input column     -> d1 / g2 pushed
+//   conv2 wgrad       split by output channel   (needs only p1, g2: local)
+//   conv2 dgrad       split by input pixel      -> g1 stays local because ...
+//   conv1 wgrad       ... is split by the same pixel ranges; each CTA emits a partial
+//
+// Six cluster barriers per image (~0.2 us each) replace what would be kernel boundaries in
+// a layer-at-a-time design. All math is fp32 FFMA, bit-compatible in structure with the
+// one-CTA kernel of fused_step.cu (which stays as the CS-independent oracle and eval path).
+//
+// reference: models/model.py:20-27 forward; autograd of data_parallelism_train.py:195-198.
+#include <cooperative_groups.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "common.cuh"
+#include "layout.h"
+
+namespace cg = cooperative_groups;
+
+namespace dnnb200 {
+
+constexpr int kCLThreads = 512;
+constexpr int kXpRow = 37;                 // padded row stride of the gather copy of the image:
+constexpr int kXpCh = 32 * kXpRow + 25;    //   bank(kh*37+kw) = 5kh+kw is distinct for the 25 taps
+constexpr int kCLRed = 9408;  // CS=2 worst case: conv2 dgrad partials 16*6*98
+
+struct __align__(16) CLSmem {
+  alignas(16) float x[kImgNumel];        // image, dense CHW (TMA bulk copy)
+  alignas(16) float xp[3 * kXpCh + 8];   // image, padded rows, for the conv1 wgrad gather
+  alignas(16) float w1[456];             // conv1.weight natural layout [o][c][kh][kw] + bias at 450
+  alignas(16) float w2[2400];            // conv2.weight natural layout [o][c][kh][kw]
+  alignas(16) float w2d[16 * 25 * 8];    // conv2.weight as [(o,kh,kw)][c8] for the data gradient
+  alignas(16) float b2[16];
+  alignas(16) float p1[1176 + 8];
+  alignas(16) float p2[400];
+  alignas(16) float h1[120];
+  alignas(16) float h2[88];
+  alignas(16) float logits[16];
+  alignas(16) float d3[16];
+  alignas(16) float d2[88];
+  alignas(16) float d1[120];
+  alignas(16) float g2[400];
+  alignas(16) float g1[1176 + 8];
+  alignas(16) float dc2p[16 * 18 * 18];
+  alignas(16) float red[kCLRed];
+  alignas(16) int poff[196];             // (2*ph)*kXpRow + 2*pw of pooled pixel q
+  alignas(8) unsigned long long mbar;
+  alignas(16) unsigned char idx1[1176 + 8];
+  alignas(16) unsigned char idx2[400];
+};
+
+__device__ __forceinline__ uint32_t cl_smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void cl_mbar_init(unsigned long long* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(cl_smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void cl_mbar_expect_tx(unsigned long long* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(cl_smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void cl_mbar_wait(unsigned long long* bar, uint32_t phase) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(cl_smem_u32(bar)),
+      "r"(phase)
+      : "memory");
+}
+__device__ __forceinline__ void cl_bulk_g2s(void* dst, const void* src, uint32_t bytes, unsigned long long* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          cl_smem_u32(dst)),
+      "l"(src), "r"(bytes), "r"(cl_smem_u32(bar))
+      : "memory");
+}
+
+template <int CS>
+struct Peers {
+  CLSmem* p[CS];
+};
+
+// rows [m0, m1) of y = act(b + W . in); results pushed into the same smem field of every CTA
+template <int CS, int K, bool kRelu>
+__device__ __forceinline__ void fc_rows_push(const float* __restrict__ W, const float* __restrict__ b,
+                                             const float* in, int m0, int m1, const Peers<CS>& peers,
+                                             size_t field_off) {
+  constexpr int K4 = K / 4;
+  constexpr int kWarps = kCLThreads / 32;
+  constexpr int kIter = (K4 + 31) / 32;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float4* in4 = reinterpret_cast<const float4*>(in);
+  for (int r0 = m0 + warp; r0 < m1; r0 += 2 * kWarps) {
+    float4 w[2][kIter];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int r = r0 + q * kWarps;
+#pragma unroll
+      for (int it = 0; it < kIter; ++it) {
+        const int k4 = lane + it * 32;
+        w[q][it] = (r < m1 && k4 < K4) ? __ldg(reinterpret_cast<const float4*>(W + (size_t)r * K) + k4)
+                                       : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int r = r0 + q * kWarps;
+      float acc = 0.f;
+#pragma unroll
+      for (int it = 0; it < kIter; ++it) {
+        const int k4 = lane + it * 32;
+        if (k4 < K4) {
+          const float4 v = in4[k4];
+          acc += w[q][it].x * v.x + w[q][it].y * v.y + w[q][it].z * v.z + w[q][it].w * v.w;
+        }
+      }
+      acc = warp_sum(acc);
+      if (r < m1) {
+        acc += __ldg(b + r);
+        const float y = kRelu ? fmaxf(acc, 0.f) : acc;
+        // lanes 0..CS-1 each push to one CTA of the cluster
+#pragma unroll
+        for (int d = 0; d < CS; ++d)
+          if (lane == d)
+            *reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(peers.p[d]) + field_off + (size_t)r * 4) = y;
+      }
+    }
+  }
+}
+
+// dx[k] = [act[k] > 0] * sum_m W[m,k] dy[m] for the float4 columns [k4lo, k4hi); pushed to every CTA
+template <int CS, int M, int K>
+__device__ __forceinline__ void fc_dx_split_push(const float* __restrict__ W, const float* dy, const float* act,
+                                                 int k4lo, int k4hi, float* red, const Peers<CS>& peers,
+                                                 size_t field_off) {
+  constexpr int G = 32;  // row groups
+  const int tid = threadIdx.x;
+  const int nk4 = k4hi - k4lo;  // <= 13 (fc1, CS=8) .. 100 (CS=1)
+  // thread = (g, j): rows g, g+G, ...; column k4lo + j.  nk4*G may exceed the CTA: loop.
+  for (int t = tid; t < nk4 * G; t += kCLThreads) {
+    const int g = t / nk4, j = t - g * nk4;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+    for (int m = g; m < M; m += G) {
+      const float4 w = __ldg(reinterpret_cast<const float4*>(W + (size_t)m * K) + k4lo + j);
+      const float d = dy[m];
+      acc.x += w.x * d; acc.y += w.y * d; acc.z += w.z * d; acc.w += w.w * d;
+    }
+    reinterpret_cast<float4*>(red)[g * nk4 + j] = acc;
+  }
+  __syncthreads();
+  for (int t = tid; t < nk4 * 4; t += kCLThreads) {
+    float s = 0.f;
+#pragma unroll 8
+    for (int g = 0; g < G; ++g) s += red[g * nk4 * 4 + t];
+    const int k = k4lo * 4 + t;
+    const float v = act[k] > 0.f ? s : 0.f;
+#pragma unroll
+    for (int d = 0; d < CS; ++d)
+      *reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(peers.p[d]) + field_off + (size_t)k * 4) = v;
+  }
+}
+
+// purely local dx (used for fc3, computed redundantly by every CTA)
+template <int M, int K>
+__device__ __forceinline__ void fc_dx_local(const float* __restrict__ W, const float* dy, const float* act,
+                                            float* dx) {
+  const int tid = threadIdx.x;
+  if (tid < K) {
+    float s = 0.f;
+#pragma unroll
+    for (int m = 0; m < M; ++m) s += __ldg(W + m * K + tid) * dy[m];
+    dx[tid] = act[tid] > 0.f ? s : 0.f;
+  }
+}
+
+template <int CS>
+__global__ void __launch_bounds__(kCLThreads, 1)
+fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict__ x,
+                       const long long* __restrict__ labels, float* __restrict__ saved,
+                       float* __restrict__ part1, float* __restrict__ part2, float* __restrict__ img_loss,
+                       int* __restrict__ img_correct, int B, float inv_batch) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  CLSmem& s = *reinterpret_cast<CLSmem*>(smem_raw);
+  cg::cluster_group cluster = cg::this_cluster();
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int r = CS > 1 ? (int)cluster.block_rank() : 0;
+  const int n_clusters = gridDim.x / CS;
+  int img = blockIdx.x / CS;
+
+  Peers<CS> peers;
+#pragma unroll
+  for (int d = 0; d < CS; ++d) peers.p[d] = CS > 1 ? cluster.map_shared_rank(&s, d) : &s;
+
+  static_assert(CS == 2 || CS == 4 || CS == 8, "the one-CTA case is fused_step.cu's fwd_bwd_kernel");
+  if (tid == 0) {
+    cl_mbar_init(&s.mbar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  uint32_t phase = 0;
+  if (tid == 0 && img < B) {
+    cl_mbar_expect_tx(&s.mbar, kImgNumel * 4);
+    cl_bulk_g2s(s.x, x + (size_t)img * kImgNumel, kImgNumel * 4, &s.mbar);
+  }
+
+  // ---- weights: conv1 + conv2 in natural layout, plus the dgrad layout of conv2 ----
+  for (int i = tid; i < 456; i += kCLThreads) s.w1[i] = __ldg(params + (i < 450 ? kOffW1 + i : kOffB1 + (i - 450)));
+  for (int i = tid; i < 2400 / 4; i += kCLThreads)
+    reinterpret_cast<float4*>(s.w2)[i] = __ldg(reinterpret_cast<const float4*>(params + kOffW2) + i);
+  if (tid < 16) s.b2[tid] = __ldg(params + kOffB2 + tid);
+  if (tid < 196) s.poff[tid] = (2 * (tid / 14)) * kXpRow + 2 * (tid % 14);
+  __syncthreads();
+  for (int i = tid; i < 16 * 25 * 8; i += kCLThreads) {
+    const int c = i & 7, ot = i >> 3, o = ot / 25, t = ot - o * 25;
+    s.w2d[i] = c < 6 ? s.w2[o * 150 + c * 25 + t] : 0.f;
+  }
+
+  // every CTA of the cluster must be running before anyone stores into its shared memory
+  cluster.sync();
+
+  // static work split of this CTA
+  const int prow0 = r * 14 / CS, prow1 = (r + 1) * 14 / CS;      // conv1: pooled rows
+  const int o0 = r * 16 / CS, o1 = (r + 1) * 16 / CS;            // conv2 / conv2 wgrad: output channels
+  const int f1m0 = r * kF1 / CS, f1m1 = (r + 1) * kF1 / CS;      // fc1 rows
+  const int f2m0 = r * kF2 / CS, f2m1 = (r + 1) * kF2 / CS;      // fc2 rows
+  const int d1k0 = r * (kF1 / 4) / CS, d1k1 = (r + 1) * (kF1 / 4) / CS;      // fc2 dX float4 columns (of 30)
+  const int g2k0 = r * (kFlat / 4) / CS, g2k1 = (r + 1) * (kFlat / 4) / CS;  // fc1 dX float4 columns (of 100)
+  const int q0 = r * 196 / CS, q1 = (r + 1) * 196 / CS;          // conv2 dgrad / conv1 wgrad: pooled pixels
+  const int nq = q1 - q0;
+
+  for (; img < B; img += n_clusters) {
+    cl_mbar_wait(&s.mbar, phase);
+    phase ^= 1u;
+    __syncthreads();
+
+    // padded copy of the image for the wgrad gather (off the critical path of conv1)
+    for (int i = tid; i < kImgNumel; i += kCLThreads) {
+      const int c = i >> 10, rem = i & 1023, h = rem >> 5, w = rem & 31;
+      s.xp[c * kXpCh + h * kXpRow + w] = s.x[i];
+    }
+
+    // ================= conv1 + bias + ReLU + maxpool, my pooled rows =================
+    {
+      const int npx = (prow1 - prow0) * 14;
+      for (int item = tid; item < npx * 6; item += kCLThreads) {
+        const int ch = item / npx, px = item - ch * npx;
+        const int ph = prow0 + px / 14, pw = px % 14;
+        float a00 = 0.f, a01 = 0.f, a10 = 0.f, a11 = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < 3; ++c) {
+          const float* xb = s.x + c * 1024 + (2 * ph) * 32 + 2 * pw;
+          float patch[6][6];
+#pragma unroll
+          for (int rr = 0; rr < 6; ++rr)
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+              const float2 v = *reinterpret_cast<const float2*>(xb + rr * 32 + 2 * q);
+              patch[rr][2 * q] = v.x;
+              patch[rr][2 * q + 1] = v.y;
+            }
+          const float* wb = s.w1 + (ch * 3 + c) * 25;
+#pragma unroll
+          for (int kh = 0; kh < 5; ++kh)
+#pragma unroll
+            for (int kw = 0; kw < 5; ++kw) {
+              const float w = wb[kh * 5 + kw];
+              a00 += w * patch[kh][kw];
+              a01 += w * patch[kh][kw + 1];
+              a10 += w * patch[kh + 1][kw];
+              a11 += w * patch[kh + 1][kw + 1];
+            }
+        }
+        const float bias = s.w1[450 + ch];
+        float best = fmaxf(a00 + bias, 0.f);
+        int bi = 0;
+        float v = fmaxf(a01 + bias, 0.f);
+        if (v > best) { best = v; bi = 1; }
+        v = fmaxf(a10 + bias, 0.f);
+        if (v > best) { best = v; bi = 2; }
+        v = fmaxf(a11 + bias, 0.f);
+        if (v > best) { best = v; bi = 3; }
+        const int oi = ch * 196 + ph * 14 + pw;
+#pragma unroll
+        for (int d = 0; d < CS; ++d) {
+          peers.p[d]->p1[oi] = best;
+          peers.p[d]->idx1[oi] = (unsigned char)bi;
+        }
+      }
+    }
+    if (CS > 1) cluster.sync(); else __syncthreads();
+
+    // ================= conv2 + bias + ReLU + maxpool, my output channels =================
+    {
+      const int no = o1 - o0;
+      for (int item = tid; item < no * 150; item += kCLThreads) {
+        const int pp = item % 25, oc = item / 25, c = oc % 6, ol = oc / 6;
+        const int ph = pp / 5, pw = pp - ph * 5;
+        const float* xb = s.p1 + c * 196 + (2 * ph) * 14 + 2 * pw;
+        float patch[6][6];
+#pragma unroll
+        for (int rr = 0; rr < 6; ++rr)
+#pragma unroll
+          for (int q = 0; q < 3; ++q) {
+            const float2 v = *reinterpret_cast<const float2*>(xb + rr * 14 + 2 * q);
+            patch[rr][2 * q] = v.x;
+            patch[rr][2 * q + 1] = v.y;
+          }
+        const float* wb = s.w2 + ((o0 + ol) * 6 + c) * 25;
+        float a00 = 0.f, a01 = 0.f, a10 = 0.f, a11 = 0.f;
+#pragma unroll
+        for (int kh = 0; kh < 5; ++kh)
+#pragma unroll
+          for (int kw = 0; kw < 5; ++kw) {
+            const float w = wb[kh * 5 + kw];
+            a00 += w * patch[kh][kw];
+            a01 += w * patch[kh][kw + 1];
+            a10 += w * patch[kh + 1][kw];
+            a11 += w * patch[kh + 1][kw + 1];
+          }
+        *reinterpret_cast<float4*>(s.red + item * 4) = make_float4(a00, a01, a10, a11);
+      }
+      __syncthreads();
+      for (int t = tid; t < no * 25; t += kCLThreads) {
+        const int ol = t / 25, pp = t - ol * 25, o = o0 + ol;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+          const float4 q = *reinterpret_cast<const float4*>(s.red + ((ol * 6 + c) * 25 + pp) * 4);
+          v.x += q.x; v.y += q.y; v.z += q.z; v.w += q.w;
+        }
+        const float bias = s.b2[o];
+        float best = fmaxf(v.x + bias, 0.f);
+        int bi = 0;
+        float u = fmaxf(v.y + bias, 0.f);
+        if (u > best) { best = u; bi = 1; }
+        u = fmaxf(v.z + bias, 0.f);
+        if (u > best) { best = u; bi = 2; }
+        u = fmaxf(v.w + bias, 0.f);
+        if (u > best) { best = u; bi = 3; }
+#pragma unroll
+        for (int d = 0; d < CS; ++d) {
+          peers.p[d]->p2[o * 25 + pp] = best;
+          peers.p[d]->idx2[o * 25 + pp] = (unsigned char)bi;
+        }
+      }
+    }
+    if (CS > 1) cluster.sync(); else __syncthreads();
+
+    // ================= fc1, fc2 (rows split), fc3 + softmax-CE (redundant) =================
+    fc_rows_push<CS, kFlat, true>(params + kOffF1W, params + kOffF1B, s.p2, f1m0, f1m1, peers,
+                                  offsetof(CLSmem, h1));
+    if (CS > 1) cluster.sync(); else __syncthreads();
+    fc_rows_push<CS, kF1, true>(params + kOffF2W, params + kOffF2B, s.h1, f2m0, f2m1, peers,
+                                offsetof(CLSmem, h2));
+    if (CS > 1) cluster.sync(); else __syncthreads();
+    {
+      Peers<1> self;
+      self.p[0] = &s;
+      fc_rows_push<1, kF2, false>(params + kOffF3W, params + kOffF3B, s.h2, 0, kF3, self,
+                                  offsetof(CLSmem, logits));
+    }
+    __syncthreads();
+    if (warp == 0) {
+      const int label = (int)__ldg(labels + img);
+      const float z = lane < 10 ? s.logits[lane] : -INFINITY;
+      const float m = warp_max(z);
+      const float e = lane < 10 ? __expf(z - m) : 0.f;
+      const float sum = warp_sum(e);
+      const float lse = m + __logf(sum);
+      const float zl = __shfl_sync(0xffffffffu, z, label & 31);
+      const unsigned int hit = __ballot_sync(0xffffffffu, lane < 10 && z == m);
+      const int pred = __ffs(hit) - 1;
+      if (lane < 10) s.d3[lane] = (e / sum - (lane == label ? 1.f : 0.f)) * inv_batch;
+      if (lane == 0 && r == 0) {
+        img_loss[img] = lse - zl;
+        if (img_correct) img_correct[img] = (pred == label) ? 1 : 0;
+      }
+    }
+    __syncthreads();
+
+    // ================= FC data gradients =================
+    fc_dx_local<kF3, kF2>(params + kOffF3W, s.d3, s.h2, s.d2);
+    __syncthreads();
+    fc_dx_split_push<CS, kF2, kF1>(params + kOffF2W, s.d2, s.h1, d1k0, d1k1, s.red, peers, offsetof(CLSmem, d1));
+    if (CS > 1) cluster.sync(); else __syncthreads();
+    fc_dx_split_push<CS, kF1, kFlat>(params + kOffF1W, s.d1, s.p2, g2k0, g2k1, s.red, peers, offsetof(CLSmem, g2));
+    if (CS > 1) cluster.sync(); else __syncthreads();
+    // from here on nothing crosses CTAs any more
+
+    if (r == 0) {  // FC record for the update kernel
+      float* sv = saved + (size_t)img * kSavStride;
+      if (tid < 400) sv[kSavP2 + tid] = s.p2[tid];
+      if (tid < 120) { sv[kSavH1 + tid] = s.h1[tid]; sv[kSavD1 + tid] = s.d1[tid]; }
+      if (tid < 84) { sv[kSavH2 + tid] = s.h2[tid]; sv[kSavD2 + tid] = s.d2[tid]; }
+      if (tid < 10) sv[kSavD3 + tid] = s.d3[tid];
+    }
+
+    // ================= conv2 weight gradient, my output channels =================
+    for (int i = tid; i < 16 * 18 * 18; i += kCLThreads) s.dc2p[i] = 0.f;
+    {
+      const int no = o1 - o0;
+      float* dst = part2 + (size_t)img * (kConvPrefix - kOffW2);
+      for (int t = tid; t < no * 150; t += kCLThreads) {
+        const int ol = t / 150, rem = t - ol * 150, c = rem / 25, tap = rem - c * 25;
+        const int kh = tap / 5, kw = tap - kh * 5, o = o0 + ol;
+        const float* gp = s.g2 + o * 25;
+        const unsigned char* ip = s.idx2 + o * 25;
+        const float* xb = s.p1 + c * 196 + kh * 14 + kw;
+        float a = 0.f;
+#pragma unroll
+        for (int pp = 0; pp < 25; ++pp) {
+          const int id = ip[pp];
+          a += gp[pp] * xb[(2 * (pp / 5) + (id >> 1)) * 14 + 2 * (pp % 5) + (id & 1)];
+        }
+        dst[o * 150 + rem] = a;
+      }
+      if (tid < no) {
+        const int o = o0 + tid;
+        float a = 0.f;
+        for (int pp = 0; pp < 25; ++pp) a += s.g2[o * 25 + pp];
+        dst[(kOffB2 - kOffW2) + o] = a;
+      }
+    }
+    __syncthreads();
+    if (tid < 400) {
+      const int o = tid / 25, pp = tid - o * 25, ph = pp / 5, pw = pp - ph * 5;
+      const int id = s.idx2[tid];
+      s.dc2p[o * 324 + (2 * ph + (id >> 1) + 4) * 18 + (2 * pw + (id & 1) + 4)] = s.g2[tid];
+    }
+    __syncthreads();
+
+    // ================= conv2 data gradient for my pooled pixels =================
+    for (int item = tid; item < nq * 16; item += kCLThreads) {
+      const int o = item / nq, ql = item - o * nq, q = q0 + ql;
+      const int ih = q / 14, iw = q - ih * 14;
+      float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int kh = 0; kh < 5; ++kh) {
+        const int rr = ih + 4 - kh;
+        if (rr < 4 || rr > 13) continue;
+        const float* row = s.dc2p + o * 324 + rr * 18 + iw + 4;
+        const float* wb = s.w2d + (o * 25 + kh * 5) * 8;
+#pragma unroll
+        for (int kw = 0; kw < 5; ++kw) {
+          const float v = row[-kw];
+          const float4 wa = *reinterpret_cast<const float4*>(wb + kw * 8);
+          const float2 wc = *reinterpret_cast<const float2*>(wb + kw * 8 + 4);
+          acc[0] += v * wa.x; acc[1] += v * wa.y; acc[2] += v * wa.z; acc[3] += v * wa.w;
+          acc[4] += v * wc.x; acc[5] += v * wc.y;
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < 6; ++c) s.red[(o * 6 + c) * nq + ql] = acc[c];
+    }
+    __syncthreads();
+    for (int t = tid; t < nq * 6; t += kCLThreads) {
+      const int c = t / nq, ql = t - c * nq;
+      float v = 0.f;
+#pragma unroll
+      for (int o = 0; o < 16; ++o) v += s.red[(o * 6 + c) * nq + ql];
+      const int gi = c * 196 + q0 + ql;
+      s.g1[gi] = s.p1[gi] > 0.f ? v : 0.f;
+    }
+    __syncthreads();
+
+    // ================= conv1 weight gradient over my pooled pixels (partial) =================
+    {
+      float* dst = part1 + ((size_t)img * CS + r) * kOffW2;
+      if (tid < 450) {
+        const int o = tid / 75, rem = tid - o * 75, c = rem / 25, tap = rem - c * 25;
+        const int kh = tap / 5, kw = tap - kh * 5;
+        const float* gp = s.g1 + o * 196;
+        const unsigned char* ip = s.idx1 + o * 196;
+        const float* xb = s.xp + c * kXpCh + kh * kXpRow + kw;
+        float a = 0.f;
+#pragma unroll 4
+        for (int q = q0; q < q1; ++q) {
+          const int id = ip[q];
+          a += gp[q] * xb[s.poff[q] + (id >> 1) * kXpRow + (id & 1)];
+        }
+        dst[tid] = a;
+      } else if (warp == 15) {
+        for (int o = 0; o < 6; ++o) {
+          float a = 0.f;
+          for (int q = q0 + lane; q < q1; q += 32) a += s.g1[o * 196 + q];
+          a = warp_sum(a);
+          if (lane == 0) dst[kOffB1 + o] = a;
+        }
+      }
+    }
+    __syncthreads();
+    if (tid == 0 && img + n_clusters < B) {
+      cl_mbar_expect_tx(&s.mbar, kImgNumel * 4);
+      cl_bulk_g2s(s.x, x + (size_t)(img + n_clusters) * kImgNumel, kImgNumel * 4, &s.mbar);
+    }
+    // the next round's pushes into p1 must not overtake a slow peer still reading p1/idx1
+    if (CS > 1 && img + n_clusters < B) cluster.sync();
+  }
+  // a CTA's shared memory must stay alive until no peer can still push into it
+  if (CS > 1) cluster.sync();
+}
+
+template <int CS>
+static int launch_cluster_t(const float* params, const float* x, const long long* labels, float* saved, float* part1,
+                            float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
+                            cudaStream_t stream) {
+  static bool attr_set = false;
+  auto kern = fwd_bwd_cluster_kernel<CS>;
+  const size_t smem = sizeof(CLSmem);
+  if (!attr_set) {
+    DNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = true;
+  }
+  const int n_clusters = B < max_clusters ? B : max_clusters;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(n_clusters * CS);
+  cfg.blockDim = dim3(kCLThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CS;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const float inv_batch = 1.f / (float)B;
+  DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, params, x, labels, saved, part1, part2, img_loss, img_correct, B,
+                                    inv_batch));
+  return kOk;
+}
+
+// Cluster size from the batch: use as many SMs as the batch allows in ONE wave.
+// (clusters of 8 pack 2 per GPC -> 16 resident; of 4 -> ~33; of 2 -> 74.)
+int pick_cluster_size(int B, int num_sms) {
+  if (B * 8 <= num_sms - 20) return 8;
+  if (B * 4 <= num_sms - 16) return 4;
+  if (B * 2 <= num_sms) return 2;
+  return 1;
+}
+
+// how many clusters of `cs` CTAs of this kernel the device can hold at once
+int max_active_clusters(int cs) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(cs * 64);
+  cfg.blockDim = dim3(kCLThreads);
+  cfg.dynamicSmemBytes = sizeof(CLSmem);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cs;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int n = 0;
+  cudaError_t e = cudaErrorInvalidValue;
+  if (cs == 8) {
+    cudaFuncSetAttribute(fwd_bwd_cluster_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CLSmem));
+    e = cudaOccupancyMaxActiveClusters(&n, fwd_bwd_cluster_kernel<8>, &cfg);
+  } else if (cs == 4) {
+    cudaFuncSetAttribute(fwd_bwd_cluster_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CLSmem));
+    e = cudaOccupancyMaxActiveClusters(&n, fwd_bwd_cluster_kernel<4>, &cfg);
+  } else if (cs == 2) {
+    cudaFuncSetAttribute(fwd_bwd_cluster_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CLSmem));
+    e = cudaOccupancyMaxActiveClusters(&n, fwd_bwd_cluster_kernel<2>, &cfg);
+  }
+  if (e != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int launch_fwd_bwd_cluster(int cs, const float* params, const float* x, const long long* labels, float* saved,
+                           float* part1, float* part2, float* img_loss, int* img_correct, int B, int num_sms /* = max resident clusters */,
+                           cudaStream_t stream) {
+  switch (cs) {
+    case 8: return launch_cluster_t<8>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, stream);
+    case 4: return launch_cluster_t<4>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, stream);
+    case 2: return launch_cluster_t<2>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, stream);
+    default: set_last_error("cluster size %d not supported", cs); return kErrArg;
+  }
+}
+
+}  // namespace dnnb200

@@ -34,27 +34,27 @@ constexpr int kFBThreads = 512;
 constexpr int kRedFloats = 6144;
 
 struct __align__(16) FBSmem {
-  float x[kImgNumel];          // input image, CHW (bulk-copied by the TMA engine)
-  float w1t[75 * 8];           // conv1 weights [(c,kh,kw)][half*4 + j]   (j<3: out channel half*3+j)
-  float b1[8];
-  float p1[1176 + 8];          // pooled relu(conv1)  [6][14][14]
-  float w2t[150 * 16];         // conv2 weights [(c,kh,kw)][o]   (forward)
-  float w2d[16 * 25 * 8];      // conv2 weights [(o,kh,kw)][c8]  (data gradient)
-  float b2[16];
-  float p2[400];               // pooled relu(conv2)  [16][5][5] == fc1 input
-  float h1[120];
-  float h2[88];
-  float logits[16];
-  float d3[16];
-  float d2[88];
-  float d1[120];
-  float g2[400];               // dL/d p2, masked by p2 > 0
-  float g1[1176 + 8];          // dL/d p1, masked by p1 > 0
-  float dc2p[16 * 18 * 18];    // dL/d conv2-out, dense, zero border of 4
-  float red[kRedFloats];       // scratch for split reductions
-  unsigned long long mbar;     // mbarrier for the bulk copy
-  unsigned char idx1[1176 + 8];
-  unsigned char idx2[400];
+  alignas(16) float x[kImgNumel];          // input image, CHW (bulk-copied by the TMA engine)
+  alignas(16) float w1t[75 * 8];           // conv1 weights [(c,kh,kw)][half*4 + j]   (j<3: out channel half*3+j)
+  alignas(16) float b1[8];
+  alignas(16) float p1[1176 + 8];          // pooled relu(conv1)  [6][14][14]
+  alignas(16) float w2t[150 * 16];         // conv2 weights [(c,kh,kw)][o]   (forward)
+  alignas(16) float w2d[16 * 25 * 8];      // conv2 weights [(o,kh,kw)][c8]  (data gradient)
+  alignas(16) float b2[16];
+  alignas(16) float p2[400];               // pooled relu(conv2)  [16][5][5] == fc1 input
+  alignas(16) float h1[120];
+  alignas(16) float h2[88];
+  alignas(16) float logits[16];
+  alignas(16) float d3[16];
+  alignas(16) float d2[88];
+  alignas(16) float d1[120];
+  alignas(16) float g2[400];               // dL/d p2, masked by p2 > 0
+  alignas(16) float g1[1176 + 8];          // dL/d p1, masked by p1 > 0
+  alignas(16) float dc2p[16 * 18 * 18];    // dL/d conv2-out, dense, zero border of 4
+  alignas(16) float red[kRedFloats];       // scratch for split reductions
+  alignas(8) unsigned long long mbar;     // mbarrier for the bulk copy
+  alignas(16) unsigned char idx1[1176 + 8];
+  alignas(16) unsigned char idx2[400];
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -173,7 +173,7 @@ template <bool kTrain>
 __global__ void __launch_bounds__(kFBThreads, 1)
 fwd_bwd_kernel(const float* __restrict__ params, const float* __restrict__ x,
                const long long* __restrict__ labels, float* __restrict__ saved,
-               float* __restrict__ partials, float* __restrict__ img_loss,
+               float* __restrict__ part1, float* __restrict__ part2, float* __restrict__ img_loss,
                int* __restrict__ img_correct, float* __restrict__ logits_out, int B,
                float inv_batch) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -392,7 +392,9 @@ fwd_bwd_kernel(const float* __restrict__ params, const float* __restrict__ x,
       if (tid < 84) { sv[kSavH2 + tid] = s.h2[tid]; sv[kSavD2 + tid] = s.d2[tid]; }
       if (tid < 10) sv[kSavD3 + tid] = s.d3[tid];
     }
-    float* part = partials + (size_t)img * kConvPrefix;
+    // conv gradients of this image: conv1 block [0,512) and conv2 block [512,2944) of the flat prefix
+    float* part = part2 + (size_t)img * (kConvPrefix - kOffW2) - kOffW2;  // indexed with flat offsets >= kOffW2
+    float* partc1 = part1 + (size_t)img * kOffW2;
 
     // ================= conv2 weight gradient over the pooled grid (K16 wgrad, K15) =================
     // zero the dense padded gradient plane for the data gradient in the same pass
@@ -481,7 +483,7 @@ fwd_bwd_kernel(const float* __restrict__ params, const float* __restrict__ x,
         float a = 0.f;
         for (int pp = lane; pp < 196; pp += 32) a += s.g1[o * 196 + pp];
         a = warp_sum(a);
-        if (lane == 0) part[kOffB1 + o] = a;
+        if (lane == 0) partc1[kOffB1 + o] = a;
       }
     }
     __syncthreads();
@@ -489,7 +491,7 @@ fwd_bwd_kernel(const float* __restrict__ params, const float* __restrict__ x,
       float a = 0.f;
 #pragma unroll
       for (int pg = 0; pg < 5; ++pg) a += s.red[pg * 450 + tid];
-      part[kOffW1 + tid] = a;
+      partc1[kOffW1 + tid] = a;
     }
     __syncthreads();  // s.x may be overwritten now
     if (tid == 0 && img + gridDim.x < B) {
@@ -506,13 +508,22 @@ constexpr int kUpdThreads = kSlice / 2;  // 256 threads, two consecutive floats 
 
 // d(loss)/d(param[i]) and param[i+1] summed over the local batch. i is even and both
 // elements lie in the same tensor row (all row lengths are even).
-__device__ __forceinline__ float2 local_grad2(const RankCtx& cx, int i, int B) {
+__device__ __forceinline__ float2 local_grad2(const RankCtx& cx, int i, int B, int n_part1) {
   float2 g = make_float2(0.f, 0.f);
+  if (i < kOffW2) {
+    const float* p = cx.part1 + i;
+#pragma unroll 8
+    for (int b = 0; b < n_part1; ++b) {
+      const float2 t = __ldg(reinterpret_cast<const float2*>(p + (size_t)b * kOffW2));
+      g.x += t.x; g.y += t.y;
+    }
+    return g;
+  }
   if (i < kConvPrefix) {
-    const float* p = cx.partials + i;
+    const float* p = cx.part2 + (i - kOffW2);
 #pragma unroll 8
     for (int b = 0; b < B; ++b) {
-      const float2 t = __ldg(reinterpret_cast<const float2*>(p + (size_t)b * kConvPrefix));
+      const float2 t = __ldg(reinterpret_cast<const float2*>(p + (size_t)b * (kConvPrefix - kOffW2)));
       g.x += t.x; g.y += t.y;
     }
     return g;
@@ -556,7 +567,7 @@ __device__ __forceinline__ float2 local_grad2(const RankCtx& cx, int i, int B) {
 }
 
 __global__ void __launch_bounds__(kUpdThreads)
-update_kernel(const RankCtx* __restrict__ ctxs, int B, int loss_slot, int flags) {
+update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slot, int flags) {
   __shared__ ExchangeShared xsh;
   const RankCtx& cx = ctxs[blockIdx.y];
   StepCtl* ctl = cx.ctl;
@@ -568,7 +579,7 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int loss_slot, int flags)
 
   float v[2] = {0.f, 0.f};
   if (in_range) {
-    const float2 g = local_grad2(cx, i, B);
+    const float2 g = local_grad2(cx, i, B, n_part1);
     v[0] = g.x; v[1] = g.y;
   }
   const bool grad_only = (flags & 1) != 0;  // tests: leave the local batch gradient in cx.grads, touch nothing else
@@ -653,7 +664,7 @@ __global__ void eval_reduce_kernel(const float* __restrict__ img_loss, const int
 // host launchers (used by engine.cpp and by the C ABI in api.cpp)
 // ============================================================================
 int launch_fwd_bwd(bool train, const float* params, const float* x, const long long* labels,
-                   float* saved, float* partials, float* img_loss, int* img_correct,
+                   float* saved, float* part1, float* part2, float* img_loss, int* img_correct,
                    float* logits_out, int B, int max_ctas, cudaStream_t stream) {
   static bool attr_set[2] = {false, false};
   const size_t smem = sizeof(FBSmem);
@@ -663,20 +674,21 @@ int launch_fwd_bwd(bool train, const float* params, const float* x, const long l
     attr_set[train ? 1 : 0] = true;
   }
   const int grid = B < max_ctas ? B : max_ctas;
-  kern<<<grid, kFBThreads, smem, stream>>>(params, x, labels, saved, partials, img_loss, img_correct,
+  kern<<<grid, kFBThreads, smem, stream>>>(params, x, labels, saved, part1, part2, img_loss, img_correct,
                                            logits_out, B, 1.f / (float)B);
   DNN_CUDA_CHECK(cudaGetLastError());
   return kOk;
 }
 
-int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int loss_slot, int flags, cudaStream_t stream) {
+int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int n_part1, int loss_slot, int flags,
+                  cudaStream_t stream) {
   dim3 grid(kNumSlices, n_virtual_ranks);
   if (n_virtual_ranks > 1) {
     // ranks emulated on ONE device wait on each other: every CTA must be resident
-    void* args[] = {(void*)&d_ctxs, (void*)&B, (void*)&loss_slot, (void*)&flags};
+    void* args[] = {(void*)&d_ctxs, (void*)&B, (void*)&n_part1, (void*)&loss_slot, (void*)&flags};
     DNN_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)update_kernel, grid, dim3(kUpdThreads), args, 0, stream));
   } else {
-    update_kernel<<<grid, kUpdThreads, 0, stream>>>(d_ctxs, B, loss_slot, flags);
+    update_kernel<<<grid, kUpdThreads, 0, stream>>>(d_ctxs, B, n_part1, loss_slot, flags);
     DNN_CUDA_CHECK(cudaGetLastError());
   }
   return kOk;

@@ -33,9 +33,14 @@ void set_last_error(const char* fmt, ...) {
 
 // ---- launchers implemented in the .cu files -----------------------------------
 int launch_fwd_bwd(bool train, const float* params, const float* x, const long long* labels, float* saved,
-                   float* partials, float* img_loss, int* img_correct, float* logits_out, int B, int max_ctas,
-                   cudaStream_t stream);
-int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int loss_slot, int flags, cudaStream_t stream);
+                   float* part1, float* part2, float* img_loss, int* img_correct, float* logits_out, int B,
+                   int max_ctas, cudaStream_t stream);
+int launch_fwd_bwd_cluster(int cs, const float* params, const float* x, const long long* labels, float* saved,
+                           float* part1, float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
+                           cudaStream_t stream);
+int max_active_clusters(int cs);
+int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int n_part1, int loss_slot, int flags,
+                  cudaStream_t stream);
 int launch_eval_reduce(const float* img_loss, const int* img_correct, int N, int bs, double* out, cudaStream_t stream);
 int launch_allreduce(const RankCtx* d_ctxs, int n_virtual_ranks, const float* const* in, float* const* out, int n,
                      int mode, int two_shot, cudaStream_t stream);
@@ -86,7 +91,9 @@ struct dnnb200_group {
 struct dnnb200_engine {
   int device = 0, max_batch = 0;
   float *params = nullptr, *momentum = nullptr, *grads = nullptr;
-  float *saved = nullptr, *partials = nullptr, *img_loss = nullptr;
+  float *saved = nullptr, *part1 = nullptr, *part2 = nullptr, *img_loss = nullptr;
+  int forced_cluster = 0;          // 0 = pick per batch size
+  int max_clusters[9] = {};        // resident clusters of the fwd/bwd kernel per cluster size (index = CS)
   int* img_correct = nullptr;
   float* eval_loss = nullptr;
   int* eval_correct = nullptr;
@@ -179,11 +186,32 @@ static int ensure_ring(dnnb200_engine* e) {
   return kOk;
 }
 
+// Cluster size for a batch: the largest one whose B clusters are all resident at once, so the
+// whole batch runs as ONE wave over as many SMs as possible; 1 = the one-CTA-per-image kernel.
+static int cluster_size_for(const dnnb200_engine* e, int B) {
+  if (e->forced_cluster) return e->forced_cluster;
+  for (int cs = 8; cs >= 2; cs >>= 1)
+    if (e->max_clusters[cs] >= B) return cs;
+  return 1;
+}
+
+// the forward/backward half of a step; returns the number of conv1 partial rows it produced
+static int fwd_bwd_any(dnnb200_engine* e, const float* x, const long long* y, int B, cudaStream_t s, int* n_part1) {
+  const int cs = cluster_size_for(e, B);
+  *n_part1 = B * cs;
+  if (cs == 1)
+    return launch_fwd_bwd(true, e->params, x, y, e->saved, e->part1, e->part2, e->img_loss, e->img_correct, nullptr,
+                          B, e->num_sms, s);
+  return launch_fwd_bwd_cluster(cs, e->params, x, y, e->saved, e->part1, e->part2, e->img_loss, e->img_correct, B,
+                                e->max_clusters[cs] > 0 ? e->max_clusters[cs] : 1, s);
+}
+
 static int step_kernels(dnnb200_engine* e, const float* x, const long long* y, int B, int flags, cudaStream_t s) {
-  int rc = launch_fwd_bwd(true, e->params, x, y, e->saved, e->partials, e->img_loss, e->img_correct, nullptr, B,
-                          e->num_sms * 2, s);
+  int n_part1 = B;
+  int rc = fwd_bwd_any(e, x, y, B, s, &n_part1);
   if (rc) return rc;
-  rc = launch_update(e->d_ctx, 1, B, (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask), flags, s);
+  rc = launch_update(e->d_ctx, 1, B, n_part1, (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask), flags,
+                     s);
   if (rc) return rc;
   e->launches += 2;
   return kOk;
@@ -304,8 +332,12 @@ int dnnb200_engine_create(float* params, float* momentum, float* grads, int max_
   e->momentum = momentum;
   e->grads = grads;
   DNN_CUDA_CHECK(cudaMalloc(&e->saved, (size_t)max_batch * kSavStride * sizeof(float)));
-  DNN_CUDA_CHECK(cudaMalloc(&e->partials, (size_t)max_batch * kConvPrefix * sizeof(float)));
-  DNN_CUDA_CHECK(cudaMemset(e->partials, 0, (size_t)max_batch * kConvPrefix * sizeof(float)));
+  // gaps of the flat layout inside the partial buffers are never written: zero them once
+  DNN_CUDA_CHECK(cudaMalloc(&e->part1, (size_t)max_batch * 8 * kOffW2 * sizeof(float)));
+  DNN_CUDA_CHECK(cudaMemset(e->part1, 0, (size_t)max_batch * 8 * kOffW2 * sizeof(float)));
+  DNN_CUDA_CHECK(cudaMalloc(&e->part2, (size_t)max_batch * (kConvPrefix - kOffW2) * sizeof(float)));
+  DNN_CUDA_CHECK(cudaMemset(e->part2, 0, (size_t)max_batch * (kConvPrefix - kOffW2) * sizeof(float)));
+  for (int cs = 2; cs <= 8; cs <<= 1) e->max_clusters[cs] = max_active_clusters(cs);
   DNN_CUDA_CHECK(cudaMemset(e->saved, 0, (size_t)max_batch * kSavStride * sizeof(float)));
   DNN_CUDA_CHECK(cudaMalloc(&e->img_loss, (size_t)max_batch * sizeof(float)));
   DNN_CUDA_CHECK(cudaMalloc(&e->img_correct, (size_t)max_batch * sizeof(int)));
@@ -327,7 +359,8 @@ int dnnb200_engine_create(float* params, float* momentum, float* grads, int max_
   e->h_ctx.momentum = momentum;
   e->h_ctx.grads = grads;
   e->h_ctx.saved = e->saved;
-  e->h_ctx.partials = e->partials;
+  e->h_ctx.part1 = e->part1;
+  e->h_ctx.part2 = e->part2;
   e->h_ctx.img_loss = e->img_loss;
   e->h_ctx.loss_ring = e->loss_ring;
   e->h_ctx.loss_ring_mask = e->loss_ring_mask;
@@ -341,7 +374,7 @@ int dnnb200_engine_create(float* params, float* momentum, float* grads, int max_
 int dnnb200_engine_destroy(dnnb200_engine* e) {
   if (!e) return kOk;
   cudaDeviceSynchronize();
-  cudaFree(e->saved); cudaFree(e->partials); cudaFree(e->img_loss); cudaFree(e->img_correct);
+  cudaFree(e->saved); cudaFree(e->part1); cudaFree(e->part2); cudaFree(e->img_loss); cudaFree(e->img_correct);
   cudaFree(e->eval_loss); cudaFree(e->eval_correct); cudaFree(e->d_eval_out);
   cudaFree(e->ctl); cudaFree(e->loss_ring); cudaFree(e->d_ctx);
   cudaFreeHost(e->h_ctx_pinned);
@@ -409,6 +442,21 @@ int dnnb200_engine_read_ctl(dnnb200_engine* e, dnnb200_ctl* h_out, void* stream)
 
 unsigned long long dnnb200_engine_launches(const dnnb200_engine* e) { return e ? e->launches : 0ull; }
 
+int dnnb200_engine_set_cluster_size(dnnb200_engine* e, int cs) {
+  DNN_ARG_CHECK(e, "null engine");
+  DNN_ARG_CHECK(cs == 0 || cs == 1 || cs == 2 || cs == 4 || cs == 8, "cluster size must be 0 (auto), 1, 2, 4 or 8");
+  DNN_ARG_CHECK(cs <= 1 || e->max_clusters[cs] > 0, "clusters of %d CTAs cannot be scheduled on this device", cs);
+  e->forced_cluster = cs;
+  return kOk;
+}
+
+int dnnb200_engine_cluster_info(const dnnb200_engine* e, int B, int* chosen, int* max_clusters9) {
+  DNN_ARG_CHECK(e, "null engine");
+  if (chosen) *chosen = cluster_size_for(e, B);
+  if (max_clusters9) memcpy(max_clusters9, e->max_clusters, sizeof(e->max_clusters));
+  return kOk;
+}
+
 int dnnb200_engine_step(dnnb200_engine* e, const float* x, const int64_t* y, int B, void* stream) {
   DNN_ARG_CHECK(e && x && y, "engine_step: null argument");
   DNN_ARG_CHECK(B >= 1 && B <= e->max_batch, "engine_step: batch %d exceeds max_batch %d", B, e->max_batch);
@@ -454,12 +502,12 @@ int dnnb200_engine_train_host(dnnb200_engine* e, const float* h_x, const int64_t
     DNN_CUDA_CHECK(cudaMemcpyAsync(e->d_y[slot], h_y + (size_t)t * B, yb, cudaMemcpyHostToDevice, e->copy_stream));
     DNN_CUDA_CHECK(cudaEventRecord(e->slot_ready[slot], e->copy_stream));
     DNN_CUDA_CHECK(cudaStreamWaitEvent(s, e->slot_ready[slot], 0));
-    rc = launch_fwd_bwd(true, e->params, e->d_x[slot], e->d_y[slot], e->saved, e->partials, e->img_loss,
-                        e->img_correct, nullptr, B, e->num_sms * 2, s);
+    int n_part1 = B;
+    rc = fwd_bwd_any(e, e->d_x[slot], e->d_y[slot], B, s, &n_part1);
     if (rc) return rc;
     DNN_CUDA_CHECK(cudaEventRecord(e->slot_free[slot], s));
     const int lslot = (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask);
-    rc = launch_update(e->d_ctx, 1, B, lslot, 0, s);
+    rc = launch_update(e->d_ctx, 1, B, n_part1, lslot, 0, s);
     if (rc) return rc;
     e->launches += 2;
     e->steps_launched += 1;
@@ -491,8 +539,8 @@ int dnnb200_engine_eval(dnnb200_engine* e, const float* x, const int64_t* y, int
     DNN_CUDA_CHECK(cudaMalloc(&e->eval_correct, (size_t)N * sizeof(int)));
     e->eval_cap = N;
   }
-  int rc = launch_fwd_bwd(false, e->params, x, (const long long*)y, nullptr, nullptr, e->eval_loss, e->eval_correct,
-                          logits, N, e->num_sms * 2, s);
+  int rc = launch_fwd_bwd(false, e->params, x, (const long long*)y, nullptr, nullptr, nullptr, e->eval_loss,
+                          e->eval_correct, logits, N, e->num_sms * 2, s);
   if (rc) return rc;
   rc = launch_eval_reduce(e->eval_loss, e->eval_correct, N, bs, e->d_eval_out, s);
   if (rc) return rc;
@@ -550,13 +598,15 @@ int dnnb200_vr_step(dnnb200_engine** engines, int n, const float* const* xs, con
                     void* stream) {
   DNN_ARG_CHECK(engines && xs && ys && n >= 1 && n <= kMaxWorld, "vr_step: bad arguments");
   cudaStream_t s = (cudaStream_t)stream;
+  int n_part1 = B;
   for (int r = 0; r < n; ++r) {
     dnnb200_engine* e = engines[r];
     if (!xs[r]) continue;  // this virtual rank sits the step out (it has left)
     DNN_ARG_CHECK(B >= 1 && B <= e->max_batch, "vr_step: batch exceeds max_batch");
-    int rc = launch_fwd_bwd(true, e->params, xs[r], (const long long*)ys[r], e->saved, e->partials, e->img_loss,
-                            e->img_correct, nullptr, B, e->num_sms * 2, s);
+    int np1 = B;
+    int rc = fwd_bwd_any(e, xs[r], (const long long*)ys[r], B, s, &np1);
     if (rc) return rc;
+    n_part1 = np1;
     e->launches += 1;
   }
   // compact the participating ranks into one cooperative launch
@@ -567,7 +617,7 @@ int dnnb200_vr_step(dnnb200_engine** engines, int n, const float* const* xs, con
   int rc = gather_ctxs(live.data(), (int)live.size(), &d);
   if (rc) return rc;
   const int lslot = (int)(live[0]->steps_launched & (unsigned long long)live[0]->loss_ring_mask);
-  rc = launch_update(d, (int)live.size(), B, lslot, 0, s);
+  rc = launch_update(d, (int)live.size(), B, n_part1, lslot, 0, s);
   cudaStreamSynchronize(s);
   cudaFree(d);
   if (rc) return rc;

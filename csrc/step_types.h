@@ -40,7 +40,8 @@ struct RankCtx {
   float* momentum;        // [kFlatNumel]
   float* grads;           // [kFlatNumel] optional: averaged gradient written back (nullptr = skip)
   const float* saved;     // [B][kSavStride]   per-image FC inputs/deltas from the fwd/bwd kernel
-  const float* partials;  // [B][kConvPrefix]  per-image conv weight/bias gradients
+  const float* part1;     // [B*CS][kOffW2]  conv1 weight/bias gradient partials (one per CTA of an image's cluster)
+  const float* part2;     // [B][kConvPrefix-kOffW2]  per-image conv2 weight/bias gradients
   const float* img_loss;  // [B]
   float* loss_ring;       // [loss_ring_mask + 1] per-step mean loss, indexed by step & mask
   StepCtl* ctl;

@@ -232,6 +232,16 @@ class Engine:
         _check(require().dnnb200_engine_read_ctl(self._h, C.byref(c), _stream()))
         return c
 
+    def set_cluster_size(self, cs: int) -> None:
+        """CTAs per image in the forward/backward kernel (0 = automatic, 1/2/4/8)."""
+        _check(require().dnnb200_engine_set_cluster_size(self._h, cs))
+
+    def cluster_info(self, B: int):
+        chosen = C.c_int()
+        mc = (C.c_int * 9)()
+        _check(require().dnnb200_engine_cluster_info(self._h, B, C.byref(chosen), mc))
+        return chosen.value, {cs: mc[cs] for cs in (2, 4, 8)}
+
     @property
     def launches(self) -> int:
         return int(require().dnnb200_engine_launches(self._h))

@@ -97,6 +97,10 @@ int dnnb200_engine_reset_loss(dnnb200_engine* e, void* stream);
 int dnnb200_engine_read_ctl(dnnb200_engine* e, dnnb200_ctl* h_out, void* stream);
 /* number of kernels this engine has launched so far */
 unsigned long long dnnb200_engine_launches(const dnnb200_engine* e);
+/* thread-block cluster size of the forward/backward kernel: each image is spread over `cs` CTAs
+ * (distributed shared memory between them). 0 = choose per batch size so the batch is one wave. */
+int dnnb200_engine_set_cluster_size(dnnb200_engine* e, int cs);
+int dnnb200_engine_cluster_info(const dnnb200_engine* e, int B, int* chosen, int* max_clusters9);
 
 /* one optimizer step on a device-resident batch: fwd/bwd kernel + update kernel
  * (reference: the loop body data_parallelism_train.py:195-203) */

@@ -24,8 +24,12 @@ def _oracle_grads(model_cpu, x, y):
     return loss.item(), model_cpu.flat_grads.clone()
 
 
+@pytest.mark.parametrize("cs", [0, 1, 2, 4, 8])
 @pytest.mark.parametrize("B", [1, 4, 16, 64])
-def test_grad_only_matches_autograd(B):
+def test_grad_only_matches_autograd(B, cs):
+    """Every cluster size of the forward/backward kernel (cs CTAs per image, DSMEM all-gathers
+    between layers) must give the autograd gradient; B=64 with cs=8 also exercises the
+    several-images-per-cluster loop."""
     torch.manual_seed(10 + B)
     ref = Network()
     gpu = copy.deepcopy(ref).cuda()
@@ -33,6 +37,7 @@ def test_grad_only_matches_autograd(B):
     loss_ref, g_ref = _oracle_grads(ref, x, y)
     mom = torch.zeros(L.FLAT_NUMEL, device="cuda")
     eng = native.Engine(gpu.flat_params, mom, None, max_batch=64, lr=0.001, mu=0.9)
+    eng.set_cluster_size(cs)
     g = torch.zeros(L.FLAT_NUMEL, device="cuda")
     p_before = gpu.flat_params.clone()
     loss = eng.grad_only(x.cuda(), y.cuda(), g)
