@@ -1,0 +1,41 @@
+"""Per-stage timeline of the clustered forward/backward kernel (SM clocks, thread 0 of each CTA)."""
+import sys
+from pathlib import Path
+
+import torch
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+from distributed_neural_network_b200 import Network  # noqa: E402
+from distributed_neural_network_b200.ops import flat as L  # noqa: E402
+from distributed_neural_network_b200.ops import native  # noqa: E402
+
+NAMES = ["start->arrive", "cluster_wait", "img+weights", "conv1", "wait p1", "conv2", "wait p2", "fc1(+wait)",
+         "fc2(+wait)", "fc3,CE,dx3,dx2(+wait)", "dx1(+wait)", "conv2 wgrad", "dgrad2", "conv1 wgrad"]
+
+
+def main():
+    B = int(sys.argv[1]) if len(sys.argv) > 1 else 16
+    cs = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+    torch.manual_seed(0)
+    m = Network().cuda()
+    eng = native.Engine(m.flat_params, torch.zeros(L.FLAT_NUMEL, device="cuda"), None, B, 0.001, 0.9)
+    eng.set_cluster_size(cs)
+    x = torch.randn(B, 3, 32, 32, device="cuda")
+    y = torch.randint(0, 10, (B,), device="cuda")
+    for _ in range(5):
+        eng.step(x, y)
+    n_cta = B * cs
+    tr = torch.zeros(n_cta * 16, dtype=torch.int64, device="cuda")
+    eng.set_trace(tr)
+    eng.step(x, y)
+    torch.cuda.synchronize()
+    eng.set_trace(None)
+    t = tr.view(n_cta, 16).cpu()
+    d = (t[:, 1:14] - t[:, 0:13]).float()
+    print(f"B={B} cs={cs}: per-stage cycles (mean / max over {n_cta} CTAs); total {(t[:,13]-t[:,0]).float().mean():.0f} cycles")
+    for k in range(13):
+        print(f"  {NAMES[k+1]:28s} {d[:,k].mean():8.0f} {d[:,k].max():8.0f}")
+
+
+if __name__ == "__main__":
+    main()

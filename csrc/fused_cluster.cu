@@ -15,8 +15,10 @@
 //   conv2 dgrad       split by input pixel      -> g1 stays local because ...
 //   conv1 wgrad       ... is split by the same pixel ranges; each CTA emits a partial
 //
-// Six cluster barriers per image (~0.2 us each) replace what would be kernel boundaries in
-// a layer-at-a-time design. All math is fp32 FFMA, bit-compatible in structure with the
+// The six all-gathers use st.async: every 4-byte DSMEM store also credits the destination
+// CTA's mbarrier (complete_tx), so a consumer simply waits until the expected byte count has
+// landed. No fence and no cluster-wide barrier sits between layers -- a first version with
+// cluster.sync() spent 45% of its time in the barrier's release fence (profiles/). All math is fp32 FFMA, bit-compatible in structure with the
 // one-CTA kernel of fused_step.cu (which stays as the CS-independent oracle and eval path).
 //
 // reference: models/model.py:20-27 forward; autograd of data_parallelism_train.py:195-198.
@@ -32,16 +34,18 @@ namespace cg = cooperative_groups;
 namespace dnnb200 {
 
 constexpr int kCLThreads = 512;
-constexpr int kXpRow = 37;                 // padded row stride of the gather copy of the image:
-constexpr int kXpCh = 32 * kXpRow + 25;    //   bank(kh*37+kw) = 5kh+kw is distinct for the 25 taps
-constexpr int kCLRed = 9408;  // CS=2 worst case: conv2 dgrad partials 16*6*98
+constexpr int kXRow = 36;                  // padded image row (floats): 16-byte aligned rows, and the five
+constexpr int kXCh = 32 * kXRow + 8;       //   kernel rows of a wgrad gather fall into different banks
+constexpr int kCLRed = 9408;               // CS=2 worst case: conv2 dgrad partials 16*6*98
+
+// stage barriers: one mbarrier per all-gather, completed by the st.async traffic itself
+enum { kBarP1 = 0, kBarP2, kBarH1, kBarH2, kBarD1, kBarG2, kNumStageBars };
 
 struct __align__(16) CLSmem {
-  alignas(16) float x[kImgNumel];        // image, dense CHW (TMA bulk copy)
-  alignas(16) float xp[3 * kXpCh + 8];   // image, padded rows, for the conv1 wgrad gather
-  alignas(16) float w1[456];             // conv1.weight natural layout [o][c][kh][kw] + bias at 450
-  alignas(16) float w2[2400];            // conv2.weight natural layout [o][c][kh][kw]
-  alignas(16) float w2d[16 * 25 * 8];    // conv2.weight as [(o,kh,kw)][c8] for the data gradient
+  alignas(16) float x[3 * kXCh];      // image, CHW with padded rows (96 row-sized TMA bulk copies)
+  alignas(16) float w1[456];          // conv1.weight natural layout [o][c][kh][kw] + bias at 450
+  alignas(16) float w2[2400];         // conv2.weight natural layout [o][c][kh][kw]
+  alignas(16) float w2d[16 * 25 * 8]; // conv2.weight as [(o,kh,kw)][c8] for the data gradient
   alignas(16) float b2[16];
   alignas(16) float p1[1176 + 8];
   alignas(16) float p2[400];
@@ -55,10 +59,11 @@ struct __align__(16) CLSmem {
   alignas(16) float g1[1176 + 8];
   alignas(16) float dc2p[16 * 18 * 18];
   alignas(16) float red[kCLRed];
-  alignas(16) int poff[196];             // (2*ph)*kXpRow + 2*pw of pooled pixel q
-  alignas(8) unsigned long long mbar;
-  alignas(16) unsigned char idx1[1176 + 8];
-  alignas(16) unsigned char idx2[400];
+  alignas(16) int idx1[1176 + 8];     // 2-bit argmax of the pooling windows (one word each: st.async granularity)
+  alignas(16) int idx2[400];
+  alignas(16) int poff[196];          // (2*ph)*kXRow + 2*pw of pooled pixel q
+  alignas(8) unsigned long long mbar;                  // image bulk copies
+  alignas(8) unsigned long long sbar[kNumStageBars];   // all-gather completion
 };
 
 __device__ __forceinline__ uint32_t cl_smem_u32(const void* p) {
@@ -71,12 +76,13 @@ __device__ __forceinline__ void cl_mbar_expect_tx(unsigned long long* bar, uint3
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(cl_smem_u32(bar)), "r"(bytes)
                : "memory");
 }
+// wait for a phase; acquire at cluster scope so data stored by peer CTAs (st.async) is visible
 __device__ __forceinline__ void cl_mbar_wait(unsigned long long* bar, uint32_t phase) {
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
       "WAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n"
       "@p bra DONE_%=;\n"
       "bra WAIT_%=;\n"
       "DONE_%=:\n"
@@ -91,17 +97,44 @@ __device__ __forceinline__ void cl_bulk_g2s(void* dst, const void* src, uint32_t
       "l"(src), "r"(bytes), "r"(cl_smem_u32(bar))
       : "memory");
 }
+__device__ __forceinline__ uint32_t cl_mapa(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+// 4-byte store into a peer CTA's shared memory that also credits 4 bytes to that CTA's mbarrier:
+// the consumer's wait completes when every expected byte has landed -- no fence, no cluster barrier.
+__device__ __forceinline__ void cl_st_async(uint32_t remote_addr, uint32_t v, uint32_t remote_bar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(remote_addr),
+               "r"(v), "r"(remote_bar)
+               : "memory");
+}
+__device__ __forceinline__ void cl_cluster_arrive() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void cl_cluster_wait() {
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// shared::cluster base address of CLSmem in every CTA of the cluster
+template <int CS>
+struct Remote {
+  uint32_t base[CS];
+};
+#define CL_OFF(field) ((uint32_t)offsetof(CLSmem, field))
+#define CL_BAR(i) ((uint32_t)(offsetof(CLSmem, sbar) + 8 * (i)))
 
 template <int CS>
-struct Peers {
-  CLSmem* p[CS];
-};
+__device__ __forceinline__ void push_all(const Remote<CS>& R, uint32_t field_off, uint32_t bar_off, uint32_t v) {
+#pragma unroll
+  for (int d = 0; d < CS; ++d) cl_st_async(R.base[d] + field_off, v, R.base[d] + bar_off);
+}
 
-// rows [m0, m1) of y = act(b + W . in); results pushed into the same smem field of every CTA
+// rows [m0, m1) of y = act(b + W . in); each result is pushed to every CTA of the cluster
 template <int CS, int K, bool kRelu>
 __device__ __forceinline__ void fc_rows_push(const float* __restrict__ W, const float* __restrict__ b,
-                                             const float* in, int m0, int m1, const Peers<CS>& peers,
-                                             size_t field_off) {
+                                             const float* in, int m0, int m1, const Remote<CS>& R,
+                                             uint32_t field_off, uint32_t bar_off) {
   constexpr int K4 = K / 4;
   constexpr int kWarps = kCLThreads / 32;
   constexpr int kIter = (K4 + 31) / 32;
@@ -109,9 +142,11 @@ __device__ __forceinline__ void fc_rows_push(const float* __restrict__ W, const 
   const float4* in4 = reinterpret_cast<const float4*>(in);
   for (int r0 = m0 + warp; r0 < m1; r0 += 2 * kWarps) {
     float4 w[2][kIter];
+    float bias[2];
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
       const int r = r0 + q * kWarps;
+      bias[q] = r < m1 ? __ldg(b + r) : 0.f;  // issued with the weights, not after the reduction
 #pragma unroll
       for (int it = 0; it < kIter; ++it) {
         const int k4 = lane + it * 32;
@@ -133,27 +168,45 @@ __device__ __forceinline__ void fc_rows_push(const float* __restrict__ W, const 
       }
       acc = warp_sum(acc);
       if (r < m1) {
-        acc += __ldg(b + r);
+        acc += bias[q];
         const float y = kRelu ? fmaxf(acc, 0.f) : acc;
-        // lanes 0..CS-1 each push to one CTA of the cluster
 #pragma unroll
-        for (int d = 0; d < CS; ++d)
-          if (lane == d)
-            *reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(peers.p[d]) + field_off + (size_t)r * 4) = y;
+        for (int d = 0; d < CS; ++d)  // lane d pushes to CTA d
+          if (lane == d) cl_st_async(R.base[d] + field_off + 4u * r, __float_as_uint(y), R.base[d] + bar_off);
       }
     }
   }
 }
 
+// same rows, result kept in this CTA only (fc3 is computed redundantly by every CTA)
+template <int M, int K>
+__device__ __forceinline__ void fc_rows_local(const float* __restrict__ W, const float* __restrict__ b,
+                                              const float* in, float* out) {
+  constexpr int K4 = K / 4;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp < M) {
+    const float4 w = lane < K4 ? __ldg(reinterpret_cast<const float4*>(W + (size_t)warp * K) + lane)
+                               : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float bias = __ldg(b + warp);
+    float acc = 0.f;
+    if (lane < K4) {
+      const float4 v = reinterpret_cast<const float4*>(in)[lane];
+      acc = w.x * v.x + w.y * v.y + w.z * v.z + w.w * v.w;
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) out[warp] = acc + bias;
+  }
+  static_assert(K4 <= 32 && M <= kCLThreads / 32, "fc_rows_local: one warp per row, one float4 per lane");
+}
+
 // dx[k] = [act[k] > 0] * sum_m W[m,k] dy[m] for the float4 columns [k4lo, k4hi); pushed to every CTA
 template <int CS, int M, int K>
 __device__ __forceinline__ void fc_dx_split_push(const float* __restrict__ W, const float* dy, const float* act,
-                                                 int k4lo, int k4hi, float* red, const Peers<CS>& peers,
-                                                 size_t field_off) {
+                                                 int k4lo, int k4hi, float* red, const Remote<CS>& R,
+                                                 uint32_t field_off, uint32_t bar_off) {
   constexpr int G = 32;  // row groups
   const int tid = threadIdx.x;
-  const int nk4 = k4hi - k4lo;  // <= 13 (fc1, CS=8) .. 100 (CS=1)
-  // thread = (g, j): rows g, g+G, ...; column k4lo + j.  nk4*G may exceed the CTA: loop.
+  const int nk4 = k4hi - k4lo;
   for (int t = tid; t < nk4 * G; t += kCLThreads) {
     const int g = t / nk4, j = t - g * nk4;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -172,13 +225,10 @@ __device__ __forceinline__ void fc_dx_split_push(const float* __restrict__ W, co
     for (int g = 0; g < G; ++g) s += red[g * nk4 * 4 + t];
     const int k = k4lo * 4 + t;
     const float v = act[k] > 0.f ? s : 0.f;
-#pragma unroll
-    for (int d = 0; d < CS; ++d)
-      *reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(peers.p[d]) + field_off + (size_t)k * 4) = v;
+    push_all<CS>(R, field_off + 4u * k, bar_off, __float_as_uint(v));
   }
 }
 
-// purely local dx (used for fc3, computed redundantly by every CTA)
 template <int M, int K>
 __device__ __forceinline__ void fc_dx_local(const float* __restrict__ W, const float* dy, const float* act,
                                             float* dx) {
@@ -191,50 +241,69 @@ __device__ __forceinline__ void fc_dx_local(const float* __restrict__ W, const f
   }
 }
 
+// development aid: thread 0 of every CTA stamps the SM clock at stage boundaries (trace == nullptr in production)
+#define CL_TRACE(k) do { if (trace != nullptr && tid == 0) trace[blockIdx.x * 16 + (k)] = clock64(); } while (0)
+
 template <int CS>
 __global__ void __launch_bounds__(kCLThreads, 1)
 fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict__ x,
                        const long long* __restrict__ labels, float* __restrict__ saved,
                        float* __restrict__ part1, float* __restrict__ part2, float* __restrict__ img_loss,
-                       int* __restrict__ img_correct, int B, float inv_batch) {
+                       int* __restrict__ img_correct, int B, float inv_batch, long long* __restrict__ trace) {
+  static_assert(CS == 2 || CS == 4 || CS == 8, "the one-CTA case is fused_step.cu's fwd_bwd_kernel");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   CLSmem& s = *reinterpret_cast<CLSmem*>(smem_raw);
   cg::cluster_group cluster = cg::this_cluster();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int r = CS > 1 ? (int)cluster.block_rank() : 0;
+  const int r = (int)cluster.block_rank();
   const int n_clusters = gridDim.x / CS;
   int img = blockIdx.x / CS;
 
-  Peers<CS> peers;
+  Remote<CS> R;
 #pragma unroll
-  for (int d = 0; d < CS; ++d) peers.p[d] = CS > 1 ? cluster.map_shared_rank(&s, d) : &s;
+  for (int d = 0; d < CS; ++d) R.base[d] = cl_mapa(cl_smem_u32(&s), (uint32_t)d);
 
-  static_assert(CS == 2 || CS == 4 || CS == 8, "the one-CTA case is fused_step.cu's fwd_bwd_kernel");
   if (tid == 0) {
     cl_mbar_init(&s.mbar, 1);
+#pragma unroll
+    for (int i = 0; i < kNumStageBars; ++i) cl_mbar_init(&s.sbar[i], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
+  // tell the cluster "my barriers exist"; the matching wait sits just before the first remote store
+  cl_cluster_arrive();
+
   uint32_t phase = 0;
-  if (tid == 0 && img < B) {
-    cl_mbar_expect_tx(&s.mbar, kImgNumel * 4);
-    cl_bulk_g2s(s.x, x + (size_t)img * kImgNumel, kImgNumel * 4, &s.mbar);
-  }
+  // image rows -> padded rows, 96 bulk copies of 128 B issued by warp 0
+  auto load_image = [&](int im) {
+    if (warp == 0) {
+      if (lane == 0) cl_mbar_expect_tx(&s.mbar, kImgNumel * 4);
+      __syncwarp();
+      const float* src = x + (size_t)im * kImgNumel;
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const int row = lane + 32 * k;  // 0..95 = c*32 + h
+        cl_bulk_g2s(s.x + (row >> 5) * kXCh + (row & 31) * kXRow, src + row * 32, 128, &s.mbar);
+      }
+    }
+  };
+  load_image(img);
 
   // ---- weights: conv1 + conv2 in natural layout, plus the dgrad layout of conv2 ----
   for (int i = tid; i < 456; i += kCLThreads) s.w1[i] = __ldg(params + (i < 450 ? kOffW1 + i : kOffB1 + (i - 450)));
   for (int i = tid; i < 2400 / 4; i += kCLThreads)
     reinterpret_cast<float4*>(s.w2)[i] = __ldg(reinterpret_cast<const float4*>(params + kOffW2) + i);
   if (tid < 16) s.b2[tid] = __ldg(params + kOffB2 + tid);
-  if (tid < 196) s.poff[tid] = (2 * (tid / 14)) * kXpRow + 2 * (tid % 14);
+  if (tid < 196) s.poff[tid] = (2 * (tid / 14)) * kXRow + 2 * (tid % 14);
   __syncthreads();
-  for (int i = tid; i < 16 * 25 * 8; i += kCLThreads) {
-    const int c = i & 7, ot = i >> 3, o = ot / 25, t = ot - o * 25;
-    s.w2d[i] = c < 6 ? s.w2[o * 150 + c * 25 + t] : 0.f;
+  for (int ot = tid; ot < 400; ot += kCLThreads) {  // one (o, tap) per thread: 8 contiguous floats
+    const int o = ot / 25, t = ot - o * 25;
+    const float* src = s.w2 + o * 150 + t;
+    float4 a = make_float4(src[0], src[25], src[50], src[75]);
+    float4 b = make_float4(src[100], src[125], 0.f, 0.f);
+    reinterpret_cast<float4*>(s.w2d)[ot * 2] = a;
+    reinterpret_cast<float4*>(s.w2d)[ot * 2 + 1] = b;
   }
-
-  // every CTA of the cluster must be running before anyone stores into its shared memory
-  cluster.sync();
 
   // static work split of this CTA
   const int prow0 = r * 14 / CS, prow1 = (r + 1) * 14 / CS;      // conv1: pooled rows
@@ -246,16 +315,22 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
   const int q0 = r * 196 / CS, q1 = (r + 1) * 196 / CS;          // conv2 dgrad / conv1 wgrad: pooled pixels
   const int nq = q1 - q0;
 
-  for (; img < B; img += n_clusters) {
-    cl_mbar_wait(&s.mbar, phase);
-    phase ^= 1u;
-    __syncthreads();
+  CL_TRACE(0);
+  cl_cluster_wait();  // every CTA of the cluster is running and has initialised its barriers
+  CL_TRACE(1);
 
-    // padded copy of the image for the wgrad gather (off the critical path of conv1)
-    for (int i = tid; i < kImgNumel; i += kCLThreads) {
-      const int c = i >> 10, rem = i & 1023, h = rem >> 5, w = rem & 31;
-      s.xp[c * kXpCh + h * kXpRow + w] = s.x[i];
+  for (; img < B; img += n_clusters) {
+    if (tid == 0) {  // arm this image's all-gathers: bytes each one will deliver into THIS CTA
+      cl_mbar_expect_tx(&s.sbar[kBarP1], 1176 * 8);
+      cl_mbar_expect_tx(&s.sbar[kBarP2], 400 * 8);
+      cl_mbar_expect_tx(&s.sbar[kBarH1], kF1 * 4);
+      cl_mbar_expect_tx(&s.sbar[kBarH2], kF2 * 4);
+      cl_mbar_expect_tx(&s.sbar[kBarD1], kF1 * 4);
+      cl_mbar_expect_tx(&s.sbar[kBarG2], kFlat * 4);
     }
+    cl_mbar_wait(&s.mbar, phase);  // image landed (also orders the weight staging of round 0: see sync below)
+    __syncthreads();
+    CL_TRACE(2);
 
     // ================= conv1 + bias + ReLU + maxpool, my pooled rows =================
     {
@@ -266,13 +341,13 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
         float a00 = 0.f, a01 = 0.f, a10 = 0.f, a11 = 0.f;
 #pragma unroll 1
         for (int c = 0; c < 3; ++c) {
-          const float* xb = s.x + c * 1024 + (2 * ph) * 32 + 2 * pw;
+          const float* xb = s.x + c * kXCh + (2 * ph) * kXRow + 2 * pw;
           float patch[6][6];
 #pragma unroll
           for (int rr = 0; rr < 6; ++rr)
 #pragma unroll
             for (int q = 0; q < 3; ++q) {
-              const float2 v = *reinterpret_cast<const float2*>(xb + rr * 32 + 2 * q);
+              const float2 v = *reinterpret_cast<const float2*>(xb + rr * kXRow + 2 * q);
               patch[rr][2 * q] = v.x;
               patch[rr][2 * q + 1] = v.y;
             }
@@ -297,15 +372,14 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
         if (v > best) { best = v; bi = 2; }
         v = fmaxf(a11 + bias, 0.f);
         if (v > best) { best = v; bi = 3; }
-        const int oi = ch * 196 + ph * 14 + pw;
-#pragma unroll
-        for (int d = 0; d < CS; ++d) {
-          peers.p[d]->p1[oi] = best;
-          peers.p[d]->idx1[oi] = (unsigned char)bi;
-        }
+        const uint32_t oi = (uint32_t)(ch * 196 + ph * 14 + pw);
+        push_all<CS>(R, CL_OFF(p1) + 4u * oi, CL_BAR(kBarP1), __float_as_uint(best));
+        push_all<CS>(R, CL_OFF(idx1) + 4u * oi, CL_BAR(kBarP1), (uint32_t)bi);
       }
     }
-    if (CS > 1) cluster.sync(); else __syncthreads();
+    CL_TRACE(3);
+    cl_mbar_wait(&s.sbar[kBarP1], phase);
+    CL_TRACE(4);
 
     // ================= conv2 + bias + ReLU + maxpool, my output channels =================
     {
@@ -355,28 +429,24 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
         if (u > best) { best = u; bi = 2; }
         u = fmaxf(v.w + bias, 0.f);
         if (u > best) { best = u; bi = 3; }
-#pragma unroll
-        for (int d = 0; d < CS; ++d) {
-          peers.p[d]->p2[o * 25 + pp] = best;
-          peers.p[d]->idx2[o * 25 + pp] = (unsigned char)bi;
-        }
+        const uint32_t oi = (uint32_t)(o * 25 + pp);
+        push_all<CS>(R, CL_OFF(p2) + 4u * oi, CL_BAR(kBarP2), __float_as_uint(best));
+        push_all<CS>(R, CL_OFF(idx2) + 4u * oi, CL_BAR(kBarP2), (uint32_t)bi);
       }
     }
-    if (CS > 1) cluster.sync(); else __syncthreads();
+    CL_TRACE(5);
+    cl_mbar_wait(&s.sbar[kBarP2], phase);
+    CL_TRACE(6);
 
     // ================= fc1, fc2 (rows split), fc3 + softmax-CE (redundant) =================
-    fc_rows_push<CS, kFlat, true>(params + kOffF1W, params + kOffF1B, s.p2, f1m0, f1m1, peers,
-                                  offsetof(CLSmem, h1));
-    if (CS > 1) cluster.sync(); else __syncthreads();
-    fc_rows_push<CS, kF1, true>(params + kOffF2W, params + kOffF2B, s.h1, f2m0, f2m1, peers,
-                                offsetof(CLSmem, h2));
-    if (CS > 1) cluster.sync(); else __syncthreads();
-    {
-      Peers<1> self;
-      self.p[0] = &s;
-      fc_rows_push<1, kF2, false>(params + kOffF3W, params + kOffF3B, s.h2, 0, kF3, self,
-                                  offsetof(CLSmem, logits));
-    }
+    fc_rows_push<CS, kFlat, true>(params + kOffF1W, params + kOffF1B, s.p2, f1m0, f1m1, R, CL_OFF(h1),
+                                  CL_BAR(kBarH1));
+    cl_mbar_wait(&s.sbar[kBarH1], phase);
+    CL_TRACE(7);
+    fc_rows_push<CS, kF1, true>(params + kOffF2W, params + kOffF2B, s.h1, f2m0, f2m1, R, CL_OFF(h2), CL_BAR(kBarH2));
+    cl_mbar_wait(&s.sbar[kBarH2], phase);
+    CL_TRACE(8);
+    fc_rows_local<kF3, kF2>(params + kOffF3W, params + kOffF3B, s.h2, s.logits);
     __syncthreads();
     if (warp == 0) {
       const int label = (int)__ldg(labels + img);
@@ -399,10 +469,16 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     // ================= FC data gradients =================
     fc_dx_local<kF3, kF2>(params + kOffF3W, s.d3, s.h2, s.d2);
     __syncthreads();
-    fc_dx_split_push<CS, kF2, kF1>(params + kOffF2W, s.d2, s.h1, d1k0, d1k1, s.red, peers, offsetof(CLSmem, d1));
-    if (CS > 1) cluster.sync(); else __syncthreads();
-    fc_dx_split_push<CS, kF1, kFlat>(params + kOffF1W, s.d1, s.p2, g2k0, g2k1, s.red, peers, offsetof(CLSmem, g2));
-    if (CS > 1) cluster.sync(); else __syncthreads();
+    fc_dx_split_push<CS, kF2, kF1>(params + kOffF2W, s.d2, s.h1, d1k0, d1k1, s.red, R, CL_OFF(d1), CL_BAR(kBarD1));
+    cl_mbar_wait(&s.sbar[kBarD1], phase);
+    CL_TRACE(9);
+    __syncthreads();  // `red` is reused by the next split
+    fc_dx_split_push<CS, kF1, kFlat>(params + kOffF1W, s.d1, s.p2, g2k0, g2k1, s.red, R, CL_OFF(g2), CL_BAR(kBarG2));
+    // zero the dense gradient plane while the g2 traffic is in flight
+    for (int i = tid; i < 16 * 18 * 18; i += kCLThreads) s.dc2p[i] = 0.f;
+    cl_mbar_wait(&s.sbar[kBarG2], phase);
+    __syncthreads();
+    CL_TRACE(10);
     // from here on nothing crosses CTAs any more
 
     if (r == 0) {  // FC record for the update kernel
@@ -412,25 +488,39 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       if (tid < 84) { sv[kSavH2 + tid] = s.h2[tid]; sv[kSavD2 + tid] = s.d2[tid]; }
       if (tid < 10) sv[kSavD3 + tid] = s.d3[tid];
     }
+    if (tid < 400) {  // scatter the pooled gradient to its argmax position (maxpool backward)
+      const int o = tid / 25, pp = tid - o * 25, ph = pp / 5, pw = pp - ph * 5;
+      const int id = s.idx2[tid];
+      s.dc2p[o * 324 + (2 * ph + (id >> 1) + 4) * 18 + (2 * pw + (id & 1) + 4)] = s.g2[tid];
+    }
 
     // ================= conv2 weight gradient, my output channels =================
-    for (int i = tid; i < 16 * 18 * 18; i += kCLThreads) s.dc2p[i] = 0.f;
+    // thread = (pixel group of 5, o, c, kh) with the five kw taps in registers
     {
       const int no = o1 - o0;
+      const int nitem = no * 30;
+      for (int t = tid; t < nitem * 5; t += kCLThreads) {
+        const int pg = t / nitem, rem = t - pg * nitem;
+        const int ol = rem / 30, r2 = rem - ol * 30, c = r2 / 5, kh = r2 - c * 5, o = o0 + ol;
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+          const int pp = pg * 5 + k;  // pooled row pg, column k
+          const float g = s.g2[o * 25 + pp];
+          const int id = s.idx2[o * 25 + pp];
+          const float* row = s.p1 + c * 196 + (2 * pg + (id >> 1) + kh) * 14 + 2 * k + (id & 1);
+          a0 += g * row[0]; a1 += g * row[1]; a2 += g * row[2]; a3 += g * row[3]; a4 += g * row[4];
+        }
+        float* dst = s.red + pg * (no * 150) + ol * 150 + c * 25 + kh * 5;
+        dst[0] = a0; dst[1] = a1; dst[2] = a2; dst[3] = a3; dst[4] = a4;
+      }
+      __syncthreads();
       float* dst = part2 + (size_t)img * (kConvPrefix - kOffW2);
       for (int t = tid; t < no * 150; t += kCLThreads) {
-        const int ol = t / 150, rem = t - ol * 150, c = rem / 25, tap = rem - c * 25;
-        const int kh = tap / 5, kw = tap - kh * 5, o = o0 + ol;
-        const float* gp = s.g2 + o * 25;
-        const unsigned char* ip = s.idx2 + o * 25;
-        const float* xb = s.p1 + c * 196 + kh * 14 + kw;
         float a = 0.f;
 #pragma unroll
-        for (int pp = 0; pp < 25; ++pp) {
-          const int id = ip[pp];
-          a += gp[pp] * xb[(2 * (pp / 5) + (id >> 1)) * 14 + 2 * (pp % 5) + (id & 1)];
-        }
-        dst[o * 150 + rem] = a;
+        for (int pg = 0; pg < 5; ++pg) a += s.red[pg * (no * 150) + t];
+        dst[o0 * 150 + t] = a;
       }
       if (tid < no) {
         const int o = o0 + tid;
@@ -440,13 +530,8 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       }
     }
     __syncthreads();
-    if (tid < 400) {
-      const int o = tid / 25, pp = tid - o * 25, ph = pp / 5, pw = pp - ph * 5;
-      const int id = s.idx2[tid];
-      s.dc2p[o * 324 + (2 * ph + (id >> 1) + 4) * 18 + (2 * pw + (id & 1) + 4)] = s.g2[tid];
-    }
-    __syncthreads();
 
+    CL_TRACE(11);
     // ================= conv2 data gradient for my pooled pixels =================
     for (int item = tid; item < nq * 16; item += kCLThreads) {
       const int o = item / nq, ql = item - o * nq, q = q0 + ql;
@@ -481,23 +566,28 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     }
     __syncthreads();
 
+    CL_TRACE(12);
     // ================= conv1 weight gradient over my pooled pixels (partial) =================
+    // thread = (pixel group of 5, o, c, kh) with the five kw taps in registers
     {
-      float* dst = part1 + ((size_t)img * CS + r) * kOffW2;
       if (tid < 450) {
-        const int o = tid / 75, rem = tid - o * 75, c = rem / 25, tap = rem - c * 25;
-        const int kh = tap / 5, kw = tap - kh * 5;
+        const int pg = tid / 90, rem = tid - pg * 90;
+        const int o = rem / 15, r2 = rem - o * 15, c = r2 / 5, kh = r2 - c * 5;
         const float* gp = s.g1 + o * 196;
-        const unsigned char* ip = s.idx1 + o * 196;
-        const float* xb = s.xp + c * kXpCh + kh * kXpRow + kw;
-        float a = 0.f;
-#pragma unroll 4
-        for (int q = q0; q < q1; ++q) {
+        const int* ip = s.idx1 + o * 196;
+        const float* xb = s.x + c * kXCh + kh * kXRow;
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+#pragma unroll 2
+        for (int q = q0 + pg; q < q1; q += 5) {
+          const float g = gp[q];
           const int id = ip[q];
-          a += gp[q] * xb[s.poff[q] + (id >> 1) * kXpRow + (id & 1)];
+          const float* row = xb + s.poff[q] + (id >> 1) * kXRow + (id & 1);
+          a0 += g * row[0]; a1 += g * row[1]; a2 += g * row[2]; a3 += g * row[3]; a4 += g * row[4];
         }
-        dst[tid] = a;
+        float* dst = s.red + pg * 450 + o * 75 + c * 25 + kh * 5;
+        dst[0] = a0; dst[1] = a1; dst[2] = a2; dst[3] = a3; dst[4] = a4;
       } else if (warp == 15) {
+        float* dst = part1 + ((size_t)img * CS + r) * kOffW2;
         for (int o = 0; o < 6; ++o) {
           float a = 0.f;
           for (int q = q0 + lane; q < q1; q += 32) a += s.g1[o * 196 + q];
@@ -505,23 +595,31 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
           if (lane == 0) dst[kOffB1 + o] = a;
         }
       }
+      __syncthreads();
+      if (tid < 450) {
+        float a = 0.f;
+#pragma unroll
+        for (int pg = 0; pg < 5; ++pg) a += s.red[pg * 450 + tid];
+        part1[((size_t)img * CS + r) * kOffW2 + tid] = a;
+      }
     }
-    __syncthreads();
-    if (tid == 0 && img + n_clusters < B) {
-      cl_mbar_expect_tx(&s.mbar, kImgNumel * 4);
-      cl_bulk_g2s(s.x, x + (size_t)(img + n_clusters) * kImgNumel, kImgNumel * 4, &s.mbar);
+    CL_TRACE(13);
+    phase ^= 1u;
+    if (img + n_clusters < B) {
+      // several images per cluster: nobody may push the next image's activations (or reload the
+      // image buffer) while a slower CTA of the cluster still reads this image's
+      __syncthreads();
+      cl_cluster_arrive();
+      cl_cluster_wait();
+      load_image(img + n_clusters);
     }
-    // the next round's pushes into p1 must not overtake a slow peer still reading p1/idx1
-    if (CS > 1 && img + n_clusters < B) cluster.sync();
   }
-  // a CTA's shared memory must stay alive until no peer can still push into it
-  if (CS > 1) cluster.sync();
 }
 
 template <int CS>
 static int launch_cluster_t(const float* params, const float* x, const long long* labels, float* saved, float* part1,
                             float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
-                            cudaStream_t stream) {
+                            long long* trace, cudaStream_t stream) {
   static bool attr_set = false;
   auto kern = fwd_bwd_cluster_kernel<CS>;
   const size_t smem = sizeof(CLSmem);
@@ -544,7 +642,7 @@ static int launch_cluster_t(const float* params, const float* x, const long long
   cfg.numAttrs = 1;
   const float inv_batch = 1.f / (float)B;
   DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, params, x, labels, saved, part1, part2, img_loss, img_correct, B,
-                                    inv_batch));
+                                    inv_batch, trace));
   return kOk;
 }
 
@@ -588,11 +686,11 @@ int max_active_clusters(int cs) {
 
 int launch_fwd_bwd_cluster(int cs, const float* params, const float* x, const long long* labels, float* saved,
                            float* part1, float* part2, float* img_loss, int* img_correct, int B, int num_sms /* = max resident clusters */,
-                           cudaStream_t stream) {
+                           long long* trace, cudaStream_t stream) {
   switch (cs) {
-    case 8: return launch_cluster_t<8>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, stream);
-    case 4: return launch_cluster_t<4>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, stream);
-    case 2: return launch_cluster_t<2>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, stream);
+    case 8: return launch_cluster_t<8>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
+    case 4: return launch_cluster_t<4>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
+    case 2: return launch_cluster_t<2>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
     default: set_last_error("cluster size %d not supported", cs); return kErrArg;
   }
 }

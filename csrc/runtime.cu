@@ -37,7 +37,7 @@ int launch_fwd_bwd(bool train, const float* params, const float* x, const long l
                    int max_ctas, cudaStream_t stream);
 int launch_fwd_bwd_cluster(int cs, const float* params, const float* x, const long long* labels, float* saved,
                            float* part1, float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
-                           cudaStream_t stream);
+                           long long* trace, cudaStream_t stream);
 int max_active_clusters(int cs);
 int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int n_part1, int loss_slot, int flags,
                   cudaStream_t stream);
@@ -92,6 +92,7 @@ struct dnnb200_engine {
   int device = 0, max_batch = 0;
   float *params = nullptr, *momentum = nullptr, *grads = nullptr;
   float *saved = nullptr, *part1 = nullptr, *part2 = nullptr, *img_loss = nullptr;
+  long long* trace = nullptr;      // development aid: per-CTA stage timestamps of the cluster kernel
   int forced_cluster = 0;          // 0 = pick per batch size
   int max_clusters[9] = {};        // resident clusters of the fwd/bwd kernel per cluster size (index = CS)
   int* img_correct = nullptr;
@@ -203,7 +204,7 @@ static int fwd_bwd_any(dnnb200_engine* e, const float* x, const long long* y, in
     return launch_fwd_bwd(true, e->params, x, y, e->saved, e->part1, e->part2, e->img_loss, e->img_correct, nullptr,
                           B, e->num_sms, s);
   return launch_fwd_bwd_cluster(cs, e->params, x, y, e->saved, e->part1, e->part2, e->img_loss, e->img_correct, B,
-                                e->max_clusters[cs] > 0 ? e->max_clusters[cs] : 1, s);
+                                e->max_clusters[cs] > 0 ? e->max_clusters[cs] : 1, e->trace, s);
 }
 
 static int step_kernels(dnnb200_engine* e, const float* x, const long long* y, int B, int flags, cudaStream_t s) {
@@ -447,6 +448,12 @@ int dnnb200_engine_set_cluster_size(dnnb200_engine* e, int cs) {
   DNN_ARG_CHECK(cs == 0 || cs == 1 || cs == 2 || cs == 4 || cs == 8, "cluster size must be 0 (auto), 1, 2, 4 or 8");
   DNN_ARG_CHECK(cs <= 1 || e->max_clusters[cs] > 0, "clusters of %d CTAs cannot be scheduled on this device", cs);
   e->forced_cluster = cs;
+  return kOk;
+}
+
+int dnnb200_engine_set_trace(dnnb200_engine* e, long long* d_trace) {
+  DNN_ARG_CHECK(e, "null engine");
+  e->trace = d_trace;
   return kOk;
 }
 

@@ -236,6 +236,11 @@ class Engine:
         """CTAs per image in the forward/backward kernel (0 = automatic, 1/2/4/8)."""
         _check(require().dnnb200_engine_set_cluster_size(self._h, cs))
 
+    def set_trace(self, trace: Optional[torch.Tensor]) -> None:
+        """int64 CUDA tensor [n_ctas*16] receiving per-stage SM clocks (development aid)."""
+        self._trace = trace
+        _check(require().dnnb200_engine_set_trace(self._h, _p(trace)))
+
     def cluster_info(self, B: int):
         chosen = C.c_int()
         mc = (C.c_int * 9)()

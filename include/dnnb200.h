@@ -101,6 +101,9 @@ unsigned long long dnnb200_engine_launches(const dnnb200_engine* e);
  * (distributed shared memory between them). 0 = choose per batch size so the batch is one wave. */
 int dnnb200_engine_set_cluster_size(dnnb200_engine* e, int cs);
 int dnnb200_engine_cluster_info(const dnnb200_engine* e, int B, int* chosen, int* max_clusters9);
+/* development aid: d_trace[cta*16 + k] receives the SM clock at stage boundary k of the clustered
+ * forward/backward kernel (NULL switches it off) */
+int dnnb200_engine_set_trace(dnnb200_engine* e, long long* d_trace);
 
 /* one optimizer step on a device-resident batch: fwd/bwd kernel + update kernel
  * (reference: the loop body data_parallelism_train.py:195-203) */
