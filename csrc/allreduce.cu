@@ -46,7 +46,8 @@ struct ArParams {
 
 __device__ __forceinline__ void finish(const RankCtx& cx, const ArParams& prm, int vr, int i, const float (&v)[4],
                                        int n) {
-  const float inv = 1.f / (float)n;
+  const unsigned int dov = cx.ctl->divisor_override;
+  const float inv = 1.f / (float)((dov && n > 0) ? (int)dov : (n > 0 ? n : 1));
   const float4 g = make_float4(v[0] * inv, v[1] * inv, v[2] * inv, v[3] * inv);
   if (prm.mode == kArSgd) {
     const float lr = cx.ctl->lr, mu = cx.ctl->mu;
@@ -124,7 +125,7 @@ allreduce_kernel(const RankCtx* __restrict__ ctxs, const ArParams prm) {
         const float4 t = ld_cg_f4(reinterpret_cast<const float4*>(
             my_recv + ((size_t)(parity * world + owner) * kFlatNumel + i)));
         v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-        finish(cx, prm, vr, i, v, 1);  // the owner already divided
+        finish(cx, prm, vr, i, v, 0);  // the owner already divided
       }
     } else {
       // owner: wait for every configured peer, reduce in rank order, broadcast the mean
@@ -153,7 +154,8 @@ allreduce_kernel(const RankCtx* __restrict__ ctxs, const ArParams prm) {
             acc[0] += t.x; acc[1] += t.y; acc[2] += t.z; acc[3] += t.w;
           }
         }
-        const float inv = 1.f / (float)n_cfg;
+        const unsigned int dov2 = ctl->divisor_override;
+        const float inv = 1.f / (float)(dov2 ? (int)dov2 : n_cfg);
         const float4 mean = make_float4(acc[0] * inv, acc[1] * inv, acc[2] * inv, acc[3] * inv);
         for (int p = 0; p < world; ++p) {
           if (p == rank || !((configured >> p) & 1u)) continue;
@@ -166,7 +168,7 @@ allreduce_kernel(const RankCtx* __restrict__ ctxs, const ArParams prm) {
         __threadfence_system();
         st_release_sys(cx.flags[tid] + (kMaxWorld + rank) * kFlagRow + slice, seq);
       }
-      if (in_range) finish(cx, prm, vr, i, v, 1);
+      if (in_range) finish(cx, prm, vr, i, v, 0);
     }
   } else {
     if (in_range) finish(cx, prm, vr, i, v, 1);

@@ -589,7 +589,8 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
   if (in_range && grad_only) {
     if (cx.grads) *reinterpret_cast<float2*>(cx.grads + i) = make_float2(v[0], v[1]);
   } else if (in_range) {
-    const float inv_n = 1.f / (float)n;
+    const unsigned int dov = ctl->divisor_override;
+    const float inv_n = 1.f / (float)(dov ? (int)dov : n);
     const float lr = ctl->lr, mu = ctl->mu;
     const float g0 = v[0] * inv_n, g1 = v[1] * inv_n;
     float2 m = *reinterpret_cast<float2*>(cx.momentum + i);

@@ -61,6 +61,7 @@ __global__ void ctl_set_membership_kernel(StepCtl* c, unsigned int mask, unsigne
   c->timeout_ns = tmo;
   c->status = 0u;
 }
+__global__ void ctl_set_divisor_kernel(StepCtl* c, unsigned int d) { c->divisor_override = d; }
 __global__ void ctl_reset_loss_kernel(StepCtl* c) { c->loss_sum = 0.f; c->loss_steps = 0u; }
 __global__ void ctl_set_step_kernel(StepCtl* c, unsigned long long step) { c->step = step; c->ctas_done = 0u; }
 // leave marker = first sequence number this rank will not take part in
@@ -420,6 +421,13 @@ int dnnb200_engine_set_membership(dnnb200_engine* e, unsigned int active_mask, u
   return kOk;
 }
 
+int dnnb200_engine_set_divisor(dnnb200_engine* e, unsigned int divisor, void* stream) {
+  DNN_ARG_CHECK(e, "null engine");
+  ctl_set_divisor_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(e->ctl, divisor);
+  DNN_CUDA_CHECK(cudaGetLastError());
+  return kOk;
+}
+
 int dnnb200_engine_zero_momentum(dnnb200_engine* e, void* stream) {
   DNN_ARG_CHECK(e, "null engine");
   DNN_CUDA_CHECK(cudaMemsetAsync(e->momentum, 0, kFlatNumel * sizeof(float), (cudaStream_t)stream));
@@ -470,6 +478,18 @@ int dnnb200_engine_step(dnnb200_engine* e, const float* x, const int64_t* y, int
   int rc = step_kernels(e, x, (const long long*)y, B, 0, (cudaStream_t)stream);
   if (rc) return rc;
   e->steps_launched += 1;
+  return kOk;
+}
+
+int dnnb200_engine_train_device(dnnb200_engine* e, const float* x, const int64_t* y, int B, int nsteps, void* stream) {
+  DNN_ARG_CHECK(e && x && y, "engine_train_device: null argument");
+  DNN_ARG_CHECK(B >= 1 && B <= e->max_batch, "engine_train_device: batch %d exceeds max_batch %d", B, e->max_batch);
+  for (int t = 0; t < nsteps; ++t) {
+    int rc = step_kernels(e, x + (size_t)t * B * kImgNumel, (const long long*)y + (size_t)t * B, B, 0,
+                          (cudaStream_t)stream);
+    if (rc) return rc;
+    e->steps_launched += 1;
+  }
   return kOk;
 }
 

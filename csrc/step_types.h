@@ -32,7 +32,8 @@ struct StepCtl {
   unsigned int ctas_done;   // last-CTA-out counter of the update kernel
   unsigned int status;      // StepStatus bits, sticky until the host clears them
   unsigned int active_mask; // ranks configured into the exchange (bit r = rank r)
-  unsigned int average_only;  // 1: out = mean(in) with no optimizer (epoch-average / replication modes)
+  unsigned int divisor_override;  // 0: divide by the ranks present; else by this (parent/children parity mode:
+                                  // the non-training parent contributes zeros and the divisor is W-1)
 };
 
 struct RankCtx {

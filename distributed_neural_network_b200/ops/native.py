@@ -39,7 +39,7 @@ class Ctl(C.Structure):
         ("ctas_done", C.c_uint),
         ("status", C.c_uint),
         ("active_mask", C.c_uint),
-        ("average_only", C.c_uint),
+        ("divisor_override", C.c_uint),
     ]
 
 
@@ -221,6 +221,10 @@ class Engine:
         _check(require().dnnb200_engine_set_membership(self._h, C.c_uint(active_mask), C.c_ulonglong(timeout_ns),
                                                        _stream()))
 
+    def set_divisor(self, divisor: int) -> None:
+        """0 = divide exchanged sums by the ranks present; n = divide by n."""
+        _check(require().dnnb200_engine_set_divisor(self._h, C.c_uint(divisor), _stream()))
+
     def zero_momentum(self) -> None:
         _check(require().dnnb200_engine_zero_momentum(self._h, _stream()))
 
@@ -257,6 +261,13 @@ class Engine:
         if y.dtype != torch.int64 or not y.is_cuda:
             raise TypeError("y must be a CUDA int64 tensor")
         _check(require().dnnb200_engine_step(self._h, _p(x), _p(y), x.shape[0], _stream()))
+
+    def train_device(self, x: torch.Tensor, y: torch.Tensor) -> None:
+        """x [steps,B,3,32,32] fp32 and y [steps,B] int64 on the device: steps optimizer steps, one native loop."""
+        _f32(x, "x")
+        steps, B = y.shape
+        assert x.shape[0] == steps and x.shape[1] == B and y.dtype == torch.int64 and y.is_contiguous()
+        _check(require().dnnb200_engine_train_device(self._h, _p(x), _p(y), B, steps, _stream()))
 
     def grad_only(self, x: torch.Tensor, y: torch.Tensor, grads_out: torch.Tensor) -> float:
         _f32(x, "x"); _f32(grads_out, "grads_out")

@@ -1,0 +1,461 @@
+"""Epoch loop and synchronisation modes shared by the three entry points.
+
+Reference orchestration: ``main``/``run_child``/``run_parent``/``eval`` of
+data_parallelism_train.py:56-254 and model_replication_train.py:31-148, and the script body of
+single_proc_train.py:16-107. What the modes mean here:
+
+``step-allreduce`` (default, new)
+    every rank trains its shard; gradients are averaged EVERY step inside the update kernel
+    (peer-memory all-reduce fused with 1/W and SGD-momentum). Replicas stay bit-identical, so
+    there is nothing to average at the epoch boundary.
+``epoch-average`` (reference parity)
+    each trainer runs plain local SGD for one epoch with a fresh optimizer (momentum zeroed,
+    reference :187), then the PARAMETERS are averaged (reference :238-240) -- with the same
+    all-reduce kernel in "mean only" mode instead of pickled state_dicts through rank 0.
+    ``reference_topology=True`` also reproduces who trains: rank 0 is a parent that only
+    evaluates, ranks 1..P-1 train contiguous shards of ``len // (P-1)`` (reference :49-53,66).
+``replication`` (reference model_replication_train.py)
+    like ``epoch-average`` but every trainer sees the full training set with its own shuffle.
+``none``
+    single process (reference single_proc_train.py).
+
+On CUDA the step runs through the native engine (two kernels per step, data resident in HBM or
+streamed from pinned memory); on CPU the same algorithm runs in plain PyTorch with gloo for the
+exchange, which is what the no-GPU tests and the "plumbing" configuration of BASELINE.json use.
+"""
+from __future__ import annotations
+
+import os
+import time
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Tuple
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+from .models.network import Network
+from .ops import flat as L
+from .ops import functional as Fn
+from .ops import native
+from .parallel import bootstrap
+from .parallel.membership import FailureSimulator, Membership
+from .utils import checkpoint as ckpt
+from .utils import data as D
+from .utils import logs
+
+
+@dataclass
+class TrainConfig:
+    lr: float = 0.001                 # reference default (data_parallelism_train.py:260)
+    momentum: float = 0.9             # :261
+    batch_size: int = 16              # :262
+    epochs: int = 25                  # :263
+    nb_proc: int = 4                  # :264 -- labels the log files only, as in the reference
+    failure_probability: float = 0.0  # :265
+    failure_duration: float = 0.0     # :267
+    failure_mode: str = "sleep"       # sleep = reference behaviour; drop = membership epoch
+    sync_mode: str = "step-allreduce"
+    reference_topology: bool = False
+    device: str = "auto"              # auto | cpu | cuda
+    data_root: str = "./data"
+    synthetic: Optional[bool] = None  # None: real CIFAR-10 if present, else synthetic
+    train_size: Optional[int] = None  # truncate / size the (synthetic) training set
+    test_size: Optional[int] = None
+    seed: Optional[int] = None        # the reference has none; set for reproducible runs
+    log_dir: str = "log"
+    jsonl: Optional[str] = None
+    save: Optional[str] = None
+    resume: Optional[str] = None
+    input_pipeline: str = "device"    # device: dataset resident in HBM; host: per-step H2D from pinned memory
+    allreduce_variant: str = "one-shot"
+    peer_timeout_s: float = 30.0
+    eval_batch_size: Optional[int] = None  # the reference evaluates with --batch-size too (Q11)
+    neptune: bool = False
+    quiet: bool = False
+
+    def __post_init__(self):
+        if self.sync_mode not in ("step-allreduce", "epoch-average", "replication", "none"):
+            raise ValueError(f"unknown sync mode {self.sync_mode!r}")
+        self.lr, self.momentum = float(self.lr), float(self.momentum)   # the reference forgets the casts (Q5)
+        self.batch_size, self.epochs = int(self.batch_size), int(self.epochs)
+
+
+def reference_global_avg_loss(total_losses: float, n_children: int) -> float:
+    """The reference's 'Global Average Training Loss' (quirk Q4: it divides the summed batch
+    losses by 10 keys x children, data_parallelism_train.py:233,248). Kept for parity tests."""
+    return total_losses / float(10 * n_children)
+
+
+class Trainer:
+    def __init__(self, cfg: TrainConfig, comm: Optional[bootstrap.Comm] = None, model: Optional[Network] = None,
+                 run=None):
+        self.cfg = cfg
+        self.comm = comm if comm is not None else bootstrap.init()
+        self.rank, self.world = self.comm.rank, self.comm.world
+        self.timers = logs.Timers()
+        self.run = run if run is not None else (logs.init_run(enabled=cfg.neptune) if self.rank == 0 else logs.NullRun())
+        self.jsonl = logs.JsonlLog(cfg.jsonl if self.rank == 0 else None)
+        self.device = self._pick_device()
+        if cfg.seed is not None:
+            torch.manual_seed(cfg.seed + self.rank)
+        self.gen = torch.Generator().manual_seed((cfg.seed if cfg.seed is not None else int(time.time())) + 1000 * self.rank)
+
+        # who trains / who evaluates
+        self.parent_only = cfg.reference_topology and self.world > 1 and self.rank == 0
+        self.trainers: List[int] = list(range(1, self.world)) if (cfg.reference_topology and self.world > 1) \
+            else list(range(self.world))
+        self.is_trainer = self.rank in self.trainers
+        self.membership = Membership(self.world, active=set(self.trainers))
+
+        self.model = (model if model is not None else Network()).to(self.device)
+        self.momentum = torch.zeros(L.FLAT_NUMEL, dtype=torch.float32, device=self.device)
+        self.start_epoch = 0
+        if cfg.resume:
+            meta = ckpt.load(cfg.resume, self.model, self.momentum)
+            self.start_epoch = int(meta.get("epoch", -1)) + 1
+        # replicas must start identical: rank 0's weights win, as the parent's do in the reference
+        # (data_parallelism_train.py:118,137)
+        if self.world > 1:
+            flat0 = self.comm.bcast(self.model.flat_params.detach().cpu() if self.rank == 0 else None, root=0)
+            self.model.flat_params.copy_(flat0.to(self.device))
+
+        self.engine: Optional[native.Engine] = None
+        self.group: Optional[native.Group] = None
+        self.first_step = True
+        if self.device.type == "cuda":
+            self.engine = native.Engine(self.model.flat_params, self.momentum, None, max(cfg.batch_size, 1),
+                                        cfg.lr, cfg.momentum)
+            if self.world > 1:
+                self.group = native.Group(self.rank, self.world)
+                handles = self.comm.allgather(self.group.handle)
+                self.group.connect(handles)
+                self.engine.attach_group(self.group)
+                self._apply_membership()
+        self.failure = FailureSimulator(cfg.failure_probability, cfg.failure_duration, cfg.failure_mode, cfg.seed,
+                                        self.rank)
+        self.dropped = False
+        self.history: List[Dict] = []
+
+    # ------------------------------------------------------------------ setup helpers
+    def _pick_device(self) -> torch.device:
+        want = self.cfg.device
+        if want == "cpu" or (want == "auto" and not torch.cuda.is_available()):
+            # P ranks on one host: give each its share of the cores. (The reference lets every rank
+            # run a fully threaded torch on the same 8 cores -- the negative scaling of its Table 1.)
+            if self.world > 1 and "OMP_NUM_THREADS" not in os.environ:
+                torch.set_num_threads(max(1, (os.cpu_count() or 1) // self.world))
+            return torch.device("cpu")
+        idx = int(os.environ.get("DNNB200_DEVICE", os.environ.get("LOCAL_RANK", self.comm.local_rank)))
+        idx %= max(1, torch.cuda.device_count())
+        torch.cuda.set_device(idx)
+        return torch.device("cuda", idx)
+
+    def _log(self, *a) -> None:
+        if not self.cfg.quiet:
+            print(*a, flush=True)
+
+    def _sync(self) -> None:
+        if self.device.type == "cuda":
+            torch.cuda.synchronize()
+
+    def _apply_membership(self, local_only: bool = False) -> None:
+        """Program the exchange kernels: who is in the sum, how long to wait for a silent peer."""
+        if self.engine is None or self.world == 1:
+            return
+        mask = (1 << self.rank) if local_only else self.membership.mask
+        self.engine.set_membership(mask, int(self.cfg.peer_timeout_s * 1e9))
+
+    # ------------------------------------------------------------------ data
+    def load_data(self) -> Tuple[Optional[D.TensorDataset], Optional[D.TensorDataset]]:
+        """Per-role data, timed like the reference (:66-96): trainers the train shard, rank 0 the test set."""
+        cfg = self.cfg
+        t0 = time.time()
+        shard = test = None
+        use_syn = cfg.synthetic
+        if self.is_trainer:
+            if use_syn:
+                full = D.synthetic(cfg.train_size or D.TRAIN_SIZE, seed=0)
+            else:
+                full = D.cifar10(cfg.data_root, True, allow_synthetic=(use_syn is None),
+                                 synthetic_size=cfg.train_size, verbose=self.rank == self.trainers[0] and not cfg.quiet)
+                if cfg.train_size and len(full) > cfg.train_size:
+                    full = D.Subset(full, range(cfg.train_size)).materialize()
+            if cfg.sync_mode == "replication" or self.world == 1:
+                part = D.Subset(full, range(len(full)))
+            elif cfg.reference_topology:
+                part = D.partition_dataset(full, self.rank, self.world)
+            else:
+                part = D.partition_symmetric(full, self.rank, self.world)
+            shard = part.materialize()
+            self._log("(Loaded Train Dataset for worker {0} of length {1})".format(self.rank, len(shard)))
+        if self.rank == 0:
+            if use_syn:
+                test = D.synthetic(cfg.test_size or D.TEST_SIZE, seed=1)
+            else:
+                test = D.cifar10(cfg.data_root, False, allow_synthetic=(use_syn is None), synthetic_size=cfg.test_size,
+                                 verbose=not cfg.quiet)
+                if cfg.test_size and len(test) > cfg.test_size:
+                    test = D.Subset(test, range(cfg.test_size)).materialize()
+        if self.device.type == "cuda":
+            if shard is not None:
+                shard = shard.to(self.device) if cfg.input_pipeline == "device" else shard.pin_memory()
+            if test is not None:
+                test = test.to(self.device)
+            self._sync()
+        self.timers.data_loading_time += time.time() - t0
+        return shard, test
+
+    # ------------------------------------------------------------------ one epoch of training
+    def train_epoch(self, shard: D.TensorDataset, drop_at: Optional[int] = None) -> Tuple[float, int]:
+        """One pass over ``shard``; returns (sum of per-batch mean losses, number of batches) like the
+        reference's ``total_loss``/``total_batches`` (:188-203). ``drop_at``: leave the group after
+        that many steps (failure drill)."""
+        cfg = self.cfg
+        B = cfg.batch_size
+        local_sgd = cfg.sync_mode in ("epoch-average", "replication", "none") or self.world == 1
+        if cfg.sync_mode in ("epoch-average", "replication"):
+            self.momentum.zero_()      # the reference builds a new optimizer every epoch (:187)
+            self.first_step = True
+        if self.engine is not None:
+            return self._train_epoch_cuda(shard, B, local_sgd, drop_at)
+        return self._train_epoch_cpu(shard, B, local_sgd, drop_at)
+
+    def _train_epoch_cuda(self, shard, B, local_sgd, drop_at) -> Tuple[float, int]:
+        eng = self.engine
+        self._apply_membership(local_only=local_sgd)
+        eng.reset_loss()
+        steps = len(shard) // B
+        x, y, tail_xy = D.epoch_tensor(shard, B, shuffle=True, generator=self.gen)
+        run_steps = steps if drop_at is None else min(steps, drop_at)
+        if self.cfg.input_pipeline == "host":
+            # per-step H2D copies from pinned memory through the engine's 4-slot ring
+            if run_steps:
+                eng.train_host(x[:run_steps].pin_memory(), y[:run_steps].pin_memory(), None)
+        elif run_steps:
+            eng.train_device(x[:run_steps], y[:run_steps])
+        if tail_xy is not None and drop_at is None:
+            # the trailing short batch, as DataLoader(drop_last=False) yields it
+            eng.step(tail_xy[0].to(self.device), tail_xy[1].to(self.device))
+        if drop_at is not None:
+            eng.leave()
+            self.dropped = True
+        ctl = eng.read_ctl()
+        if ctl.status & 1:
+            self._log(f"[rank {self.rank}] peers timed out during the epoch: mask 0x{(ctl.status >> 8) & 0xffff:x}")
+        return float(ctl.loss_sum), int(ctl.loss_steps)
+
+    def _train_epoch_cpu(self, shard, B, local_sgd, drop_at) -> Tuple[float, int]:
+        model, cfg = self.model, self.cfg
+        model.train()
+        total, nb = 0.0, 0
+        exch = torch.zeros(L.FLAT_NUMEL + 1)
+        for i, (x, y) in enumerate(D.batches(shard, B, shuffle=True, generator=self.gen)):
+            gone = drop_at is not None and i >= drop_at
+            if not gone:
+                model.zero_grad()
+                loss = F.cross_entropy(model(x), y)
+                loss.backward()
+                total += loss.item()
+                nb += 1
+            if not local_sgd:
+                # gloo stand-in for the peer-memory exchange: the extra element counts who is present,
+                # so a dropped rank (zeros, count 0) changes the divisor exactly like a leave marker
+                exch[:-1] = 0.0 if gone else model.flat_grads
+                exch[-1] = 0.0 if gone else 1.0
+                self.comm.allreduce_sum_(exch)
+                if gone:
+                    continue
+                g = exch[:-1] / exch[-1].clamp_min(1.0)
+            else:
+                if gone:
+                    break
+                g = model.flat_grads
+            Fn.sgd_momentum_(model.flat_params.data, g, self.momentum, cfg.lr, cfg.momentum, self.first_step)
+            self.first_step = False
+        if drop_at is not None:
+            self.dropped = True
+        return total, nb
+
+    # ------------------------------------------------------------------ parameter averaging (R1)
+    @torch.no_grad()
+    def average_parameters(self) -> None:
+        """mean over the trainers of the flat parameter vector; everyone (parent included) gets it."""
+        if self.world == 1:
+            return
+        n_tr = len(self.membership.active)
+        if self.engine is not None:
+            contrib = self.model.flat_params if (self.is_trainer and self.rank in self.membership.active) \
+                else torch.zeros_like(self.model.flat_params)
+            full = (1 << self.world) - 1
+            self.engine.set_membership(full, int(self.cfg.peer_timeout_s * 1e9))
+            self.engine.set_divisor(n_tr)
+            out = torch.empty_like(self.model.flat_params)
+            self.engine.allreduce(contrib.contiguous(), out, mode=0, two_shot=self.cfg.allreduce_variant == "two-shot")
+            self.model.flat_params.copy_(out)
+            self.engine.set_divisor(0)
+            self._sync()
+        else:
+            buf = self.model.flat_params.detach().clone() if (self.is_trainer and self.rank in self.membership.active) \
+                else torch.zeros(L.FLAT_NUMEL)
+            self.comm.allreduce_sum_(buf)
+            self.model.flat_params.copy_(buf / float(n_tr))
+
+    # ------------------------------------------------------------------ evaluation
+    @torch.no_grad()
+    def evaluate(self, test: D.TensorDataset) -> Tuple[float, float]:
+        """(mean of per-batch mean losses, accuracy %) -- reference eval :157-183."""
+        bs = self.cfg.eval_batch_size or self.cfg.batch_size
+        if self.engine is not None:
+            loss, hits = self.engine.evaluate(test.images, test.labels, bs)
+            return loss, 100.0 * hits / len(test)
+        self.model.eval()
+        losses, corrects, total = [], 0, 0
+        for x, y in D.batches(test, bs, shuffle=False):
+            out = self.model(x)
+            losses.append(F.cross_entropy(out, y).item())
+            corrects += (torch.argmax(out, dim=1) == y).sum().item()
+            total += y.size(0)
+        return float(np.mean(losses)), 100.0 * corrects / total
+
+    # ------------------------------------------------------------------ membership at epoch boundaries
+    def _epoch_boundary(self) -> None:
+        """Membership epoch: agree on who is present; returning ranks adopt a survivor's state."""
+        if self.world == 1:
+            return
+        status = self.comm.allgather({"rank": self.rank, "dropped": self.dropped})
+        came_back = [s["rank"] for s in status if s["dropped"]]
+        for r in came_back:
+            self.membership.leave(r)
+        if not came_back:
+            return
+        donor = self.membership.donor()
+        state = None
+        if self.rank == donor:
+            step = self.engine.read_ctl().step if self.engine is not None else 0
+            state = (self.model.flat_params.detach().cpu(), self.momentum.detach().cpu(), int(step))
+        state = self.comm.bcast(state, root=donor)
+        if self.dropped:
+            self.model.flat_params.copy_(state[0].to(self.device))
+            self.momentum.copy_(state[1].to(self.device))
+            if self.engine is not None:
+                self.engine.rejoin(state[2])
+                self._sync()
+            self.dropped = False
+        for r in came_back:
+            self.membership.join(r)
+        self.comm.barrier()  # nobody steps before every marker is cleared
+        self._apply_membership()
+
+    # ------------------------------------------------------------------ the whole run
+    def fit(self, shard: Optional[D.TensorDataset] = None, test: Optional[D.TensorDataset] = None) -> List[Dict]:
+        cfg = self.cfg
+        if shard is None and test is None:
+            shard, test = self.load_data()
+        if self.rank == 0:
+            self.run["parameters"] = {"learning_rate": cfg.lr, "optimizer": "SGD", "model_name": "distmodel",
+                                      "epochs": cfg.epochs, "sync_mode": cfg.sync_mode, "world": self.world}
+        steps_per_epoch = (len(shard) + cfg.batch_size - 1) // cfg.batch_size if shard is not None else 0
+        for epoch in range(self.start_epoch, cfg.epochs):
+            if self.rank == 0:
+                self._log("Starting epoch ", epoch)
+            self._epoch_boundary()
+            ev = self.failure.draw(steps_per_epoch) if cfg.failure_probability > 0 else None
+            drop_at = None
+            if ev is not None and cfg.failure_mode == "sleep":
+                # parent: inside the communication timer, children: untimed (reference :116-120,141)
+                if self.parent_only:
+                    with self.timers.add("mpi_communication_time_parent"):
+                        self.failure.sleep(ev)
+                else:
+                    self.failure.sleep(ev)
+            elif ev is not None and not (self.is_trainer and cfg.sync_mode == "step-allreduce"
+                                         and len(self.membership.active) > 1):
+                self.failure.sleep(ev)  # nothing to drop out of: behave like the reference
+            elif ev is not None:
+                drop_at = ev.at_step
+                self._log(f"Process {self.rank} failed! Leaving the group at step {drop_at} for {ev.duration} seconds.")
+
+            total_loss, n_batches = 0.0, 0
+            t_dev = None
+            if self.is_trainer:
+                ev0 = ev1 = None
+                if self.device.type == "cuda":
+                    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                with self.timers.add("training_time", self._sync):
+                    if ev0 is not None:
+                        ev0.record()
+                    total_loss, n_batches = self.train_epoch(shard, drop_at)
+                    if ev1 is not None:
+                        ev1.record()
+                if ev0 is not None:
+                    self._sync()
+                    t_dev = ev0.elapsed_time(ev1) / 1e3
+                if drop_at is not None:
+                    time.sleep(ev.duration)
+                    self._log(f"Process {self.rank} woke up!")
+
+            if cfg.sync_mode in ("epoch-average", "replication") and self.world > 1:
+                if self.rank == 0:
+                    self._log("* Averaging models...")
+                tname = "mpi_communication_time_parent" if self.rank == 0 else "mpi_communication_time_children"
+                with self.timers.add(tname, self._sync):
+                    self.average_parameters()
+
+            # loss bookkeeping: true mean over all batches of all trainers
+            stats = self.comm.allgather((total_loss, n_batches, t_dev, len(shard) if shard is not None else 0))
+            sum_loss = sum(s[0] for s in stats)
+            sum_batches = sum(s[1] for s in stats)
+            mean_loss = sum_loss / max(1, sum_batches)
+            rec: Dict = {"epoch": epoch, "train_loss": mean_loss, "membership_epoch": self.membership.epoch,
+                         "active": sorted(self.membership.active)}
+            tds = [s[2] for s in stats if s[2] is not None]
+            if tds:
+                t_max = max(tds)                      # device-timed, max over ranks
+                imgs = sum(s[3] for s in stats)
+                rec.update(train_seconds_device_max=t_max, images_per_s=imgs / t_max if t_max > 0 else None,
+                           step_us=1e6 * t_max / max(1, max(s[1] for s in stats)))
+            if self.rank == 0:
+                self._log(f"Global Average Training Loss: {mean_loss}")
+                self.run["train/loss"].append(mean_loss)
+                self._log("evaluating model")
+                with self.timers.add("evaluation_time", self._sync):
+                    val_loss, val_acc = self.evaluate(test)
+                self.run["val/loss"].append(val_loss)
+                self.run["val/acc"].append(val_acc)
+                self._log("Validation loss of updated master model: ", val_loss)
+                self._log("Validation Accuracy: %.2f %%" % val_acc)
+                rec.update(val_loss=val_loss, val_acc=val_acc)
+                self.jsonl.write(**rec)
+            self.history.append(rec)
+            if cfg.save and self.rank == 0:
+                ckpt.save(cfg.save, self.model, self.momentum, epoch=epoch, membership_epoch=self.membership.epoch)
+            self.comm.barrier()  # children wait for the parent's evaluation, as they do in recv (:135)
+        self._epoch_boundary()   # ranks that dropped out in the last epoch still end with the final model
+        self._write_logs()
+        return self.history
+
+    def _write_logs(self) -> None:
+        cfg = self.cfg
+        if self.rank == 0:
+            logs.print_parent_summary(self.timers)
+            logs.write_parent_log(self.timers, cfg.batch_size, cfg.epochs, cfg.nb_proc, cfg.log_dir)
+        # the reference writes the children file from rank 2 only (:143); fall back to the last trainer
+        writer = 2 if 2 in self.trainers else self.trainers[-1]
+        if self.rank == writer and (self.world > 1):
+            logs.print_children_summary(self.timers)
+            logs.write_children_log(self.timers, cfg.batch_size, cfg.epochs, cfg.nb_proc, cfg.log_dir)
+
+    def close(self) -> None:
+        if self.engine is not None:
+            self._sync()
+            self.engine.close()
+            self.engine = None
+        if self.group is not None:
+            self.comm.barrier()
+            self.group.close()
+            self.group = None
+        try:
+            self.run.stop()
+        except Exception:
+            pass

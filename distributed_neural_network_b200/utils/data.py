@@ -170,10 +170,10 @@ def batches(ds: TensorDataset, batch_size: int, shuffle: bool, generator: Option
             yield ds.images[i:i + batch_size], ds.labels[i:i + batch_size]
 
 
-def epoch_tensor(ds: TensorDataset, batch_size: int, shuffle: bool,
-                 generator: Optional[torch.Generator] = None) -> Tuple[torch.Tensor, torch.Tensor, int]:
-    """One epoch as [steps, B, 3, 32, 32] / [steps, B] (full batches) plus the size of the
-    trailing short batch (0 if none); the layout the native host-fed pipeline consumes."""
+def epoch_tensor(ds: TensorDataset, batch_size: int, shuffle: bool, generator: Optional[torch.Generator] = None):
+    """One epoch as ``x [steps, B, 3, 32, 32]``, ``y [steps, B]`` (the full batches; the layout the
+    native multi-step loops consume) plus the trailing short batch ``(x_tail, y_tail)`` or ``None`` --
+    DataLoader(drop_last=False) semantics."""
     n = len(ds)
     steps = n // batch_size
     perm = torch.randperm(n, generator=generator) if shuffle else torch.arange(n)
@@ -181,4 +181,8 @@ def epoch_tensor(ds: TensorDataset, batch_size: int, shuffle: bool,
     full = perm[: steps * batch_size]
     x = ds.images[full].view(steps, batch_size, 3, 32, 32)
     y = ds.labels[full].view(steps, batch_size)
-    return x, y, n - steps * batch_size
+    tail = None
+    if n > steps * batch_size:
+        rest = perm[steps * batch_size:]
+        tail = (ds.images[rest].contiguous(), ds.labels[rest].contiguous())
+    return x, y, tail

@@ -77,7 +77,7 @@ typedef struct dnnb200_ctl {
   unsigned int ctas_done;
   unsigned int status;
   unsigned int active_mask;
-  unsigned int average_only;
+  unsigned int divisor_override;
 } dnnb200_ctl;
 
 /* params/momentum (and optional grads, may be NULL) are caller-owned flat buffers of
@@ -89,6 +89,8 @@ int dnnb200_engine_attach_group(dnnb200_engine* e, dnnb200_group* g);
 int dnnb200_engine_set_hparams(dnnb200_engine* e, float lr, float mu, void* stream);
 int dnnb200_engine_set_membership(dnnb200_engine* e, unsigned int active_mask, unsigned long long timeout_ns,
                                   void* stream);
+/* 0 = divide the exchanged sum by the number of ranks present (default); n = divide by n */
+int dnnb200_engine_set_divisor(dnnb200_engine* e, unsigned int divisor, void* stream);
 /* zero the momentum buffer (the reference re-creates its optimizer every epoch:
  * data_parallelism_train.py:187) */
 int dnnb200_engine_zero_momentum(dnnb200_engine* e, void* stream);
@@ -108,6 +110,9 @@ int dnnb200_engine_set_trace(dnnb200_engine* e, long long* d_trace);
 /* one optimizer step on a device-resident batch: fwd/bwd kernel + update kernel
  * (reference: the loop body data_parallelism_train.py:195-203) */
 int dnnb200_engine_step(dnnb200_engine* e, const float* x, const int64_t* y, int B, void* stream);
+/* nsteps steps over device-resident batches x[nsteps][B][3][32][32], y[nsteps][B]: one native loop,
+ * no per-step Python (the whole dataset fits in HBM many times over) */
+int dnnb200_engine_train_device(dnnb200_engine* e, const float* x, const int64_t* y, int B, int nsteps, void* stream);
 /* nsteps steps fed from PINNED host memory: per step an async H2D copy of that step's
  * inputs (4-slot device ring on a copy stream), the two kernels, and an async D2H copy of
  * the step's mean loss into h_losses[t] (pinned). Returns after everything is enqueued;

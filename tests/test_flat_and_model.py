@@ -1,0 +1,94 @@
+"""Contracts of the model and its flat storage."""
+import copy
+import re
+from pathlib import Path
+
+import pytest
+import torch
+
+from distributed_neural_network_b200 import Network
+from distributed_neural_network_b200.ops import flat as L
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def test_layout_constants_match_cuda_header():
+    hdr = (ROOT / "csrc" / "layout.h").read_text()
+    vals = {m.group(1): int(m.group(2)) for m in re.finditer(r"constexpr int (k\w+) = (\d+);", hdr)}
+    names = ["kOffW1", "kOffB1", "kOffW2", "kOffB2", "kOffF1W", "kOffF1B", "kOffF2W", "kOffF2B", "kOffF3W", "kOffF3B"]
+    assert [vals[n] for n in names] == list(L.PARAM_OFFSETS.values())
+    assert vals["kFlatNumel"] == L.FLAT_NUMEL and vals["kParamNumel"] == L.PARAM_NUMEL == 62006
+    hdr_c = (ROOT / "include" / "dnnb200.h").read_text()
+    assert f"#define DNNB200_FLAT_NUMEL {L.FLAT_NUMEL}" in hdr_c
+
+
+def test_state_dict_contract():
+    m = Network()
+    sd = m.state_dict()
+    assert list(sd.keys()) == list(L.PARAM_SHAPES.keys())
+    for k, shape in L.PARAM_SHAPES.items():
+        assert tuple(sd[k].shape) == shape and sd[k].dtype == torch.float32
+    assert sum(v.numel() for v in sd.values()) == 62006
+    assert len(list(m.parameters())) == 10
+
+
+def test_parameters_alias_flat_buffer_and_survive_moves():
+    m = Network()
+    assert m.conv1.weight.data_ptr() == m.flat_params.data_ptr()
+    off = L.PARAM_OFFSETS["fc1.weight"]
+    m.flat_params[off] = 123.0
+    assert m.fc1.weight[0, 0].item() == 123.0
+    m2 = copy.deepcopy(m).to("cpu")
+    m2.flat_params[off] = 7.0
+    assert m2.fc1.weight[0, 0].item() == 7.0 and m.fc1.weight[0, 0].item() == 123.0
+    # gradients accumulate into the flat gradient buffer
+    m.zero_grad()
+    m(torch.randn(2, 3, 32, 32)).sum().backward()
+    assert m.flat_grads.abs().sum() > 0
+    assert m.fc3.bias.grad.data_ptr() == m.flat_grads[L.PARAM_OFFSETS["fc3.bias"]:].data_ptr()
+    # padding never receives gradient
+    assert m.flat_grads[~L.real_mask()].abs().sum() == 0
+
+
+def test_pack_unpack_roundtrip():
+    m = Network()
+    flat = L.pack(m.state_dict())
+    assert torch.equal(flat, m.flat_params)
+    sd = L.unpack(flat)
+    m2 = Network()
+    m2.load_state_dict(sd)
+    assert torch.equal(m2.flat_params, m.flat_params)
+
+
+def test_default_init_matches_pytorch_bounds():
+    torch.manual_seed(0)
+    m = Network()
+    for mod, fan_in in ((m.conv1, 75), (m.conv2, 150), (m.fc1, 400), (m.fc2, 120), (m.fc3, 84)):
+        bound = fan_in ** -0.5
+        assert mod.weight.abs().max() <= bound and mod.weight.abs().max() > 0.8 * bound
+        assert mod.bias.abs().max() <= bound
+
+
+def test_forward_matches_reference_network(reference_network_cls):
+    torch.manual_seed(1)
+    ref = reference_network_cls()
+    ours = Network()
+    ours.load_state_dict(ref.state_dict())        # reference checkpoint loads into ours ...
+    ref.load_state_dict(ours.state_dict())        # ... and ours into the reference
+    x = torch.randn(5, 3, 32, 32)
+    assert torch.allclose(ours(x), ref(x), atol=1e-6)
+    # and the gradients agree tensor by tensor
+    y = torch.randint(0, 10, (5,))
+    torch.nn.functional.cross_entropy(ref(x), y).backward()
+    ours.zero_grad()
+    torch.nn.functional.cross_entropy(ours(x), y).backward()
+    for (n1, p1), (n2, p2) in zip(ref.named_parameters(), ours.named_parameters()):
+        assert n1 == n2 and torch.allclose(p1.grad, p2.grad, atol=1e-6)
+
+
+def test_top_level_import_path():
+    import importlib
+    import sys
+    sys.path.insert(0, str(ROOT))
+    mod = importlib.import_module("models.model")
+    assert mod.Network is Network

@@ -1,0 +1,174 @@
+"""Trainer on CPU: single process, and world_size > 1 over gloo through the bundled launcher
+(SURVEY §4 'collective (fake backend)' and 'end-to-end' rows; BASELINE.json configs 1 and 2)."""
+import copy
+import json
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from distributed_neural_network_b200 import Network
+from distributed_neural_network_b200.parallel import bootstrap
+from distributed_neural_network_b200.parallel.membership import FailureSimulator, Membership
+from distributed_neural_network_b200.trainer import TrainConfig, Trainer, reference_global_avg_loss
+from distributed_neural_network_b200.utils import data as D
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def _launch(n, out_dir, mode, **kw):
+    from distributed_neural_network_b200.parallel import launch
+    env = {"OMP_NUM_THREADS": "1"}
+    rc = launch.spawn(n, [sys.executable, str(ROOT / "tests" / "_mp_worker.py"), str(out_dir), mode, json.dumps(kw)],
+                      env_extra=env, gpus=0)
+    assert rc == 0
+    return [torch.load(f"{out_dir}/rank{r}.pt", weights_only=False) for r in range(n)]
+
+
+def test_single_process_matches_plain_pytorch_loop():
+    """Same seed, same batches: the Trainer's CPU path is the reference's loop (single_proc_train.py:57-75)."""
+    cfg = TrainConfig(device="cpu", synthetic=True, train_size=96, test_size=32, epochs=2, batch_size=16, lr=0.05,
+                      sync_mode="none", seed=5, quiet=True, log_dir="/tmp/_dnn_test_log")
+    tr = Trainer(cfg, comm=bootstrap.Comm())
+    ref = copy.deepcopy(tr.model)
+    opt = torch.optim.SGD(ref.parameters(), lr=0.05, momentum=0.9)
+    shard, test = tr.load_data()
+    gen = copy.deepcopy(tr.gen)
+    hist = tr.fit(shard, test)
+    for _ in range(2):
+        for x, y in D.batches(shard, 16, shuffle=True, generator=gen):
+            ref.zero_grad()
+            F.cross_entropy(ref(x), y).backward()
+            opt.step()
+    assert torch.allclose(tr.model.flat_params, ref.flat_params, atol=1e-6)
+    assert len(hist) == 2 and 0 <= hist[-1]["val_acc"] <= 100
+
+
+def test_training_learns_on_synthetic_data():
+    cfg = TrainConfig(device="cpu", synthetic=True, train_size=512, test_size=128, epochs=4, batch_size=16, lr=0.05,
+                      sync_mode="none", seed=0, quiet=True, log_dir="/tmp/_dnn_test_log")
+    tr = Trainer(cfg, comm=bootstrap.Comm())
+    hist = tr.fit()
+    assert hist[-1]["train_loss"] < hist[0]["train_loss"] - 0.3
+    assert hist[-1]["val_acc"] > 50
+
+
+def test_step_allreduce_world2_equals_big_batch(tmp_path):
+    res = _launch(2, tmp_path, "step-allreduce", train_size=128, test_size=32, epochs=1, batch_size=8, lr=0.05, seed=11)
+    assert torch.equal(res[0]["flat"], res[1]["flat"]), "replicas must stay bit-identical"
+    # oracle: one process, batch 16 = the two ranks' batches concatenated, same shuffles
+    cfg = TrainConfig(device="cpu", synthetic=True, train_size=128, test_size=32, epochs=1, batch_size=8, lr=0.05,
+                      seed=11, quiet=True, sync_mode="none", log_dir=str(tmp_path / "l"))
+    torch.manual_seed(11)          # rank 0's seed: its initial weights are broadcast to everyone
+    model = Network()
+    full = D.synthetic(128, seed=0)
+    shards = [D.partition_symmetric(full, r, 2).materialize() for r in range(2)]
+    gens = [torch.Generator().manual_seed(11 + 1000 * r) for r in range(2)]
+    opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9)
+    its = [D.batches(shards[r], 8, True, gens[r]) for r in range(2)]
+    for (x0, y0), (x1, y1) in zip(*its):
+        model.zero_grad()
+        F.cross_entropy(model(torch.cat([x0, x1])), torch.cat([y0, y1])).backward()
+        opt.step()
+    assert torch.allclose(res[0]["flat"], model.flat_params, atol=2e-6)
+
+
+def test_epoch_average_reference_topology_world3(tmp_path):
+    """The reference's algorithm: rank 0 parent, children train contiguous shards with a fresh optimizer,
+    parameters are averaged once per epoch (data_parallelism_train.py:114-121,134-142,185-244)."""
+    res = _launch(3, tmp_path, "epoch-average", reference_topology=True, train_size=96, test_size=32, epochs=2,
+                  batch_size=8, lr=0.05, seed=21, nb_proc=3)
+    for r in (1, 2):
+        assert torch.equal(res[0]["flat"], res[r]["flat"])
+    torch.manual_seed(21)
+    master = Network()
+    full = D.synthetic(96, seed=0)
+    gens = {r: torch.Generator().manual_seed(21 + 1000 * r) for r in (1, 2)}
+    for _ in range(2):
+        kids = []
+        for r in (1, 2):
+            child = copy.deepcopy(master)
+            opt = torch.optim.SGD(child.parameters(), lr=0.05, momentum=0.9)   # new optimizer each epoch (:187)
+            shard = D.partition_dataset(full, r, 3).materialize()
+            for x, y in D.batches(shard, 8, True, gens[r]):
+                child.zero_grad()
+                F.cross_entropy(child(x), y).backward()
+                opt.step()
+            kids.append(child.flat_params.clone())
+        master.flat_params.copy_(sum(kids) / float(len(kids)))                  # :238-240
+    assert torch.allclose(res[0]["flat"], master.flat_params, atol=2e-6)
+    # timing logs: parent file from rank 0, children file from rank 2 (:126-129,143-152)
+    names = sorted(os.listdir(tmp_path / "log"))
+    assert names == ["bs8_log_epochs2_proc3_children.txt", "bs8_log_epochs2_proc3_parent.txt"]
+    assert res[0]["timers"]["training_time"] == 0.0 and res[2]["timers"]["training_time"] > 0.0
+
+
+def test_replication_mode_world3(tmp_path):
+    res = _launch(3, tmp_path, "replication", reference_topology=True, train_size=64, test_size=32, epochs=1,
+                  batch_size=16, lr=0.05, seed=4)
+    assert torch.equal(res[0]["flat"], res[1]["flat"]) and torch.equal(res[1]["flat"], res[2]["flat"])
+    assert res[0]["history"][0]["train_loss"] > 0
+
+
+def test_drop_mode_survivors_continue_world4(tmp_path):
+    """Ranks leave mid-epoch with high probability; nobody hangs, everybody agrees afterwards."""
+    res = _launch(4, tmp_path, "step-allreduce", train_size=256, test_size=32, epochs=3, batch_size=8, lr=0.02,
+                  seed=9, failure_probability=0.6, failure_duration=0.05, failure_mode="drop")
+    h = res[0]["history"]
+    assert len(h) == 3 and h[-1]["membership_epoch"] > 0      # membership actually changed
+    for r in range(1, 4):
+        assert torch.equal(res[0]["flat"], res[r]["flat"])    # returning ranks adopted the survivors' state
+    assert all(torch.isfinite(r["flat"]).all() for r in res)
+
+
+def test_membership_and_failure_simulator():
+    m = Membership(4)
+    assert m.mask == 0b1111 and m.divisor == 4 and m.epoch == 0
+    assert m.leave(2) and m.mask == 0b1011 and m.divisor == 3 and m.epoch == 1
+    assert not m.leave(2) and m.donor() == 0
+    assert m.join(2) and m.epoch == 2 and m.divisor == 4
+    for r in (0, 1, 3):
+        m.leave(r)
+    assert not m.leave(2), "the last member cannot leave"
+    sim = FailureSimulator(1.0, 0.0, "drop", seed=1, rank=3)
+    ev = sim.draw(10)
+    assert ev is not None and ev.rank == 3 and 0 <= ev.at_step < 10
+    assert FailureSimulator(0.0, 1.0, "sleep", seed=1).draw() is None
+    with pytest.raises(ValueError):
+        FailureSimulator(0.1, 1.0, "explode")
+
+
+def test_rank_discovery_from_launcher_environments(monkeypatch):
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "OMPI_COMM_WORLD_RANK", "OMPI_COMM_WORLD_SIZE", "PMI_RANK",
+              "PMI_SIZE", "SLURM_PROCID", "SLURM_NTASKS"):
+        monkeypatch.delenv(k, raising=False)
+    assert bootstrap.discover() == (0, 1, 0)
+    monkeypatch.setenv("OMPI_COMM_WORLD_RANK", "2")
+    monkeypatch.setenv("OMPI_COMM_WORLD_SIZE", "4")
+    monkeypatch.setenv("OMPI_COMM_WORLD_LOCAL_RANK", "1")
+    assert bootstrap.discover() == (2, 4, 1)
+    monkeypatch.setenv("RANK", "3")
+    monkeypatch.setenv("WORLD_SIZE", "8")
+    monkeypatch.setenv("LOCAL_RANK", "3")
+    assert bootstrap.discover() == (3, 8, 3)
+
+
+def test_reference_loss_formula_kept_for_parity():
+    assert reference_global_avg_loss(60.0, 3) == 2.0     # sum of batch losses / (10 keys * children), quirk Q4
+
+
+def test_mpiexec_front_end_runs_the_documented_command_line(tmp_path):
+    out = subprocess.run([str(ROOT / "bin" / "mpiexec"), "-n", "2", sys.executable,
+                          str(ROOT / "data_parallelism_train.py"), "--nb-proc", "2", "--batch-size", "8", "--epochs", "1",
+                          "--synthetic", "--train-size", "64", "--test-size", "16", "--device", "cpu", "--log-dir",
+                          str(tmp_path / "log"), "--save", str(tmp_path / "model.pt")],
+                         capture_output=True, text=True, cwd=ROOT, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert "Starting epoch  0" in out.stdout and "Validation loss of updated master model" in out.stdout
+    assert (tmp_path / "log" / "bs8_log_epochs1_proc2_parent.txt").exists()
+    sd = torch.load(tmp_path / "model.pt", weights_only=True)
+    assert len(sd) == 10
