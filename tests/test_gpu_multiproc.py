@@ -1,0 +1,60 @@
+"""Real multi-process, multi-GPU path: CUDA-IPC peer group + fused exchange, one process per GPU.
+Needs at least 2 GPUs (`gpurun --gpus 2`); ranks sharing ONE GPU must never spin on each other."""
+import json
+import sys
+from pathlib import Path
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parent.parent
+
+needs2 = pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+
+
+def _launch(n, out_dir, mode, **kw):
+    from distributed_neural_network_b200.parallel import launch
+    kw["device"] = "cuda"
+    rc = launch.spawn(n, [sys.executable, str(ROOT / "tests" / "_mp_worker.py"), str(out_dir), mode, json.dumps(kw)])
+    assert rc == 0
+    return [torch.load(f"{out_dir}/rank{r}.pt", weights_only=False) for r in range(n)]
+
+
+@needs2
+def test_ipc_step_allreduce_replicas_identical_and_match_cpu_run(tmp_path):
+    n = min(torch.cuda.device_count(), 8)
+    kw = dict(train_size=64 * n, test_size=32, epochs=2, batch_size=8, lr=0.05, seed=11)
+    gpu = _launch(n, tmp_path / "gpu", "step-allreduce", **kw)
+    for r in range(1, n):
+        assert torch.equal(gpu[0]["flat"], gpu[r]["flat"]), f"rank {r} is not bit-identical to rank 0"
+    # the same run on CPU over gloo (same seeds => same shuffles and initial weights)
+    from distributed_neural_network_b200.parallel import launch
+    (tmp_path / "cpu").mkdir()
+    kw_cpu = dict(kw, device="cpu")
+    rc = launch.spawn(n, [sys.executable, str(ROOT / "tests" / "_mp_worker.py"), str(tmp_path / "cpu"),
+                          "step-allreduce", json.dumps(kw_cpu)], env_extra={"OMP_NUM_THREADS": "1"}, gpus=0)
+    assert rc == 0
+    cpu = torch.load(tmp_path / "cpu" / "rank0.pt", weights_only=False)
+    rel = ((gpu[0]["flat"] - cpu["flat"]).abs().max() / cpu["flat"].abs().max()).item()
+    assert rel < 1e-4, rel
+
+
+@needs2
+def test_ipc_epoch_average_reference_topology(tmp_path):
+    n = min(torch.cuda.device_count(), 4)
+    res = _launch(n, tmp_path, "epoch-average", reference_topology=True, train_size=96, test_size=32, epochs=2,
+                  batch_size=8, lr=0.05, seed=21, nb_proc=n)
+    for r in range(1, n):
+        assert torch.equal(res[0]["flat"], res[r]["flat"])
+    assert res[0]["timers"]["training_time"] == 0.0     # the parent never trains
+
+
+@needs2
+def test_ipc_drop_mode_survivors_continue(tmp_path):
+    n = min(torch.cuda.device_count(), 8)
+    res = _launch(n, tmp_path, "step-allreduce", train_size=128 * n, test_size=32, epochs=3, batch_size=8, lr=0.02,
+                  seed=9, failure_probability=0.5, failure_duration=0.05, failure_mode="drop", peer_timeout_s=20.0)
+    assert res[0]["history"][-1]["membership_epoch"] > 0
+    for r in range(1, n):
+        assert torch.equal(res[0]["flat"], res[r]["flat"])
