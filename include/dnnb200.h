@@ -129,6 +129,25 @@ int dnnb200_engine_eval(dnnb200_engine* e, const float* x, const int64_t* y, int
 int dnnb200_engine_grad_only(dnnb200_engine* e, const float* x, const int64_t* y, int B, float* grads_out,
                              float* h_loss, void* stream);
 
+/* (No counterpart in the reference: it has no native code and no notion of a memory budget.)
+ * Batch gradient WITHOUT any allocation, for callers that may not call cudaMalloc: processes whose
+ * device memory is fully owned by another allocator (a server that reserved the GPU up front, a
+ * framework's caching allocator at its cap), and latency-critical loops or foreign-runtime callbacks
+ * where cudaMalloc/cudaFree are ruled out because they take driver locks and can synchronise the device.
+ * Same math as dnnb200_engine_grad_only, but the per-image scratch lives in a fixed array inside the
+ * library image (DNNB200_NOALLOC_SCRATCH_BYTES on every GPU that loads the library, until exit).
+ *   params [DNNB200_FLAT_NUMEL], x [B,3,32,32], y [B] int64: inputs;  grads_out [DNNB200_FLAT_NUMEL]:
+ *   d(mean loss)/d(params), zeros in the alignment gaps;  loss_out [1]: mean loss (may be NULL).
+ * Limits and rules: 1 <= B <= DNNB200_NOALLOC_MAX_BATCH, otherwise DNNB200_ERR_ARG and nothing is
+ * launched. All calls on one device share the array, so calls that can overlap on the GPU race:
+ * keep them on one stream or order them yourself. Nothing in the array needs clearing between calls.
+ * The FIRST call on each device resolves the array's device address (cudaGetSymbolAddress); make that
+ * call at start-up, before any stream capture begins. Calls cudaMalloc/cudaFree/torch never. */
+#define DNNB200_NOALLOC_MAX_BATCH 64
+#define DNNB200_NOALLOC_SCRATCH_BYTES 967168
+int dnnb200_batch_grad_noalloc(const float* params, const float* x, const int64_t* y, int B, float* grads_out,
+                               float* loss_out, void* stream);
+
 /* peer-memory all-reduce of a flat vector (n % 4 == 0, n <= FLAT_NUMEL).
  * mode 0: out = mean(in); mode 1: fused SGD-momentum on the engine's params with g = mean(in)
  * (out may be NULL). two_shot selects the reduce-scatter/all-gather variant. */
