@@ -61,7 +61,8 @@ __device__ __forceinline__ void finish(const RankCtx& cx, const ArParams& prm, i
   if (prm.out[vr]) *reinterpret_cast<float4*>(prm.out[vr] + i) = g;
 }
 
-__global__ void __launch_bounds__(kArThreads)
+template <bool kEmulated>  // see update_kernel: emulated ranks need 8 x 122 co-resident CTAs
+__global__ void __launch_bounds__(kArThreads, kEmulated ? 8 : 1)
 allreduce_kernel(const RankCtx* __restrict__ ctxs, const ArParams prm) {
   __shared__ ExchangeShared xsh;
   __shared__ unsigned int s_ok;
@@ -197,9 +198,9 @@ int launch_allreduce(const RankCtx* d_ctxs, int n_virtual_ranks, const float* co
   dim3 grid((n + kSlice - 1) / kSlice, n_virtual_ranks);
   if (n_virtual_ranks > 1) {
     void* args[] = {(void*)&d_ctxs, (void*)&prm};
-    DNN_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)allreduce_kernel, grid, dim3(kArThreads), args, 0, stream));
+    DNN_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)allreduce_kernel<true>, grid, dim3(kArThreads), args, 0, stream));
   } else {
-    allreduce_kernel<<<grid, kArThreads, 0, stream>>>(d_ctxs, prm);
+    allreduce_kernel<false><<<grid, kArThreads, 0, stream>>>(d_ctxs, prm);
     DNN_CUDA_CHECK(cudaGetLastError());
   }
   return kOk;

@@ -5,16 +5,18 @@
 // SURVEY §2.5) with direct NVLink stores into every peer's receive area:
 //
 //   for every slice s of the flat vector, the CTA that owns s on rank r
-//     1. stores its local values into recv[p][parity][r][s] of every peer p  (remote st over NVLink)
-//     2. __syncthreads, fence.sys, st.release.sys flags[p][r][s] = seq        (publish)
-//     3. spins on its OWN flags[r][p][s] >= seq for every peer p              (local ld.acquire.sys)
-//     4. sums the W contributions in rank order 0..W-1 (its own from registers)
+//     1. stores its local values into recv[p][parity][r][s] of every peer p as 16-byte
+//        LL lines {value, seq, value, seq}                                   (remote st over NVLink)
+//     2. polls its OWN recv[r][parity][p][s] until the lines of every peer p carry `seq`
+//        (local ld.volatile; the data IS the flag: no fence, no second round trip)
+//     3. sums the W contributions in rank order 0..W-1 (its own from registers)
 //        so every rank gets bit-identical results
 //
 // There is no barrier across slices or CTAs: slice s is exchanged while other
 // CTAs still compute their wgrad tiles. Two parities of the receive area make the
-// pushes of step t+1 safe against a slow reader of step t; flags carry a
-// monotonically increasing sequence number and are never reset.
+// pushes of step t+1 safe against a slow reader of step t; sequence numbers only
+// grow and nothing is ever reset. (A first version used plain stores + fence.sys +
+// a release flag per slice: ~9 us per step at 2 GPUs; see profiles/.)
 //
 // Membership (north-star item 3): a rank that leaves writes a
 // "leave marker" L (the first sequence number it will not take part in) into
@@ -38,7 +40,29 @@ __device__ __forceinline__ bool seq_reached(unsigned int v, unsigned int seq) {
   return v != 0u && (int)(v - seq) >= 0;
 }
 
-// Values: each thread owns kVec consecutive floats at flat index `i` (16B/8B aligned).
+// ---- LL ("low latency") lines: 16 bytes = {value0, seq, value1, seq} -------------------------
+// A 16-byte store is delivered as two atomic 8-byte halves, so a reader that sees BOTH sequence
+// words equal to `seq` also sees both values. Data and "it has arrived" travel in the same store:
+// no fence and no separate flag round trip on the critical path (the idea of NCCL's LL protocol).
+__device__ __forceinline__ void st_ll(float* line, float a, float b, unsigned int seq) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(line), "r"(__float_as_uint(a)), "r"(seq),
+               "r"(__float_as_uint(b)), "r"(seq)
+               : "memory");
+}
+__device__ __forceinline__ bool ld_ll(const float* line, unsigned int seq, float* a, float* b) {
+  unsigned int x, f0, y, f1;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x), "=r"(f0), "=r"(y), "=r"(f1) : "l"(line)
+               : "memory");
+  *a = __uint_as_float(x);
+  *b = __uint_as_float(y);
+  return f0 == seq && f1 == seq;
+}
+
+// Receive area of one rank, LL layout: [2 parities][world][kFlatNumel] VALUES, each pair of values
+// occupying one 16-byte line => 2 * kFlatNumel floats per (parity, source).
+constexpr size_t kLLStride = 2 * (size_t)kFlatNumel;
+
+// Values: each thread owns kVec consecutive floats at flat index `i` (kVec = 2 or 4, i % kVec == 0).
 // Returns the sum over present ranks in rank order; *n_present gets the divisor.
 template <int kVec>
 __device__ __forceinline__ void exchange_slice(const RankCtx& cx, ExchangeShared* sh, int slice,
@@ -49,89 +73,101 @@ __device__ __forceinline__ void exchange_slice(const RankCtx& cx, ExchangeShared
   const int tid = threadIdx.x;
   const unsigned int parity = seq & 1u;
   const unsigned int configured = cx.ctl->active_mask;
-  unsigned int* my_flags = cx.flags[rank];
+  const unsigned int* my_flags = cx.flags[rank];
 
-  // 1. push my values to every configured peer (departed peers keep their memory mapped,
-  //    so a late store to them is harmless and saves a flag read here)
+  // 1. push my values to every configured peer: one 16-byte LL line per pair of floats.
+  //    (Departed peers keep their memory mapped, so a late store to them is harmless.)
   if (in_range) {
     for (int p = 0; p < world; ++p) {
       if (p == rank || !((configured >> p) & 1u)) continue;
-      float* dst = cx.recv[p] + ((size_t)(parity * world + rank) * kFlatNumel + i);
-      if (kVec == 4) {
-        *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
-      } else {
-        *reinterpret_cast<float2*>(dst) = make_float2(v[0], v[1]);
-      }
+      float* dst = cx.recv[p] + ((size_t)(parity * world + rank) * kLLStride + 2 * (size_t)i);
+#pragma unroll
+      for (int k = 0; k < kVec; k += 2) st_ll(dst + 2 * k, v[k], v[k + 1], seq);
     }
   }
-  __syncthreads();  // all stores of this CTA are issued ...
-  if (tid < world && tid != rank && ((configured >> tid) & 1u)) {
-    __threadfence_system();  // ... and ordered before the flag, cumulatively, at system scope
-    st_release_sys(cx.flags[tid] + rank * kFlagRow + slice, seq);
-  }
 
-  // 2. wait for every configured peer's slice (or its leave marker)
-  if (tid == 0) sh->present = 0u;
+  // 2. gather: poll my own receive area until each peer's line carries this step's sequence number.
+  //    While nothing arrives, look at the peer's leave marker and at the clock.
+  if (tid == 0) sh->present = configured;
   __syncthreads();
-  if (tid < world && ((configured >> tid) & 1u)) {
-    bool here = false;
-    if (tid == rank) {
-      here = true;
-    } else {
-      const unsigned int* f = my_flags + tid * kFlagRow + slice;
-      const unsigned int* lv = my_flags + tid * kFlagRow + kLeaveSlot;
-      const unsigned long long tmo = cx.ctl->timeout_ns;
-      unsigned long long t0 = 0;
+  float acc[kVec];
+#pragma unroll
+  for (int k = 0; k < kVec; ++k) acc[k] = 0.f;
+  unsigned int absent = 0u;
+  const float* my_recv = cx.recv[rank];
+  const unsigned long long tmo = cx.ctl->timeout_ns;
+  for (int p = 0; p < world; ++p) {
+    if (!((configured >> p) & 1u)) continue;
+    if (p == rank) {
+#pragma unroll
+      for (int k = 0; k < kVec; ++k) acc[k] += v[k];
+      continue;
+    }
+    if (!in_range) continue;
+    const float* src = my_recv + ((size_t)(parity * world + p) * kLLStride + 2 * (size_t)i);
+    float t[kVec];
+    bool got = true;
+#pragma unroll
+    for (int k = 0; k < kVec; k += 2) {
       unsigned int spins = 0;
-      for (;;) {
-        if (seq_reached(ld_acquire_sys(f), seq)) { here = true; break; }
-        const unsigned int l = ld_acquire_sys(lv);
+      unsigned long long t0 = 0;
+      while (!ld_ll(src + 2 * k, seq, &t[k], &t[k + 1])) {
+        if ((++spins & 0xffu) != 0u) continue;
+        // a peer that left pushed every line of its last step before it wrote the marker
+        const unsigned int l = ld_acquire_sys(my_flags + p * kFlagRow + kLeaveSlot);
         if (l != 0u && (int)(seq - l) >= 0) {
-          // the marker may have overtaken nothing: p pushes every slice of its last step
-          // before it writes the marker, so one more look at the flag settles it
-          here = seq_reached(ld_acquire_sys(f), seq);
-          break;
+          got = ld_ll(src + 2 * k, seq, &t[k], &t[k + 1]);
+          if (!got) break;
+          continue;
         }
-        if (tmo != 0ull && (++spins & 0x3ffu) == 0u) {
+        if (tmo != 0ull) {
           const unsigned long long now = globaltimer_ns();
           if (t0 == 0ull) t0 = now;
           else if (now - t0 > tmo) {
-            atomicOr(&cx.ctl->status, kStatusTimeout | (1u << (8 + tid)));
+            atomicOr(&cx.ctl->status, kStatusTimeout | (1u << (8 + p)));
+            got = false;
             break;
           }
         }
       }
+      if (!got) break;
     }
-    if (here) atomicOr(&sh->present, 1u << tid);
+    if (got) {
+#pragma unroll
+      for (int k = 0; k < kVec; ++k) acc[k] += t[k];
+    } else {
+      absent |= 1u << p;
+    }
   }
+  // every thread of the CTA must agree on who is present (a rank pushes all lines of a step or none,
+  // so disagreement can only come from a timeout racing with late data: take the union of "absent")
+  if (absent) atomicAnd(&sh->present, ~absent);
   __syncthreads();
   const unsigned int present = sh->present;
-
-  // 3. rank-ordered sum; peers' data was written by another GPU -> read through L2
-  float acc[kVec];
+  if (present == configured) {  // the normal case: everybody configured has delivered
 #pragma unroll
-  for (int k = 0; k < kVec; ++k) acc[k] = 0.f;
-  if (in_range) {
-    const float* my_recv = cx.recv[rank];
+    for (int k = 0; k < kVec; ++k) v[k] = acc[k];
+  } else if (in_range) {
+    // somebody in this CTA declared a peer absent: redo the sum without it, in rank order
+#pragma unroll
+    for (int k = 0; k < kVec; ++k) acc[k] = 0.f;
     for (int p = 0; p < world; ++p) {
       if (!((present >> p) & 1u)) continue;
       if (p == rank) {
 #pragma unroll
         for (int k = 0; k < kVec; ++k) acc[k] += v[k];
       } else {
-        const float* src = my_recv + ((size_t)(parity * world + p) * kFlatNumel + i);
-        if (kVec == 4) {
-          const float4 t = ld_cg_f4(reinterpret_cast<const float4*>(src));
-          acc[0] += t.x; acc[1] += t.y; acc[2] += t.z; acc[3] += t.w;
-        } else {
-          const float2 t = __ldcg(reinterpret_cast<const float2*>(src));
-          acc[0] += t.x; acc[1] += t.y;
-        }
+        const float* src = my_recv + ((size_t)(parity * world + p) * kLLStride + 2 * (size_t)i);
+        float t[kVec];
+#pragma unroll
+        for (int k = 0; k < kVec; k += 2) (void)ld_ll(src + 2 * k, seq, &t[k], &t[k + 1]);
+#pragma unroll
+        for (int k = 0; k < kVec; ++k) acc[k] += t[k];
       }
     }
-  }
 #pragma unroll
-  for (int k = 0; k < kVec; ++k) v[k] = acc[k];
+    for (int k = 0; k < kVec; ++k) v[k] = acc[k];
+  }
   *n_present = __popc(present);
 }
 

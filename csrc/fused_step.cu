@@ -566,7 +566,10 @@ __device__ __forceinline__ float2 local_grad2(const RankCtx& cx, int i, int B, i
   return g;
 }
 
-__global__ void __launch_bounds__(kUpdThreads)
+// kEmulated: several ranks emulated on one GPU wait on each other inside ONE cooperative launch, so
+// 8 x 122 CTAs must be co-resident (7 per SM => 36 registers). Production (one rank per GPU) is unconstrained.
+template <bool kEmulated>
+__global__ void __launch_bounds__(kUpdThreads, kEmulated ? 7 : 1)
 update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slot, int flags) {
   __shared__ ExchangeShared xsh;
   const RankCtx& cx = ctxs[blockIdx.y];
@@ -687,9 +690,9 @@ int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int n_part1
   if (n_virtual_ranks > 1) {
     // ranks emulated on ONE device wait on each other: every CTA must be resident
     void* args[] = {(void*)&d_ctxs, (void*)&B, (void*)&n_part1, (void*)&loss_slot, (void*)&flags};
-    DNN_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)update_kernel, grid, dim3(kUpdThreads), args, 0, stream));
+    DNN_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)update_kernel<true>, grid, dim3(kUpdThreads), args, 0, stream));
   } else {
-    update_kernel<<<grid, kUpdThreads, 0, stream>>>(d_ctxs, B, n_part1, loss_slot, flags);
+    update_kernel<false><<<grid, kUpdThreads, 0, stream>>>(d_ctxs, B, n_part1, loss_slot, flags);
     DNN_CUDA_CHECK(cudaGetLastError());
   }
   return kOk;

@@ -140,7 +140,7 @@ static int group_create(int rank, int world, dnnb200_group** out, void* h_handle
   g->rank = rank;
   g->world = world;
   DNN_CUDA_CHECK(cudaGetDevice(&g->device));
-  g->bytes = kFlagBytes + (size_t)2 * world * kFlatNumel * sizeof(float);
+  g->bytes = kFlagBytes + (size_t)2 * world * 2 * kFlatNumel * sizeof(float);  // LL lines: 2 floats per value
   DNN_CUDA_CHECK(cudaMalloc(&g->base, g->bytes));
   DNN_CUDA_CHECK(cudaMemset(g->base, 0, g->bytes));
   DNN_CUDA_CHECK(cudaDeviceSynchronize());

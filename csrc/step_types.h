@@ -13,8 +13,9 @@ constexpr int kFlagRow = 128;
 constexpr int kLeaveSlot = kNumSlices;  // 122
 static_assert(kLeaveSlot < kFlagRow, "flag row too small");
 
-// Receive area of one rank: [2 parities][world][kFlatNumel] floats. Parity = seq & 1,
-// so the pushes of step t+1 never land on data a slow reader still sums for step t.
+// Receive area of one rank: [2 parities][world][kFlatNumel] values stored as 16-byte LL lines
+// {value, seq, value, seq} (exchange.cuh), i.e. 2*kFlatNumel floats per (parity, source).
+// Parity = seq & 1, so the pushes of step t+1 never land on data a slow reader still sums for step t.
 
 enum StepStatus : unsigned int {
   kStatusOk = 0,

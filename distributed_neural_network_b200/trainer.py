@@ -277,6 +277,16 @@ class Trainer:
             self.dropped = True
         return total, nb
 
+    def _align_sequence(self) -> None:
+        """Ranks that took a different number of local steps (or none: the parent) carry different
+        exchange sequence numbers; agree on the largest one before the next collective exchange."""
+        if self.engine is None or self.world == 1:
+            return
+        steps = self.comm.allgather(int(self.engine.read_ctl().step))
+        self.engine.rejoin(max(steps))
+        self._sync()
+        self.comm.barrier()
+
     # ------------------------------------------------------------------ parameter averaging (R1)
     @torch.no_grad()
     def average_parameters(self) -> None:
@@ -285,6 +295,7 @@ class Trainer:
             return
         n_tr = len(self.membership.active)
         if self.engine is not None:
+            self._align_sequence()
             contrib = self.model.flat_params if (self.is_trainer and self.rank in self.membership.active) \
                 else torch.zeros_like(self.model.flat_params)
             full = (1 << self.world) - 1
@@ -395,7 +406,10 @@ class Trainer:
                     time.sleep(ev.duration)
                     self._log(f"Process {self.rank} woke up!")
 
-            if cfg.sync_mode in ("epoch-average", "replication") and self.world > 1:
+            # parity modes average once per epoch; with a non-training parent the parent also needs the
+            # trainers' (identical) weights in step-allreduce mode before it can evaluate
+            if (cfg.sync_mode in ("epoch-average", "replication") or
+                    (cfg.sync_mode == "step-allreduce" and cfg.reference_topology)) and self.world > 1:
                 if self.rank == 0:
                     self._log("* Averaging models...")
                 tname = "mpi_communication_time_parent" if self.rank == 0 else "mpi_communication_time_children"
