@@ -53,6 +53,9 @@ int launch_linear_bwd(const float*, const float*, const float*, const float*, fl
                       int, cudaStream_t);
 int launch_softmax_xent(const float*, const long long*, float*, float*, int, int, cudaStream_t);
 int launch_sgd_momentum(float*, const float*, float*, int, float, float, int, float, cudaStream_t);
+int launch_tc_conv_relu_pool_fwd(const float*, const float*, const float*, float*, unsigned char*, int, int, int, int,
+                                 int, cudaStream_t);
+int launch_tc_gemm_probe(const float*, const float*, float*, int, cudaStream_t);
 
 // ---- tiny control kernels ---------------------------------------------------
 __global__ void ctl_set_hparams_kernel(StepCtl* c, float lr, float mu) { c->lr = lr; c->mu = mu; }
@@ -247,6 +250,14 @@ int dnnb200_conv_relu_pool_bwd(const float* x, const float* w, const float* y, c
                                float* dx, float* dw, float* db, int N, int Ci, int H, int W, int Co, void* stream) {
   DNN_ARG_CHECK(N > 0 && Ci > 0 && Co > 0, "conv_relu_pool_bwd: bad shape");
   return launch_conv_relu_pool_bwd(x, w, y, idx, dy, dx, dw, db, N, Ci, H, W, Co, (cudaStream_t)stream);
+}
+int dnnb200_tc_conv_relu_pool_fwd(const float* x, const float* w, const float* b, float* y, uint8_t* idx, int N,
+                                  int Ci, int H, int W, int Co, void* stream) {
+  DNN_ARG_CHECK(N > 0, "tc_conv_relu_pool_fwd: empty batch");
+  return launch_tc_conv_relu_pool_fwd(x, w, b, y, idx, N, Ci, H, W, Co, (cudaStream_t)stream);
+}
+int dnnb200_tc_gemm_probe(const float* A, const float* B, float* D, int K, void* stream) {
+  return launch_tc_gemm_probe(A, B, D, K, (cudaStream_t)stream);
 }
 int dnnb200_linear_fwd(const float* x, const float* w, const float* b, float* y, int N, int M, int K, int relu,
                        void* stream) {

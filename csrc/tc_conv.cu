@@ -1,0 +1,281 @@
+// conv5x5 + bias + ReLU + maxpool2x2 forward as an implicit GEMM on the 5th-generation tensor
+// cores (tcgen05.mma kind::tf32, accumulators in TMEM), for both conv layers of the CNN
+// (reference: models/model.py:21-22; kernels K1-K6 of SURVEY §2.7).
+//
+// The im2col matrix is never built. The image is kept in shared memory as NHWC with the channels
+// padded to groups of 4 floats, so one pixel of one channel group is exactly one 16-byte K-chunk
+// of a K-major UMMA operand. With the GEMM row index m taken as the LINEAR pixel index of the
+// input plane (m = oh*W_in + ow), the A operand of filter tap (kh,kw) is the same plane shifted by
+// (kh*W_in + kw) pixels: 8 consecutive pixels are 8 rows 16 bytes apart (a core matrix), groups of
+// 8 pixels are 128 bytes apart (SBO), and the two K-chunks of one MMA are two taps (conv1) or the two
+// channel groups of one tap (conv2), LBO apart. Every MMA therefore just gets a different START
+// ADDRESS into the same plane -- the shared-memory descriptor does the im2col. Rows with
+// ow >= W_out are computed on wrapped pixels and discarded in the epilogue (12.5% / 49% of the tile
+// for conv1 / conv2; the tensor pipe is nowhere near the bottleneck at these sizes).
+//
+//   GEMM per image   conv1: M = 896 (7 tiles of 128), N = 16 (6 used), K = 26 chunks x 4 = 104
+//                    conv2: M = 256 (2 tiles),        N = 16,          K = 50 chunks x 4 = 200
+//
+// Pipeline per CTA (persistent over images): TMA bulk copy of the CHW image -> re-layout to NHWC4
+// planes -> one thread issues all tcgen05.mma of the image -> tcgen05.commit -> mbarrier ->
+// 4 warps tcgen05.ld their 32 TMEM lanes -> bias+ReLU -> shared tile -> 2x2 max/argmax -> global.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace dnnb200 {
+
+using namespace tc;
+
+// ------------------------------------------------------------------------------------------
+// probe: D[128][16] = A[128][K] * B[16][K]^T with every descriptor field exercised the way the
+// conv kernel uses them (development aid + unit test of the encodings)
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+tc_gemm_probe_kernel(const float* __restrict__ A, const float* __restrict__ B, float* __restrict__ D, int K) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int kc = K / 4;                               // K-chunks of 16 bytes
+  float* sA = reinterpret_cast<float*>(smem);         // [kc][16 groups][8 rows][4]
+  float* sB = sA + (size_t)kc * 128 * 4;              // [kc][2 groups][8 rows][4]
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < 128 * K; i += 128) {
+    const int m = i / K, k = i - m * K;
+    sA[((size_t)(k >> 2) * 16 + (m >> 3)) * 32 + (m & 7) * 4 + (k & 3)] = A[i];
+  }
+  for (int i = tid; i < 16 * K; i += 128) {
+    const int n = i / K, k = i - n * K;
+    sB[((size_t)(k >> 2) * 2 + (n >> 3)) * 32 + (n & 7) * 4 + (k & 3)] = B[i];
+  }
+  if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+  if (warp == 0) tmem_alloc<32>(&tmem_slot);
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  if (tid == 0) {
+    const uint32_t idesc = idesc_tf32(128, 16);
+    for (int ks = 0; ks < K / 8; ++ks) {
+      const uint64_t ad = smem_desc_nosw(smem_u32(sA) + (uint32_t)(2 * ks) * 16 * 128, 16 * 128, 128);
+      const uint64_t bd = smem_desc_nosw(smem_u32(sB) + (uint32_t)(2 * ks) * 2 * 128, 2 * 128, 128);
+      mma_tf32(tmem, ad, bd, idesc, ks > 0);
+    }
+    mma_commit(&bar);
+  }
+  mbar_wait(&bar, 0);
+  tc_fence_after();
+  float v[16];
+  tmem_ld16(tmem + ((uint32_t)(warp * 32) << 16), v);
+#pragma unroll
+  for (int n = 0; n < 16; ++n) D[(warp * 32 + lane) * 16 + n] = v[n];
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_free<32>(tmem);
+}
+
+// ------------------------------------------------------------------------------------------
+// the conv kernel
+// ------------------------------------------------------------------------------------------
+template <int CI, int HIN, int CO>
+struct ConvCfg {
+  static constexpr int G = (CI + 3) / 4;                       // channel groups of 4 floats (one K-chunk each)
+  static constexpr int WIN = HIN;
+  static constexpr int HOUT = HIN - 4, WOUT = HIN - 4, HP = HOUT / 2;
+  static constexpr int P = HIN * WIN;                          // pixels of one input plane
+  static constexpr int MEXT = (HOUT - 1) * WIN + WOUT;         // GEMM rows that contain a valid output
+  static constexpr int TILES = (MEXT + 127) / 128;
+  static constexpr int PLANE_PIX = ((TILES * 128 + 4 * WIN + 4 + 8 + 7) / 8) * 8;  // + reach of the last tap
+  static constexpr int CHUNKS = 25 * G;                        // real K-chunks
+  static constexpr int NMMA = (CHUNKS + 1) / 2;                // MMAs per tile (K = 2 chunks each)
+  static constexpr int TMEM_COLS = TILES * 16 <= 32 ? 32 : (TILES * 16 <= 64 ? 64 : 128);
+  static constexpr int STAGE_FLOATS = CI * P;
+  static constexpr size_t kPlaneBytes = (size_t)PLANE_PIX * 16;
+  static constexpr size_t kBBytes = (size_t)2 * (2 * NMMA) * 128;   // [2 n-groups][2*NMMA chunks][8][4] floats
+  static constexpr size_t kSmemBytes = (size_t)STAGE_FLOATS * 4 + G * kPlaneBytes + kBBytes + (size_t)CO * HOUT * WOUT * 4 + 64;
+  static_assert(TILES * 16 <= 128, "TMEM budget");
+  static_assert((STAGE_FLOATS * 4) % 16 == 0, "bulk copy granularity");
+};
+
+template <int CI, int HIN, int CO>
+__global__ void __launch_bounds__(128)
+tc_conv_relu_pool_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+                             float* __restrict__ y, unsigned char* __restrict__ idx, int N) {
+  using C = ConvCfg<CI, HIN, CO>;
+  extern __shared__ __align__(128) unsigned char smem[];
+  float* stage = reinterpret_cast<float*>(smem);                                  // CHW image as it is in global
+  float* planes = stage + C::STAGE_FLOATS;                                        // G planes of NHWC4 pixels
+  float* sB = planes + (size_t)C::G * C::PLANE_PIX * 4;                           // weights, canonical K-major
+  float* cbuf = sB + C::kBBytes / 4;                                              // relu(conv) of the image [CO][HOUT][WOUT]
+  float* sbias = cbuf + CO * C::HOUT * C::WOUT;
+  __shared__ uint64_t bar_img, bar_mma;
+  __shared__ uint32_t tmem_slot;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  if (tid == 0) { mbar_init(&bar_img, 1); mbar_init(&bar_mma, 1); mbar_fence_init(); }
+  if (warp == 0) tmem_alloc<C::TMEM_COLS>(&tmem_slot);
+  __syncthreads();
+  int img = blockIdx.x;
+  if (tid == 0 && img < N) {
+    mbar_expect_tx(&bar_img, C::STAGE_FLOATS * 4);
+    bulk_g2s(stage, x + (size_t)img * C::STAGE_FLOATS, C::STAGE_FLOATS * 4, &bar_img);
+  }
+  // weights -> canonical no-swizzle K-major B operand; zero the planes once (their padding stays zero)
+  for (int i = tid; i < (int)(C::kBBytes / 4); i += 128) {
+    const int c = i & 3, nr = (i >> 2) & 7, q = (i >> 5) % (2 * C::NMMA), ng = (i >> 5) / (2 * C::NMMA);
+    const int n = ng * 8 + nr;
+    float v = 0.f;
+    if (n < CO && q < C::CHUNKS) {
+      const int tap = q / C::G, ch = (q % C::G) * 4 + c;
+      if (ch < CI) v = __ldg(w + ((size_t)n * CI + ch) * 25 + tap);
+    }
+    sB[i] = v;
+  }
+  for (int i = tid; i < C::G * C::PLANE_PIX * 4; i += 128) planes[i] = 0.f;
+  if (tid < 16) sbias[tid] = tid < CO ? __ldg(b + tid) : 0.f;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  constexpr uint32_t kIdesc = idesc_tf32(128, 16);
+  uint32_t phase = 0;
+
+  for (; img < N; img += gridDim.x) {
+    mbar_wait(&bar_img, phase);
+    // ---- CHW -> NHWC4 planes (one 16-byte pixel per channel group) ----
+    for (int p = tid; p < C::P; p += 128) {
+#pragma unroll
+      for (int g = 0; g < C::G; ++g) {
+        float4 v;
+        v.x = stage[(g * 4 + 0) * C::P + p];
+        v.y = (g * 4 + 1 < CI) ? stage[(g * 4 + 1) * C::P + p] : 0.f;
+        v.z = (g * 4 + 2 < CI) ? stage[(g * 4 + 2) * C::P + p] : 0.f;
+        v.w = (g * 4 + 3 < CI) ? stage[(g * 4 + 3) * C::P + p] : 0.f;
+        reinterpret_cast<float4*>(planes)[(size_t)g * C::PLANE_PIX + p] = v;
+      }
+    }
+    fence_proxy_async();   // the planes were written with st.shared; the tensor core reads them through the async proxy
+    __syncthreads();
+    if (tid == 0) {
+      if (img + (int)gridDim.x < N) {  // staging is free again: prefetch the next image under the MMAs
+        mbar_expect_tx(&bar_img, C::STAGE_FLOATS * 4);
+        bulk_g2s(stage, x + (size_t)(img + gridDim.x) * C::STAGE_FLOATS, C::STAGE_FLOATS * 4, &bar_img);
+      }
+      const uint32_t a0 = smem_u32(planes), b0 = smem_u32(sB);
+#pragma unroll 1
+      for (int t = 0; t < C::TILES; ++t) {
+#pragma unroll 1
+        for (int j = 0; j < C::NMMA; ++j) {
+          uint32_t a_start, lbo;
+          if (C::G == 1) {            // K-chunks = taps 2j and 2j+1 of the single plane
+            const int t0 = 2 * j, t1 = 2 * j + 1;
+            const int off0 = (t0 / 5) * C::WIN + (t0 % 5);
+            const int off1 = t1 < 25 ? (t1 / 5) * C::WIN + (t1 % 5) : off0 + 1;   // chunk 25 does not exist: B is zero there
+            a_start = a0 + (uint32_t)(t * 128 + off0) * 16;
+            lbo = (uint32_t)(off1 - off0) * 16;
+          } else {                    // K-chunks = the two channel groups of tap j
+            const int off0 = (j / 5) * C::WIN + (j % 5);
+            a_start = a0 + (uint32_t)(t * 128 + off0) * 16;
+            lbo = (uint32_t)C::kPlaneBytes;
+          }
+          const uint64_t ad = smem_desc_nosw(a_start, lbo, 128);
+          const uint64_t bd = smem_desc_nosw(b0 + (uint32_t)(2 * j) * 128, 128, (uint32_t)(2 * C::NMMA) * 128);
+          mma_tf32(tmem + (uint32_t)t * 16, ad, bd, kIdesc, j > 0);
+        }
+      }
+      mma_commit(&bar_mma);
+    }
+    mbar_wait(&bar_mma, phase);
+    tc_fence_after();
+    // ---- epilogue 1: TMEM -> registers -> bias + ReLU -> shared [CO][HOUT][WOUT] ----
+#pragma unroll 1
+    for (int t = 0; t < C::TILES; ++t) {
+      const int m = t * 128 + warp * 32 + lane;
+      const int oh = m / C::WIN, ow = m - oh * C::WIN;
+      const bool valid = oh < C::HOUT && ow < C::WOUT;
+      const uint32_t ta = tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)t * 16;
+      if (CO <= 8) {
+        float v[8];
+        tmem_ld8(ta, v);
+        if (valid) {
+#pragma unroll
+          for (int o = 0; o < CO; ++o) cbuf[(o * C::HOUT + oh) * C::WOUT + ow] = fmaxf(v[o] + sbias[o], 0.f);
+        }
+      } else {
+        float v[16];
+        tmem_ld16(ta, v);
+        if (valid) {
+#pragma unroll
+          for (int o = 0; o < CO; ++o) cbuf[(o * C::HOUT + oh) * C::WOUT + ow] = fmaxf(v[o] + sbias[o], 0.f);
+        }
+      }
+    }
+    tc_fence_before();   // TMEM reads are done before the next image's MMAs may overwrite the accumulators
+    __syncthreads();
+    // ---- epilogue 2: 2x2 max + argmax (first maximum wins), to global NCHW ----
+    for (int i = tid; i < CO * C::HP * C::HP; i += 128) {
+      const int o = i / (C::HP * C::HP), pp = i - o * (C::HP * C::HP), ph = pp / C::HP, pw = pp - ph * C::HP;
+      const float* c0 = cbuf + (o * C::HOUT + 2 * ph) * C::WOUT + 2 * pw;
+      float best = c0[0];
+      int bi = 0;
+      if (c0[1] > best) { best = c0[1]; bi = 1; }
+      if (c0[C::WOUT] > best) { best = c0[C::WOUT]; bi = 2; }
+      if (c0[C::WOUT + 1] > best) { best = c0[C::WOUT + 1]; bi = 3; }
+      const size_t oi = (size_t)img * CO * C::HP * C::HP + i;
+      y[oi] = best;
+      idx[oi] = (unsigned char)bi;
+    }
+    __syncthreads();     // cbuf and the planes are rewritten by the next image
+    phase ^= 1u;
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_free<C::TMEM_COLS>(tmem);
+}
+
+template <int CI, int HIN, int CO>
+static int launch_tc_conv_t(const float* x, const float* w, const float* b, float* y, unsigned char* idx, int N,
+                            cudaStream_t s) {
+  using C = ConvCfg<CI, HIN, CO>;
+  static bool attr_set = false;
+  auto kern = tc_conv_relu_pool_fwd_kernel<CI, HIN, CO>;
+  if (!attr_set) {
+    DNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::kSmemBytes));
+    attr_set = true;
+  }
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int per_sm = (int)(200 * 1024 / C::kSmemBytes) < 512 / C::TMEM_COLS ? (int)(200 * 1024 / C::kSmemBytes)
+                                                                             : 512 / C::TMEM_COLS;
+  const int grid = N < sms * per_sm ? N : sms * per_sm;
+  kern<<<grid, 128, C::kSmemBytes, s>>>(x, w, b, y, idx, N);
+  DNN_CUDA_CHECK(cudaGetLastError());
+  return kOk;
+}
+
+int launch_tc_conv_relu_pool_fwd(const float* x, const float* w, const float* b, float* y, unsigned char* idx, int N,
+                                 int Ci, int H, int W, int Co, cudaStream_t s) {
+  if (Ci == 3 && H == 32 && W == 32 && Co == 6) return launch_tc_conv_t<3, 32, 6>(x, w, b, y, idx, N, s);
+  if (Ci == 6 && H == 14 && W == 14 && Co == 16) return launch_tc_conv_t<6, 14, 16>(x, w, b, y, idx, N, s);
+  set_last_error("tc_conv_relu_pool_fwd: only the two conv layers of the CNN are instantiated (3x32x32->6, 6x14x14->16)");
+  return kErrArg;
+}
+
+int launch_tc_gemm_probe(const float* A, const float* B, float* D, int K, cudaStream_t s) {
+  DNN_ARG_CHECK(K >= 8 && K % 8 == 0 && K <= 256, "tc_gemm_probe: K must be a multiple of 8 in [8, 256]");
+  const size_t smem = (size_t)(K / 4) * (128 + 16) * 16;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DNN_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    attr_set = true;
+  }
+  tc_gemm_probe_kernel<<<1, 128, smem, s>>>(A, B, D, K);
+  DNN_CUDA_CHECK(cudaGetLastError());
+  return kOk;
+}
+
+}  // namespace dnnb200

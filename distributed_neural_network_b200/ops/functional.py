@@ -20,6 +20,22 @@ import torch.nn.functional as F
 from . import native
 
 
+# Precision of the conv forward on CUDA: "tf32" runs the tcgen05 implicit-GEMM kernel (TF32 operands,
+# fp32 accumulate -- what PyTorch itself does for cuDNN convolutions by default), "fp32" the FFMA kernel.
+_conv_precision = "tf32"
+
+
+def set_conv_precision(mode: str) -> None:
+    global _conv_precision
+    if mode not in ("tf32", "fp32"):
+        raise ValueError("conv precision must be 'tf32' or 'fp32'")
+    _conv_precision = mode
+
+
+def get_conv_precision() -> str:
+    return _conv_precision
+
+
 def _use_native(t: torch.Tensor) -> bool:
     if not t.is_cuda:
         return False
@@ -39,7 +55,10 @@ class _ConvReluPool(torch.autograd.Function):
         Hp, Wp = (H - 4) // 2, (W - 4) // 2
         y = torch.empty((N, Co, Hp, Wp), device=x.device, dtype=torch.float32)
         idx = torch.empty((N, Co, Hp, Wp), device=x.device, dtype=torch.uint8)
-        native.conv_relu_pool_fwd(x, w.contiguous(), b.contiguous(), y, idx)
+        if _conv_precision == "tf32" and native.tc_conv_supported(x, w):
+            native.tc_conv_relu_pool_fwd(x, w.contiguous(), b.contiguous(), y, idx)
+        else:
+            native.conv_relu_pool_fwd(x, w.contiguous(), b.contiguous(), y, idx)
         ctx.save_for_backward(x, w, y, idx)
         ctx.needs_dx = x.requires_grad
         return y

@@ -120,6 +120,22 @@ def conv_relu_pool_fwd(x, w, b, y, idx) -> None:
                                           _p(idx), N, Ci, H, W, w.shape[0], _stream()))
 
 
+def tc_conv_relu_pool_fwd(x, w, b, y, idx) -> None:
+    """Tensor-core (tcgen05, TF32) version of conv_relu_pool_fwd for the CNN's two conv shapes."""
+    lib = require()
+    N, Ci, H, W = x.shape
+    _check(lib.dnnb200_tc_conv_relu_pool_fwd(_p(_f32(x, "x")), _p(_f32(w, "w")), _p(_f32(b, "b")), _p(_f32(y, "y")),
+                                             _p(idx), N, Ci, H, W, w.shape[0], _stream()))
+
+
+def tc_conv_supported(x, w) -> bool:
+    return tuple(x.shape[1:]) + (w.shape[0],) in ((3, 32, 32, 6), (6, 14, 14, 16))
+
+
+def tc_gemm_probe(A, B, D) -> None:
+    _check(require().dnnb200_tc_gemm_probe(_p(_f32(A, "A")), _p(_f32(B, "B")), _p(_f32(D, "D")), A.shape[1], _stream()))
+
+
 def conv_relu_pool_bwd(x, w, y, idx, dy, dx, dw, db) -> None:
     lib = require()
     N, Ci, H, W = x.shape

@@ -40,6 +40,13 @@ int dnnb200_conv_relu_pool_fwd(const float* x, const float* w, const float* b, f
 int dnnb200_conv_relu_pool_bwd(const float* x, const float* w, const float* y, const uint8_t* idx,
                                const float* dy, float* dx, float* dw, float* db,
                                int N, int Ci, int H, int W, int Co, void* stream);
+/* the same forward on the tensor cores: implicit GEMM, tcgen05.mma kind::tf32 with TMEM accumulators,
+ * the shared-memory descriptor performs the im2col (csrc/tc_conv.cu). TF32 operands, fp32 accumulate.
+ * Instantiated for the two conv layers of the CNN: (Ci,H,W,Co) = (3,32,32,6) and (6,14,14,16). */
+int dnnb200_tc_conv_relu_pool_fwd(const float* x, const float* w, const float* b, float* y, uint8_t* idx,
+                                  int N, int Ci, int H, int W, int Co, void* stream);
+/* D[128,16] = A[128,K] B[16,K]^T through the same descriptors (unit test of the encodings) */
+int dnnb200_tc_gemm_probe(const float* A, const float* B, float* D, int K, void* stream);
 /* y[N,M] = act(x[N,K] w[M,K]^T + b[M]) (K8-K10) */
 int dnnb200_linear_fwd(const float* x, const float* w, const float* b, float* y, int N, int M, int K,
                        int relu, void* stream);

@@ -130,7 +130,14 @@ def test_network_autograd_path_on_gpu():
     x, y = torch.randn(16, 3, 32, 32), torch.randint(0, 10, (16,))
     _, g_ref = _oracle_grads(ref, x, y)
     from distributed_neural_network_b200.ops import functional as Fn
-    gpu.zero_grad()
-    loss = Fn.cross_entropy(gpu(x.cuda()), y.cuda())
-    loss.backward()
+    Fn.set_conv_precision("fp32")
+    try:
+        gpu.zero_grad()
+        loss = Fn.cross_entropy(gpu(x.cuda()), y.cuda())
+        loss.backward()
+    finally:
+        Fn.set_conv_precision("tf32")
     assert _rel(gpu.flat_grads, g_ref) < 5e-5
+    gpu.zero_grad()                                  # default: TF32 tensor-core conv forward
+    Fn.cross_entropy(gpu(x.cuda()), y.cuda()).backward()
+    assert _rel(gpu.flat_grads, g_ref) < 2e-2

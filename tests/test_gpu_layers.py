@@ -9,6 +9,14 @@ from distributed_neural_network_b200.ops import native
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True)
+def _fp32_convs():
+    """These tests compare at fp32 tolerances: use the FFMA conv forward (tests/test_gpu_tc.py covers TF32)."""
+    Fn.set_conv_precision("fp32")
+    yield
+    Fn.set_conv_precision("tf32")
+
+
 def _close(a, b, tol=2e-5):
     a, b = a.detach().cpu().double(), b.detach().cpu().double()
     denom = b.abs().max().clamp_min(1e-6)
