@@ -39,7 +39,7 @@ def main():
         out[f"fused_img_per_s_B{B}"] = round(B / us * 1e6)
         out[f"cluster_B{B}"] = str(eng.cluster_info(B))
         if B in (16, 64):
-            for cs in (1, 2, 4, 8):
+            for cs in (1, 2, 3, 4, 5, 6, 7, 8):
                 eng.set_cluster_size(cs)
                 out[f"fused_step_us_B{B}_cs{cs}"] = round(time_steps(lambda: eng.step(x, y), 300), 2)
             eng.set_cluster_size(0)

@@ -35,6 +35,9 @@ def main():
     print(f"B={B} cs={cs}: per-stage cycles (mean / max over {n_cta} CTAs); total {(t[:,13]-t[:,0]).float().mean():.0f} cycles")
     for k in range(13):
         print(f"  {NAMES[k+1]:28s} {d[:,k].mean():8.0f} {d[:,k].max():8.0f}")
+    if (t[:, 14] > 0).all():
+        a, b, c = (t[:, 14] - t[:, 6]).float(), (t[:, 15] - t[:, 14]).float(), (t[:, 7] - t[:, 15]).float()
+        print(f"  fc1 detail: weight-prefetch wait {a.mean():.0f}/{a.max():.0f}  compute+push {b.mean():.0f}/{b.max():.0f}  gather wait {c.mean():.0f}/{c.max():.0f}")
 
 
 if __name__ == "__main__":

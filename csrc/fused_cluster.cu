@@ -241,6 +241,77 @@ __device__ __forceinline__ void fc_dx_local(const float* __restrict__ W, const f
   }
 }
 
+
+// ---- FC weights resident in shared memory (clusters of 4 and 8) ---------------------------------
+// The FC layers are a chain of dependent matrix-vector products; reading their weights from L2 at
+// each link made the chain 41% of the kernel (profiles/). Each CTA therefore prefetches, with TMA
+// bulk copies issued at kernel start and hidden under the conv layers, exactly the ROW slices of
+// fc1/fc2 it owns (and all of the tiny fc3). The SAME slices serve the backward pass: a CTA
+// multiplies its rows by its part of the incoming delta, which yields a partial sum over its rows
+// for every input column; the CS partials are exchanged with st.async and added in CTA order.
+template <int CS>
+struct FCSmem {
+  static constexpr int kR1 = (kF1 + CS - 1) / CS;
+  static constexpr int kR2 = (kF2 + CS - 1) / CS;
+  alignas(16) float wf1[kR1 * kFlat];
+  alignas(16) float wf2[kR2 * kF1];
+  alignas(16) float wf3[kF3 * kF2];
+  alignas(16) float bf1[kF1];
+  alignas(16) float bf2[kF2 + 4];
+  alignas(16) float bf3[16];
+  alignas(16) float rx_d1[CS * kF1];    // partial dL/dh1 from every CTA of the cluster
+  alignas(16) float rx_g2[CS * kFlat];  // partial dL/dp2
+  alignas(8) unsigned long long wbar;   // weight prefetch
+};
+constexpr size_t kFcOff = (sizeof(CLSmem) + 127) & ~(size_t)127;
+template <int CS>
+constexpr size_t cluster_smem_bytes() {
+  return CS >= 4 ? kFcOff + sizeof(FCSmem<CS>) : sizeof(CLSmem);
+}
+
+// rows [m0, m1) of y = act(b + W . in) with the rows in shared memory (wsm[0] is row m0)
+template <int CS, int K, bool kRelu>
+__device__ __forceinline__ void fc_rows_smem_push(const float* wsm, const float* bsm, const float* in, int m0, int m1,
+                                                  const Remote<CS>& R, uint32_t field_off, uint32_t bar_off) {
+  constexpr int K4 = K / 4;
+  constexpr int kIter = (K4 + 31) / 32;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float4* in4 = reinterpret_cast<const float4*>(in);
+  for (int r = m0 + warp; r < m1; r += kCLThreads / 32) {
+    const float4* w4 = reinterpret_cast<const float4*>(wsm + (size_t)(r - m0) * K);
+    float acc = 0.f;
+#pragma unroll
+    for (int it = 0; it < kIter; ++it) {
+      const int k4 = lane + it * 32;
+      if (k4 < K4) {
+        const float4 w = w4[k4], v = in4[k4];
+        acc += w.x * v.x + w.y * v.y + w.z * v.z + w.w * v.w;
+      }
+    }
+    acc = warp_sum(acc) + bsm[r];
+    const float y = kRelu ? fmaxf(acc, 0.f) : acc;
+#pragma unroll
+    for (int d = 0; d < CS; ++d)
+      if (lane == d) cl_st_async(R.base[d] + field_off + 4u * r, __float_as_uint(y), R.base[d] + bar_off);
+  }
+}
+
+// partial[k] = sum over my rows m of W[m,k] * dy[m], pushed into slot `rank` of every CTA's rx buffer
+template <int CS, int K>
+__device__ __forceinline__ void fc_dx_partial_push(const float* wsm, const float* dy, int m0, int m1, int rank,
+                                                   const Remote<CS>& R, uint32_t rx_off, uint32_t bar_off) {
+  for (int k = threadIdx.x; k < K; k += kCLThreads) {
+    float a0 = 0.f, a1 = 0.f;
+    int m = m0;
+    for (; m + 1 < m1; m += 2) {
+      a0 += wsm[(size_t)(m - m0) * K + k] * dy[m];
+      a1 += wsm[(size_t)(m + 1 - m0) * K + k] * dy[m + 1];
+    }
+    if (m < m1) a0 += wsm[(size_t)(m - m0) * K + k] * dy[m];
+    push_all<CS>(R, rx_off + 4u * (uint32_t)(rank * K + k), bar_off, __float_as_uint(a0 + a1));
+  }
+}
+
 // development aid: thread 0 of every CTA stamps the SM clock at stage boundaries (trace == nullptr in production)
 #define CL_TRACE(k) do { if (trace != nullptr && tid == 0) trace[blockIdx.x * 16 + (k)] = clock64(); } while (0)
 
@@ -250,7 +321,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
                        const long long* __restrict__ labels, float* __restrict__ saved,
                        float* __restrict__ part1, float* __restrict__ part2, float* __restrict__ img_loss,
                        int* __restrict__ img_correct, int B, float inv_batch, long long* __restrict__ trace) {
-  static_assert(CS == 2 || CS == 4 || CS == 8, "the one-CTA case is fused_step.cu's fwd_bwd_kernel");
+  static_assert(CS >= 2 && CS <= 8, "the one-CTA case is fused_step.cu's fwd_bwd_kernel");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   CLSmem& s = *reinterpret_cast<CLSmem*>(smem_raw);
   cg::cluster_group cluster = cg::this_cluster();
@@ -258,6 +329,11 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
   const int r = (int)cluster.block_rank();
   const int n_clusters = gridDim.x / CS;
   int img = blockIdx.x / CS;
+
+  constexpr bool kPre = CS >= 4;  // FC weight slices resident in shared memory
+  FCSmem<kPre ? CS : 4>& f = *reinterpret_cast<FCSmem<kPre ? CS : 4>*>(smem_raw + kFcOff);
+  constexpr uint32_t kRxD1 = (uint32_t)(kFcOff + offsetof(FCSmem<kPre ? CS : 4>, rx_d1));
+  constexpr uint32_t kRxG2 = (uint32_t)(kFcOff + offsetof(FCSmem<kPre ? CS : 4>, rx_g2));
 
   Remote<CS> R;
 #pragma unroll
@@ -267,9 +343,19 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     cl_mbar_init(&s.mbar, 1);
 #pragma unroll
     for (int i = 0; i < kNumStageBars; ++i) cl_mbar_init(&s.sbar[i], 1);
+    if (kPre) cl_mbar_init(&f.wbar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
+  if (kPre && tid == 0) {
+    // my FC weight slices: three TMA bulk copies that land while the conv layers run
+    const int a0 = r * kF1 / CS, a1 = (r + 1) * kF1 / CS, c0 = r * kF2 / CS, c1 = (r + 1) * kF2 / CS;
+    const uint32_t n1 = (uint32_t)(a1 - a0) * kFlat * 4, n2 = (uint32_t)(c1 - c0) * kF1 * 4, n3 = kF3 * kF2 * 4;
+    cl_mbar_expect_tx(&f.wbar, n1 + n2 + n3);
+    cl_bulk_g2s(f.wf1, params + kOffF1W + (size_t)a0 * kFlat, n1, &f.wbar);
+    cl_bulk_g2s(f.wf2, params + kOffF2W + (size_t)c0 * kF1, n2, &f.wbar);
+    cl_bulk_g2s(f.wf3, params + kOffF3W, n3, &f.wbar);
+  }
   // tell the cluster "my barriers exist"; the matching wait sits just before the first remote store
   cl_cluster_arrive();
 
@@ -294,6 +380,11 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
   for (int i = tid; i < 2400 / 4; i += kCLThreads)
     reinterpret_cast<float4*>(s.w2)[i] = __ldg(reinterpret_cast<const float4*>(params + kOffW2) + i);
   if (tid < 16) s.b2[tid] = __ldg(params + kOffB2 + tid);
+  if (kPre) {
+    if (tid < kF1) f.bf1[tid] = __ldg(params + kOffF1B + tid);
+    if (tid < kF2) f.bf2[tid] = __ldg(params + kOffF2B + tid);
+    if (tid < kF3) f.bf3[tid] = __ldg(params + kOffF3B + tid);
+  }
   if (tid < 196) s.poff[tid] = (2 * (tid / 14)) * kXRow + 2 * (tid % 14);
   __syncthreads();
   for (int ot = tid; ot < 400; ot += kCLThreads) {  // one (o, tap) per thread: 8 contiguous floats
@@ -325,8 +416,8 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       cl_mbar_expect_tx(&s.sbar[kBarP2], 400 * 8);
       cl_mbar_expect_tx(&s.sbar[kBarH1], kF1 * 4);
       cl_mbar_expect_tx(&s.sbar[kBarH2], kF2 * 4);
-      cl_mbar_expect_tx(&s.sbar[kBarD1], kF1 * 4);
-      cl_mbar_expect_tx(&s.sbar[kBarG2], kFlat * 4);
+      cl_mbar_expect_tx(&s.sbar[kBarD1], (kPre ? CS : 1) * kF1 * 4);
+      cl_mbar_expect_tx(&s.sbar[kBarG2], (kPre ? CS : 1) * kFlat * 4);
     }
     cl_mbar_wait(&s.mbar, phase);  // image landed (also orders the weight staging of round 0: see sync below)
     __syncthreads();
@@ -439,14 +530,37 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     CL_TRACE(6);
 
     // ================= fc1, fc2 (rows split), fc3 + softmax-CE (redundant) =================
-    fc_rows_push<CS, kFlat, true>(params + kOffF1W, params + kOffF1B, s.p2, f1m0, f1m1, R, CL_OFF(h1),
-                                  CL_BAR(kBarH1));
-    cl_mbar_wait(&s.sbar[kBarH1], phase);
-    CL_TRACE(7);
-    fc_rows_push<CS, kF1, true>(params + kOffF2W, params + kOffF2B, s.h1, f2m0, f2m1, R, CL_OFF(h2), CL_BAR(kBarH2));
-    cl_mbar_wait(&s.sbar[kBarH2], phase);
-    CL_TRACE(8);
-    fc_rows_local<kF3, kF2>(params + kOffF3W, params + kOffF3B, s.h2, s.logits);
+    if (kPre) {
+      cl_mbar_wait(&f.wbar, 0);  // weight slices have landed (completed long ago; stays complete)
+      CL_TRACE(14);
+      fc_rows_smem_push<CS, kFlat, true>(f.wf1, f.bf1, s.p2, f1m0, f1m1, R, CL_OFF(h1), CL_BAR(kBarH1));
+      CL_TRACE(15);
+      cl_mbar_wait(&s.sbar[kBarH1], phase);
+      CL_TRACE(7);
+      fc_rows_smem_push<CS, kF1, true>(f.wf2, f.bf2, s.h1, f2m0, f2m1, R, CL_OFF(h2), CL_BAR(kBarH2));
+      cl_mbar_wait(&s.sbar[kBarH2], phase);
+      CL_TRACE(8);
+      if (warp < kF3) {  // fc3 redundantly in every CTA: one warp per logit
+        const float4 w = lane < kF2 / 4 ? reinterpret_cast<const float4*>(f.wf3 + warp * kF2)[lane]
+                                        : make_float4(0.f, 0.f, 0.f, 0.f);
+        float acc = 0.f;
+        if (lane < kF2 / 4) {
+          const float4 v = reinterpret_cast<const float4*>(s.h2)[lane];
+          acc = w.x * v.x + w.y * v.y + w.z * v.z + w.w * v.w;
+        }
+        acc = warp_sum(acc);
+        if (lane == 0) s.logits[warp] = acc + f.bf3[warp];
+      }
+    } else {
+      fc_rows_push<CS, kFlat, true>(params + kOffF1W, params + kOffF1B, s.p2, f1m0, f1m1, R, CL_OFF(h1),
+                                    CL_BAR(kBarH1));
+      cl_mbar_wait(&s.sbar[kBarH1], phase);
+      CL_TRACE(7);
+      fc_rows_push<CS, kF1, true>(params + kOffF2W, params + kOffF2B, s.h1, f2m0, f2m1, R, CL_OFF(h2), CL_BAR(kBarH2));
+      cl_mbar_wait(&s.sbar[kBarH2], phase);
+      CL_TRACE(8);
+      fc_rows_local<kF3, kF2>(params + kOffF3W, params + kOffF3B, s.h2, s.logits);
+    }
     __syncthreads();
     if (warp == 0) {
       const int label = (int)__ldg(labels + img);
@@ -467,18 +581,50 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     __syncthreads();
 
     // ================= FC data gradients =================
-    fc_dx_local<kF3, kF2>(params + kOffF3W, s.d3, s.h2, s.d2);
-    __syncthreads();
-    fc_dx_split_push<CS, kF2, kF1>(params + kOffF2W, s.d2, s.h1, d1k0, d1k1, s.red, R, CL_OFF(d1), CL_BAR(kBarD1));
-    cl_mbar_wait(&s.sbar[kBarD1], phase);
-    CL_TRACE(9);
-    __syncthreads();  // `red` is reused by the next split
-    fc_dx_split_push<CS, kF1, kFlat>(params + kOffF1W, s.d1, s.p2, g2k0, g2k1, s.red, R, CL_OFF(g2), CL_BAR(kBarG2));
-    // zero the dense gradient plane while the g2 traffic is in flight
-    for (int i = tid; i < 16 * 18 * 18; i += kCLThreads) s.dc2p[i] = 0.f;
-    cl_mbar_wait(&s.sbar[kBarG2], phase);
-    __syncthreads();
-    CL_TRACE(10);
+    if (kPre) {
+      if (tid < kF2) {  // dL/dh2, redundantly: 10 x 84 from shared memory
+        float a = 0.f;
+#pragma unroll
+        for (int m = 0; m < kF3; ++m) a += f.wf3[m * kF2 + tid] * s.d3[m];
+        s.d2[tid] = s.h2[tid] > 0.f ? a : 0.f;
+      }
+      __syncthreads();
+      // dL/dh1: partial sums over MY fc2 rows for all 120 columns, exchanged and added in CTA order
+      fc_dx_partial_push<CS, kF1>(f.wf2, s.d2, f2m0, f2m1, r, R, kRxD1, CL_BAR(kBarD1));
+      cl_mbar_wait(&s.sbar[kBarD1], phase);
+      if (tid < kF1) {
+        float a = 0.f;
+#pragma unroll
+        for (int d = 0; d < CS; ++d) a += f.rx_d1[d * kF1 + tid];
+        s.d1[tid] = s.h1[tid] > 0.f ? a : 0.f;
+      }
+      __syncthreads();
+      CL_TRACE(9);
+      fc_dx_partial_push<CS, kFlat>(f.wf1, s.d1, f1m0, f1m1, r, R, kRxG2, CL_BAR(kBarG2));
+      for (int i = tid; i < 16 * 18 * 18; i += kCLThreads) s.dc2p[i] = 0.f;  // while the partials are in flight
+      cl_mbar_wait(&s.sbar[kBarG2], phase);
+      if (tid < kFlat) {
+        float a = 0.f;
+#pragma unroll
+        for (int d = 0; d < CS; ++d) a += f.rx_g2[d * kFlat + tid];
+        s.g2[tid] = s.p2[tid] > 0.f ? a : 0.f;
+      }
+      __syncthreads();
+      CL_TRACE(10);
+    } else {
+      fc_dx_local<kF3, kF2>(params + kOffF3W, s.d3, s.h2, s.d2);
+      __syncthreads();
+      fc_dx_split_push<CS, kF2, kF1>(params + kOffF2W, s.d2, s.h1, d1k0, d1k1, s.red, R, CL_OFF(d1), CL_BAR(kBarD1));
+      cl_mbar_wait(&s.sbar[kBarD1], phase);
+      CL_TRACE(9);
+      __syncthreads();  // `red` is reused by the next split
+      fc_dx_split_push<CS, kF1, kFlat>(params + kOffF1W, s.d1, s.p2, g2k0, g2k1, s.red, R, CL_OFF(g2), CL_BAR(kBarG2));
+      // zero the dense gradient plane while the g2 traffic is in flight
+      for (int i = tid; i < 16 * 18 * 18; i += kCLThreads) s.dc2p[i] = 0.f;
+      cl_mbar_wait(&s.sbar[kBarG2], phase);
+      __syncthreads();
+      CL_TRACE(10);
+    }
     // from here on nothing crosses CTAs any more
 
     if (r == 0) {  // FC record for the update kernel
@@ -622,7 +768,7 @@ static int launch_cluster_t(const float* params, const float* x, const long long
                             long long* trace, cudaStream_t stream) {
   static bool attr_set = false;
   auto kern = fwd_bwd_cluster_kernel<CS>;
-  const size_t smem = sizeof(CLSmem);
+  const size_t smem = cluster_smem_bytes<CS>();
   if (!attr_set) {
     DNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
@@ -655,33 +801,40 @@ int pick_cluster_size(int B, int num_sms) {
   return 1;
 }
 
-// how many clusters of `cs` CTAs of this kernel the device can hold at once
-int max_active_clusters(int cs) {
+// how many clusters of CS CTAs of this kernel the device can hold at once
+template <int CS>
+static int max_active_clusters_t() {
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(cs * 64);
+  cfg.gridDim = dim3(CS * 64);
   cfg.blockDim = dim3(kCLThreads);
-  cfg.dynamicSmemBytes = sizeof(CLSmem);
+  cfg.dynamicSmemBytes = cluster_smem_bytes<CS>();
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = cs;
+  attr[0].val.clusterDim.x = CS;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   int n = 0;
-  cudaError_t e = cudaErrorInvalidValue;
-  if (cs == 8) {
-    cudaFuncSetAttribute(fwd_bwd_cluster_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CLSmem));
-    e = cudaOccupancyMaxActiveClusters(&n, fwd_bwd_cluster_kernel<8>, &cfg);
-  } else if (cs == 4) {
-    cudaFuncSetAttribute(fwd_bwd_cluster_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CLSmem));
-    e = cudaOccupancyMaxActiveClusters(&n, fwd_bwd_cluster_kernel<4>, &cfg);
-  } else if (cs == 2) {
-    cudaFuncSetAttribute(fwd_bwd_cluster_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CLSmem));
-    e = cudaOccupancyMaxActiveClusters(&n, fwd_bwd_cluster_kernel<2>, &cfg);
+  cudaFuncSetAttribute(fwd_bwd_cluster_kernel<CS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                       (int)cluster_smem_bytes<CS>());
+  if (cudaOccupancyMaxActiveClusters(&n, fwd_bwd_cluster_kernel<CS>, &cfg) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
   }
-  if (e != cudaSuccess) { cudaGetLastError(); return 0; }
   return n;
+}
+int max_active_clusters(int cs) {
+  switch (cs) {
+    case 2: return max_active_clusters_t<2>();
+    case 3: return max_active_clusters_t<3>();
+    case 4: return max_active_clusters_t<4>();
+    case 5: return max_active_clusters_t<5>();
+    case 6: return max_active_clusters_t<6>();
+    case 7: return max_active_clusters_t<7>();
+    case 8: return max_active_clusters_t<8>();
+    default: return 0;
+  }
 }
 
 int launch_fwd_bwd_cluster(int cs, const float* params, const float* x, const long long* labels, float* saved,
@@ -689,7 +842,11 @@ int launch_fwd_bwd_cluster(int cs, const float* params, const float* x, const lo
                            long long* trace, cudaStream_t stream) {
   switch (cs) {
     case 8: return launch_cluster_t<8>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
+    case 7: return launch_cluster_t<7>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
+    case 6: return launch_cluster_t<6>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
+    case 5: return launch_cluster_t<5>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
     case 4: return launch_cluster_t<4>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
+    case 3: return launch_cluster_t<3>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
     case 2: return launch_cluster_t<2>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
     default: set_last_error("cluster size %d not supported", cs); return kErrArg;
   }

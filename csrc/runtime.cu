@@ -195,7 +195,7 @@ static int ensure_ring(dnnb200_engine* e) {
 // whole batch runs as ONE wave over as many SMs as possible; 1 = the one-CTA-per-image kernel.
 static int cluster_size_for(const dnnb200_engine* e, int B) {
   if (e->forced_cluster) return e->forced_cluster;
-  for (int cs = 8; cs >= 2; cs >>= 1)
+  for (int cs = 8; cs >= 2; --cs)
     if (e->max_clusters[cs] >= B) return cs;
   return 1;
 }
@@ -350,7 +350,7 @@ int dnnb200_engine_create(float* params, float* momentum, float* grads, int max_
   DNN_CUDA_CHECK(cudaMemset(e->part1, 0, (size_t)max_batch * 8 * kOffW2 * sizeof(float)));
   DNN_CUDA_CHECK(cudaMalloc(&e->part2, (size_t)max_batch * (kConvPrefix - kOffW2) * sizeof(float)));
   DNN_CUDA_CHECK(cudaMemset(e->part2, 0, (size_t)max_batch * (kConvPrefix - kOffW2) * sizeof(float)));
-  for (int cs = 2; cs <= 8; cs <<= 1) e->max_clusters[cs] = max_active_clusters(cs);
+  for (int cs = 2; cs <= 8; ++cs) e->max_clusters[cs] = max_active_clusters(cs);
   DNN_CUDA_CHECK(cudaMemset(e->saved, 0, (size_t)max_batch * kSavStride * sizeof(float)));
   DNN_CUDA_CHECK(cudaMalloc(&e->img_loss, (size_t)max_batch * sizeof(float)));
   DNN_CUDA_CHECK(cudaMalloc(&e->img_correct, (size_t)max_batch * sizeof(int)));
@@ -464,7 +464,7 @@ unsigned long long dnnb200_engine_launches(const dnnb200_engine* e) { return e ?
 
 int dnnb200_engine_set_cluster_size(dnnb200_engine* e, int cs) {
   DNN_ARG_CHECK(e, "null engine");
-  DNN_ARG_CHECK(cs == 0 || cs == 1 || cs == 2 || cs == 4 || cs == 8, "cluster size must be 0 (auto), 1, 2, 4 or 8");
+  DNN_ARG_CHECK(cs >= 0 && cs <= 8, "cluster size must be 0 (auto) or 1..8");
   DNN_ARG_CHECK(cs <= 1 || e->max_clusters[cs] > 0, "clusters of %d CTAs cannot be scheduled on this device", cs);
   e->forced_cluster = cs;
   return kOk;

@@ -265,7 +265,7 @@ class Engine:
         chosen = C.c_int()
         mc = (C.c_int * 9)()
         _check(require().dnnb200_engine_cluster_info(self._h, B, C.byref(chosen), mc))
-        return chosen.value, {cs: mc[cs] for cs in (2, 4, 8)}
+        return chosen.value, {cs: mc[cs] for cs in range(2, 9)}
 
     @property
     def launches(self) -> int:

@@ -24,7 +24,7 @@ def _oracle_grads(model_cpu, x, y):
     return loss.item(), model_cpu.flat_grads.clone()
 
 
-@pytest.mark.parametrize("cs", [0, 1, 2, 4, 8])
+@pytest.mark.parametrize("cs", [0, 1, 2, 3, 4, 5, 6, 7, 8])
 @pytest.mark.parametrize("B", [1, 4, 16, 64])
 def test_grad_only_matches_autograd(B, cs):
     """Every cluster size of the forward/backward kernel (cs CTAs per image, DSMEM all-gathers
