@@ -25,19 +25,26 @@ def main():
     for _ in range(5):
         eng.step(x, y)
     n_cta = B * cs
-    tr = torch.zeros(n_cta * 16, dtype=torch.int64, device="cuda")
+    tr = torch.zeros(n_cta * 32, dtype=torch.int64, device="cuda")
     eng.set_trace(tr)
     eng.step(x, y)
     torch.cuda.synchronize()
     eng.set_trace(None)
-    t = tr.view(n_cta, 16).cpu()
+    t = tr.view(n_cta, 32).cpu()
     d = (t[:, 1:14] - t[:, 0:13]).float()
     print(f"B={B} cs={cs}: per-stage cycles (mean / max over {n_cta} CTAs); total {(t[:,13]-t[:,0]).float().mean():.0f} cycles")
     for k in range(13):
         print(f"  {NAMES[k+1]:28s} {d[:,k].mean():8.0f} {d[:,k].max():8.0f}")
-    if (t[:, 14] > 0).all():
-        a, b, c = (t[:, 14] - t[:, 6]).float(), (t[:, 15] - t[:, 14]).float(), (t[:, 7] - t[:, 15]).float()
-        print(f"  fc1 detail: weight-prefetch wait {a.mean():.0f}/{a.max():.0f}  compute+push {b.mean():.0f}/{b.max():.0f}  gather wait {c.mean():.0f}/{c.max():.0f}")
+    ent, ext = t[:, 14].double(), t[:, 15].double()
+    print(f"  globaltimer: first CTA entry -> last CTA entry {ent.max()-ent.min():.0f} ns; "
+          f"entry -> end of image loop, per CTA mean {(ext-ent).mean():.0f} ns; first entry -> last exit {ext.max()-ent.min():.0f} ns")
+    pr = t[:, 16:21].double()
+    names = ["entry->mbar init+sync", "cluster arrive", "issue image TMA + weight loads issued", "weights landed (sync)"]
+    for k in range(4):
+        print(f"    prologue {names[k]:40s} {(pr[:, k+1]-pr[:, k]).mean():8.0f} cycles")
+    print(f"    prologue w2d build + split consts -> trace0 {(t[:,0]-t[:,20]).double().mean():8.0f} cycles")
+    loop_ns = (t[:, 13] - t[:, 0]).double().mean() / 1.965
+    print(f"  image loop {loop_ns:.0f} ns  => prologue (entry -> cluster barrier) ~ {(ext-ent).mean() - loop_ns:.0f} ns")
 
 
 if __name__ == "__main__":

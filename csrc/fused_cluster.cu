@@ -42,7 +42,8 @@ constexpr int kCLRed = 9408;               // CS=2 worst case: conv2 dgrad parti
 enum { kBarP1 = 0, kBarP2, kBarH1, kBarH2, kBarD1, kBarG2, kNumStageBars };
 
 struct __align__(16) CLSmem {
-  alignas(16) float x[3 * kXCh];      // image, CHW with padded rows (96 row-sized TMA bulk copies)
+  alignas(16) float xd[kImgNumel];    // image as it is in global memory (ONE 12 KB TMA bulk copy)
+  alignas(16) float x[3 * kXCh];      // image, CHW with padded rows (re-laid out by the threads)
   alignas(16) float w1[456];          // conv1.weight natural layout [o][c][kh][kw] + bias at 450
   alignas(16) float w2[2400];         // conv2.weight natural layout [o][c][kh][kw]
   alignas(16) float w2d[16 * 25 * 8]; // conv2.weight as [(o,kh,kw)][c8] for the data gradient
@@ -111,6 +112,10 @@ __device__ __forceinline__ void cl_st_async(uint32_t remote_addr, uint32_t v, ui
 }
 __device__ __forceinline__ void cl_cluster_arrive() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+}
+// no memory ordering needed (the mbarrier inits are published by fence.mbarrier_init): much cheaper
+__device__ __forceinline__ void cl_cluster_arrive_relaxed() {
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void cl_cluster_wait() {
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -313,7 +318,7 @@ __device__ __forceinline__ void fc_dx_partial_push(const float* wsm, const float
 }
 
 // development aid: thread 0 of every CTA stamps the SM clock at stage boundaries (trace == nullptr in production)
-#define CL_TRACE(k) do { if (trace != nullptr && tid == 0) trace[blockIdx.x * 16 + (k)] = clock64(); } while (0)
+#define CL_TRACE(k) do { if (trace != nullptr && tid == 0) trace[blockIdx.x * 32 + (k)] = clock64(); } while (0)
 
 template <int CS>
 __global__ void __launch_bounds__(kCLThreads, 1)
@@ -326,6 +331,8 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
   CLSmem& s = *reinterpret_cast<CLSmem*>(smem_raw);
   cg::cluster_group cluster = cg::this_cluster();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (trace != nullptr && tid == 0) trace[blockIdx.x * 32 + 14] = (long long)globaltimer_ns();
+  CL_TRACE(16);
   const int r = (int)cluster.block_rank();
   const int n_clusters = gridDim.x / CS;
   int img = blockIdx.x / CS;
@@ -357,20 +364,17 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     cl_bulk_g2s(f.wf3, params + kOffF3W, n3, &f.wbar);
   }
   // tell the cluster "my barriers exist"; the matching wait sits just before the first remote store
-  cl_cluster_arrive();
+  CL_TRACE(17);
+  cl_cluster_arrive_relaxed();
+  CL_TRACE(18);
 
   uint32_t phase = 0;
-  // image rows -> padded rows, 96 bulk copies of 128 B issued by warp 0
+  // One bulk copy per image. (Copying the 96 rows separately into the padded layout was tried first:
+  // 96 tiny cp.async.bulk serialise in the TMA unit and cost 4.3 us per launch -- see profiles/.)
   auto load_image = [&](int im) {
-    if (warp == 0) {
-      if (lane == 0) cl_mbar_expect_tx(&s.mbar, kImgNumel * 4);
-      __syncwarp();
-      const float* src = x + (size_t)im * kImgNumel;
-#pragma unroll
-      for (int k = 0; k < 3; ++k) {
-        const int row = lane + 32 * k;  // 0..95 = c*32 + h
-        cl_bulk_g2s(s.x + (row >> 5) * kXCh + (row & 31) * kXRow, src + row * 32, 128, &s.mbar);
-      }
+    if (tid == 0) {
+      cl_mbar_expect_tx(&s.mbar, kImgNumel * 4);
+      cl_bulk_g2s(s.xd, x + (size_t)im * kImgNumel, kImgNumel * 4, &s.mbar);
     }
   };
   load_image(img);
@@ -386,7 +390,9 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     if (tid < kF3) f.bf3[tid] = __ldg(params + kOffF3B + tid);
   }
   if (tid < 196) s.poff[tid] = (2 * (tid / 14)) * kXRow + 2 * (tid % 14);
+  CL_TRACE(19);
   __syncthreads();
+  CL_TRACE(20);
   for (int ot = tid; ot < 400; ot += kCLThreads) {  // one (o, tap) per thread: 8 contiguous floats
     const int o = ot / 25, t = ot - o * 25;
     const float* src = s.w2 + o * 150 + t;
@@ -419,7 +425,12 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       cl_mbar_expect_tx(&s.sbar[kBarD1], (kPre ? CS : 1) * kF1 * 4);
       cl_mbar_expect_tx(&s.sbar[kBarG2], (kPre ? CS : 1) * kFlat * 4);
     }
-    cl_mbar_wait(&s.mbar, phase);  // image landed (also orders the weight staging of round 0: see sync below)
+    cl_mbar_wait(&s.mbar, phase);  // image landed
+    for (int i = tid; i < kImgNumel / 4; i += kCLThreads) {  // dense -> padded rows (36 floats, 16-byte aligned)
+      const float4 v = reinterpret_cast<const float4*>(s.xd)[i];
+      const int e = i * 4, c = e >> 10, h = (e >> 5) & 31, w = e & 31;
+      *reinterpret_cast<float4*>(s.x + c * kXCh + h * kXRow + w) = v;
+    }
     __syncthreads();
     CL_TRACE(2);
 
@@ -532,9 +543,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     // ================= fc1, fc2 (rows split), fc3 + softmax-CE (redundant) =================
     if (kPre) {
       cl_mbar_wait(&f.wbar, 0);  // weight slices have landed (completed long ago; stays complete)
-      CL_TRACE(14);
       fc_rows_smem_push<CS, kFlat, true>(f.wf1, f.bf1, s.p2, f1m0, f1m1, R, CL_OFF(h1), CL_BAR(kBarH1));
-      CL_TRACE(15);
       cl_mbar_wait(&s.sbar[kBarH1], phase);
       CL_TRACE(7);
       fc_rows_smem_push<CS, kF1, true>(f.wf2, f.bf2, s.h1, f2m0, f2m1, R, CL_OFF(h2), CL_BAR(kBarH2));
@@ -750,6 +759,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       }
     }
     CL_TRACE(13);
+    if (trace != nullptr && tid == 0) trace[blockIdx.x * 32 + 15] = (long long)globaltimer_ns();
     phase ^= 1u;
     if (img + n_clusters < B) {
       // several images per cluster: nobody may push the next image's activations (or reload the
