@@ -66,6 +66,12 @@ __device__ __forceinline__ unsigned int ld_relaxed_sys(const unsigned int* p) {
 __device__ __forceinline__ float4 ld_cg_f4(const float4* p) { return __ldcg(p); }
 __device__ __forceinline__ float ld_cg_f(const float* p) { return __ldcg(p); }
 
+// Programmatic dependent launch: a kernel launched with the programmatic-stream-serialization attribute may
+// start while its predecessor in the stream is still running; it must not touch the predecessor's results
+// before pdl_wait(). pdl_trigger() in the predecessor says "my successor may start being scheduled now".
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));

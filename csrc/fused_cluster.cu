@@ -44,10 +44,9 @@ enum { kBarP1 = 0, kBarP2, kBarH1, kBarH2, kBarD1, kBarG2, kNumStageBars };
 struct __align__(16) CLSmem {
   alignas(16) float xd[kImgNumel];    // image as it is in global memory (ONE 12 KB TMA bulk copy)
   alignas(16) float x[3 * kXCh];      // image, CHW with padded rows (re-laid out by the threads)
-  alignas(16) float w1[456];          // conv1.weight natural layout [o][c][kh][kw] + bias at 450
-  alignas(16) float w2[2400];         // conv2.weight natural layout [o][c][kh][kw]
+  alignas(16) float cw[kConvPrefix];  // conv1.weight | conv1.bias | conv2.weight | conv2.bias exactly as in the flat
+                                      // parameter vector (offsets kOffW1, kOffB1, kOffW2, kOffB2): one TMA bulk copy
   alignas(16) float w2d[16 * 25 * 8]; // conv2.weight as [(o,kh,kw)][c8] for the data gradient
-  alignas(16) float b2[16];
   alignas(16) float p1[1176 + 8];
   alignas(16) float p2[400];
   alignas(16) float h1[120];
@@ -64,6 +63,7 @@ struct __align__(16) CLSmem {
   alignas(16) int idx2[400];
   alignas(16) int poff[196];          // (2*ph)*kXRow + 2*pw of pooled pixel q
   alignas(8) unsigned long long mbar;                  // image bulk copies
+  alignas(8) unsigned long long cbar;                  // conv weights bulk copy (once per launch)
   alignas(8) unsigned long long sbar[kNumStageBars];   // all-gather completion
 };
 
@@ -348,27 +348,20 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
 
   if (tid == 0) {
     cl_mbar_init(&s.mbar, 1);
+    cl_mbar_init(&s.cbar, 1);
 #pragma unroll
     for (int i = 0; i < kNumStageBars; ++i) cl_mbar_init(&s.sbar[i], 1);
     if (kPre) cl_mbar_init(&f.wbar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  if (kPre && tid == 0) {
-    // my FC weight slices: three TMA bulk copies that land while the conv layers run
-    const int a0 = r * kF1 / CS, a1 = (r + 1) * kF1 / CS, c0 = r * kF2 / CS, c1 = (r + 1) * kF2 / CS;
-    const uint32_t n1 = (uint32_t)(a1 - a0) * kFlat * 4, n2 = (uint32_t)(c1 - c0) * kF1 * 4, n3 = kF3 * kF2 * 4;
-    cl_mbar_expect_tx(&f.wbar, n1 + n2 + n3);
-    cl_bulk_g2s(f.wf1, params + kOffF1W + (size_t)a0 * kFlat, n1, &f.wbar);
-    cl_bulk_g2s(f.wf2, params + kOffF2W + (size_t)c0 * kF1, n2, &f.wbar);
-    cl_bulk_g2s(f.wf3, params + kOffF3W, n3, &f.wbar);
-  }
   // tell the cluster "my barriers exist"; the matching wait sits just before the first remote store
   CL_TRACE(17);
   cl_cluster_arrive_relaxed();
   CL_TRACE(18);
 
   uint32_t phase = 0;
+  bool first_img = true;
   // One bulk copy per image. (Copying the 96 rows separately into the padded layout was tried first:
   // 96 tiny cp.async.bulk serialise in the TMA unit and cost 4.3 us per launch -- see profiles/.)
   auto load_image = [&](int im) {
@@ -377,30 +370,30 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       cl_bulk_g2s(s.xd, x + (size_t)im * kImgNumel, kImgNumel * 4, &s.mbar);
     }
   };
-  load_image(img);
-
-  // ---- weights: conv1 + conv2 in natural layout, plus the dgrad layout of conv2 ----
-  for (int i = tid; i < 456; i += kCLThreads) s.w1[i] = __ldg(params + (i < 450 ? kOffW1 + i : kOffB1 + (i - 450)));
-  for (int i = tid; i < 2400 / 4; i += kCLThreads)
-    reinterpret_cast<float4*>(s.w2)[i] = __ldg(reinterpret_cast<const float4*>(params + kOffW2) + i);
-  if (tid < 16) s.b2[tid] = __ldg(params + kOffB2 + tid);
-  if (kPre) {
-    if (tid < kF1) f.bf1[tid] = __ldg(params + kOffF1B + tid);
-    if (tid < kF2) f.bf2[tid] = __ldg(params + kOffF2B + tid);
-    if (tid < kF3) f.bf3[tid] = __ldg(params + kOffF3B + tid);
+  load_image(img);   // the input batch does not depend on the previous kernel of the stream ...
+  pdl_trigger();     // ... whose successor (the update kernel) may be scheduled from now on,
+  pdl_wait();        // but the weights do: they are written by the previous step's update kernel
+  if (tid == 0) {
+    // every weight this CTA needs arrives by TMA bulk copy, issued before anything else: the conv block now,
+    // (clusters >= 4) my FC row slices + the FC biases, which land while the conv layers run
+    cl_mbar_expect_tx(&s.cbar, kConvPrefix * 4);
+    cl_bulk_g2s(s.cw, params, kConvPrefix * 4, &s.cbar);
+    if (kPre) {
+      const int a0 = r * kF1 / CS, a1 = (r + 1) * kF1 / CS, c0 = r * kF2 / CS, c1 = (r + 1) * kF2 / CS;
+      const uint32_t n1 = (uint32_t)(a1 - a0) * kFlat * 4, n2 = (uint32_t)(c1 - c0) * kF1 * 4, n3 = kF3 * kF2 * 4;
+      cl_mbar_expect_tx(&f.wbar, n1 + n2 + n3 + kF1 * 4 + kF2 * 4 + 48);
+      cl_bulk_g2s(f.wf1, params + kOffF1W + (size_t)a0 * kFlat, n1, &f.wbar);
+      cl_bulk_g2s(f.wf2, params + kOffF2W + (size_t)c0 * kF1, n2, &f.wbar);
+      cl_bulk_g2s(f.wf3, params + kOffF3W, n3, &f.wbar);
+      cl_bulk_g2s(f.bf1, params + kOffF1B, kF1 * 4, &f.wbar);
+      cl_bulk_g2s(f.bf2, params + kOffF2B, kF2 * 4, &f.wbar);
+      cl_bulk_g2s(f.bf3, params + kOffF3B, 48, &f.wbar);  // 10 biases + 2 floats of the (zero) alignment gap
+    }
   }
+
   if (tid < 196) s.poff[tid] = (2 * (tid / 14)) * kXRow + 2 * (tid % 14);
   CL_TRACE(19);
-  __syncthreads();
   CL_TRACE(20);
-  for (int ot = tid; ot < 400; ot += kCLThreads) {  // one (o, tap) per thread: 8 contiguous floats
-    const int o = ot / 25, t = ot - o * 25;
-    const float* src = s.w2 + o * 150 + t;
-    float4 a = make_float4(src[0], src[25], src[50], src[75]);
-    float4 b = make_float4(src[100], src[125], 0.f, 0.f);
-    reinterpret_cast<float4*>(s.w2d)[ot * 2] = a;
-    reinterpret_cast<float4*>(s.w2d)[ot * 2 + 1] = b;
-  }
 
   // static work split of this CTA
   const int prow0 = r * 14 / CS, prow1 = (r + 1) * 14 / CS;      // conv1: pooled rows
@@ -426,6 +419,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       cl_mbar_expect_tx(&s.sbar[kBarG2], (kPre ? CS : 1) * kFlat * 4);
     }
     cl_mbar_wait(&s.mbar, phase);  // image landed
+    cl_mbar_wait(&s.cbar, 0);      // conv weights landed (first image; complete ever after)
     for (int i = tid; i < kImgNumel / 4; i += kCLThreads) {  // dense -> padded rows (36 floats, 16-byte aligned)
       const float4 v = reinterpret_cast<const float4*>(s.xd)[i];
       const int e = i * 4, c = e >> 10, h = (e >> 5) & 31, w = e & 31;
@@ -453,7 +447,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
               patch[rr][2 * q] = v.x;
               patch[rr][2 * q + 1] = v.y;
             }
-          const float* wb = s.w1 + (ch * 3 + c) * 25;
+          const float* wb = s.cw + kOffW1 + (ch * 3 + c) * 25;
 #pragma unroll
           for (int kh = 0; kh < 5; ++kh)
 #pragma unroll
@@ -465,7 +459,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
               a11 += w * patch[kh + 1][kw + 1];
             }
         }
-        const float bias = s.w1[450 + ch];
+        const float bias = s.cw[kOffB1 + ch];
         float best = fmaxf(a00 + bias, 0.f);
         int bi = 0;
         float v = fmaxf(a01 + bias, 0.f);
@@ -477,6 +471,14 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
         const uint32_t oi = (uint32_t)(ch * 196 + ph * 14 + pw);
         push_all<CS>(R, CL_OFF(p1) + 4u * oi, CL_BAR(kBarP1), __float_as_uint(best));
         push_all<CS>(R, CL_OFF(idx1) + 4u * oi, CL_BAR(kBarP1), (uint32_t)bi);
+      }
+    }
+    if (first_img) {  // conv2 weights in data-gradient layout [(o,tap)][c8]: built once, off the critical path
+      for (int ot = tid; ot < 400; ot += kCLThreads) {
+        const int o = ot / 25, t = ot - o * 25;
+        const float* src = s.cw + kOffW2 + o * 150 + t;
+        reinterpret_cast<float4*>(s.w2d)[ot * 2] = make_float4(src[0], src[25], src[50], src[75]);
+        reinterpret_cast<float4*>(s.w2d)[ot * 2 + 1] = make_float4(src[100], src[125], 0.f, 0.f);
       }
     }
     CL_TRACE(3);
@@ -499,7 +501,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
             patch[rr][2 * q] = v.x;
             patch[rr][2 * q + 1] = v.y;
           }
-        const float* wb = s.w2 + ((o0 + ol) * 6 + c) * 25;
+        const float* wb = s.cw + kOffW2 + ((o0 + ol) * 6 + c) * 25;
         float a00 = 0.f, a01 = 0.f, a10 = 0.f, a11 = 0.f;
 #pragma unroll
         for (int kh = 0; kh < 5; ++kh)
@@ -522,7 +524,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
           const float4 q = *reinterpret_cast<const float4*>(s.red + ((ol * 6 + c) * 25 + pp) * 4);
           v.x += q.x; v.y += q.y; v.z += q.z; v.w += q.w;
         }
-        const float bias = s.b2[o];
+        const float bias = s.cw[kOffB2 + o];
         float best = fmaxf(v.x + bias, 0.f);
         int bi = 0;
         float u = fmaxf(v.y + bias, 0.f);
@@ -759,6 +761,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       }
     }
     CL_TRACE(13);
+    first_img = false;
     if (trace != nullptr && tid == 0) trace[blockIdx.x * 32 + 15] = (long long)globaltimer_ns();
     phase ^= 1u;
     if (img + n_clusters < B) {
@@ -789,13 +792,17 @@ static int launch_cluster_t(const float* params, const float* x, const long long
   cfg.blockDim = dim3(kCLThreads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CS;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  // programmatic dependent launch: this kernel may be scheduled while the previous step's update kernel is
+  // still running; it loads its inputs, then waits (griddepcontrol.wait) before it reads the weights
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = 2;
   const float inv_batch = 1.f / (float)B;
   DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, params, x, labels, saved, part1, part2, img_loss, img_correct, B,
                                     inv_batch, trace));

@@ -577,6 +577,11 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
   const int slice = blockIdx.x, tid = threadIdx.x;
   const int i = slice * kSlice + 2 * tid;
   const bool in_range = i < kFlatNumel;
+  // programmatic dependent launch: the next step's forward/backward kernel may be scheduled from now on (it
+  // loads its input batch and then waits for us); we wait for OUR predecessor before touching anything it,
+  // or transitively the previous update kernel, has written
+  pdl_trigger();
+  pdl_wait();
   const unsigned long long step = *reinterpret_cast<volatile unsigned long long*>(&ctl->step);
   const unsigned int seq = (unsigned int)(step + 1ull);
 
@@ -692,8 +697,17 @@ int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int n_part1
     void* args[] = {(void*)&d_ctxs, (void*)&B, (void*)&n_part1, (void*)&loss_slot, (void*)&flags};
     DNN_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)update_kernel<true>, grid, dim3(kUpdThreads), args, 0, stream));
   } else {
-    update_kernel<false><<<grid, kUpdThreads, 0, stream>>>(d_ctxs, B, n_part1, loss_slot, flags);
-    DNN_CUDA_CHECK(cudaGetLastError());
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(kUpdThreads);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, update_kernel<false>, d_ctxs, B, n_part1, loss_slot, flags));
   }
   return kOk;
 }
