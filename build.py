@@ -54,6 +54,8 @@ def compile_one(src: Path, force: bool) -> Path:
     (OBJ_DIR / (src.stem + ".ptxas.log")).write_text(r.stderr)
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)
+        if LIB.exists():
+            LIB.unlink()  # never leave a stale library behind: a GPU run must not silently test old code
         raise RuntimeError(f"nvcc failed on {src.name}")
     stamp.write_text(dig)
     return obj

@@ -39,7 +39,7 @@ constexpr int kXCh = 32 * kXRow + 8;       //   kernel rows of a wgrad gather fa
 constexpr int kCLRed = 9408;               // CS=2 worst case: conv2 dgrad partials 16*6*98
 
 // stage barriers: one mbarrier per all-gather, completed by the st.async traffic itself
-enum { kBarP1 = 0, kBarP2, kBarH1, kBarH2, kBarD1, kBarG2, kNumStageBars };
+enum { kBarP1 = 0, kBarP2, kBarH1, kBarH2, kBarD1, kBarG2, kBarW1, kNumStageBars };
 
 struct __align__(16) CLSmem {
   alignas(16) float xd[kImgNumel];    // image as it is in global memory (ONE 12 KB TMA bulk copy)
@@ -269,10 +269,22 @@ struct FCSmem {
   alignas(8) unsigned long long wbar;   // weight prefetch
 };
 constexpr size_t kFcOff = (sizeof(CLSmem) + 127) & ~(size_t)127;
+// conv1 weight-gradient partials of the CTAs of a cluster, collected by CTA 0 (row d = CTA d: 450 weights + 6 biases)
+constexpr int kW1Row = 456;
 template <int CS>
-constexpr size_t cluster_smem_bytes() {
-  return CS >= 4 ? kFcOff + sizeof(FCSmem<CS>) : sizeof(CLSmem);
+struct W1Rx {
+  alignas(16) float rx[CS * kW1Row];
+};
+template <int CS>
+__host__ __device__ constexpr size_t w1rx_offset() {
+  return CS >= 4 ? ((kFcOff + sizeof(FCSmem<CS>) + 127) & ~(size_t)127) : kFcOff;
 }
+template <int CS>
+__host__ __device__ constexpr size_t cluster_smem_bytes() {
+  return w1rx_offset<CS>() + sizeof(W1Rx<CS>);
+}
+static_assert(cluster_smem_bytes<4>() <= 227 * 1024 && cluster_smem_bytes<2>() <= 227 * 1024 &&
+              cluster_smem_bytes<8>() <= 227 * 1024, "shared memory budget");
 
 // rows [m0, m1) of y = act(b + W . in) with the rows in shared memory (wsm[0] is row m0)
 template <int CS, int K, bool kRelu>
@@ -341,6 +353,8 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
   FCSmem<kPre ? CS : 4>& f = *reinterpret_cast<FCSmem<kPre ? CS : 4>*>(smem_raw + kFcOff);
   constexpr uint32_t kRxD1 = (uint32_t)(kFcOff + offsetof(FCSmem<kPre ? CS : 4>, rx_d1));
   constexpr uint32_t kRxG2 = (uint32_t)(kFcOff + offsetof(FCSmem<kPre ? CS : 4>, rx_g2));
+  constexpr uint32_t kRxW1 = (uint32_t)w1rx_offset<CS>();
+  const float* rx_w1 = reinterpret_cast<const float*>(smem_raw + w1rx_offset<CS>());
 
   Remote<CS> R;
 #pragma unroll
@@ -417,6 +431,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       cl_mbar_expect_tx(&s.sbar[kBarH2], kF2 * 4);
       cl_mbar_expect_tx(&s.sbar[kBarD1], (kPre ? CS : 1) * kF1 * 4);
       cl_mbar_expect_tx(&s.sbar[kBarG2], (kPre ? CS : 1) * kFlat * 4);
+      if (r == 0) cl_mbar_expect_tx(&s.sbar[kBarW1], CS * kW1Row * 4);
     }
     cl_mbar_wait(&s.mbar, phase);  // image landed
     cl_mbar_wait(&s.cbar, 0);      // conv weights landed (first image; complete ever after)
@@ -744,12 +759,13 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
         float* dst = s.red + pg * 450 + o * 75 + c * 25 + kh * 5;
         dst[0] = a0; dst[1] = a1; dst[2] = a2; dst[3] = a3; dst[4] = a4;
       } else if (warp == 15) {
-        float* dst = part1 + ((size_t)img * CS + r) * kOffW2;
-        for (int o = 0; o < 6; ++o) {
+        for (int o = 0; o < 6; ++o) {   // bias partial straight to CTA 0
           float a = 0.f;
           for (int q = q0 + lane; q < q1; q += 32) a += s.g1[o * 196 + q];
           a = warp_sum(a);
-          if (lane == 0) dst[kOffB1 + o] = a;
+          if (lane == 0)
+            cl_st_async(R.base[0] + kRxW1 + 4u * (uint32_t)(r * kW1Row + 450 + o), __float_as_uint(a),
+                        R.base[0] + CL_BAR(kBarW1));
         }
       }
       __syncthreads();
@@ -757,7 +773,19 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
         float a = 0.f;
 #pragma unroll
         for (int pg = 0; pg < 5; ++pg) a += s.red[pg * 450 + tid];
-        part1[((size_t)img * CS + r) * kOffW2 + tid] = a;
+        cl_st_async(R.base[0] + kRxW1 + 4u * (uint32_t)(r * kW1Row + tid), __float_as_uint(a),
+                    R.base[0] + CL_BAR(kBarW1));
+      }
+      if (r == 0) {
+        // CTA 0 adds the CS partials in CTA order and writes ONE conv1 gradient row per image, so the update
+        // kernel's first slice sums B rows instead of B*CS (it was that kernel's critical path)
+        cl_mbar_wait(&s.sbar[kBarW1], phase);
+        if (tid < kW1Row) {
+          float a = 0.f;
+#pragma unroll
+          for (int d = 0; d < CS; ++d) a += rx_w1[d * kW1Row + tid];
+          part1[(size_t)img * kOffW2 + (tid < 450 ? kOffW1 + tid : kOffB1 + (tid - 450))] = a;
+        }
       }
     }
     CL_TRACE(13);

@@ -203,7 +203,7 @@ static int cluster_size_for(const dnnb200_engine* e, int B) {
 // the forward/backward half of a step; returns the number of conv1 partial rows it produced
 static int fwd_bwd_any(dnnb200_engine* e, const float* x, const long long* y, int B, cudaStream_t s, int* n_part1) {
   const int cs = cluster_size_for(e, B);
-  *n_part1 = B * cs;
+  *n_part1 = B;  // clusters reduce their conv1 partials to one row per image before they write them
   if (cs == 1)
     return launch_fwd_bwd(true, e->params, x, y, e->saved, e->part1, e->part2, e->img_loss, e->img_correct, nullptr,
                           B, e->num_sms, s);
