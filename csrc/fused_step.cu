@@ -570,7 +570,8 @@ __device__ __forceinline__ float2 local_grad2(const RankCtx& cx, int i, int B, i
 // 8 x 122 CTAs must be co-resident (7 per SM => 36 registers). Production (one rank per GPU) is unconstrained.
 template <bool kEmulated>
 __global__ void __launch_bounds__(kUpdThreads, kEmulated ? 7 : 1)
-update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slot, int flags) {
+update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slot, int flags,
+              float* __restrict__ host_loss) {
   __shared__ ExchangeShared xsh;
   const RankCtx& cx = ctxs[blockIdx.y];
   StepCtl* ctl = cx.ctl;
@@ -619,6 +620,12 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
     if (tid == 0) {
       const float mean = a / (float)B;
       cx.loss_ring[loss_slot & cx.loss_ring_mask] = mean;
+      if (host_loss != nullptr) {
+        // the step's result goes straight to the caller's pinned host buffer: a 4-byte store over PCIe,
+        // no copy-engine operation and no extra stream dependency on the step path
+        *reinterpret_cast<volatile float*>(host_loss) = mean;
+        __threadfence_system();
+      }
       if (!grad_only) {
         ctl->loss_sum += mean;
         ctl->loss_steps += 1u;
@@ -690,11 +697,11 @@ int launch_fwd_bwd(bool train, const float* params, const float* x, const long l
 }
 
 int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int n_part1, int loss_slot, int flags,
-                  cudaStream_t stream) {
+                  float* host_loss, cudaStream_t stream) {
   dim3 grid(kNumSlices, n_virtual_ranks);
   if (n_virtual_ranks > 1) {
     // ranks emulated on ONE device wait on each other: every CTA must be resident
-    void* args[] = {(void*)&d_ctxs, (void*)&B, (void*)&n_part1, (void*)&loss_slot, (void*)&flags};
+    void* args[] = {(void*)&d_ctxs, (void*)&B, (void*)&n_part1, (void*)&loss_slot, (void*)&flags, (void*)&host_loss};
     DNN_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)update_kernel<true>, grid, dim3(kUpdThreads), args, 0, stream));
   } else {
     cudaLaunchConfig_t cfg = {};
@@ -707,7 +714,7 @@ int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int n_part1
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, update_kernel<false>, d_ctxs, B, n_part1, loss_slot, flags));
+    DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, update_kernel<false>, d_ctxs, B, n_part1, loss_slot, flags, host_loss));
   }
   return kOk;
 }

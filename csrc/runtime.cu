@@ -40,7 +40,7 @@ int launch_fwd_bwd_cluster(int cs, const float* params, const float* x, const lo
                            long long* trace, cudaStream_t stream);
 int max_active_clusters(int cs);
 int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int n_part1, int loss_slot, int flags,
-                  cudaStream_t stream);
+                  float* host_loss, cudaStream_t stream);
 int launch_eval_reduce(const float* img_loss, const int* img_correct, int N, int bs, double* out, cudaStream_t stream);
 int launch_allreduce(const RankCtx* d_ctxs, int n_virtual_ranks, const float* const* in, float* const* out, int n,
                      int mode, int two_shot, cudaStream_t stream);
@@ -115,7 +115,8 @@ struct dnnb200_engine {
   unsigned long long steps_launched = 0;  // host mirror: update launches (loss ring slot)
   int num_sms = 148;
   // host-fed ring
-  static constexpr int kRing = 4;
+  static constexpr int kRing = 16;   // device input slots
+  static constexpr int kGroup = 4;   // steps per event group (stream events break the kernels' programmatic overlap)
   cudaStream_t copy_stream = nullptr, d2h_stream = nullptr;
   cudaEvent_t slot_ready[kRing] = {}, slot_free[kRing] = {}, step_done[kRing] = {};
   float* d_x[kRing] = {};
@@ -216,7 +217,7 @@ static int step_kernels(dnnb200_engine* e, const float* x, const long long* y, i
   int rc = fwd_bwd_any(e, x, y, B, s, &n_part1);
   if (rc) return rc;
   rc = launch_update(e->d_ctx, 1, B, n_part1, (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask), flags,
-                     s);
+                     nullptr, s);
   if (rc) return rc;
   e->launches += 2;
   return kOk;
@@ -532,34 +533,38 @@ int dnnb200_engine_train_host(dnnb200_engine* e, const float* h_x, const int64_t
   cudaStream_t s = (cudaStream_t)stream;
   constexpr int R = dnnb200_engine::kRing;
   const size_t xb = (size_t)B * kImgNumel * sizeof(float), yb = (size_t)B * sizeof(long long);
-  for (int t = 0; t < nsteps; ++t) {
-    const int slot = (int)(e->ring_uses % R);
-    // copy stream: wait until the fwd/bwd kernel that last read this slot has finished
-    if (e->ring_uses >= (unsigned long long)R) DNN_CUDA_CHECK(cudaStreamWaitEvent(e->copy_stream, e->slot_free[slot], 0));
-    DNN_CUDA_CHECK(cudaMemcpyAsync(e->d_x[slot], h_x + (size_t)t * B * kImgNumel, xb, cudaMemcpyHostToDevice, e->copy_stream));
-    DNN_CUDA_CHECK(cudaMemcpyAsync(e->d_y[slot], h_y + (size_t)t * B, yb, cudaMemcpyHostToDevice, e->copy_stream));
-    DNN_CUDA_CHECK(cudaEventRecord(e->slot_ready[slot], e->copy_stream));
-    DNN_CUDA_CHECK(cudaStreamWaitEvent(s, e->slot_ready[slot], 0));
-    int n_part1 = B;
-    rc = fwd_bwd_any(e, e->d_x[slot], e->d_y[slot], B, s, &n_part1);
-    if (rc) return rc;
-    DNN_CUDA_CHECK(cudaEventRecord(e->slot_free[slot], s));
-    const int lslot = (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask);
-    rc = launch_update(e->d_ctx, 1, B, n_part1, lslot, 0, s);
-    if (rc) return rc;
-    e->launches += 2;
-    e->steps_launched += 1;
-    e->ring_uses += 1;
-    if (h_losses) {
-      DNN_CUDA_CHECK(cudaEventRecord(e->step_done[slot], s));
-      DNN_CUDA_CHECK(cudaStreamWaitEvent(e->d2h_stream, e->step_done[slot], 0));
-      DNN_CUDA_CHECK(cudaMemcpyAsync(h_losses + t, e->loss_ring + lslot, sizeof(float), cudaMemcpyDeviceToHost, e->d2h_stream));
+  // pinned host memory is addressable from the device (unified addressing): resolve the device view once
+  float* d_losses = nullptr;
+  if (h_losses) DNN_CUDA_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&d_losses), h_losses, 0));
+  // Steps are enqueued in groups of kGroup: each step still gets its own H2D copies, but the cross-stream events
+  // (inputs ready / slots free) are recorded once per group, so that inside a group nothing sits between the
+  // kernels in the stream and their programmatic dependent launches overlap.
+  constexpr int G = dnnb200_engine::kGroup;
+  for (int t0 = 0; t0 < nsteps; t0 += G) {
+    const int n = nsteps - t0 < G ? nsteps - t0 : G;
+    const int gslot = (int)((e->ring_uses / G) % (R / G));        // group index in the ring
+    if (e->ring_uses >= (unsigned long long)R) DNN_CUDA_CHECK(cudaStreamWaitEvent(e->copy_stream, e->slot_free[gslot], 0));
+    for (int k = 0; k < n; ++k) {
+      const int slot = gslot * G + k, t = t0 + k;
+      DNN_CUDA_CHECK(cudaMemcpyAsync(e->d_x[slot], h_x + (size_t)t * B * kImgNumel, xb, cudaMemcpyHostToDevice, e->copy_stream));
+      DNN_CUDA_CHECK(cudaMemcpyAsync(e->d_y[slot], h_y + (size_t)t * B, yb, cudaMemcpyHostToDevice, e->copy_stream));
     }
-  }
-  if (h_losses) {
-    // make `stream` the single thing the caller has to synchronise
-    DNN_CUDA_CHECK(cudaEventRecord(e->step_done[0], e->d2h_stream));
-    DNN_CUDA_CHECK(cudaStreamWaitEvent(s, e->step_done[0], 0));
+    DNN_CUDA_CHECK(cudaEventRecord(e->slot_ready[gslot], e->copy_stream));
+    DNN_CUDA_CHECK(cudaStreamWaitEvent(s, e->slot_ready[gslot], 0));
+    for (int k = 0; k < n; ++k) {
+      const int slot = gslot * G + k, t = t0 + k;
+      int n_part1 = B;
+      rc = fwd_bwd_any(e, e->d_x[slot], e->d_y[slot], B, s, &n_part1);
+      if (rc) return rc;
+      // The step's mean loss is written by the update kernel itself into h_losses[t] (device->host, 4 bytes).
+      const int lslot = (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask);
+      rc = launch_update(e->d_ctx, 1, B, n_part1, lslot, 0, d_losses ? d_losses + t : nullptr, s);
+      if (rc) return rc;
+      e->launches += 2;
+      e->steps_launched += 1;
+    }
+    DNN_CUDA_CHECK(cudaEventRecord(e->slot_free[gslot], s));
+    e->ring_uses += G;   // a short last group still consumes a whole group of slots
   }
   return kOk;
 }
@@ -655,7 +660,7 @@ int dnnb200_vr_step(dnnb200_engine** engines, int n, const float* const* xs, con
   int rc = gather_ctxs(live.data(), (int)live.size(), &d);
   if (rc) return rc;
   const int lslot = (int)(live[0]->steps_launched & (unsigned long long)live[0]->loss_ring_mask);
-  rc = launch_update(d, (int)live.size(), B, n_part1, lslot, 0, s);
+  rc = launch_update(d, (int)live.size(), B, n_part1, lslot, 0, nullptr, s);
   cudaStreamSynchronize(s);
   cudaFree(d);
   if (rc) return rc;

@@ -121,9 +121,10 @@ int dnnb200_engine_step(dnnb200_engine* e, const float* x, const int64_t* y, int
  * no per-step Python (the whole dataset fits in HBM many times over) */
 int dnnb200_engine_train_device(dnnb200_engine* e, const float* x, const int64_t* y, int B, int nsteps, void* stream);
 /* nsteps steps fed from PINNED host memory: per step an async H2D copy of that step's
- * inputs (4-slot device ring on a copy stream), the two kernels, and an async D2H copy of
- * the step's mean loss into h_losses[t] (pinned). Returns after everything is enqueued;
- * the caller synchronises `stream` before reading h_losses. */
+ * inputs (16-slot device ring on a copy stream, events every 4 steps) and the two kernels; the update kernel writes
+ * the step's mean loss straight into h_losses[t] (pinned host memory, 4 bytes device->host per
+ * step). Returns after everything is enqueued; the caller synchronises `stream` before reading
+ * h_losses. */
 int dnnb200_engine_train_host(dnnb200_engine* e, const float* h_x, const int64_t* h_y, int B, int nsteps,
                               float* h_losses, void* stream);
 /* forward only over N device-resident images; h_out2 = {mean over batches of the batch-mean
