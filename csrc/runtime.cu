@@ -56,6 +56,7 @@ int launch_sgd_momentum(float*, const float*, float*, int, float, float, int, fl
 int launch_tc_conv_relu_pool_fwd(const float*, const float*, const float*, float*, unsigned char*, int, int, int, int,
                                  int, cudaStream_t);
 int launch_tc_gemm_probe(const float*, const float*, float*, int, cudaStream_t);
+int launch_tc_linear_fwd(const float*, const float*, const float*, float*, int, int, int, int, cudaStream_t);
 
 // ---- tiny control kernels ---------------------------------------------------
 __global__ void ctl_set_hparams_kernel(StepCtl* c, float lr, float mu) { c->lr = lr; c->mu = mu; }
@@ -256,6 +257,11 @@ int dnnb200_tc_conv_relu_pool_fwd(const float* x, const float* w, const float* b
                                   int Ci, int H, int W, int Co, void* stream) {
   DNN_ARG_CHECK(N > 0, "tc_conv_relu_pool_fwd: empty batch");
   return launch_tc_conv_relu_pool_fwd(x, w, b, y, idx, N, Ci, H, W, Co, (cudaStream_t)stream);
+}
+int dnnb200_tc_linear_fwd(const float* x, const float* w, const float* b, float* y, int N, int M, int K, int relu,
+                          void* stream) {
+  DNN_ARG_CHECK(N > 0, "tc_linear_fwd: empty batch");
+  return launch_tc_linear_fwd(x, w, b, y, N, M, K, relu, (cudaStream_t)stream);
 }
 int dnnb200_tc_gemm_probe(const float* A, const float* B, float* D, int K, void* stream) {
   return launch_tc_gemm_probe(A, B, D, K, (cudaStream_t)stream);

@@ -20,8 +20,9 @@ import torch.nn.functional as F
 from . import native
 
 
-# Precision of the conv forward on CUDA: "tf32" runs the tcgen05 implicit-GEMM kernel (TF32 operands,
-# fp32 accumulate -- what PyTorch itself does for cuDNN convolutions by default), "fp32" the FFMA kernel.
+# Precision of the GEMM-shaped FORWARD ops (conv, linear) on CUDA: "tf32" runs the tcgen05 kernels (TF32
+# operands, fp32 accumulate -- what PyTorch itself does for cuDNN convolutions by default), "fp32" the FFMA
+# kernels. Backward and the fused step engine are fp32 either way.
 _conv_precision = "tf32"
 
 
@@ -89,7 +90,11 @@ class _Linear(torch.autograd.Function):
     def forward(ctx, x, w, b, relu):
         x = x.contiguous().float()
         y = torch.empty((x.shape[0], w.shape[0]), device=x.device, dtype=torch.float32)
-        native.linear_fwd(x, w.contiguous(), b.contiguous(), y, relu)
+        w = w.contiguous()
+        if _conv_precision == "tf32" and native.tc_linear_supported(x, w):
+            native.tc_linear_fwd(x, w, b.contiguous(), y, relu)
+        else:
+            native.linear_fwd(x, w, b.contiguous(), y, relu)
         ctx.save_for_backward(x, w, y)
         ctx.relu = relu
         ctx.needs_dx = x.requires_grad

@@ -151,6 +151,18 @@ def linear_fwd(x, w, b, y, relu: bool) -> None:
                                   N, w.shape[0], K, int(relu), _stream()))
 
 
+def tc_linear_fwd(x, w, b, y, relu: bool) -> None:
+    """Tensor-core (tcgen05 + TMA, TF32) version of linear_fwd; needs M <= 128 and K % 4 == 0."""
+    lib = require()
+    N, K = x.shape
+    _check(lib.dnnb200_tc_linear_fwd(_p(_f32(x, "x")), _p(_f32(w, "w")), _p(_f32(b, "b")), _p(_f32(y, "y")),
+                                     N, w.shape[0], K, int(relu), _stream()))
+
+
+def tc_linear_supported(x, w) -> bool:
+    return w.shape[0] <= 128 and x.shape[1] % 4 == 0 and x.data_ptr() % 16 == 0 and w.data_ptr() % 16 == 0
+
+
 def linear_bwd(x, w, y, dy, dx, dw, db, relu: bool) -> None:
     lib = require()
     N, K = x.shape

@@ -50,6 +50,10 @@ int dnnb200_tc_gemm_probe(const float* A, const float* B, float* D, int K, void*
 /* y[N,M] = act(x[N,K] w[M,K]^T + b[M]) (K8-K10) */
 int dnnb200_linear_fwd(const float* x, const float* w, const float* b, float* y, int N, int M, int K,
                        int relu, void* stream);
+/* the same forward on the tensor cores: tcgen05.mma kind::tf32, TMEM accumulators, both operands loaded by
+ * TMA through 2-D tensor maps with 128-byte swizzle (csrc/tc_linear.cu). M <= 128, K % 4 == 0. */
+int dnnb200_tc_linear_fwd(const float* x, const float* w, const float* b, float* y, int N, int M, int K,
+                          int relu, void* stream);
 /* dx may be NULL; y is the layer OUTPUT (its sign gives ReLU') (K13, K14) */
 int dnnb200_linear_bwd(const float* x, const float* w, const float* y, const float* dy, float* dx,
                        float* dw, float* db, int N, int M, int K, int relu, void* stream);

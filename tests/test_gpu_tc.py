@@ -51,6 +51,20 @@ def test_tc_conv_relu_pool_forward(N, Ci, H, Co):
     assert agree.float().mean().item() > 0.995          # TF32 rounding may flip near-ties
 
 
+@pytest.mark.parametrize("N,K,M,relu", [(16, 400, 120, True), (16, 120, 84, True), (16, 84, 10, False),
+                                        (1, 400, 120, True), (300, 400, 120, True), (1000, 120, 84, False)])
+def test_tc_linear_forward_tma_tcgen05(N, K, M, relu):
+    torch.manual_seed(N + K)
+    x, w, b = torch.randn(N, K), torch.randn(M, K) * K ** -0.5, torch.randn(M) * 0.1
+    want = F.linear(x, w, b)
+    want = F.relu(want) if relu else want
+    y = torch.full((N, M), float("nan"), device="cuda")
+    native.tc_linear_fwd(x.cuda(), w.cuda(), b.cuda(), y, relu)
+    torch.cuda.synchronize()
+    assert torch.isfinite(y).all()
+    assert _rel(y, want) < 4e-3, _rel(y, want)
+
+
 def test_network_forward_uses_tensor_cores_by_default_and_fp32_on_request():
     from distributed_neural_network_b200 import Network
     import copy
