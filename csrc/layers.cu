@@ -277,11 +277,16 @@ int launch_conv_relu_pool_fwd(const float* x, const float* w, const float* b, fl
   return kOk;
 }
 
+int launch_tc_conv2_dgrad(const float* w, const float* y, const unsigned char* idx, const float* dy, float* dx, int N,
+                          cudaStream_t s);
+
 int launch_conv_relu_pool_bwd(const float* x, const float* w, const float* y, const unsigned char* idx,
                               const float* dy, float* dx, float* dw, float* db, int N, int Ci, int H, int W,
-                              int Co, cudaStream_t s) {
+                              int Co, int tensor_core_dgrad, cudaStream_t s) {
   conv_relu_pool_wgrad_kernel<<<Co * Ci, 256, 0, s>>>(x, y, idx, dy, dw, db, N, Ci, H, W, Co);
   DNN_CUDA_CHECK(cudaGetLastError());
+  if (dx && tensor_core_dgrad && Ci == 6 && H == 14 && W == 14 && Co == 16)
+    return launch_tc_conv2_dgrad(w, y, idx, dy, dx, N, s);   // tcgen05 implicit GEMM (TF32)
   if (dx) {
     conv_relu_pool_dgrad_kernel<<<grid_for((long long)N * Ci * H * W, 256), 256, 0, s>>>(w, y, idx, dy, dx, N, Ci,
                                                                                          H, W, Co);

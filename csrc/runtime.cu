@@ -47,7 +47,7 @@ int launch_allreduce(const RankCtx* d_ctxs, int n_virtual_ranks, const float* co
 int launch_conv_relu_pool_fwd(const float*, const float*, const float*, float*, unsigned char*, int, int, int, int,
                               int, cudaStream_t);
 int launch_conv_relu_pool_bwd(const float*, const float*, const float*, const unsigned char*, const float*, float*,
-                              float*, float*, int, int, int, int, int, cudaStream_t);
+                              float*, float*, int, int, int, int, int, int, cudaStream_t);
 int launch_linear_fwd(const float*, const float*, const float*, float*, int, int, int, int, cudaStream_t);
 int launch_linear_bwd(const float*, const float*, const float*, const float*, float*, float*, float*, int, int, int,
                       int, cudaStream_t);
@@ -251,7 +251,12 @@ int dnnb200_conv_relu_pool_fwd(const float* x, const float* w, const float* b, f
 int dnnb200_conv_relu_pool_bwd(const float* x, const float* w, const float* y, const uint8_t* idx, const float* dy,
                                float* dx, float* dw, float* db, int N, int Ci, int H, int W, int Co, void* stream) {
   DNN_ARG_CHECK(N > 0 && Ci > 0 && Co > 0, "conv_relu_pool_bwd: bad shape");
-  return launch_conv_relu_pool_bwd(x, w, y, idx, dy, dx, dw, db, N, Ci, H, W, Co, (cudaStream_t)stream);
+  return launch_conv_relu_pool_bwd(x, w, y, idx, dy, dx, dw, db, N, Ci, H, W, Co, 0, (cudaStream_t)stream);
+}
+int dnnb200_conv_relu_pool_bwd_tc(const float* x, const float* w, const float* y, const uint8_t* idx, const float* dy,
+                                  float* dx, float* dw, float* db, int N, int Ci, int H, int W, int Co, void* stream) {
+  DNN_ARG_CHECK(N > 0 && Ci > 0 && Co > 0, "conv_relu_pool_bwd_tc: bad shape");
+  return launch_conv_relu_pool_bwd(x, w, y, idx, dy, dx, dw, db, N, Ci, H, W, Co, 1, (cudaStream_t)stream);
 }
 int dnnb200_tc_conv_relu_pool_fwd(const float* x, const float* w, const float* b, float* y, uint8_t* idx, int N,
                                   int Ci, int H, int W, int Co, void* stream) {

@@ -236,6 +236,115 @@ tc_conv_relu_pool_fwd_kernel(const float* __restrict__ x, const float* __restric
   if (warp == 0) tmem_free<C::TMEM_COLS>(tmem);
 }
 
+// ------------------------------------------------------------------------------------------
+// conv2 data gradient (K16 dgrad) with ReLU'/maxpool' folded into the prologue (K14/K15):
+//   dX[c][ih][iw] = sum_{o,kh,kw} dC[o][ih-kh][iw-kw] W[o][c][kh][kw]
+// is a correlation of the zero-padded dense gradient plane dCp (18x18, border 4) with the FLIPPED
+// filter: dX[ih][iw] = sum_{a,b} dCp[ih+a][iw+b] W[4-a][4-b]. So it is the same implicit GEMM as the
+// forward: the 16 conv2 channels are four NHWC4 planes, GEMM row m = ih*18 + iw, the A operand of
+// tap (a,b) is the plane shifted by a*18+b pixels, K = 25 taps x 4 planes = 100 chunks (50 MMAs per
+// tile of 128 rows), N = 16 (6 input channels used). The prologue scatters the pooled gradient to the
+// argmax position of each 2x2 window, masked by ReLU, directly into the planes.
+// ------------------------------------------------------------------------------------------
+struct DgradCfg {
+  static constexpr int WP = 18;                           // padded plane width/height
+  static constexpr int TILES = 2;                         // rows 0 .. 13*18+13 = 247
+  static constexpr int PLANE_PIX = 2 * 128 + 4 * 18 + 4 + 12;   // reach of the last tap, multiple of 8 -> 344
+  static constexpr int NMMA = 50;
+  static constexpr size_t kPlaneBytes = (size_t)PLANE_PIX * 16;
+  static constexpr size_t kBBytes = (size_t)2 * 100 * 128;
+  static constexpr size_t kSmemBytes = 4 * kPlaneBytes + kBBytes;
+};
+
+__global__ void __launch_bounds__(128)
+tc_conv2_dgrad_kernel(const float* __restrict__ w, const float* __restrict__ y, const unsigned char* __restrict__ idx,
+                      const float* __restrict__ dy, float* __restrict__ dx, int N) {
+  using C = DgradCfg;
+  extern __shared__ __align__(128) unsigned char smem[];
+  float* planes = reinterpret_cast<float*>(smem);                 // 4 planes of NHWC4 pixels
+  float* sB = planes + 4 * C::PLANE_PIX * 4;                      // flipped weights, canonical K-major
+  __shared__ uint64_t bar_mma;
+  __shared__ uint32_t tmem_slot;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) { mbar_init(&bar_mma, 1); mbar_fence_init(); }
+  if (warp == 0) tmem_alloc<32>(&tmem_slot);
+  // B[n = c][chunk q = tap*4 + g][k = channel o%4]: W[o = g*4+k][c][4-a][4-b] with tap = a*5+b
+  for (int i = tid; i < (int)(C::kBBytes / 4); i += 128) {
+    const int k = i & 3, nr = (i >> 2) & 7, q = (i >> 5) % 100, ng = (i >> 5) / 100;
+    const int c = ng * 8 + nr, tap = q >> 2, g = q & 3, o = g * 4 + k;
+    const int a = tap / 5, b = tap - a * 5;
+    sB[i] = c < 6 ? __ldg(w + ((size_t)o * 6 + c) * 25 + (4 - a) * 5 + (4 - b)) : 0.f;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  constexpr uint32_t kIdesc = idesc_tf32(128, 16);
+  uint32_t phase = 0;
+  for (int img = blockIdx.x; img < N; img += gridDim.x) {
+    for (int i = tid; i < 4 * C::PLANE_PIX; i += 128) reinterpret_cast<float4*>(planes)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncthreads();
+    for (int i = tid; i < 400; i += 128) {   // maxpool' + ReLU': gradient goes to the argmax of its window
+      const int o = i / 25, pp = i - o * 25, ph = pp / 5, pw = pp - ph * 5;
+      const size_t gi = (size_t)img * 400 + i;
+      const float g = y[gi] > 0.f ? dy[gi] : 0.f;
+      const int id = idx[gi];
+      const int pix = (2 * ph + (id >> 1) + 4) * C::WP + 2 * pw + (id & 1) + 4;
+      planes[((size_t)(o >> 2) * C::PLANE_PIX + pix) * 4 + (o & 3)] = g;
+    }
+    fence_proxy_async();
+    __syncthreads();
+    if (tid == 0) {
+      const uint32_t a0 = smem_u32(planes), b0 = smem_u32(sB);
+#pragma unroll 1
+      for (int t = 0; t < C::TILES; ++t)
+#pragma unroll 1
+        for (int j = 0; j < C::NMMA; ++j) {
+          const int tap = j >> 1, gp = (j & 1) * 2;   // this MMA: planes gp and gp+1 of tap
+          const int off = (tap / 5) * C::WP + (tap % 5);
+          const uint64_t ad = smem_desc_nosw(a0 + (uint32_t)(gp * C::kPlaneBytes) + (uint32_t)(t * 128 + off) * 16,
+                                             (uint32_t)C::kPlaneBytes, 128);
+          const uint64_t bd = smem_desc_nosw(b0 + (uint32_t)(2 * j) * 128, 128, 100 * 128);
+          mma_tf32(tmem + (uint32_t)t * 16, ad, bd, kIdesc, j > 0);
+        }
+      mma_commit(&bar_mma);
+    }
+    mbar_wait(&bar_mma, phase);
+    tc_fence_after();
+#pragma unroll 1
+    for (int t = 0; t < C::TILES; ++t) {
+      const int m = t * 128 + warp * 32 + lane, ih = m / C::WP, iw = m - ih * C::WP;
+      float v[8];
+      tmem_ld8(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)t * 16, v);
+      if (ih < 14 && iw < 14) {
+#pragma unroll
+        for (int c = 0; c < 6; ++c) dx[((size_t)img * 6 + c) * 196 + ih * 14 + iw] = v[c];
+      }
+    }
+    tc_fence_before();
+    __syncthreads();
+    phase ^= 1u;
+  }
+  if (warp == 0) tmem_free<32>(tmem);
+}
+
+int launch_tc_conv2_dgrad(const float* w, const float* y, const unsigned char* idx, const float* dy, float* dx, int N,
+                          cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    DNN_CUDA_CHECK(cudaFuncSetAttribute(tc_conv2_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)DgradCfg::kSmemBytes));
+    attr_set = true;
+  }
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int grid = N < sms * 4 ? N : sms * 4;
+  tc_conv2_dgrad_kernel<<<grid, 128, DgradCfg::kSmemBytes, s>>>(w, y, idx, dy, dx, N);
+  DNN_CUDA_CHECK(cudaGetLastError());
+  return kOk;
+}
+
 template <int CI, int HIN, int CO>
 static int launch_tc_conv_t(const float* x, const float* w, const float* b, float* y, unsigned char* idx, int N,
                             cudaStream_t s) {

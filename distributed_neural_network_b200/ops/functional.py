@@ -71,7 +71,7 @@ class _ConvReluPool(torch.autograd.Function):
         dx = torch.empty_like(x) if ctx.needs_dx else None
         dw = torch.empty_like(w)
         db = torch.empty(w.shape[0], device=w.device, dtype=torch.float32)
-        native.conv_relu_pool_bwd(x, w.contiguous(), y, idx, dy, dx, dw, db)
+        native.conv_relu_pool_bwd(x, w.contiguous(), y, idx, dy, dx, dw, db, tensor_cores=_conv_precision == "tf32")
         return dx, dw, db
 
 

@@ -136,10 +136,11 @@ def tc_gemm_probe(A, B, D) -> None:
     _check(require().dnnb200_tc_gemm_probe(_p(_f32(A, "A")), _p(_f32(B, "B")), _p(_f32(D, "D")), A.shape[1], _stream()))
 
 
-def conv_relu_pool_bwd(x, w, y, idx, dy, dx, dw, db) -> None:
+def conv_relu_pool_bwd(x, w, y, idx, dy, dx, dw, db, tensor_cores: bool = False) -> None:
     lib = require()
     N, Ci, H, W = x.shape
-    _check(lib.dnnb200_conv_relu_pool_bwd(_p(_f32(x, "x")), _p(_f32(w, "w")), _p(_f32(y, "y")), _p(idx),
+    fn = lib.dnnb200_conv_relu_pool_bwd_tc if tensor_cores else lib.dnnb200_conv_relu_pool_bwd
+    _check(fn(_p(_f32(x, "x")), _p(_f32(w, "w")), _p(_f32(y, "y")), _p(idx),
                                           _p(_f32(dy, "dy")), _p(dx), _p(_f32(dw, "dw")), _p(_f32(db, "db")),
                                           N, Ci, H, W, w.shape[0], _stream()))
 

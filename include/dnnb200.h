@@ -40,6 +40,11 @@ int dnnb200_conv_relu_pool_fwd(const float* x, const float* w, const float* b, f
 int dnnb200_conv_relu_pool_bwd(const float* x, const float* w, const float* y, const uint8_t* idx,
                                const float* dy, float* dx, float* dw, float* db,
                                int N, int Ci, int H, int W, int Co, void* stream);
+/* as above, with the data gradient of the 6x14x14 -> 16 layer computed on the tensor cores (tcgen05 implicit
+ * GEMM over the zero-padded gradient planes with the flipped filter; TF32). Other shapes fall back to FFMA. */
+int dnnb200_conv_relu_pool_bwd_tc(const float* x, const float* w, const float* y, const uint8_t* idx,
+                                  const float* dy, float* dx, float* dw, float* db,
+                                  int N, int Ci, int H, int W, int Co, void* stream);
 /* the same forward on the tensor cores: implicit GEMM, tcgen05.mma kind::tf32 with TMEM accumulators,
  * the shared-memory descriptor performs the im2col (csrc/tc_conv.cu). TF32 operands, fp32 accumulate.
  * Instantiated for the two conv layers of the CNN: (Ci,H,W,Co) = (3,32,32,6) and (6,14,14,16). */

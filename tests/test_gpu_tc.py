@@ -65,6 +65,27 @@ def test_tc_linear_forward_tma_tcgen05(N, K, M, relu):
     assert _rel(y, want) < 4e-3, _rel(y, want)
 
 
+@pytest.mark.parametrize("N", [1, 16, 333])
+def test_tc_conv2_dgrad(N):
+    torch.manual_seed(N)
+    x = torch.randn(N, 6, 14, 14, requires_grad=True)
+    w = (torch.randn(16, 6, 5, 5) * 150 ** -0.5).requires_grad_(True)
+    b = (torch.randn(16) * 0.1).requires_grad_(True)
+    out = F.max_pool2d(F.relu(F.conv2d(x, w, b)), 2, 2)
+    gy = torch.randn_like(out)
+    out.backward(gy)
+    xg = x.detach().cuda().requires_grad_(True)
+    wg, bg = w.detach().cuda().requires_grad_(True), b.detach().cuda().requires_grad_(True)
+    Fn.set_conv_precision("fp32")                      # exact forward (argmax identical to the oracle) ...
+    try:
+        yg = Fn.conv_relu_pool(xg, wg, bg)
+    finally:
+        Fn.set_conv_precision("tf32")
+    yg.backward(gy.cuda())                             # ... tensor-core data gradient, FFMA weight gradient
+    assert _rel(xg.grad, x.grad) < 4e-3, _rel(xg.grad, x.grad)
+    assert _rel(wg.grad, w.grad) < 1e-4 and _rel(bg.grad, b.grad) < 1e-4
+
+
 def test_network_forward_uses_tensor_cores_by_default_and_fp32_on_request():
     from distributed_neural_network_b200 import Network
     import copy
