@@ -187,6 +187,37 @@ allreduce_kernel(const RankCtx* __restrict__ ctxs, const ArParams prm) {
   }
 }
 
+// ---- latency probe: ping-pong of one 16-byte LL line between two ranks over peer memory -------------
+// (mailbox = word 124.. of the second flag bank, which no collective uses)
+__global__ void pingpong_kernel(const RankCtx* __restrict__ cxp, int peer, int iters, unsigned int base_seq,
+                                long long* __restrict__ out_ns) {
+  const RankCtx& cx = *cxp;
+  if (threadIdx.x != 0) return;
+  float* mine = reinterpret_cast<float*>(cx.flags[cx.rank] + (kMaxWorld + peer) * kFlagRow + 124);
+  float* theirs = reinterpret_cast<float*>(cx.flags[peer] + (kMaxWorld + cx.rank) * kFlagRow + 124);
+  const bool first = cx.rank < peer;
+  const unsigned long long t0 = globaltimer_ns();
+  float a, b;
+  for (int i = 0; i < iters; ++i) {
+    const unsigned int seq = base_seq + (unsigned int)i;
+    if (first) {
+      st_ll(theirs, 1.f, 2.f, seq);
+      while (!ld_ll(mine, seq, &a, &b)) {}
+    } else {
+      while (!ld_ll(mine, seq, &a, &b)) {}
+      st_ll(theirs, 1.f, 2.f, seq);
+    }
+  }
+  *out_ns = (long long)(globaltimer_ns() - t0);
+}
+
+int launch_pingpong(const RankCtx* d_ctx, int peer, int iters, unsigned int base_seq, long long* d_out_ns,
+                    cudaStream_t stream) {
+  pingpong_kernel<<<1, 32, 0, stream>>>(d_ctx, peer, iters, base_seq, d_out_ns);
+  DNN_CUDA_CHECK(cudaGetLastError());
+  return kOk;
+}
+
 int launch_allreduce(const RankCtx* d_ctxs, int n_virtual_ranks, const float* const* in, float* const* out,
                      int n, int mode, int two_shot, cudaStream_t stream) {
   DNN_ARG_CHECK(n > 0 && n <= kFlatNumel && (n % 4) == 0, "allreduce: n must be a multiple of 4 and <= %d", kFlatNumel);

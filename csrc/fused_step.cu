@@ -581,8 +581,11 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
   // programmatic dependent launch: the next step's forward/backward kernel may be scheduled from now on (it
   // loads its input batch and then waits for us); we wait for OUR predecessor before touching anything it,
   // or transitively the previous update kernel, has written
-  pdl_trigger();
+  long long* tr = cx.trace;
+  if (tr && tid == 0) tr[slice * 4 + 0] = (long long)globaltimer_ns();
+  if (!(flags & 2)) pdl_trigger();
   pdl_wait();
+  if (tr && tid == 0) tr[slice * 4 + 1] = (long long)globaltimer_ns();
   const unsigned long long step = *reinterpret_cast<volatile unsigned long long*>(&ctl->step);
   const unsigned int seq = (unsigned int)(step + 1ull);
 
@@ -593,7 +596,9 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
   }
   const bool grad_only = (flags & 1) != 0;  // tests: leave the local batch gradient in cx.grads, touch nothing else
   int n = 1;
+  if (tr && tid == 0) tr[slice * 4 + 2] = (long long)globaltimer_ns();
   if (cx.world > 1 && !grad_only) exchange_slice<2>(cx, &xsh, slice, seq, i, in_range, v, &n);
+  if (tr && tid == 0) tr[slice * 4 + 3] = (long long)globaltimer_ns();
 
   if (in_range && grad_only) {
     if (cx.grads) *reinterpret_cast<float2*>(cx.grads + i) = make_float2(v[0], v[1]);

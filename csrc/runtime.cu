@@ -39,6 +39,8 @@ int launch_fwd_bwd_cluster(int cs, const float* params, const float* x, const lo
                            float* part1, float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
                            long long* trace, cudaStream_t stream);
 int max_active_clusters(int cs);
+int launch_pingpong(const RankCtx* d_ctx, int peer, int iters, unsigned int base_seq, long long* d_out_ns,
+                    cudaStream_t stream);
 int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int n_part1, int loss_slot, int flags,
                   float* host_loss, cudaStream_t stream);
 int launch_eval_reduce(const float* img_loss, const int* img_correct, int N, int bs, double* out, cudaStream_t stream);
@@ -98,6 +100,7 @@ struct dnnb200_engine {
   float *params = nullptr, *momentum = nullptr, *grads = nullptr;
   float *saved = nullptr, *part1 = nullptr, *part2 = nullptr, *img_loss = nullptr;
   long long* trace = nullptr;      // development aid: per-CTA stage timestamps of the cluster kernel
+  int debug_flags = 0;             // OR-ed into the update kernel's flags (bit 1: no early launch of the successor)
   int forced_cluster = 0;          // 0 = pick per batch size
   int max_clusters[9] = {};        // resident clusters of the fwd/bwd kernel per cluster size (index = CS)
   int* img_correct = nullptr;
@@ -217,8 +220,8 @@ static int step_kernels(dnnb200_engine* e, const float* x, const long long* y, i
   int n_part1 = B;
   int rc = fwd_bwd_any(e, x, y, B, s, &n_part1);
   if (rc) return rc;
-  rc = launch_update(e->d_ctx, 1, B, n_part1, (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask), flags,
-                     nullptr, s);
+  rc = launch_update(e->d_ctx, 1, B, n_part1, (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask),
+                     flags | e->debug_flags, nullptr, s);
   if (rc) return rc;
   e->launches += 2;
   return kOk;
@@ -486,6 +489,33 @@ int dnnb200_engine_set_trace(dnnb200_engine* e, long long* d_trace) {
   DNN_ARG_CHECK(e, "null engine");
   e->trace = d_trace;
   return kOk;
+}
+
+int dnnb200_engine_pingpong(dnnb200_engine* e, int peer, int iters, double* h_one_way_us, void* stream) {
+  DNN_ARG_CHECK(e && h_one_way_us && e->group && e->group->world > 1, "pingpong needs an attached group of >= 2 ranks");
+  DNN_ARG_CHECK(peer >= 0 && peer < e->group->world && peer != e->group->rank && iters > 0, "pingpong: bad peer/iters");
+  static unsigned int seq = 1000;   // every call uses fresh sequence numbers (both ranks call in lockstep)
+  int rc = launch_pingpong(e->d_ctx, peer, iters, seq, reinterpret_cast<long long*>(e->d_eval_out), (cudaStream_t)stream);
+  seq += (unsigned int)iters;
+  if (rc) return rc;
+  long long ns = 0;
+  DNN_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
+  DNN_CUDA_CHECK(cudaMemcpy(&ns, e->d_eval_out, sizeof(ns), cudaMemcpyDeviceToHost));
+  *h_one_way_us = (double)ns / 1e3 / (2.0 * iters);
+  e->launches += 1;
+  return kOk;
+}
+
+int dnnb200_engine_set_debug_flags(dnnb200_engine* e, int flags) {
+  DNN_ARG_CHECK(e, "null engine");
+  e->debug_flags = flags;
+  return kOk;
+}
+
+int dnnb200_engine_set_update_trace(dnnb200_engine* e, long long* d_trace) {
+  DNN_ARG_CHECK(e, "null engine");
+  e->h_ctx.trace = d_trace;
+  return push_ctx(e, nullptr);
 }
 
 int dnnb200_engine_cluster_info(const dnnb200_engine* e, int B, int* chosen, int* max_clusters9) {

@@ -51,6 +51,7 @@ struct RankCtx {
   int rank;
   int world;
   int pad_;
+  long long* trace;       // development aid: update-kernel timestamps (globaltimer ns), nullptr in production
   float* recv[kMaxWorld];          // recv[p]  = rank p's receive area as mapped in THIS process
   unsigned int* flags[kMaxWorld];  // flags[p] = rank p's flag area as mapped in THIS process
 };

@@ -274,6 +274,20 @@ class Engine:
         self._trace = trace
         _check(require().dnnb200_engine_set_trace(self._h, _p(trace)))
 
+    def pingpong(self, peer: int, iters: int = 1000) -> float:
+        """One-way latency (us) of a 16-byte LL line to rank `peer`; the peer must call pingpong(my_rank) too."""
+        out = C.c_double()
+        _check(require().dnnb200_engine_pingpong(self._h, peer, iters, C.byref(out), _stream()))
+        return float(out.value)
+
+    def set_debug_flags(self, flags: int) -> None:
+        _check(require().dnnb200_engine_set_debug_flags(self._h, flags))
+
+    def set_update_trace(self, trace: Optional[torch.Tensor]) -> None:
+        """int64 CUDA tensor [122*4]: update-kernel timestamps per slice (development aid)."""
+        self._utrace = trace
+        _check(require().dnnb200_engine_set_update_trace(self._h, _p(trace)))
+
     def cluster_info(self, B: int):
         chosen = C.c_int()
         mc = (C.c_int * 9)()

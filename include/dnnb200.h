@@ -122,6 +122,11 @@ int dnnb200_engine_cluster_info(const dnnb200_engine* e, int B, int* chosen, int
 /* development aid: d_trace[cta*16 + k] receives the SM clock at stage boundary k of the clustered
  * forward/backward kernel (NULL switches it off) */
 int dnnb200_engine_set_trace(dnnb200_engine* e, long long* d_trace);
+/* same for the update kernel: d_trace[slice*4 + {0,1,2,3}] = globaltimer (ns) at entry, after the dependency
+ * wait, after the local gradient, after the exchange */
+int dnnb200_engine_set_update_trace(dnnb200_engine* e, long long* d_trace);
+/* development aid: bit 1 = the update kernel does not trigger the early launch of the next kernel */
+int dnnb200_engine_set_debug_flags(dnnb200_engine* e, int flags);
 
 /* one optimizer step on a device-resident batch: fwd/bwd kernel + update kernel
  * (reference: the loop body data_parallelism_train.py:195-203) */
@@ -170,6 +175,10 @@ int dnnb200_batch_grad_noalloc(const float* params, const float* x, const int64_
  * (out may be NULL). two_shot selects the reduce-scatter/all-gather variant. */
 int dnnb200_engine_allreduce(dnnb200_engine* e, const float* in, float* out, int n, int mode, int two_shot,
                              void* stream);
+
+/* latency probe: `iters` round trips of one 16-byte LL line with rank `peer` (which must make the matching call);
+ * returns the one-way store->visible latency over peer memory in microseconds. Synchronises. */
+int dnnb200_engine_pingpong(dnnb200_engine* e, int peer, int iters, double* h_one_way_us, void* stream);
 
 /* membership epoch: announce that this rank stops taking part after the steps
  * already enqueued; peers divide by the survivors from then on */
