@@ -118,7 +118,7 @@ def run_ours(args) -> int:
             cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                    "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 500), __file__,
                    "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup),
-                   "--batch", str(args.batch)]
+                   "--batch", str(args.batch), "--exchange", args.exchange]
             return subprocess.call(cmd)
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     if not torch.cuda.is_available():
@@ -128,10 +128,12 @@ def run_ours(args) -> int:
     B, K, W = args.batch, args.steps, max(3, args.warmup)
 
     cfg = TrainConfig(batch_size=B, sync_mode="step-allreduce" if world > 1 else "none", synthetic=True, quiet=True,
-                      seed=1234, lr=0.001, momentum=0.9, device="cuda", peer_timeout_s=60.0)
+                      seed=1234, lr=0.001, momentum=0.9, device="cuda", peer_timeout_s=60.0,
+                      allreduce_variant=args.exchange)
     trainer = Trainer(cfg)            # public API: model + engine + peer group + control plane
     eng, comm = trainer.engine, trainer.comm
     dev = trainer.device
+    two_shot = world > 1 and trainer._exchange_two_shot()
 
     # ---- data: pools of distinct synthetic batches, larger than L2 -------------------------------
     pool = args.pool
@@ -207,7 +209,8 @@ def run_ours(args) -> int:
                        "global_batch": world * B, "per_gpu_batch": B, "seq_len": None,
                        "parallelism": f"dp{world}", "optimizer": "SGD lr=0.001 momentum=0.9 (inside the timed step)",
                        "exchange": "none (1 GPU)" if world == 1 else
-                                   "one-shot push all-reduce over NVLink peer memory, fused into the update kernel",
+                                   ("two-shot (owner-reduce + broadcast)" if two_shot else "one-shot push") +
+                                   " all-reduce over NVLink peer memory with 16-byte LL lines, fused into the update kernel",
                        "l2": f"inputs cycle through a pool of {pool} distinct batches = {pool_bytes >> 20} MiB on the "
                              f"device (> 126 MB L2); no explicit flush",
                        "cluster_size": cs, "kernels_per_step": 2},
@@ -315,6 +318,8 @@ def main() -> int:
     ap.add_argument("--batch", type=int, default=PER_GPU_BATCH, help="per-GPU batch (the headline config is 16)")
     ap.add_argument("--pool", type=int, default=1024, help="distinct batches cycled through (1024 x 16 = 201 MB > L2)")
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--exchange", choices=["auto", "one-shot", "two-shot"], default="auto",
+                    help="gradient exchange variant (auto: by world size, from the measured table in profiles/)")
     ap.add_argument("--ref-max-steps", type=int, default=400)
     ap.add_argument("--ref-timeout", type=float, default=1500.0)
     a = ap.parse_args()

@@ -65,7 +65,6 @@ template <bool kEmulated>  // see update_kernel: emulated ranks need 8 x 122 co-
 __global__ void __launch_bounds__(kArThreads, kEmulated ? 8 : 1)
 allreduce_kernel(const RankCtx* __restrict__ ctxs, const ArParams prm) {
   __shared__ ExchangeShared xsh;
-  __shared__ unsigned int s_ok;
   const int vr = blockIdx.y;
   const RankCtx& cx = ctxs[vr];
   StepCtl* ctl = cx.ctl;
@@ -86,91 +85,8 @@ allreduce_kernel(const RankCtx* __restrict__ ctxs, const ArParams prm) {
     exchange_slice<4>(cx, &xsh, slice, seq, i, in_range, v, &n);
     if (in_range) finish(cx, prm, vr, i, v, n);
   } else if (world > 1) {
-    // ---------------- two-shot ----------------
-    const unsigned int configured = ctl->active_mask;
-    const int n_cfg = __popc(configured);
-    // owner = the (slice mod n_cfg)-th set bit of the configured mask
-    int owner = 0;
-    {
-      int k = slice % n_cfg;
-      for (int p = 0; p < world; ++p)
-        if ((configured >> p) & 1u) { if (k == 0) { owner = p; break; } --k; }
-    }
-    const unsigned int parity = seq & 1u;
-    unsigned int* my_flags = cx.flags[rank];
-    const unsigned long long tmo = ctl->timeout_ns;
-    float* my_recv = cx.recv[rank];
-    if (rank != owner) {
-      // phase 1: push to the owner only
-      if (in_range)
-        *reinterpret_cast<float4*>(cx.recv[owner] + ((size_t)(parity * world + rank) * kFlatNumel + i)) =
-            make_float4(v[0], v[1], v[2], v[3]);
-      __syncthreads();
-      if (tid == 0) {
-        __threadfence_system();
-        st_release_sys(cx.flags[owner] + rank * kFlagRow + slice, seq);
-        // phase 2: wait for the owner's result (second flag bank)
-        const unsigned int* f = my_flags + (kMaxWorld + owner) * kFlagRow + slice;
-        unsigned long long t0 = 0; unsigned int spins = 0; unsigned int ok = 1u;
-        while (!seq_reached(ld_acquire_sys(f), seq)) {
-          if (tmo != 0ull && (++spins & 0x3ffu) == 0u) {
-            const unsigned long long now = globaltimer_ns();
-            if (t0 == 0ull) t0 = now;
-            else if (now - t0 > tmo) { atomicOr(&ctl->status, kStatusTimeout | (1u << (8 + owner))); ok = 0u; break; }
-          }
-        }
-        s_ok = ok;
-      }
-      __syncthreads();
-      if (in_range && s_ok) {
-        const float4 t = ld_cg_f4(reinterpret_cast<const float4*>(
-            my_recv + ((size_t)(parity * world + owner) * kFlatNumel + i)));
-        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-        finish(cx, prm, vr, i, v, 0);  // the owner already divided
-      }
-    } else {
-      // owner: wait for every configured peer, reduce in rank order, broadcast the mean
-      if (tid == 0) s_ok = 1u;
-      __syncthreads();
-      if (tid < world && tid != rank && ((configured >> tid) & 1u)) {
-        const unsigned int* f = my_flags + tid * kFlagRow + slice;
-        unsigned long long t0 = 0; unsigned int spins = 0;
-        while (!seq_reached(ld_acquire_sys(f), seq)) {
-          if (tmo != 0ull && (++spins & 0x3ffu) == 0u) {
-            const unsigned long long now = globaltimer_ns();
-            if (t0 == 0ull) t0 = now;
-            else if (now - t0 > tmo) { atomicOr(&ctl->status, kStatusTimeout | (1u << (8 + tid))); atomicAnd(&s_ok, 0u); break; }
-          }
-        }
-      }
-      __syncthreads();
-      float acc[4] = {0.f, 0.f, 0.f, 0.f};
-      if (in_range) {
-        for (int p = 0; p < world; ++p) {
-          if (!((configured >> p) & 1u)) continue;
-          if (p == rank) { acc[0] += v[0]; acc[1] += v[1]; acc[2] += v[2]; acc[3] += v[3]; }
-          else {
-            const float4 t = ld_cg_f4(reinterpret_cast<const float4*>(
-                my_recv + ((size_t)(parity * world + p) * kFlatNumel + i)));
-            acc[0] += t.x; acc[1] += t.y; acc[2] += t.z; acc[3] += t.w;
-          }
-        }
-        const unsigned int dov2 = ctl->divisor_override;
-        const float inv = 1.f / (float)(dov2 ? (int)dov2 : n_cfg);
-        const float4 mean = make_float4(acc[0] * inv, acc[1] * inv, acc[2] * inv, acc[3] * inv);
-        for (int p = 0; p < world; ++p) {
-          if (p == rank || !((configured >> p) & 1u)) continue;
-          *reinterpret_cast<float4*>(cx.recv[p] + ((size_t)(parity * world + rank) * kFlatNumel + i)) = mean;
-        }
-        v[0] = mean.x; v[1] = mean.y; v[2] = mean.z; v[3] = mean.w;
-      }
-      __syncthreads();
-      if (tid < world && tid != rank && ((configured >> tid) & 1u)) {
-        __threadfence_system();
-        st_release_sys(cx.flags[tid] + (kMaxWorld + rank) * kFlagRow + slice, seq);
-      }
-      if (in_range) finish(cx, prm, vr, i, v, 0);
-    }
+    exchange_slice_two_shot<4>(cx, slice, seq, i, in_range, v, &n);
+    if (in_range) finish(cx, prm, vr, i, v, n);
   } else {
     if (in_range) finish(cx, prm, vr, i, v, 1);
   }

@@ -597,7 +597,10 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
   const bool grad_only = (flags & 1) != 0;  // tests: leave the local batch gradient in cx.grads, touch nothing else
   int n = 1;
   if (tr && tid == 0) tr[slice * 4 + 2] = (long long)globaltimer_ns();
-  if (cx.world > 1 && !grad_only) exchange_slice<2>(cx, &xsh, slice, seq, i, in_range, v, &n);
+  if (cx.world > 1 && !grad_only) {
+    if (ctl->two_shot) exchange_slice_two_shot<2>(cx, slice, seq, i, in_range, v, &n);
+    else exchange_slice<2>(cx, &xsh, slice, seq, i, in_range, v, &n);
+  }
   if (tr && tid == 0) tr[slice * 4 + 3] = (long long)globaltimer_ns();
 
   if (in_range && grad_only) {

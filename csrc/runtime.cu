@@ -68,6 +68,7 @@ __global__ void ctl_set_membership_kernel(StepCtl* c, unsigned int mask, unsigne
   c->status = 0u;
 }
 __global__ void ctl_set_divisor_kernel(StepCtl* c, unsigned int d) { c->divisor_override = d; }
+__global__ void ctl_set_variant_kernel(StepCtl* c, unsigned int two_shot) { c->two_shot = two_shot; }
 __global__ void ctl_reset_loss_kernel(StepCtl* c) { c->loss_sum = 0.f; c->loss_steps = 0u; }
 __global__ void ctl_set_step_kernel(StepCtl* c, unsigned long long step) { c->step = step; c->ctas_done = 0u; }
 // leave marker = first sequence number this rank will not take part in
@@ -443,6 +444,13 @@ int dnnb200_engine_set_membership(dnnb200_engine* e, unsigned int active_mask, u
                                   void* stream) {
   DNN_ARG_CHECK(e, "null engine");
   ctl_set_membership_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(e->ctl, active_mask, timeout_ns);
+  DNN_CUDA_CHECK(cudaGetLastError());
+  return kOk;
+}
+
+int dnnb200_engine_set_exchange_variant(dnnb200_engine* e, int two_shot, void* stream) {
+  DNN_ARG_CHECK(e, "null engine");
+  ctl_set_variant_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(e->ctl, two_shot ? 1u : 0u);
   DNN_CUDA_CHECK(cudaGetLastError());
   return kOk;
 }

@@ -39,6 +39,8 @@ class Ctl(C.Structure):
         ("ctas_done", C.c_uint),
         ("status", C.c_uint),
         ("active_mask", C.c_uint),
+        ("two_shot", C.c_uint),
+        ("pad0_", C.c_uint),
         ("divisor_override", C.c_uint),
     ]
 
@@ -249,6 +251,10 @@ class Engine:
     def set_membership(self, active_mask: int, timeout_ns: int = 0) -> None:
         _check(require().dnnb200_engine_set_membership(self._h, C.c_uint(active_mask), C.c_ulonglong(timeout_ns),
                                                        _stream()))
+
+    def set_exchange_variant(self, two_shot: bool) -> None:
+        """Fused exchange: one-shot (False; tolerates ranks leaving) or two-shot (True; static membership)."""
+        _check(require().dnnb200_engine_set_exchange_variant(self._h, int(two_shot), _stream()))
 
     def set_divisor(self, divisor: int) -> None:
         """0 = divide exchanged sums by the ranks present; n = divide by n."""

@@ -68,7 +68,7 @@ class TrainConfig:
     save: Optional[str] = None
     resume: Optional[str] = None
     input_pipeline: str = "device"    # device: dataset resident in HBM; host: per-step H2D from pinned memory
-    allreduce_variant: str = "one-shot"
+    allreduce_variant: str = "auto"        # auto | one-shot | two-shot (see _exchange_two_shot)
     peer_timeout_s: float = 30.0
     eval_batch_size: Optional[int] = None  # the reference evaluates with --batch-size too (Q11)
     neptune: bool = False
@@ -159,12 +159,26 @@ class Trainer:
         if self.device.type == "cuda":
             torch.cuda.synchronize()
 
+    def _exchange_two_shot(self) -> bool:
+        """Variant of the fused gradient exchange. One-shot (everyone pushes to everyone) has one latency hop
+        but moves (W-1) x the vector per GPU; two-shot (slice owners reduce, then broadcast) has two hops and
+        moves 2(W-1)/W x. Measured on 8xB200 (profiles/): one-shot wins up to 2 GPUs, two-shot from 4 on.
+        Two-shot needs a static membership, so the failure drill that drops ranks always uses one-shot."""
+        v = self.cfg.allreduce_variant
+        can_drop = self.cfg.failure_mode == "drop" and self.cfg.failure_probability > 0
+        if v == "two-shot":
+            return not can_drop
+        if v == "one-shot" or can_drop:
+            return False
+        return len(self.membership.active) >= 4
+
     def _apply_membership(self, local_only: bool = False) -> None:
         """Program the exchange kernels: who is in the sum, how long to wait for a silent peer."""
         if self.engine is None or self.world == 1:
             return
         mask = (1 << self.rank) if local_only else self.membership.mask
         self.engine.set_membership(mask, int(self.cfg.peer_timeout_s * 1e9))
+        self.engine.set_exchange_variant(self._exchange_two_shot() and not local_only)
 
     # ------------------------------------------------------------------ data
     def load_data(self) -> Tuple[Optional[D.TensorDataset], Optional[D.TensorDataset]]:
@@ -302,7 +316,8 @@ class Trainer:
             self.engine.set_membership(full, int(self.cfg.peer_timeout_s * 1e9))
             self.engine.set_divisor(n_tr)
             out = torch.empty_like(self.model.flat_params)
-            self.engine.allreduce(contrib.contiguous(), out, mode=0, two_shot=self.cfg.allreduce_variant == "two-shot")
+            self.engine.allreduce(contrib.contiguous(), out, mode=0, two_shot=self.cfg.allreduce_variant == "two-shot" or
+                                  (self.cfg.allreduce_variant == "auto" and self.world >= 4))
             self.model.flat_params.copy_(out)
             self.engine.set_divisor(0)
             self._sync()

@@ -93,6 +93,8 @@ typedef struct dnnb200_ctl {
   unsigned int ctas_done;
   unsigned int status;
   unsigned int active_mask;
+  unsigned int two_shot;
+  unsigned int pad0_;
   unsigned int divisor_override;
 } dnnb200_ctl;
 
@@ -105,6 +107,9 @@ int dnnb200_engine_attach_group(dnnb200_engine* e, dnnb200_group* g);
 int dnnb200_engine_set_hparams(dnnb200_engine* e, float lr, float mu, void* stream);
 int dnnb200_engine_set_membership(dnnb200_engine* e, unsigned int active_mask, unsigned long long timeout_ns,
                                   void* stream);
+/* variant of the exchange fused into the update kernel: 0 = one-shot (every rank pushes to every rank; tolerates
+ * ranks leaving mid-epoch), 1 = two-shot (slice owners reduce and broadcast; static membership only) */
+int dnnb200_engine_set_exchange_variant(dnnb200_engine* e, int two_shot, void* stream);
 /* 0 = divide the exchanged sum by the number of ranks present (default); n = divide by n */
 int dnnb200_engine_set_divisor(dnnb200_engine* e, unsigned int divisor, void* stream);
 /* zero the momentum buffer (the reference re-creates its optimizer every epoch:

@@ -46,10 +46,13 @@ def _rel(a, b):
     return ((a - b).abs().max() / b.abs().max().clamp_min(1e-9)).item()
 
 
+@pytest.mark.parametrize("two_shot", [False, True])
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_vr_step_replicas_identical_and_match_oracle(world):
+def test_vr_step_replicas_identical_and_match_oracle(world, two_shot):
     B = 16
     base, models, groups, engines = _make(world, B=B, seed=world)
+    for e in engines:
+        e.set_exchange_variant(two_shot)
     ref = copy.deepcopy(base)
     opt = torch.optim.SGD(ref.parameters(), lr=0.01, momentum=0.9)
     for step in range(4):
