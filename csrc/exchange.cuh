@@ -86,57 +86,76 @@ __device__ __forceinline__ void exchange_slice(const RankCtx& cx, ExchangeShared
     }
   }
 
-  // 2. gather: poll my own receive area until each peer's line carries this step's sequence number.
-  //    While nothing arrives, look at the peer's leave marker and at the clock.
+  // 2. gather: poll my own receive area until each peer's lines carry this step's sequence number.
+  //    All pending peers are polled in ONE batch of independent loads per round (8 peers at a time): polling
+  //    them one after the other costs one L2 round trip per peer even when everything has already arrived.
   if (tid == 0) sh->present = configured;
   __syncthreads();
+  const float* my_recv = cx.recv[rank];
+  const unsigned long long tmo = cx.ctl->timeout_ns;
   float acc[kVec];
 #pragma unroll
   for (int k = 0; k < kVec; ++k) acc[k] = 0.f;
   unsigned int absent = 0u;
-  const float* my_recv = cx.recv[rank];
-  const unsigned long long tmo = cx.ctl->timeout_ns;
-  for (int p = 0; p < world; ++p) {
-    if (!((configured >> p) & 1u)) continue;
-    if (p == rank) {
+  for (int g0 = 0; g0 < world; g0 += 8) {   // groups of 8 ranks (one group unless world > 8)
+    float t[8][kVec];
+    unsigned int pending = in_range ? ((configured >> g0) & 0xffu) : 0u;
+    if (rank >= g0 && rank < g0 + 8) pending &= ~(1u << (rank - g0));
+    if (world - g0 < 8) pending &= (1u << (world - g0)) - 1u;
+    unsigned int spins = 0;
+    unsigned long long t0 = 0;
+    while (pending) {
+      unsigned int arrived = 0u;
 #pragma unroll
-      for (int k = 0; k < kVec; ++k) acc[k] += v[k];
-      continue;
-    }
-    if (!in_range) continue;
-    const float* src = my_recv + ((size_t)(parity * world + p) * kLLStride + 2 * (size_t)i);
-    float t[kVec];
-    bool got = true;
+      for (int j = 0; j < 8; ++j) {
+        if ((pending >> j) & 1u) {
+          const float* src = my_recv + ((size_t)(parity * world + g0 + j) * kLLStride + 2 * (size_t)i);
+          bool ok = true;
 #pragma unroll
-    for (int k = 0; k < kVec; k += 2) {
-      unsigned int spins = 0;
-      unsigned long long t0 = 0;
-      while (!ld_ll(src + 2 * k, seq, &t[k], &t[k + 1])) {
-        if ((++spins & 0xffu) != 0u) continue;
-        // a peer that left pushed every line of its last step before it wrote the marker
-        const unsigned int l = ld_acquire_sys(my_flags + p * kFlagRow + kLeaveSlot);
-        if (l != 0u && (int)(seq - l) >= 0) {
-          got = ld_ll(src + 2 * k, seq, &t[k], &t[k + 1]);
-          if (!got) break;
-          continue;
-        }
-        if (tmo != 0ull) {
-          const unsigned long long now = globaltimer_ns();
-          if (t0 == 0ull) t0 = now;
-          else if (now - t0 > tmo) {
-            atomicOr(&cx.ctl->status, kStatusTimeout | (1u << (8 + p)));
-            got = false;
-            break;
-          }
+          for (int k = 0; k < kVec; k += 2) ok = ld_ll(src + 2 * k, seq, &t[j][k], &t[j][k + 1]) && ok;
+          if (ok) arrived |= 1u << j;
         }
       }
-      if (!got) break;
-    }
-    if (got) {
+      pending &= ~arrived;
+      if (!pending) break;
+      if ((++spins & 0x3fu) != 0u) continue;
+      // something is late: has it left, or is it time to give up?
 #pragma unroll
-      for (int k = 0; k < kVec; ++k) acc[k] += t[k];
-    } else {
-      absent |= 1u << p;
+      for (int j = 0; j < 8; ++j) {
+        if (!((pending >> j) & 1u)) continue;
+        const unsigned int l = ld_acquire_sys(my_flags + (g0 + j) * kFlagRow + kLeaveSlot);
+        if (l != 0u && (int)(seq - l) >= 0) {
+          // a peer that left pushed every line of its last step BEFORE it wrote the marker: one more look settles it
+          const float* src = my_recv + ((size_t)(parity * world + g0 + j) * kLLStride + 2 * (size_t)i);
+          bool ok = true;
+#pragma unroll
+          for (int k = 0; k < kVec; k += 2) ok = ld_ll(src + 2 * k, seq, &t[j][k], &t[j][k + 1]) && ok;
+          if (!ok) absent |= 1u << (g0 + j);
+          pending &= ~(1u << j);
+        }
+      }
+      if (pending && tmo != 0ull) {
+        const unsigned long long now = globaltimer_ns();
+        if (t0 == 0ull) t0 = now;
+        else if (now - t0 > tmo) {
+          atomicOr(&cx.ctl->status, kStatusTimeout | (pending << (8 + g0)));
+          absent |= pending << g0;
+          pending = 0u;
+        }
+      }
+    }
+    // rank-ordered sum of this group (my own contribution from registers at its rank position)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int pr = g0 + j;
+      if (pr >= world || !((configured >> pr) & 1u)) continue;
+      if (pr == rank) {
+#pragma unroll
+        for (int k = 0; k < kVec; ++k) acc[k] += v[k];
+      } else if (in_range && !((absent >> pr) & 1u)) {
+#pragma unroll
+        for (int k = 0; k < kVec; ++k) acc[k] += t[j][k];
+      }
     }
   }
   // every thread of the CTA must agree on who is present (a rank pushes all lines of a step or none,
@@ -144,11 +163,11 @@ __device__ __forceinline__ void exchange_slice(const RankCtx& cx, ExchangeShared
   if (absent) atomicAnd(&sh->present, ~absent);
   __syncthreads();
   const unsigned int present = sh->present;
-  if (present == configured) {  // the normal case: everybody configured has delivered
+  if (present == (configured & ~absent)) {  // the normal case: my view is the CTA's view
 #pragma unroll
     for (int k = 0; k < kVec; ++k) v[k] = acc[k];
   } else if (in_range) {
-    // somebody in this CTA declared a peer absent: redo the sum without it, in rank order
+    // another thread of this CTA declared a peer absent that I had received: redo the sum without it
 #pragma unroll
     for (int k = 0; k < kVec; ++k) acc[k] = 0.f;
     for (int p = 0; p < world; ++p) {
@@ -158,11 +177,11 @@ __device__ __forceinline__ void exchange_slice(const RankCtx& cx, ExchangeShared
         for (int k = 0; k < kVec; ++k) acc[k] += v[k];
       } else {
         const float* src = my_recv + ((size_t)(parity * world + p) * kLLStride + 2 * (size_t)i);
-        float t[kVec];
+        float t2[kVec];
 #pragma unroll
-        for (int k = 0; k < kVec; k += 2) (void)ld_ll(src + 2 * k, seq, &t[k], &t[k + 1]);
+        for (int k = 0; k < kVec; k += 2) (void)ld_ll(src + 2 * k, seq, &t2[k], &t2[k + 1]);
 #pragma unroll
-        for (int k = 0; k < kVec; ++k) acc[k] += t[k];
+        for (int k = 0; k < kVec; ++k) acc[k] += t2[k];
       }
     }
 #pragma unroll
@@ -224,23 +243,52 @@ __device__ __forceinline__ void exchange_slice_two_shot(const RankCtx& cx, int s
     float acc[kVec];
 #pragma unroll
     for (int k = 0; k < kVec; ++k) acc[k] = 0.f;
-    for (int p = 0; p < world; ++p) {
-      if (!((configured >> p) & 1u)) continue;
-      if (p == rank) {
+    for (int g0 = 0; g0 < world; g0 += 8) {   // all pending contributions are polled as one batch of loads
+      float t[8][kVec];
+      unsigned int pending = (configured >> g0) & 0xffu;
+      if (rank >= g0 && rank < g0 + 8) pending &= ~(1u << (rank - g0));
+      if (world - g0 < 8) pending &= (1u << (world - g0)) - 1u;
+      unsigned int spins = 0;
+      unsigned long long t0 = 0;
+      while (pending) {
+        unsigned int arrived = 0u;
 #pragma unroll
-        for (int k = 0; k < kVec; ++k) acc[k] += v[k];
-        continue;
+        for (int j = 0; j < 8; ++j) {
+          if ((pending >> j) & 1u) {
+            const float* src = my_recv + ((size_t)(parity * world + g0 + j) * kLLStride + 2 * (size_t)i);
+            bool ok = true;
+#pragma unroll
+            for (int k = 0; k < kVec; k += 2) ok = ld_ll(src + 2 * k, seq, &t[j][k], &t[j][k + 1]) && ok;
+            if (ok) arrived |= 1u << j;
+          }
+        }
+        pending &= ~arrived;
+        if (pending && tmo != 0ull && (++spins & 0x3ffu) == 0u) {
+          const unsigned long long now = globaltimer_ns();
+          if (t0 == 0ull) t0 = now;
+          else if (now - t0 > tmo) {
+            atomicOr(&cx.ctl->status, kStatusTimeout | (pending << (8 + g0)));
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if ((pending >> j) & 1u) {
+#pragma unroll
+                for (int k = 0; k < kVec; ++k) t[j][k] = 0.f;
+              }
+            pending = 0u;
+          }
+        }
       }
-      const float* src = my_recv + ((size_t)(parity * world + p) * kLLStride + 2 * (size_t)i);
-      float t[kVec];
-      bool ok = true;
 #pragma unroll
-      for (int k = 0; k < kVec; k += 2) ok = ll_poll(src + 2 * k, seq, &t[k], &t[k + 1], tmo) && ok;
-      if (ok) {
+      for (int j = 0; j < 8; ++j) {
+        const int pr = g0 + j;
+        if (pr >= world || !((configured >> pr) & 1u)) continue;
+        if (pr == rank) {
 #pragma unroll
-        for (int k = 0; k < kVec; ++k) acc[k] += t[k];
-      } else {
-        atomicOr(&cx.ctl->status, kStatusTimeout | (1u << (8 + p)));
+          for (int k = 0; k < kVec; ++k) acc[k] += v[k];
+        } else {
+#pragma unroll
+          for (int k = 0; k < kVec; ++k) acc[k] += t[j][k];
+        }
       }
     }
     for (int p = 0; p < world; ++p) {

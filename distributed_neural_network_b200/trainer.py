@@ -162,7 +162,7 @@ class Trainer:
     def _exchange_two_shot(self) -> bool:
         """Variant of the fused gradient exchange. One-shot (everyone pushes to everyone) has one latency hop
         but moves (W-1) x the vector per GPU; two-shot (slice owners reduce, then broadcast) has two hops and
-        moves 2(W-1)/W x. Measured on 8xB200 (profiles/): one-shot wins up to 2 GPUs, two-shot from 4 on.
+        moves 2(W-1)/W x. Measured on 8xB200 (profiles/): one-shot wins at 2 GPUs, they tie at 4, two-shot wins at 8.
         Two-shot needs a static membership, so the failure drill that drops ranks always uses one-shot."""
         v = self.cfg.allreduce_variant
         can_drop = self.cfg.failure_mode == "drop" and self.cfg.failure_probability > 0
@@ -170,7 +170,7 @@ class Trainer:
             return not can_drop
         if v == "one-shot" or can_drop:
             return False
-        return len(self.membership.active) >= 4
+        return len(self.membership.active) >= 6
 
     def _apply_membership(self, local_only: bool = False) -> None:
         """Program the exchange kernels: who is in the sum, how long to wait for a silent peer."""
@@ -317,7 +317,7 @@ class Trainer:
             self.engine.set_divisor(n_tr)
             out = torch.empty_like(self.model.flat_params)
             self.engine.allreduce(contrib.contiguous(), out, mode=0, two_shot=self.cfg.allreduce_variant == "two-shot" or
-                                  (self.cfg.allreduce_variant == "auto" and self.world >= 4))
+                                  (self.cfg.allreduce_variant == "auto" and self.world >= 6))
             self.model.flat_params.copy_(out)
             self.engine.set_divisor(0)
             self._sync()
