@@ -135,6 +135,7 @@ class Trainer:
         self.failure = FailureSimulator(cfg.failure_probability, cfg.failure_duration, cfg.failure_mode, cfg.seed,
                                         self.rank)
         self.dropped = False
+        self.saw_timeout = False
         self.history: List[Dict] = []
 
     # ------------------------------------------------------------------ setup helpers
@@ -257,6 +258,7 @@ class Trainer:
         ctl = eng.read_ctl()
         if ctl.status & 1:
             self._log(f"[rank {self.rank}] peers timed out during the epoch: mask 0x{(ctl.status >> 8) & 0xffff:x}")
+            self.saw_timeout = True
         return float(ctl.loss_sum), int(ctl.loss_steps)
 
     def _train_epoch_cpu(self, shard, B, local_sgd, drop_at) -> Tuple[float, int]:
@@ -349,7 +351,14 @@ class Trainer:
         """Membership epoch: agree on who is present; returning ranks adopt a survivor's state."""
         if self.world == 1:
             return
-        status = self.comm.allgather({"rank": self.rank, "dropped": self.dropped})
+        status = self.comm.allgather({"rank": self.rank, "dropped": self.dropped, "timeout": self.saw_timeout})
+        if any(s["timeout"] for s in status) and self.cfg.sync_mode == "step-allreduce":
+            # A peer was given up on mid-epoch (unannounced stall): different ranks may have summed different sets
+            # for some slices, so the replicas can differ in the last bits. Re-establish identical replicas by
+            # averaging parameters and momentum over the trainers, and clear the sticky status.
+            self._log(f"[rank {self.rank}] re-synchronising replicas after a peer timeout")
+            self._resync_state()
+            self.saw_timeout = False
         came_back = [s["rank"] for s in status if s["dropped"]]
         for r in came_back:
             self.membership.leave(r)
@@ -371,6 +380,26 @@ class Trainer:
         for r in came_back:
             self.membership.join(r)
         self.comm.barrier()  # nobody steps before every marker is cleared
+        self._apply_membership()
+
+    @torch.no_grad()
+    def _resync_state(self) -> None:
+        for buf in (self.model.flat_params, self.momentum):
+            if self.engine is not None:
+                self._align_sequence()
+                full = (1 << self.world) - 1
+                self.engine.set_membership(full, int(self.cfg.peer_timeout_s * 1e9))
+                self.engine.set_divisor(len(self.trainers))
+                contrib = buf.clone() if self.is_trainer else torch.zeros_like(buf)
+                out = torch.empty_like(buf)
+                self.engine.allreduce(contrib, out, mode=0, two_shot=False)
+                buf.copy_(out)
+                self.engine.set_divisor(0)
+                self._sync()
+            else:
+                t = buf.detach().clone() if self.is_trainer else torch.zeros_like(buf)
+                self.comm.allreduce_sum_(t)
+                buf.copy_(t / float(len(self.trainers)))
         self._apply_membership()
 
     # ------------------------------------------------------------------ the whole run
