@@ -36,7 +36,7 @@ namespace dnnb200 {
 constexpr int kCLThreads = 512;
 constexpr int kXRow = 36;                  // padded image row (floats): 16-byte aligned rows, and the five
 constexpr int kXCh = 32 * kXRow + 8;       //   kernel rows of a wgrad gather fall into different banks
-constexpr int kCLRed = 9408;               // CS=2 worst case: conv2 dgrad partials 16*6*98
+
 
 // stage barriers: one mbarrier per all-gather, completed by the st.async traffic itself
 enum { kBarP1 = 0, kBarP2, kBarH1, kBarH2, kBarD1, kBarG2, kBarW1, kNumStageBars };
@@ -58,7 +58,6 @@ struct __align__(16) CLSmem {
   alignas(16) float g2[400];
   alignas(16) float g1[1176 + 8];
   alignas(16) float dc2p[16 * 18 * 18];
-  alignas(16) float red[kCLRed];
   alignas(16) int idx1[1176 + 8];     // 2-bit argmax of the pooling windows (one word each: st.async granularity)
   alignas(16) int idx2[400];
   alignas(16) int poff[196];          // (2*ph)*kXRow + 2*pw of pooled pixel q
@@ -271,8 +270,14 @@ struct FCSmem {
 constexpr size_t kFcOff = (sizeof(CLSmem) + 127) & ~(size_t)127;
 // conv1 weight-gradient partials of the CTAs of a cluster, collected by CTA 0 (row d = CTA d: 450 weights + 6 biases)
 constexpr int kW1Row = 456;
+// scratch for split reductions, sized for the cluster size: conv2 dgrad partials 16*6*nq + conv2 wgrad partials
+// 5*no*150 live together; every other use (conv2 forward partials, conv1 wgrad partials, CS<4 FC splits) is smaller
 template <int CS>
 struct W1Rx {
+  static constexpr int kNq = (196 + CS - 1) / CS, kNo = (16 + CS - 1) / CS;
+  static constexpr int kRed0 = 96 * kNq + 5 * kNo * 150;
+  static constexpr int kRed = kRed0 > 6400 ? kRed0 : 6400;
+  alignas(16) float red[kRed];
   alignas(16) float rx[CS * kW1Row];
 };
 template <int CS>
@@ -353,8 +358,10 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
   FCSmem<kPre ? CS : 4>& f = *reinterpret_cast<FCSmem<kPre ? CS : 4>*>(smem_raw + kFcOff);
   constexpr uint32_t kRxD1 = (uint32_t)(kFcOff + offsetof(FCSmem<kPre ? CS : 4>, rx_d1));
   constexpr uint32_t kRxG2 = (uint32_t)(kFcOff + offsetof(FCSmem<kPre ? CS : 4>, rx_g2));
-  constexpr uint32_t kRxW1 = (uint32_t)w1rx_offset<CS>();
-  const float* rx_w1 = reinterpret_cast<const float*>(smem_raw + w1rx_offset<CS>());
+  W1Rx<CS>& tail = *reinterpret_cast<W1Rx<CS>*>(smem_raw + w1rx_offset<CS>());
+  constexpr uint32_t kRxW1 = (uint32_t)(w1rx_offset<CS>() + offsetof(W1Rx<CS>, rx));
+  const float* rx_w1 = tail.rx;
+  float* const sred = tail.red;
 
   Remote<CS> R;
 #pragma unroll
@@ -410,7 +417,6 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
   CL_TRACE(20);
 
   // static work split of this CTA
-  const int prow0 = r * 14 / CS, prow1 = (r + 1) * 14 / CS;      // conv1: pooled rows
   const int o0 = r * 16 / CS, o1 = (r + 1) * 16 / CS;            // conv2 / conv2 wgrad: output channels
   const int f1m0 = r * kF1 / CS, f1m1 = (r + 1) * kF1 / CS;      // fc1 rows
   const int f2m0 = r * kF2 / CS, f2m1 = (r + 1) * kF2 / CS;      // fc2 rows
@@ -443,12 +449,13 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     __syncthreads();
     CL_TRACE(2);
 
-    // ================= conv1 + bias + ReLU + maxpool, my pooled rows =================
+    // ================= conv1 + bias + ReLU + maxpool, my pooled pixels =================
+    // (split by pooled PIXEL range, not by row: 196 pixels divide evenly over any cluster size)
     {
-      const int npx = (prow1 - prow0) * 14;
+      const int npx = nq;
       for (int item = tid; item < npx * 6; item += kCLThreads) {
         const int ch = item / npx, px = item - ch * npx;
-        const int ph = prow0 + px / 14, pw = px % 14;
+        const int ph = (q0 + px) / 14, pw = (q0 + px) % 14;
         float a00 = 0.f, a01 = 0.f, a10 = 0.f, a11 = 0.f;
 #pragma unroll 1
         for (int c = 0; c < 3; ++c) {
@@ -528,7 +535,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
             a10 += w * patch[kh + 1][kw];
             a11 += w * patch[kh + 1][kw + 1];
           }
-        *reinterpret_cast<float4*>(s.red + item * 4) = make_float4(a00, a01, a10, a11);
+        *reinterpret_cast<float4*>(sred + item * 4) = make_float4(a00, a01, a10, a11);
       }
       __syncthreads();
       for (int t = tid; t < no * 25; t += kCLThreads) {
@@ -536,7 +543,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
         for (int c = 0; c < 6; ++c) {
-          const float4 q = *reinterpret_cast<const float4*>(s.red + ((ol * 6 + c) * 25 + pp) * 4);
+          const float4 q = *reinterpret_cast<const float4*>(sred + ((ol * 6 + c) * 25 + pp) * 4);
           v.x += q.x; v.y += q.y; v.z += q.z; v.w += q.w;
         }
         const float bias = s.cw[kOffB2 + o];
@@ -640,11 +647,11 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     } else {
       fc_dx_local<kF3, kF2>(params + kOffF3W, s.d3, s.h2, s.d2);
       __syncthreads();
-      fc_dx_split_push<CS, kF2, kF1>(params + kOffF2W, s.d2, s.h1, d1k0, d1k1, s.red, R, CL_OFF(d1), CL_BAR(kBarD1));
+      fc_dx_split_push<CS, kF2, kF1>(params + kOffF2W, s.d2, s.h1, d1k0, d1k1, sred, R, CL_OFF(d1), CL_BAR(kBarD1));
       cl_mbar_wait(&s.sbar[kBarD1], phase);
       CL_TRACE(9);
       __syncthreads();  // `red` is reused by the next split
-      fc_dx_split_push<CS, kF1, kFlat>(params + kOffF1W, s.d1, s.p2, g2k0, g2k1, s.red, R, CL_OFF(g2), CL_BAR(kBarG2));
+      fc_dx_split_push<CS, kF1, kFlat>(params + kOffF1W, s.d1, s.p2, g2k0, g2k1, sred, R, CL_OFF(g2), CL_BAR(kBarG2));
       // zero the dense gradient plane while the g2 traffic is in flight
       for (int i = tid; i < 16 * 18 * 18; i += kCLThreads) s.dc2p[i] = 0.f;
       cl_mbar_wait(&s.sbar[kBarG2], phase);
@@ -666,75 +673,79 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       s.dc2p[o * 324 + (2 * ph + (id >> 1) + 4) * 18 + (2 * pw + (id & 1) + 4)] = s.g2[tid];
     }
 
-    // ================= conv2 weight gradient, my output channels =================
-    // thread = (pixel group of 5, o, c, kh) with the five kw taps in registers
+    // ================= conv2 data gradient (my pooled pixels) + conv2 weight gradient (my channels) ==========
+    // The two are independent, so they share ONE pair of phases: the longer data-gradient items are handed out
+    // first, the weight-gradient items fill the remaining threads, and only two block barriers are needed.
     {
       const int no = o1 - o0;
-      const int nitem = no * 30;
-      for (int t = tid; t < nitem * 5; t += kCLThreads) {
-        const int pg = t / nitem, rem = t - pg * nitem;
-        const int ol = rem / 30, r2 = rem - ol * 30, c = r2 / 5, kh = r2 - c * 5, o = o0 + ol;
-        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+      const int n_dg = nq * 16;           // data gradient: (o, pixel) -> 6 channel sums
+      const int n_wg = no * 30 * 5;       // weight gradient: (pixel row, o, c, kh) -> 5 taps
+      float* red_dg = sred;              // [16*6][nq]
+      float* red_wg = sred + 96 * nq;    // [5][no*150]
+      for (int item = tid; item < n_dg + n_wg; item += kCLThreads) {
+        if (item < n_dg) {
+          const int o = item / nq, ql = item - o * nq, q = q0 + ql;
+          const int ih = q / 14, iw = q - ih * 14;
+          float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int k = 0; k < 5; ++k) {
-          const int pp = pg * 5 + k;  // pooled row pg, column k
-          const float g = s.g2[o * 25 + pp];
-          const int id = s.idx2[o * 25 + pp];
-          const float* row = s.p1 + c * 196 + (2 * pg + (id >> 1) + kh) * 14 + 2 * k + (id & 1);
-          a0 += g * row[0]; a1 += g * row[1]; a2 += g * row[2]; a3 += g * row[3]; a4 += g * row[4];
+          for (int kh = 0; kh < 5; ++kh) {
+            const int rr = ih + 4 - kh;
+            if (rr < 4 || rr > 13) continue;
+            const float* row = s.dc2p + o * 324 + rr * 18 + iw + 4;
+            const float* wb = s.w2d + (o * 25 + kh * 5) * 8;
+#pragma unroll
+            for (int kw = 0; kw < 5; ++kw) {
+              const float v = row[-kw];
+              const float4 wa = *reinterpret_cast<const float4*>(wb + kw * 8);
+              const float2 wc = *reinterpret_cast<const float2*>(wb + kw * 8 + 4);
+              acc[0] += v * wa.x; acc[1] += v * wa.y; acc[2] += v * wa.z; acc[3] += v * wa.w;
+              acc[4] += v * wc.x; acc[5] += v * wc.y;
+            }
+          }
+#pragma unroll
+          for (int c = 0; c < 6; ++c) red_dg[(o * 6 + c) * nq + ql] = acc[c];
+        } else {
+          const int t = item - n_dg, nitem = no * 30;
+          const int pg = t / nitem, rem = t - pg * nitem;
+          const int ol = rem / 30, r2 = rem - ol * 30, c = r2 / 5, kh = r2 - c * 5, o = o0 + ol;
+          float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+#pragma unroll
+          for (int k = 0; k < 5; ++k) {
+            const int pp = pg * 5 + k;  // pooled row pg, column k
+            const float g = s.g2[o * 25 + pp];
+            const int id = s.idx2[o * 25 + pp];
+            const float* row = s.p1 + c * 196 + (2 * pg + (id >> 1) + kh) * 14 + 2 * k + (id & 1);
+            a0 += g * row[0]; a1 += g * row[1]; a2 += g * row[2]; a3 += g * row[3]; a4 += g * row[4];
+          }
+          float* dst = red_wg + pg * (no * 150) + ol * 150 + c * 25 + kh * 5;
+          dst[0] = a0; dst[1] = a1; dst[2] = a2; dst[3] = a3; dst[4] = a4;
         }
-        float* dst = s.red + pg * (no * 150) + ol * 150 + c * 25 + kh * 5;
-        dst[0] = a0; dst[1] = a1; dst[2] = a2; dst[3] = a3; dst[4] = a4;
       }
       __syncthreads();
+      CL_TRACE(11);
       float* dst = part2 + (size_t)img * (kConvPrefix - kOffW2);
-      for (int t = tid; t < no * 150; t += kCLThreads) {
-        float a = 0.f;
+      const int n_g1 = nq * 6, n_w2 = no * 150;
+      for (int t = tid; t < n_g1 + n_w2 + no; t += kCLThreads) {
+        if (t < n_g1) {                    // dL/dp1 for my pixels, masked by ReLU (stays in this CTA)
+          const int c = t / nq, ql = t - c * nq;
+          float v = 0.f;
 #pragma unroll
-        for (int pg = 0; pg < 5; ++pg) a += s.red[pg * (no * 150) + t];
-        dst[o0 * 150 + t] = a;
-      }
-      if (tid < no) {
-        const int o = o0 + tid;
-        float a = 0.f;
-        for (int pp = 0; pp < 25; ++pp) a += s.g2[o * 25 + pp];
-        dst[(kOffB2 - kOffW2) + o] = a;
-      }
-    }
-    __syncthreads();
-
-    CL_TRACE(11);
-    // ================= conv2 data gradient for my pooled pixels =================
-    for (int item = tid; item < nq * 16; item += kCLThreads) {
-      const int o = item / nq, ql = item - o * nq, q = q0 + ql;
-      const int ih = q / 14, iw = q - ih * 14;
-      float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+          for (int o = 0; o < 16; ++o) v += red_dg[(o * 6 + c) * nq + ql];
+          const int gi = c * 196 + q0 + ql;
+          s.g1[gi] = s.p1[gi] > 0.f ? v : 0.f;
+        } else if (t < n_g1 + n_w2) {      // conv2.weight gradient of this image, my channels
+          const int u = t - n_g1;
+          float a = 0.f;
 #pragma unroll
-      for (int kh = 0; kh < 5; ++kh) {
-        const int rr = ih + 4 - kh;
-        if (rr < 4 || rr > 13) continue;
-        const float* row = s.dc2p + o * 324 + rr * 18 + iw + 4;
-        const float* wb = s.w2d + (o * 25 + kh * 5) * 8;
-#pragma unroll
-        for (int kw = 0; kw < 5; ++kw) {
-          const float v = row[-kw];
-          const float4 wa = *reinterpret_cast<const float4*>(wb + kw * 8);
-          const float2 wc = *reinterpret_cast<const float2*>(wb + kw * 8 + 4);
-          acc[0] += v * wa.x; acc[1] += v * wa.y; acc[2] += v * wa.z; acc[3] += v * wa.w;
-          acc[4] += v * wc.x; acc[5] += v * wc.y;
+          for (int pg = 0; pg < 5; ++pg) a += red_wg[pg * n_w2 + u];
+          dst[o0 * 150 + u] = a;
+        } else {                           // conv2.bias gradient
+          const int o = o0 + (t - n_g1 - n_w2);
+          float a = 0.f;
+          for (int pp = 0; pp < 25; ++pp) a += s.g2[o * 25 + pp];
+          dst[(kOffB2 - kOffW2) + o] = a;
         }
       }
-#pragma unroll
-      for (int c = 0; c < 6; ++c) s.red[(o * 6 + c) * nq + ql] = acc[c];
-    }
-    __syncthreads();
-    for (int t = tid; t < nq * 6; t += kCLThreads) {
-      const int c = t / nq, ql = t - c * nq;
-      float v = 0.f;
-#pragma unroll
-      for (int o = 0; o < 16; ++o) v += s.red[(o * 6 + c) * nq + ql];
-      const int gi = c * 196 + q0 + ql;
-      s.g1[gi] = s.p1[gi] > 0.f ? v : 0.f;
     }
     __syncthreads();
 
@@ -749,14 +760,14 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
         const int* ip = s.idx1 + o * 196;
         const float* xb = s.x + c * kXCh + kh * kXRow;
         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
-#pragma unroll 2
+#pragma unroll 4
         for (int q = q0 + pg; q < q1; q += 5) {
           const float g = gp[q];
           const int id = ip[q];
           const float* row = xb + s.poff[q] + (id >> 1) * kXRow + (id & 1);
           a0 += g * row[0]; a1 += g * row[1]; a2 += g * row[2]; a3 += g * row[3]; a4 += g * row[4];
         }
-        float* dst = s.red + pg * 450 + o * 75 + c * 25 + kh * 5;
+        float* dst = sred + pg * 450 + o * 75 + c * 25 + kh * 5;
         dst[0] = a0; dst[1] = a1; dst[2] = a2; dst[3] = a3; dst[4] = a4;
       } else if (warp == 15) {
         for (int o = 0; o < 6; ++o) {   // bias partial straight to CTA 0
@@ -772,7 +783,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       if (tid < 450) {
         float a = 0.f;
 #pragma unroll
-        for (int pg = 0; pg < 5; ++pg) a += s.red[pg * 450 + tid];
+        for (int pg = 0; pg < 5; ++pg) a += sred[pg * 450 + tid];
         cl_st_async(R.base[0] + kRxW1 + 4u * (uint32_t)(r * kW1Row + tid), __float_as_uint(a),
                     R.base[0] + CL_BAR(kBarW1));
       }
