@@ -672,6 +672,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       const int id = s.idx2[tid];
       s.dc2p[o * 324 + (2 * ph + (id >> 1) + 4) * 18 + (2 * pw + (id & 1) + 4)] = s.g2[tid];
     }
+    __syncthreads();  // the data-gradient items below read the plane just scattered
 
     // ================= conv2 data gradient (my pooled pixels) + conv2 weight gradient (my channels) ==========
     // The two are independent, so they share ONE pair of phases: the longer data-gradient items are handed out
