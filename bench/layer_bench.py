@@ -1,0 +1,69 @@
+"""Layer kernels: tcgen05 (TF32) vs FFMA (fp32) vs PyTorch/cuDNN/cuBLAS, and eval throughput. Device-timed."""
+import json
+import sys
+from pathlib import Path
+
+import torch
+import torch.nn.functional as F
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+from distributed_neural_network_b200 import Network  # noqa: E402
+from distributed_neural_network_b200.ops import flat as L  # noqa: E402
+from distributed_neural_network_b200.ops import native  # noqa: E402
+
+
+def t_us(fn, iters=50, warm=10):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) * 1e3 / iters
+
+
+def main():
+    out = {}
+    torch.manual_seed(0)
+    for N in (16, 1024, 10000):
+        for name, (Ci, H, Co) in (("conv1", (3, 32, 6)), ("conv2", (6, 14, 16))):
+            x = torch.randn(N, Ci, H, H, device="cuda")
+            w = torch.randn(Co, Ci, 5, 5, device="cuda") * 0.1
+            b = torch.randn(Co, device="cuda") * 0.1
+            Hp = (H - 4) // 2
+            y = torch.empty(N, Co, Hp, Hp, device="cuda")
+            idx = torch.empty(N, Co, Hp, Hp, dtype=torch.uint8, device="cuda")
+            out[f"{name}_fwd_N{N}_tcgen05_us"] = round(t_us(lambda: native.tc_conv_relu_pool_fwd(x, w, b, y, idx)), 2)
+            out[f"{name}_fwd_N{N}_ffma_us"] = round(t_us(lambda: native.conv_relu_pool_fwd(x, w, b, y, idx)), 2)
+            out[f"{name}_fwd_N{N}_torch_cudnn_us"] = round(t_us(lambda: F.max_pool2d(F.relu(F.conv2d(x, w, b)), 2, 2)), 2)
+        for name, (K, M) in (("fc1", (400, 120)), ("fc2", (120, 84))):
+            x = torch.randn(N, K, device="cuda")
+            w = torch.randn(M, K, device="cuda") * 0.1
+            b = torch.randn(M, device="cuda")
+            y = torch.empty(N, M, device="cuda")
+            out[f"{name}_fwd_N{N}_tcgen05_tma_us"] = round(t_us(lambda: native.tc_linear_fwd(x, w, b, y, True)), 2)
+            out[f"{name}_fwd_N{N}_ffma_us"] = round(t_us(lambda: native.linear_fwd(x, w, b, y, True)), 2)
+            out[f"{name}_fwd_N{N}_torch_cublas_us"] = round(t_us(lambda: F.relu(F.linear(x, w, b))), 2)
+    # eval of 10 000 test images (reference eval loop semantics), batch 16
+    m = Network().cuda()
+    eng = native.Engine(m.flat_params, torch.zeros(L.FLAT_NUMEL, device="cuda"), None, 16, 0.001, 0.9)
+    x = torch.randn(10000, 3, 32, 32, device="cuda")
+    y = torch.randint(0, 10, (10000,), device="cuda")
+    out["eval_10000_fused_engine_us"] = round(t_us(lambda: eng.evaluate(x, y, 16), 10, 3), 1)
+
+    def torch_eval():
+        with torch.no_grad():
+            for i in range(0, 10000, 16):
+                o = m(x[i:i + 16])
+                F.cross_entropy(o, y[i:i + 16]).item()
+    out["eval_10000_layer_kernels_bs16_with_item_us"] = round(t_us(torch_eval, 2, 1), 1)
+    print(json.dumps(out, indent=1))
+    Path("gpurun_out").mkdir(exist_ok=True)
+    Path("gpurun_out/layer_bench.json").write_text(json.dumps(out, indent=1))
+
+
+if __name__ == "__main__":
+    main()

@@ -143,6 +143,9 @@ __device__ __forceinline__ void fc_rows_push(const float* __restrict__ W, const 
   constexpr int kWarps = kCLThreads / 32;
   constexpr int kIter = (K4 + 31) / 32;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint32_t my_dst = 0;  // lane d pushes to CTA d: select its base once, without divergent branches in the loop
+#pragma unroll
+  for (int d = 0; d < CS; ++d) my_dst = lane == d ? R.base[d] : my_dst;
   const float4* in4 = reinterpret_cast<const float4*>(in);
   for (int r0 = m0 + warp; r0 < m1; r0 += 2 * kWarps) {
     float4 w[2][kIter];
@@ -174,9 +177,7 @@ __device__ __forceinline__ void fc_rows_push(const float* __restrict__ W, const 
       if (r < m1) {
         acc += bias[q];
         const float y = kRelu ? fmaxf(acc, 0.f) : acc;
-#pragma unroll
-        for (int d = 0; d < CS; ++d)  // lane d pushes to CTA d
-          if (lane == d) cl_st_async(R.base[d] + field_off + 4u * r, __float_as_uint(y), R.base[d] + bar_off);
+        if (lane < CS) cl_st_async(my_dst + field_off + 4u * r, __float_as_uint(y), my_dst + bar_off);  // lane d -> CTA d
       }
     }
   }
@@ -298,6 +299,9 @@ __device__ __forceinline__ void fc_rows_smem_push(const float* wsm, const float*
   constexpr int K4 = K / 4;
   constexpr int kIter = (K4 + 31) / 32;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint32_t my_dst = 0;
+#pragma unroll
+  for (int d = 0; d < CS; ++d) my_dst = lane == d ? R.base[d] : my_dst;
   const float4* in4 = reinterpret_cast<const float4*>(in);
   for (int r = m0 + warp; r < m1; r += kCLThreads / 32) {
     const float4* w4 = reinterpret_cast<const float4*>(wsm + (size_t)(r - m0) * K);
@@ -312,9 +316,7 @@ __device__ __forceinline__ void fc_rows_smem_push(const float* wsm, const float*
     }
     acc = warp_sum(acc) + bsm[r];
     const float y = kRelu ? fmaxf(acc, 0.f) : acc;
-#pragma unroll
-    for (int d = 0; d < CS; ++d)
-      if (lane == d) cl_st_async(R.base[d] + field_off + 4u * r, __float_as_uint(y), R.base[d] + bar_off);
+    if (lane < CS) cl_st_async(my_dst + field_off + 4u * r, __float_as_uint(y), my_dst + bar_off);  // lane d -> CTA d
   }
 }
 
