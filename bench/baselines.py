@@ -130,6 +130,11 @@ def main():
                     for two in (False, True):
                         us = timed(lambda: eng.allreduce(src_t[:n], dst_t[:n], mode=0, two_shot=two), a.iters, 30, world)
                         out[f"ours_allreduce_{'two' if two else 'one'}_shot_us_{n}f"] = round(us, 2)
+                if tr.nvls_ok:
+                    for n in (4096, L.FLAT_NUMEL):
+                        us = timed(lambda: eng.allreduce(src_t[:n], dst_t[:n], mode=0, two_shot="nvls"), a.iters, 30, world)
+                        out[f"ours_allreduce_nvls_us_{n}f"] = round(us, 2)
+                out["nvls_available"] = bool(tr.nvls_ok)
                 if world >= 2 and rank < 2:   # one-way latency of a 16-byte line between ranks 0 and 1
                     lat = eng.pingpong(1 - rank, 2000)
                     out["ours_ll_one_way_latency_us"] = round(lat, 3)

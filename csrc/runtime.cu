@@ -514,6 +514,13 @@ int dnnb200_engine_pingpong(dnnb200_engine* e, int peer, int iters, double* h_on
   return kOk;
 }
 
+int dnnb200_engine_attach_nvls(dnnb200_engine* e, float* local_buf, float* multicast_buf) {
+  DNN_ARG_CHECK(e, "null engine");
+  e->h_ctx.nvls_local = local_buf;
+  e->h_ctx.nvls_mc = multicast_buf;
+  return push_ctx(e, nullptr);
+}
+
 int dnnb200_engine_set_debug_flags(dnnb200_engine* e, int flags) {
   DNN_ARG_CHECK(e, "null engine");
   e->debug_flags = flags;
@@ -645,6 +652,8 @@ int dnnb200_engine_eval(dnnb200_engine* e, const float* x, const int64_t* y, int
 int dnnb200_engine_allreduce(dnnb200_engine* e, const float* in, float* out, int n, int mode, int two_shot,
                              void* stream) {
   DNN_ARG_CHECK(e && in, "engine_allreduce: null argument");
+  DNN_ARG_CHECK(two_shot != 2 || (e->h_ctx.nvls_mc != nullptr && e->h_ctx.nvls_local != nullptr),
+                "engine_allreduce: the NVLS variant needs dnnb200_engine_attach_nvls first");
   const float* ins[1] = {in};
   float* outs[1] = {out};
   int rc = launch_allreduce(e->d_ctx, 1, ins, outs, n, mode, two_shot, (cudaStream_t)stream);

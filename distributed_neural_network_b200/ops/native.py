@@ -23,6 +23,7 @@ _lib: Optional[C.CDLL] = None
 _load_error: Optional[str] = None
 
 FLAT_NUMEL = 62144
+NVLS_FLOATS = 2 * FLAT_NUMEL + 2 * 16 * 128
 IPC_HANDLE_BYTES = 64
 
 
@@ -341,10 +342,17 @@ class Engine:
         _check(require().dnnb200_engine_eval(self._h, _p(x), _p(y), x.shape[0], bs, _p(logits), out, _stream()))
         return float(out[0]), int(out[1])
 
-    def allreduce(self, inp: torch.Tensor, out: Optional[torch.Tensor], mode: int = 0, two_shot: bool = False) -> None:
+    def allreduce(self, inp: torch.Tensor, out: Optional[torch.Tensor], mode: int = 0, two_shot=False) -> None:
+        """``two_shot``: False/0 one-shot, True/1 two-shot, 2 or "nvls" the in-switch (multimem) variant."""
         _f32(inp, "in")
-        _check(require().dnnb200_engine_allreduce(self._h, _p(inp), _p(out), inp.numel(), mode, int(two_shot),
-                                                  _stream()))
+        variant = 2 if two_shot == "nvls" else int(two_shot)
+        _check(require().dnnb200_engine_allreduce(self._h, _p(inp), _p(out), inp.numel(), mode, variant, _stream()))
+
+    def attach_nvls(self, local_buf: torch.Tensor, multicast_ptr: int) -> None:
+        _f32(local_buf, "local_buf")
+        assert local_buf.numel() >= NVLS_FLOATS
+        self._nvls_buf = local_buf
+        _check(require().dnnb200_engine_attach_nvls(self._h, _p(local_buf), C.c_void_p(multicast_ptr)))
 
     def leave(self) -> None:
         _check(require().dnnb200_engine_leave(self._h, _stream()))

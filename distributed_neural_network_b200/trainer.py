@@ -38,7 +38,7 @@ from .models.network import Network
 from .ops import flat as L
 from .ops import functional as Fn
 from .ops import native
-from .parallel import bootstrap
+from .parallel import bootstrap, nvls
 from .parallel.membership import FailureSimulator, Membership
 from .utils import checkpoint as ckpt
 from .utils import data as D
@@ -123,6 +123,7 @@ class Trainer:
         self.engine: Optional[native.Engine] = None
         self.group: Optional[native.Group] = None
         self.first_step = True
+        self.nvls_ok = False
         if self.device.type == "cuda":
             self.engine = native.Engine(self.model.flat_params, self.momentum, None, max(cfg.batch_size, 1),
                                         cfg.lr, cfg.momentum)
@@ -132,6 +133,12 @@ class Trainer:
                 self.group.connect(handles)
                 self.engine.attach_group(self.group)
                 self._apply_membership()
+                # NVLS (in-switch reduction) where the host exposes NVLink multicast; all ranks or nobody
+                made = nvls.try_create(self.device)
+                if all(self.comm.allgather(made is not None)):
+                    self.nvls_buf, self.nvls_mc = made
+                    self.engine.attach_nvls(self.nvls_buf, self.nvls_mc)
+                    self.nvls_ok = True
         self.failure = FailureSimulator(cfg.failure_probability, cfg.failure_duration, cfg.failure_mode, cfg.seed,
                                         self.rank)
         self.dropped = False
@@ -172,6 +179,17 @@ class Trainer:
         if v == "one-shot" or can_drop:
             return False
         return len(self.membership.active) >= 6
+
+    def _standalone_variant(self):
+        """Variant of the stand-alone all-reduce (parameter averaging): 0 one-shot, 1 two-shot, 2 NVLS."""
+        v = self.cfg.allreduce_variant
+        if v == "nvls":
+            if not self.nvls_ok:
+                raise RuntimeError("--allreduce-variant nvls: NVLink multicast is not available to this job")
+            return 2
+        if v == "two-shot" or (v == "auto" and self.world >= 6):
+            return 1
+        return 0
 
     def _apply_membership(self, local_only: bool = False) -> None:
         """Program the exchange kernels: who is in the sum, how long to wait for a silent peer."""
@@ -318,8 +336,7 @@ class Trainer:
             self.engine.set_membership(full, int(self.cfg.peer_timeout_s * 1e9))
             self.engine.set_divisor(n_tr)
             out = torch.empty_like(self.model.flat_params)
-            self.engine.allreduce(contrib.contiguous(), out, mode=0, two_shot=self.cfg.allreduce_variant == "two-shot" or
-                                  (self.cfg.allreduce_variant == "auto" and self.world >= 6))
+            self.engine.allreduce(contrib.contiguous(), out, mode=0, two_shot=self._standalone_variant())
             self.model.flat_params.copy_(out)
             self.engine.set_divisor(0)
             self._sync()

@@ -177,9 +177,16 @@ int dnnb200_batch_grad_noalloc(const float* params, const float* x, const int64_
 
 /* peer-memory all-reduce of a flat vector (n % 4 == 0, n <= FLAT_NUMEL).
  * mode 0: out = mean(in); mode 1: fused SGD-momentum on the engine's params with g = mean(in)
- * (out may be NULL). two_shot selects the reduce-scatter/all-gather variant. */
+ * (out may be NULL). variant (argument `two_shot`): 0 one-shot push, 1 two-shot (owner-reduce + broadcast),
+ * 2 NVLS (in-switch reduction through a multicast mapping; needs dnnb200_engine_attach_nvls). */
 int dnnb200_engine_allreduce(dnnb200_engine* e, const float* in, float* out, int n, int mode, int two_shot,
                              void* stream);
+
+/* NVLS: give the engine a symmetric buffer of DNNB200_NVLS_FLOATS floats that every rank allocated and mapped
+ * into one NVLink multicast object (e.g. with torch.distributed._symmetric_memory): `local_buf` is this rank's
+ * copy, `multicast_buf` the multicast address. The buffer must be zero-initialised. */
+#define DNNB200_NVLS_FLOATS (2 * DNNB200_FLAT_NUMEL + 2 * 16 * 128)
+int dnnb200_engine_attach_nvls(dnnb200_engine* e, float* local_buf, float* multicast_buf);
 
 /* latency probe: `iters` round trips of one 16-byte LL line with rank `peer` (which must make the matching call);
  * returns the one-way store->visible latency over peer memory in microseconds. Synchronises. */

@@ -58,3 +58,24 @@ def test_ipc_drop_mode_survivors_continue(tmp_path):
     assert res[0]["history"][-1]["membership_epoch"] > 0
     for r in range(1, n):
         assert torch.equal(res[0]["flat"], res[r]["flat"])
+
+
+@needs2
+def test_nvls_in_switch_allreduce_matches_peer_memory_variant(tmp_path):
+    """multimem.ld_reduce / multimem.st over an NVLink multicast mapping vs the one-shot push variant."""
+    from distributed_neural_network_b200.parallel import launch
+    n = min(torch.cuda.device_count(), 8)
+    rc = launch.spawn(n, [sys.executable, str(ROOT / "tests" / "_mp_nvls_worker.py"), str(tmp_path)])
+    assert rc == 0
+    res = [torch.load(f"{tmp_path}/rank{r}.pt", weights_only=False) for r in range(n)]
+    if not all(r["nvls"] for r in res):
+        pytest.skip("NVLink multicast is not exposed on this host")
+    assert all(r["status"] == 0 for r in res)
+    for key in res[0]["outs"]:
+        nelem = int(key.split("_")[0])
+        want = torch.stack([r["outs"][key][0][:nelem].double() for r in res]).mean(0)
+        for r in res:
+            x, y_one, y_nvls = r["outs"][key]
+            assert torch.equal(y_nvls, res[0]["outs"][key][2]), "NVLS result differs between ranks"
+            assert (y_nvls[:nelem].double() - want).abs().max() < 1e-6
+            assert (y_one[:nelem].double() - want).abs().max() < 1e-6
