@@ -43,6 +43,11 @@ def main():
     for k in range(4):
         print(f"    prologue {names[k]:40s} {(pr[:, k+1]-pr[:, k]).mean():8.0f} cycles")
     print(f"    prologue w2d build + split consts -> trace0 {(t[:,0]-t[:,20]).double().mean():8.0f} cycles")
+    fc = t[:, 22:30].double()
+    print("    fc1 warp0: row0 dot %.0f, sum+bias %.0f, st.async %.0f | gap %.0f | row1 dot %.0f, sum %.0f, st.async %.0f (cycles, mean)" % (
+        (fc[:,1]-fc[:,0]).mean(), (fc[:,2]-fc[:,1]).mean(), (fc[:,3]-fc[:,2]).mean(), (fc[:,4]-fc[:,3]).mean(),
+        (fc[:,5]-fc[:,4]).mean(), (fc[:,6]-fc[:,5]).mean(), (fc[:,7]-fc[:,6]).mean()))
+    print(f"    fc1 stage start (trace6) -> first row start {(fc[:,0]-t[:,6].double()).mean():.0f} cycles")
     loop_ns = (t[:, 13] - t[:, 0]).double().mean() / 1.965
     print(f"  image loop {loop_ns:.0f} ns  => prologue (entry -> cluster barrier) ~ {(ext-ent).mean() - loop_ns:.0f} ns")
 

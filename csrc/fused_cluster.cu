@@ -295,7 +295,8 @@ static_assert(cluster_smem_bytes<4>() <= 227 * 1024 && cluster_smem_bytes<2>() <
 // rows [m0, m1) of y = act(b + W . in) with the rows in shared memory (wsm[0] is row m0)
 template <int CS, int K, bool kRelu>
 __device__ __forceinline__ void fc_rows_smem_push(const float* wsm, const float* bsm, const float* in, int m0, int m1,
-                                                  const Remote<CS>& R, uint32_t field_off, uint32_t bar_off) {
+                                                  const Remote<CS>& R, uint32_t field_off, uint32_t bar_off,
+                                                  long long* dbg = nullptr) {
   constexpr int K4 = K / 4;
   constexpr int kIter = (K4 + 31) / 32;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -303,7 +304,9 @@ __device__ __forceinline__ void fc_rows_smem_push(const float* wsm, const float*
 #pragma unroll
   for (int d = 0; d < CS; ++d) my_dst = lane == d ? R.base[d] : my_dst;
   const float4* in4 = reinterpret_cast<const float4*>(in);
+  int dbg_n = 0;
   for (int r = m0 + warp; r < m1; r += kCLThreads / 32) {
+    if (dbg && threadIdx.x == 0 && dbg_n < 2) dbg[dbg_n * 4 + 0] = clock64();
     const float4* w4 = reinterpret_cast<const float4*>(wsm + (size_t)(r - m0) * K);
     float acc = 0.f;
 #pragma unroll
@@ -314,9 +317,13 @@ __device__ __forceinline__ void fc_rows_smem_push(const float* wsm, const float*
         acc += w.x * v.x + w.y * v.y + w.z * v.z + w.w * v.w;
       }
     }
+    if (dbg && threadIdx.x == 0 && dbg_n < 2) dbg[dbg_n * 4 + 1] = clock64();
     acc = warp_sum(acc) + bsm[r];
     const float y = kRelu ? fmaxf(acc, 0.f) : acc;
+    if (dbg && threadIdx.x == 0 && dbg_n < 2) dbg[dbg_n * 4 + 2] = clock64();
     if (lane < CS) cl_st_async(my_dst + field_off + 4u * r, __float_as_uint(y), my_dst + bar_off);  // lane d -> CTA d
+    if (dbg && threadIdx.x == 0 && dbg_n < 2) dbg[dbg_n * 4 + 3] = clock64();
+    ++dbg_n;
   }
 }
 
@@ -569,7 +576,8 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     // ================= fc1, fc2 (rows split), fc3 + softmax-CE (redundant) =================
     if (kPre) {
       cl_mbar_wait(&f.wbar, 0);  // weight slices have landed (completed long ago; stays complete)
-      fc_rows_smem_push<CS, kFlat, true>(f.wf1, f.bf1, s.p2, f1m0, f1m1, R, CL_OFF(h1), CL_BAR(kBarH1));
+      fc_rows_smem_push<CS, kFlat, true>(f.wf1, f.bf1, s.p2, f1m0, f1m1, R, CL_OFF(h1), CL_BAR(kBarH1),
+                                         trace ? trace + blockIdx.x * 32 + 22 : nullptr);
       cl_mbar_wait(&s.sbar[kBarH1], phase);
       CL_TRACE(7);
       fc_rows_smem_push<CS, kF1, true>(f.wf2, f.bf2, s.h1, f2m0, f2m1, R, CL_OFF(h2), CL_BAR(kBarH2));
