@@ -132,8 +132,10 @@ def run_ours(args) -> int:
                       allreduce_variant=args.exchange)
     trainer = Trainer(cfg)            # public API: model + engine + peer group + control plane
     eng, comm = trainer.engine, trainer.comm
+    eng.set_debug_flags(int(os.environ.get("DNN_DEBUG_FLAGS", "0")))   # development aid, 0 in every reported run
     dev = trainer.device
-    two_shot = world > 1 and trainer._exchange_two_shot()
+    variant = trainer._exchange_variant() if world > 1 else 0
+    two_shot = variant == 1
 
     # ---- data: pools of distinct synthetic batches, larger than L2 -------------------------------
     pool = args.pool
@@ -209,8 +211,10 @@ def run_ours(args) -> int:
                        "global_batch": world * B, "per_gpu_batch": B, "seq_len": None,
                        "parallelism": f"dp{world}", "optimizer": "SGD lr=0.001 momentum=0.9 (inside the timed step)",
                        "exchange": "none (1 GPU)" if world == 1 else
-                                   ("two-shot (owner-reduce + broadcast)" if two_shot else "one-shot push") +
-                                   " all-reduce over NVLink peer memory with 16-byte LL lines, fused into the update kernel",
+                                   ("NVLS in-switch reduction (multimem.ld_reduce), fused into the update kernel"
+                                    if variant == 2 else
+                                    ("two-shot (owner-reduce + broadcast)" if two_shot else "one-shot push") +
+                                    " all-reduce over NVLink peer memory with 16-byte LL lines, fused into the update kernel"),
                        "l2": f"inputs cycle through a pool of {pool} distinct batches = {pool_bytes >> 20} MiB on the "
                              f"device (> 126 MB L2); no explicit flush",
                        "cluster_size": cs, "kernels_per_step": 2},
@@ -318,7 +322,7 @@ def main() -> int:
     ap.add_argument("--batch", type=int, default=PER_GPU_BATCH, help="per-GPU batch (the headline config is 16)")
     ap.add_argument("--pool", type=int, default=1024, help="distinct batches cycled through (1024 x 16 = 201 MB > L2)")
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
-    ap.add_argument("--exchange", choices=["auto", "one-shot", "two-shot"], default="auto",
+    ap.add_argument("--exchange", choices=["auto", "one-shot", "two-shot", "nvls"], default="auto",
                     help="gradient exchange variant (auto: by world size, from the measured table in profiles/)")
     ap.add_argument("--ref-max-steps", type=int, default=400)
     ap.add_argument("--ref-timeout", type=float, default=1500.0)

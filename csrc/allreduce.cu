@@ -85,46 +85,8 @@ allreduce_kernel(const RankCtx* __restrict__ ctxs, const ArParams prm) {
     exchange_slice<4>(cx, &xsh, slice, seq, i, in_range, v, &n);
     if (in_range) finish(cx, prm, vr, i, v, n);
   } else if (world > 1 && prm.two_shot == 2) {
-    // ---- NVLS: every rank parks its values in its own symmetric buffer, ONE multimem.st publishes "slice s of
-    // rank r is there" to all ranks at once, and multimem.ld_reduce has the switch add the W copies in flight.
-    // Per GPU the wire carries the reduced vector once (plus serving the peers' reads), with no unicast fan-out.
-    const unsigned int parity = seq & 1u;
-    const unsigned int configured = ctl->active_mask;
-    float* loc = cx.nvls_local;
-    float* mc = cx.nvls_mc;
-    if (in_range) *reinterpret_cast<float4*>(loc + (size_t)parity * kFlatNumel + i) = make_float4(v[0], v[1], v[2], v[3]);
-    __syncthreads();
-    const unsigned int* lflags = reinterpret_cast<const unsigned int*>(loc + 2 * (size_t)kFlatNumel);
-    unsigned int* mflags = reinterpret_cast<unsigned int*>(mc + 2 * (size_t)kFlatNumel);
-    if (tid == 0) {
-      __threadfence_system();  // the CTA's stores, cumulatively, before the flag
-      asm volatile("multimem.st.relaxed.sys.global.b32 [%0], %1;" ::"l"(mflags + (parity * kMaxWorld + rank) * kFlagRow + slice),
-                   "r"(seq)
-                   : "memory");
-    }
-    if (tid < world && ((configured >> tid) & 1u)) {
-      const unsigned int* f = lflags + (parity * kMaxWorld + tid) * kFlagRow + slice;
-      const unsigned long long tmo = ctl->timeout_ns;
-      unsigned long long t0 = 0;
-      unsigned int spins = 0;
-      while (ld_acquire_sys(f) != seq) {
-        if (tmo != 0ull && (++spins & 0x3ffu) == 0u) {
-          const unsigned long long now = globaltimer_ns();
-          if (t0 == 0ull) t0 = now;
-          else if (now - t0 > tmo) { atomicOr(&ctl->status, kStatusTimeout | (1u << (8 + tid))); break; }
-        }
-      }
-    }
-    __syncthreads();
-    if (in_range) {
-      float4 r4;
-      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
-                   : "=f"(r4.x), "=f"(r4.y), "=f"(r4.z), "=f"(r4.w)
-                   : "l"(mc + (size_t)parity * kFlatNumel + i)
-                   : "memory");
-      v[0] = r4.x; v[1] = r4.y; v[2] = r4.z; v[3] = r4.w;
-      finish(cx, prm, vr, i, v, world);   // every member of the multicast group is summed by the switch
-    }
+    exchange_slice_nvls<4>(cx, slice, seq, i, in_range, v, &n);   // in-switch reduction (exchange.cuh)
+    if (in_range) finish(cx, prm, vr, i, v, n);
   } else if (world > 1) {
     exchange_slice_two_shot<4>(cx, slice, seq, i, in_range, v, &n);
     if (in_range) finish(cx, prm, vr, i, v, n);

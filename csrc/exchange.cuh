@@ -302,4 +302,62 @@ __device__ __forceinline__ void exchange_slice_two_shot(const RankCtx& cx, int s
   }
 }
 
+// ---- NVLS variant (in-switch reduction) ------------------------------------------------------------
+// Each rank parks its values in its own symmetric buffer; ONE multimem.st publishes "slice s of rank r is
+// there" to every rank; multimem.ld_reduce returns the switch's sum of all W copies. Static membership (the
+// switch adds every member of the multicast group). Used when the host exposes NVLink multicast.
+template <int kVec>
+__device__ __forceinline__ void exchange_slice_nvls(const RankCtx& cx, int slice, unsigned int seq, int i,
+                                                    bool in_range, float (&v)[kVec], int* n_present) {
+  static_assert(kVec == 2 || kVec == 4, "vector width");
+  const int world = cx.world, rank = cx.rank, tid = threadIdx.x;
+  const unsigned int parity = seq & 1u;
+  const unsigned int configured = cx.ctl->active_mask;
+  float* loc = cx.nvls_local;
+  float* mc = cx.nvls_mc;
+  *n_present = world;
+  if (in_range) {
+    float* dst = loc + (size_t)parity * kFlatNumel + i;
+    if (kVec == 4) *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+    else *reinterpret_cast<float2*>(dst) = make_float2(v[0], v[1]);
+  }
+  __syncthreads();
+  const unsigned int* lflags = reinterpret_cast<const unsigned int*>(loc + 2 * (size_t)kFlatNumel);
+  unsigned int* mflags = reinterpret_cast<unsigned int*>(mc + 2 * (size_t)kFlatNumel);
+  if (tid == 0) {
+    __threadfence_system();  // the CTA's stores, cumulatively, before the flag
+    asm volatile("multimem.st.relaxed.sys.global.b32 [%0], %1;" ::"l"(mflags + (parity * kMaxWorld + rank) * kFlagRow + slice),
+                 "r"(seq)
+                 : "memory");
+  }
+  if (tid < world && ((configured >> tid) & 1u)) {
+    const unsigned int* f = lflags + (parity * kMaxWorld + tid) * kFlagRow + slice;
+    const unsigned long long tmo = cx.ctl->timeout_ns;
+    unsigned long long t0 = 0;
+    unsigned int spins = 0;
+    while (ld_acquire_sys(f) != seq) {
+      if (tmo != 0ull && (++spins & 0x3ffu) == 0u) {
+        const unsigned long long now = globaltimer_ns();
+        if (t0 == 0ull) t0 = now;
+        else if (now - t0 > tmo) { atomicOr(&cx.ctl->status, kStatusTimeout | (1u << (8 + tid))); break; }
+      }
+    }
+  }
+  __syncthreads();
+  if (in_range) {
+    const float* src = mc + (size_t)parity * kFlatNumel + i;
+    if (kVec == 4) {
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                   : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3])
+                   : "l"(src)
+                   : "memory");
+    } else {
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v2.f32 {%0, %1}, [%2];"
+                   : "=f"(v[0]), "=f"(v[1])
+                   : "l"(src)
+                   : "memory");
+    }
+  }
+}
+
 }  // namespace dnnb200

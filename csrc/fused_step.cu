@@ -573,7 +573,7 @@ __device__ __forceinline__ float2 local_grad2(const RankCtx& cx, int i, int B, i
 // kEmulated: several ranks emulated on one GPU wait on each other inside ONE cooperative launch, so
 // 8 x 122 CTAs must be co-resident (7 per SM => 36 registers). Production (one rank per GPU) is unconstrained.
 template <bool kEmulated>
-__global__ void __launch_bounds__(kUpdThreads, kEmulated ? 7 : 3)  // 3/SM: all 122 CTAs fit beside a 96-SM fwd/bwd grid
+__global__ void __launch_bounds__(kUpdThreads, kEmulated ? 7 : 1)
 update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slot, int flags,
               float* __restrict__ host_loss, unsigned long long fc_target) {
   __shared__ ExchangeShared xsh;
@@ -614,7 +614,9 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
   int n = 1;
   if (tr && tid == 0) tr[slice * 4 + 2] = (long long)globaltimer_ns();
   if (cx.world > 1 && !grad_only) {
-    if (ctl->two_shot) exchange_slice_two_shot<2>(cx, slice, seq, i, in_range, v, &n);
+    const unsigned int variant = ctl->two_shot;   // 0 one-shot, 1 two-shot, 2 NVLS
+    if (variant == 2u && cx.nvls_mc != nullptr) exchange_slice_nvls<2>(cx, slice, seq, i, in_range, v, &n);
+    else if (variant == 1u) exchange_slice_two_shot<2>(cx, slice, seq, i, in_range, v, &n);
     else exchange_slice<2>(cx, &xsh, slice, seq, i, in_range, v, &n);
   }
   if (tr && tid == 0) tr[slice * 4 + 3] = (long long)globaltimer_ns();

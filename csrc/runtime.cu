@@ -68,7 +68,7 @@ __global__ void ctl_set_membership_kernel(StepCtl* c, unsigned int mask, unsigne
   c->status = 0u;
 }
 __global__ void ctl_set_divisor_kernel(StepCtl* c, unsigned int d) { c->divisor_override = d; }
-__global__ void ctl_set_variant_kernel(StepCtl* c, unsigned int two_shot) { c->two_shot = two_shot; }
+__global__ void ctl_set_variant_kernel(StepCtl* c, unsigned int variant) { c->two_shot = variant; }
 __global__ void ctl_reset_loss_kernel(StepCtl* c) { c->loss_sum = 0.f; c->loss_steps = 0u; }
 __global__ void ctl_set_step_kernel(StepCtl* c, unsigned long long step) { c->step = step; c->ctas_done = 0u; }
 // leave marker = first sequence number this rank will not take part in
@@ -453,7 +453,9 @@ int dnnb200_engine_set_membership(dnnb200_engine* e, unsigned int active_mask, u
 
 int dnnb200_engine_set_exchange_variant(dnnb200_engine* e, int two_shot, void* stream) {
   DNN_ARG_CHECK(e, "null engine");
-  ctl_set_variant_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(e->ctl, two_shot ? 1u : 0u);
+  DNN_ARG_CHECK(two_shot >= 0 && two_shot <= 2, "exchange variant must be 0 (one-shot), 1 (two-shot) or 2 (NVLS)");
+  DNN_ARG_CHECK(two_shot != 2 || e->h_ctx.nvls_mc != nullptr, "the NVLS variant needs dnnb200_engine_attach_nvls first");
+  ctl_set_variant_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(e->ctl, (unsigned int)two_shot);
   DNN_CUDA_CHECK(cudaGetLastError());
   return kOk;
 }

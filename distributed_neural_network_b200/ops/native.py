@@ -254,9 +254,11 @@ class Engine:
         _check(require().dnnb200_engine_set_membership(self._h, C.c_uint(active_mask), C.c_ulonglong(timeout_ns),
                                                        _stream()))
 
-    def set_exchange_variant(self, two_shot: bool) -> None:
-        """Fused exchange: one-shot (False; tolerates ranks leaving) or two-shot (True; static membership)."""
-        _check(require().dnnb200_engine_set_exchange_variant(self._h, int(two_shot), _stream()))
+    def set_exchange_variant(self, variant) -> None:
+        """Fused exchange: 0/False one-shot (tolerates ranks leaving), 1/True two-shot, 2/"nvls" in-switch reduction
+        (the last two need a static membership)."""
+        v = 2 if variant == "nvls" else int(variant)
+        _check(require().dnnb200_engine_set_exchange_variant(self._h, v, _stream()))
 
     def set_divisor(self, divisor: int) -> None:
         """0 = divide exchanged sums by the ranks present; n = divide by n."""

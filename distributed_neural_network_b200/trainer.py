@@ -139,6 +139,7 @@ class Trainer:
                     self.nvls_buf, self.nvls_mc = made
                     self.engine.attach_nvls(self.nvls_buf, self.nvls_mc)
                     self.nvls_ok = True
+                    self._apply_membership()
         self.failure = FailureSimulator(cfg.failure_probability, cfg.failure_duration, cfg.failure_mode, cfg.seed,
                                         self.rank)
         self.dropped = False
@@ -166,6 +167,15 @@ class Trainer:
     def _sync(self) -> None:
         if self.device.type == "cuda":
             torch.cuda.synchronize()
+
+    def _exchange_variant(self) -> int:
+        """0 one-shot, 1 two-shot, 2 NVLS for the exchange fused into the update kernel."""
+        can_drop = self.cfg.failure_mode == "drop" and self.cfg.failure_probability > 0
+        # the switch adds EVERY member of the multicast group: all ranks must be stepping trainers
+        if (self.cfg.allreduce_variant == "nvls" and self.nvls_ok and not can_drop
+                and len(self.membership.active) == self.world):
+            return 2
+        return 1 if self._exchange_two_shot() else 0
 
     def _exchange_two_shot(self) -> bool:
         """Variant of the fused gradient exchange. One-shot (everyone pushes to everyone) has one latency hop
@@ -197,7 +207,7 @@ class Trainer:
             return
         mask = (1 << self.rank) if local_only else self.membership.mask
         self.engine.set_membership(mask, int(self.cfg.peer_timeout_s * 1e9))
-        self.engine.set_exchange_variant(self._exchange_two_shot() and not local_only)
+        self.engine.set_exchange_variant(0 if local_only else self._exchange_variant())
 
     # ------------------------------------------------------------------ data
     def load_data(self) -> Tuple[Optional[D.TensorDataset], Optional[D.TensorDataset]]:

@@ -109,7 +109,8 @@ int dnnb200_engine_set_hparams(dnnb200_engine* e, float lr, float mu, void* stre
 int dnnb200_engine_set_membership(dnnb200_engine* e, unsigned int active_mask, unsigned long long timeout_ns,
                                   void* stream);
 /* variant of the exchange fused into the update kernel: 0 = one-shot (every rank pushes to every rank; tolerates
- * ranks leaving mid-epoch), 1 = two-shot (slice owners reduce and broadcast; static membership only) */
+ * ranks leaving mid-epoch), 1 = two-shot (slice owners reduce and broadcast; static membership only),
+ * 2 = NVLS (multimem.st flags + multimem.ld_reduce in the NVSwitch; static membership, needs attach_nvls) */
 int dnnb200_engine_set_exchange_variant(dnnb200_engine* e, int two_shot, void* stream);
 /* 0 = divide the exchanged sum by the number of ranks present (default); n = divide by n */
 int dnnb200_engine_set_divisor(dnnb200_engine* e, unsigned int divisor, void* stream);

@@ -79,3 +79,16 @@ def test_nvls_in_switch_allreduce_matches_peer_memory_variant(tmp_path):
             assert torch.equal(y_nvls, res[0]["outs"][key][2]), "NVLS result differs between ranks"
             assert (y_nvls[:nelem].double() - want).abs().max() < 1e-6
             assert (y_one[:nelem].double() - want).abs().max() < 1e-6
+
+
+@needs2
+def test_ipc_fused_step_with_nvls_exchange_matches_one_shot(tmp_path):
+    """Same seeds, same data: the step with the in-switch (NVLS) exchange must train the same model as with one-shot."""
+    n = min(torch.cuda.device_count(), 8)
+    kw = dict(train_size=64 * n, test_size=32, epochs=2, batch_size=8, lr=0.05, seed=11)
+    a = _launch(n, tmp_path / "one", "step-allreduce", allreduce_variant="one-shot", **kw)
+    b = _launch(n, tmp_path / "nvls", "step-allreduce", allreduce_variant="nvls", **kw)
+    for r in range(1, n):
+        assert torch.equal(b[0]["flat"], b[r]["flat"]), "NVLS replicas differ between ranks"
+    rel = ((a[0]["flat"] - b[0]["flat"]).abs().max() / a[0]["flat"].abs().max()).item()
+    assert rel < 1e-5, rel     # summation order inside the switch differs from rank order: last-bit differences only
