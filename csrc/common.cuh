@@ -62,11 +62,6 @@ __device__ __forceinline__ unsigned int ld_relaxed_sys(const unsigned int* p) {
   asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ unsigned long long ld_acquire_gpu_u64(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
 // L2-coherent loads (skip the non-coherent L1) for data a peer GPU wrote.
 __device__ __forceinline__ float4 ld_cg_f4(const float4* p) { return __ldcg(p); }
 __device__ __forceinline__ float ld_cg_f(const float* p) { return __ldcg(p); }

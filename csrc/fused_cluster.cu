@@ -351,8 +351,7 @@ __global__ void __launch_bounds__(kCLThreads, 1)
 fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict__ x,
                        const long long* __restrict__ labels, float* __restrict__ saved,
                        float* __restrict__ part1, float* __restrict__ part2, float* __restrict__ img_loss,
-                       int* __restrict__ img_correct, int B, float inv_batch, long long* __restrict__ trace,
-                       unsigned long long* __restrict__ fc_ready) {
+                       int* __restrict__ img_correct, int B, float inv_batch, long long* __restrict__ trace) {
   static_assert(CS >= 2 && CS <= 8, "the one-CTA case is fused_step.cu's fwd_bwd_kernel");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   CLSmem& s = *reinterpret_cast<CLSmem*>(smem_raw);
@@ -684,12 +683,6 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       s.dc2p[o * 324 + (2 * ph + (id >> 1) + 4) * 18 + (2 * pw + (id & 1) + 4)] = s.g2[tid];
     }
     __syncthreads();  // the data-gradient items below read the plane just scattered
-    // this image's FC record is complete in global memory: the update kernel's FC slices may start on it
-    // while the conv backward of this kernel is still running
-    if (r == 0 && tid == 0 && fc_ready != nullptr) {
-      __threadfence();
-      atomicAdd(fc_ready, 1ull);
-    }
 
     // ================= conv2 data gradient (my pooled pixels) + conv2 weight gradient (my channels) ==========
     // The two are independent, so they share ONE pair of phases: the longer data-gradient items are handed out
@@ -835,7 +828,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
 template <int CS>
 static int launch_cluster_t(const float* params, const float* x, const long long* labels, float* saved, float* part1,
                             float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
-                            long long* trace, unsigned long long* fc_ready, cudaStream_t stream) {
+                            long long* trace, cudaStream_t stream) {
   static bool attr_set = false;
   auto kern = fwd_bwd_cluster_kernel<CS>;
   const size_t smem = cluster_smem_bytes<CS>();
@@ -862,7 +855,7 @@ static int launch_cluster_t(const float* params, const float* x, const long long
   cfg.numAttrs = 2;
   const float inv_batch = 1.f / (float)B;
   DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, params, x, labels, saved, part1, part2, img_loss, img_correct, B,
-                                    inv_batch, trace, fc_ready));
+                                    inv_batch, trace));
   return kOk;
 }
 
@@ -913,15 +906,15 @@ int max_active_clusters(int cs) {
 
 int launch_fwd_bwd_cluster(int cs, const float* params, const float* x, const long long* labels, float* saved,
                            float* part1, float* part2, float* img_loss, int* img_correct, int B, int num_sms /* = max resident clusters */,
-                           long long* trace, unsigned long long* fc_ready, cudaStream_t stream) {
+                           long long* trace, cudaStream_t stream) {
   switch (cs) {
-    case 8: return launch_cluster_t<8>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, fc_ready, stream);
-    case 7: return launch_cluster_t<7>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, fc_ready, stream);
-    case 6: return launch_cluster_t<6>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, fc_ready, stream);
-    case 5: return launch_cluster_t<5>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, fc_ready, stream);
-    case 4: return launch_cluster_t<4>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, fc_ready, stream);
-    case 3: return launch_cluster_t<3>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, fc_ready, stream);
-    case 2: return launch_cluster_t<2>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, fc_ready, stream);
+    case 8: return launch_cluster_t<8>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
+    case 7: return launch_cluster_t<7>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
+    case 6: return launch_cluster_t<6>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
+    case 5: return launch_cluster_t<5>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
+    case 4: return launch_cluster_t<4>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
+    case 3: return launch_cluster_t<3>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
+    case 2: return launch_cluster_t<2>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
     default: set_last_error("cluster size %d not supported", cs); return kErrArg;
   }
 }

@@ -175,7 +175,7 @@ fwd_bwd_kernel(const float* __restrict__ params, const float* __restrict__ x,
                const long long* __restrict__ labels, float* __restrict__ saved,
                float* __restrict__ part1, float* __restrict__ part2, float* __restrict__ img_loss,
                int* __restrict__ img_correct, float* __restrict__ logits_out, int B,
-               float inv_batch, unsigned long long* __restrict__ fc_ready) {
+               float inv_batch) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   FBSmem& s = *reinterpret_cast<FBSmem*>(smem_raw);
   const int tid = threadIdx.x;
@@ -419,10 +419,6 @@ fwd_bwd_kernel(const float* __restrict__ params, const float* __restrict__ x,
       part[kOffB2 + o] = a;
     }
     __syncthreads();
-    if (tid == 0 && fc_ready != nullptr) {  // this image's FC record is complete: the update kernel's FC slices may use it
-      __threadfence();
-      atomicAdd(fc_ready, 1ull);
-    }
     if (tid < 400) {  // scatter pooled gradient to its argmax position (K15)
       const int o = tid / 25, pp = tid - o * 25, ph = pp / 5, pw = pp - ph * 5;
       const int id = s.idx2[tid];
@@ -575,7 +571,7 @@ __device__ __forceinline__ float2 local_grad2(const RankCtx& cx, int i, int B, i
 template <bool kEmulated>
 __global__ void __launch_bounds__(kUpdThreads, kEmulated ? 7 : 1)
 update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slot, int flags,
-              float* __restrict__ host_loss, unsigned long long fc_target) {
+              float* __restrict__ host_loss) {
   __shared__ ExchangeShared xsh;
   const RankCtx& cx = ctxs[blockIdx.y];
   StepCtl* ctl = cx.ctl;
@@ -588,19 +584,7 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
   long long* tr = cx.trace;
   if (tr && tid == 0) tr[slice * 4 + 0] = (long long)globaltimer_ns();
   if (!(flags & 2)) pdl_trigger();
-  // Slices that hold only FC parameters need nothing from the conv backward: they start as soon as every image's
-  // FC record is complete (a counter the forward/backward kernel bumps mid-kernel), so their gradient reduction
-  // AND their exchange over NVLink overlap with the tail of the forward/backward kernel. The few conv slices
-  // wait for the whole predecessor as usual.
-  const bool fc_only = fc_target != 0ull && slice * kSlice >= kConvPrefix;
-  if (fc_only) {
-    if (tid == 0) {
-      while (ld_acquire_gpu_u64(&ctl->fc_ready) < fc_target) {}
-    }
-    __syncthreads();
-  } else {
-    pdl_wait();
-  }
+  pdl_wait();
   if (tr && tid == 0) tr[slice * 4 + 1] = (long long)globaltimer_ns();
   const unsigned long long step = *reinterpret_cast<volatile unsigned long long*>(&ctl->step);
   const unsigned int seq = (unsigned int)(step + 1ull);
@@ -707,7 +691,7 @@ __global__ void eval_reduce_kernel(const float* __restrict__ img_loss, const int
 // ============================================================================
 int launch_fwd_bwd(bool train, const float* params, const float* x, const long long* labels,
                    float* saved, float* part1, float* part2, float* img_loss, int* img_correct,
-                   float* logits_out, int B, int max_ctas, unsigned long long* fc_ready, cudaStream_t stream) {
+                   float* logits_out, int B, int max_ctas, cudaStream_t stream) {
   static bool attr_set[2] = {false, false};
   const size_t smem = sizeof(FBSmem);
   auto kern = train ? fwd_bwd_kernel<true> : fwd_bwd_kernel<false>;
@@ -717,19 +701,17 @@ int launch_fwd_bwd(bool train, const float* params, const float* x, const long l
   }
   const int grid = B < max_ctas ? B : max_ctas;
   kern<<<grid, kFBThreads, smem, stream>>>(params, x, labels, saved, part1, part2, img_loss, img_correct,
-                                           logits_out, B, 1.f / (float)B, fc_ready);
+                                           logits_out, B, 1.f / (float)B);
   DNN_CUDA_CHECK(cudaGetLastError());
   return kOk;
 }
 
 int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int n_part1, int loss_slot, int flags,
-                  float* host_loss, unsigned long long fc_target, cudaStream_t stream) {
+                  float* host_loss, cudaStream_t stream) {
   dim3 grid(kNumSlices, n_virtual_ranks);
   if (n_virtual_ranks > 1) {
     // ranks emulated on ONE device wait on each other: every CTA must be resident
-    unsigned long long no_target = 0ull;  // emulated ranks may have different histories: plain dependency wait
-    void* args[] = {(void*)&d_ctxs, (void*)&B, (void*)&n_part1, (void*)&loss_slot, (void*)&flags, (void*)&host_loss,
-                    (void*)&no_target};
+    void* args[] = {(void*)&d_ctxs, (void*)&B, (void*)&n_part1, (void*)&loss_slot, (void*)&flags, (void*)&host_loss};
     DNN_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)update_kernel<true>, grid, dim3(kUpdThreads), args, 0, stream));
   } else {
     cudaLaunchConfig_t cfg = {};
@@ -742,8 +724,7 @@ int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int n_part1
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, update_kernel<false>, d_ctxs, B, n_part1, loss_slot, flags, host_loss,
-                                      fc_target));
+    DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, update_kernel<false>, d_ctxs, B, n_part1, loss_slot, flags, host_loss));
   }
   return kOk;
 }

@@ -41,7 +41,7 @@ namespace dnnb200 {
 // existing launcher from fused_step.cu (takes its scratch as plain pointers; allocates nothing)
 int launch_fwd_bwd(bool train, const float* params, const float* x, const long long* labels, float* saved,
                    float* part1, float* part2, float* img_loss, int* img_correct, float* logits_out, int B,
-                   int max_ctas, unsigned long long* fc_ready, cudaStream_t stream);
+                   int max_ctas, cudaStream_t stream);
 
 constexpr int kNaMaxBatch = DNNB200_NOALLOC_MAX_BATCH;
 constexpr int kPart2Stride = kConvPrefix - kOffW2;  // 2432
@@ -153,7 +153,7 @@ extern "C" int dnnb200_batch_grad_noalloc(const float* params, const float* x, c
   }
   cudaStream_t s = (cudaStream_t)stream;
   int rc = launch_fwd_bwd(true, params, x, (const long long*)y, sc + kNaSaved, sc + kNaPart1, sc + kNaPart2,
-                          sc + kNaLoss, reinterpret_cast<int*>(sc + kNaCorrect), nullptr, B, kNaMaxBatch, nullptr, s);
+                          sc + kNaLoss, reinterpret_cast<int*>(sc + kNaCorrect), nullptr, B, kNaMaxBatch, s);
   if (rc) return rc;
   noalloc_grad_reduce_kernel<<<(kFlatNumel + 255) / 256, 256, 0, s>>>(sc, B, grads_out, loss_out);
   DNN_CUDA_CHECK(cudaGetLastError());

@@ -34,15 +34,15 @@ void set_last_error(const char* fmt, ...) {
 // ---- launchers implemented in the .cu files -----------------------------------
 int launch_fwd_bwd(bool train, const float* params, const float* x, const long long* labels, float* saved,
                    float* part1, float* part2, float* img_loss, int* img_correct, float* logits_out, int B,
-                   int max_ctas, unsigned long long* fc_ready, cudaStream_t stream);
+                   int max_ctas, cudaStream_t stream);
 int launch_fwd_bwd_cluster(int cs, const float* params, const float* x, const long long* labels, float* saved,
                            float* part1, float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
-                           long long* trace, unsigned long long* fc_ready, cudaStream_t stream);
+                           long long* trace, cudaStream_t stream);
 int max_active_clusters(int cs);
 int launch_pingpong(const RankCtx* d_ctx, int peer, int iters, unsigned int base_seq, long long* d_out_ns,
                     cudaStream_t stream);
 int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int n_part1, int loss_slot, int flags,
-                  float* host_loss, unsigned long long fc_target, cudaStream_t stream);
+                  float* host_loss, cudaStream_t stream);
 int launch_eval_reduce(const float* img_loss, const int* img_correct, int N, int bs, double* out, cudaStream_t stream);
 int launch_allreduce(const RankCtx* d_ctxs, int n_virtual_ranks, const float* const* in, float* const* out, int n,
                      int mode, int two_shot, cudaStream_t stream);
@@ -118,7 +118,6 @@ struct dnnb200_engine {
   dnnb200_group* group = nullptr;
   unsigned long long launches = 0;
   unsigned long long steps_launched = 0;  // host mirror: update launches (loss ring slot)
-  unsigned long long images_launched = 0; // host mirror of StepCtl::fc_ready after everything enqueued so far
   int num_sms = 148;
   // host-fed ring
   static constexpr int kRing = 16;   // device input slots
@@ -211,13 +210,11 @@ static int cluster_size_for(const dnnb200_engine* e, int B) {
 static int fwd_bwd_any(dnnb200_engine* e, const float* x, const long long* y, int B, cudaStream_t s, int* n_part1) {
   const int cs = cluster_size_for(e, B);
   *n_part1 = B;  // clusters reduce their conv1 partials to one row per image before they write them
-  unsigned long long* fc_ready = &e->ctl->fc_ready;
-  e->images_launched += (unsigned long long)B;
   if (cs == 1)
     return launch_fwd_bwd(true, e->params, x, y, e->saved, e->part1, e->part2, e->img_loss, e->img_correct, nullptr,
-                          B, e->num_sms, fc_ready, s);
+                          B, e->num_sms, s);
   return launch_fwd_bwd_cluster(cs, e->params, x, y, e->saved, e->part1, e->part2, e->img_loss, e->img_correct, B,
-                                e->max_clusters[cs] > 0 ? e->max_clusters[cs] : 1, e->trace, fc_ready, s);
+                                e->max_clusters[cs] > 0 ? e->max_clusters[cs] : 1, e->trace, s);
 }
 
 static int step_kernels(dnnb200_engine* e, const float* x, const long long* y, int B, int flags, cudaStream_t s) {
@@ -225,7 +222,7 @@ static int step_kernels(dnnb200_engine* e, const float* x, const long long* y, i
   int rc = fwd_bwd_any(e, x, y, B, s, &n_part1);
   if (rc) return rc;
   rc = launch_update(e->d_ctx, 1, B, n_part1, (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask),
-                     flags | e->debug_flags, nullptr, (e->debug_flags & 4) ? 0ull : e->images_launched, s);
+                     flags | e->debug_flags, nullptr, s);
   if (rc) return rc;
   e->launches += 2;
   return kOk;
@@ -619,8 +616,7 @@ int dnnb200_engine_train_host(dnnb200_engine* e, const float* h_x, const int64_t
       if (rc) return rc;
       // The step's mean loss is written by the update kernel itself into h_losses[t] (device->host, 4 bytes).
       const int lslot = (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask);
-      rc = launch_update(e->d_ctx, 1, B, n_part1, lslot, e->debug_flags, d_losses ? d_losses + t : nullptr,
-                         (e->debug_flags & 4) ? 0ull : e->images_launched, s);
+      rc = launch_update(e->d_ctx, 1, B, n_part1, lslot, 0, d_losses ? d_losses + t : nullptr, s);
       if (rc) return rc;
       e->launches += 2;
       e->steps_launched += 1;
@@ -645,7 +641,7 @@ int dnnb200_engine_eval(dnnb200_engine* e, const float* x, const int64_t* y, int
     e->eval_cap = N;
   }
   int rc = launch_fwd_bwd(false, e->params, x, (const long long*)y, nullptr, nullptr, nullptr, e->eval_loss,
-                          e->eval_correct, logits, N, e->num_sms * 2, nullptr, s);
+                          e->eval_correct, logits, N, e->num_sms * 2, s);
   if (rc) return rc;
   rc = launch_eval_reduce(e->eval_loss, e->eval_correct, N, bs, e->d_eval_out, s);
   if (rc) return rc;
@@ -724,7 +720,7 @@ int dnnb200_vr_step(dnnb200_engine** engines, int n, const float* const* xs, con
   int rc = gather_ctxs(live.data(), (int)live.size(), &d);
   if (rc) return rc;
   const int lslot = (int)(live[0]->steps_launched & (unsigned long long)live[0]->loss_ring_mask);
-  rc = launch_update(d, (int)live.size(), B, n_part1, lslot, 0, nullptr, 0ull, s);
+  rc = launch_update(d, (int)live.size(), B, n_part1, lslot, 0, nullptr, s);
   cudaStreamSynchronize(s);
   cudaFree(d);
   if (rc) return rc;

@@ -33,7 +33,6 @@ struct StepCtl {
   unsigned int ctas_done;   // last-CTA-out counter of the update kernel
   unsigned int status;      // StepStatus bits, sticky until the host clears them
   unsigned int active_mask; // ranks configured into the exchange (bit r = rank r)
-  unsigned long long fc_ready;    // images whose FC records are complete (forward/backward kernels count up, never reset)
   unsigned int two_shot;          // fused exchange variant: 0 one-shot (membership-safe), 1 two-shot (static membership)
   unsigned int pad0_;
   unsigned int divisor_override;  // 0: divide by the ranks present; else by this (parent/children parity mode:

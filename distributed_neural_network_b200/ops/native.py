@@ -40,7 +40,6 @@ class Ctl(C.Structure):
         ("ctas_done", C.c_uint),
         ("status", C.c_uint),
         ("active_mask", C.c_uint),
-        ("fc_ready", C.c_ulonglong),
         ("two_shot", C.c_uint),
         ("pad0_", C.c_uint),
         ("divisor_override", C.c_uint),

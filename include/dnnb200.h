@@ -93,7 +93,6 @@ typedef struct dnnb200_ctl {
   unsigned int ctas_done;
   unsigned int status;
   unsigned int active_mask;
-  unsigned long long fc_ready;
   unsigned int two_shot;
   unsigned int pad0_;
   unsigned int divisor_override;
@@ -132,8 +131,7 @@ int dnnb200_engine_set_trace(dnnb200_engine* e, long long* d_trace);
 /* same for the update kernel: d_trace[slice*4 + {0,1,2,3}] = globaltimer (ns) at entry, after the dependency
  * wait, after the local gradient, after the exchange */
 int dnnb200_engine_set_update_trace(dnnb200_engine* e, long long* d_trace);
-/* development aid: bit 1 (2) = the update kernel does not trigger the early launch of the next kernel;
- * bit 2 (4) = its FC slices wait for the whole forward/backward kernel instead of the FC-record counter */
+/* development aid: bit 1 = the update kernel does not trigger the early launch of the next kernel */
 int dnnb200_engine_set_debug_flags(dnnb200_engine* e, int flags);
 
 /* one optimizer step on a device-resident batch: fwd/bwd kernel + update kernel
