@@ -132,7 +132,6 @@ def run_ours(args) -> int:
                       allreduce_variant=args.exchange)
     trainer = Trainer(cfg)            # public API: model + engine + peer group + control plane
     eng, comm = trainer.engine, trainer.comm
-    eng.set_debug_flags(int(os.environ.get("DNN_DEBUG_FLAGS", "0")))   # development aid, 0 in every reported run
     dev = trainer.device
     variant = trainer._exchange_variant() if world > 1 else 0
     two_shot = variant == 1
