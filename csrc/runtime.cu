@@ -59,6 +59,10 @@ int launch_tc_conv_relu_pool_fwd(const float*, const float*, const float*, float
                                  int, cudaStream_t);
 int launch_tc_gemm_probe(const float*, const float*, float*, int, cudaStream_t);
 int launch_tc_linear_fwd(const float*, const float*, const float*, float*, int, int, int, int, cudaStream_t);
+int launch_tc_lab(const float*, int, const float*, int, unsigned long long, unsigned long long, unsigned int, int, int,
+                  int, float*, int, cudaStream_t);
+int launch_tc_linear_bwd(const float*, const float*, const float*, const float*, float*, float*, float*, float*, int,
+                         int, int, int, cudaStream_t);
 
 // ---- tiny control kernels ---------------------------------------------------
 __global__ void ctl_set_hparams_kernel(StepCtl* c, float lr, float mu) { c->lr = lr; c->mu = mu; }
@@ -271,6 +275,17 @@ int dnnb200_tc_linear_fwd(const float* x, const float* w, const float* b, float*
                           void* stream) {
   DNN_ARG_CHECK(N > 0, "tc_linear_fwd: empty batch");
   return launch_tc_linear_fwd(x, w, b, y, N, M, K, relu, (cudaStream_t)stream);
+}
+int dnnb200_tc_linear_bwd(const float* x, const float* w, const float* y, const float* dy, float* dy_scratch,
+                          float* dx, float* dw, float* db, int N, int M, int K, int relu, void* stream) {
+  DNN_ARG_CHECK(N > 0, "tc_linear_bwd: empty batch");
+  return launch_tc_linear_bwd(x, w, y, dy, dy_scratch, dx, dw, db, N, M, K, relu, (cudaStream_t)stream);
+}
+int dnnb200_tc_lab(const float* a_img, int a_floats, const float* b_img, int b_floats, unsigned long long adesc,
+                   unsigned long long bdesc, unsigned int idesc, int nmma, int a_step, int b_step, float* D, int ncols,
+                   void* stream) {
+  return launch_tc_lab(a_img, a_floats, b_img, b_floats, adesc, bdesc, idesc, nmma, a_step, b_step, D, ncols,
+                       (cudaStream_t)stream);
 }
 int dnnb200_tc_gemm_probe(const float* A, const float* B, float* D, int K, void* stream) {
   return launch_tc_gemm_probe(A, B, D, K, (cudaStream_t)stream);

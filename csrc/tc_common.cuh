@@ -124,11 +124,29 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr, uint32_t sbo
   d |= (uint64_t)2 << 61;  // LayoutType::SWIZZLE_128B
   return d;
 }
-// Instruction descriptor for kind::tf32, fp32 accumulate, both operands K-major
-__host__ __device__ constexpr uint32_t idesc_tf32(int M, int N) {
+// MN-major operand of 4-byte elements (the M/N index is the contiguous one, as in a row-major
+// [reduction][M] matrix). The tensor core accepts exactly one layout for it, "128-byte swizzle with 32-byte
+// atomicity" (layout type 1; every other layout type silently reads zeros -- measured with csrc/tc_lab.cu):
+// rows of 32 floats of M/N, reduction rows 128 bytes apart, the 32-byte chunk c of row r stored at chunk
+// c ^ (r & 3). That is what a TMA box of [rows][32 floats] with CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B leaves in
+// shared memory. LBO = distance between 32-float atoms along M/N, SBO = distance between groups of 4
+// reduction rows (512 bytes when the rows are contiguous); one kind::tf32 MMA (K = 8) reads two groups.
+//   byte(m, k) = (m/32)*LBO + (k/4)*SBO + (k%4)*128 + (((m%32)/8) ^ (k%4))*32 + (m%8)*4
+__device__ __forceinline__ uint64_t smem_desc_mn_sw128_32b(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3fffu);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3fffu) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3fffu) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)1 << 61;  // LayoutType::SWIZZLE_128B_BASE32B
+  return d;
+}
+// Instruction descriptor for kind::tf32, fp32 accumulate; a_mn / b_mn select an MN-major operand
+__host__ __device__ constexpr uint32_t idesc_tf32(int M, int N, bool a_mn = false, bool b_mn = false) {
   return (1u << 4)      // c_format = F32
          | (2u << 7)    // a_format = TF32
          | (2u << 10)   // b_format = TF32
+         | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16)
          | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 

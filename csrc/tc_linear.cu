@@ -16,10 +16,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-#include <mutex>
-
 #include "common.cuh"
 #include "tc_common.cuh"
+#include "tc_tmap.h"
 
 namespace dnnb200 {
 
@@ -119,39 +118,6 @@ tc_linear_fwd_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_co
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_free<kTmemCols>(tmem);
-}
-
-// ---- host: tensor maps through the driver entry point (no libcuda link dependency) ----------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn encode_tiled_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-  });
-  return fn;
-}
-
-// row-major fp32 matrix [rows][cols]; box = [box_rows][32 floats], 128-byte swizzle, zero fill out of bounds
-static int make_tmap_2d(CUtensorMap* tm, const float* base, int rows, int cols, int box_rows) {
-  EncodeTiledFn enc = encode_tiled_fn();
-  if (!enc) { set_last_error("cuTensorMapEncodeTiled is not available from this driver"); return kErrCuda; }
-  const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  const cuuint64_t strides[1] = {(cuuint64_t)cols * sizeof(float)};
-  const cuuint32_t box[2] = {(cuuint32_t)kLinBK, (cuuint32_t)box_rows};
-  const cuuint32_t estr[2] = {1, 1};
-  const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
-                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) { set_last_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return kErrCuda; }
-  return kOk;
 }
 
 template <int BN>

@@ -85,6 +85,11 @@ def conv_relu_pool(x: torch.Tensor, w: torch.Tensor, b: torch.Tensor) -> torch.T
 # ----------------------------------------------------------------------------
 # linear + bias (+ ReLU)
 # ----------------------------------------------------------------------------
+# below this batch size the two scalar kernels of layers.cu are faster than prep + two tensor-core GEMMs
+# (launch-bound: 33 vs 35 us at 256 rows of fc1, 36 vs 114 us at 1024; bench/tc_bwd_probe.py)
+_TC_LINEAR_BWD_MIN_BATCH = 256
+
+
 class _Linear(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, b, relu):
@@ -107,7 +112,12 @@ class _Linear(torch.autograd.Function):
         dx = torch.empty_like(x) if ctx.needs_dx else None
         dw = torch.empty_like(w)
         db = torch.empty(w.shape[0], device=w.device, dtype=torch.float32)
-        native.linear_bwd(x, w.contiguous(), y, dy, dx, dw, db, ctx.relu)
+        w = w.contiguous()
+        if (_conv_precision == "tf32" and x.shape[0] >= _TC_LINEAR_BWD_MIN_BATCH
+                and native.tc_linear_bwd_supported(x, w, dy)):
+            native.tc_linear_bwd(x, w, y, dy, dx, dw, db, ctx.relu)
+        else:
+            native.linear_bwd(x, w, y, dy, dx, dw, db, ctx.relu)
         return dx, dw, db, None
 
 

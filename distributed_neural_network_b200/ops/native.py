@@ -167,6 +167,32 @@ def tc_linear_supported(x, w) -> bool:
     return w.shape[0] <= 128 and x.shape[1] % 4 == 0 and x.data_ptr() % 16 == 0 and w.data_ptr() % 16 == 0
 
 
+def tc_lab(a_img, b_img, adesc: int, bdesc: int, idesc: int, ncols: int, nmma: int = 1, a_step: int = 0,
+           b_step: int = 0):
+    """Descriptor laboratory: raw smem images + raw descriptors -> D[128, ncols] (csrc/tc_lab.cu)."""
+    lib = require()
+    D = torch.full((128, ncols), float("nan"), device=a_img.device)
+    _check(lib.dnnb200_tc_lab(_p(_f32(a_img, "a_img")), a_img.numel(), _p(_f32(b_img, "b_img")), b_img.numel(),
+                              C.c_ulonglong(adesc), C.c_ulonglong(bdesc), C.c_uint(idesc), nmma, a_step, b_step,
+                              _p(D), ncols, _stream()))
+    return D
+
+
+def tc_linear_bwd_supported(x, w, dy) -> bool:
+    M = w.shape[0]
+    return (tc_linear_supported(x, w) and M % 4 == 0 and M >= 4 and dy.data_ptr() % 16 == 0)
+
+
+def tc_linear_bwd(x, w, y, dy, dx, dw, db, relu: bool) -> None:
+    """Tensor-core (tcgen05 + TMA, TF32) linear backward: dX, dW and db (csrc/tc_linear_bwd.cu)."""
+    lib = require()
+    N, K = x.shape
+    scratch = torch.empty_like(dy) if relu else None
+    _check(lib.dnnb200_tc_linear_bwd(_p(_f32(x, "x")), _p(_f32(w, "w")), _p(_f32(y, "y")), _p(_f32(dy, "dy")),
+                                     _p(scratch), _p(dx), _p(_f32(dw, "dw")), _p(_f32(db, "db")),
+                                     N, w.shape[0], K, int(relu), _stream()))
+
+
 def linear_bwd(x, w, y, dy, dx, dw, db, relu: bool) -> None:
     lib = require()
     N, K = x.shape

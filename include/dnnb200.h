@@ -50,6 +50,11 @@ int dnnb200_conv_relu_pool_bwd_tc(const float* x, const float* w, const float* y
  * Instantiated for the two conv layers of the CNN: (Ci,H,W,Co) = (3,32,32,6) and (6,14,14,16). */
 int dnnb200_tc_conv_relu_pool_fwd(const float* x, const float* w, const float* b, float* y, uint8_t* idx,
                                   int N, int Ci, int H, int W, int Co, void* stream);
+/* descriptor laboratory (csrc/tc_lab.cu): raw shared-memory images + raw descriptors (start address 0) in,
+ * D[128, ncols] out; nmma MMAs with the start addresses advancing by a_step / b_step bytes */
+int dnnb200_tc_lab(const float* a_img, int a_floats, const float* b_img, int b_floats, unsigned long long adesc,
+                   unsigned long long bdesc, unsigned int idesc, int nmma, int a_step, int b_step, float* D,
+                   int ncols, void* stream);
 /* D[128,16] = A[128,K] B[16,K]^T through the same descriptors (unit test of the encodings) */
 int dnnb200_tc_gemm_probe(const float* A, const float* B, float* D, int K, void* stream);
 /* y[N,M] = act(x[N,K] w[M,K]^T + b[M]) (K8-K10) */
@@ -59,6 +64,12 @@ int dnnb200_linear_fwd(const float* x, const float* w, const float* b, float* y,
  * TMA through 2-D tensor maps with 128-byte swizzle (csrc/tc_linear.cu). M <= 128, K % 4 == 0. */
 int dnnb200_tc_linear_fwd(const float* x, const float* w, const float* b, float* y, int N, int M, int K,
                           int relu, void* stream);
+/* backward of the same layer on the tensor cores (csrc/tc_linear_bwd.cu): dX and dW are tcgen05 GEMMs whose
+ * operands are TMA boxes of the row-major matrices read through MN-major shared-memory descriptors (no
+ * transposes). M % 4 == 0, M <= 128, K % 4 == 0. dy_scratch [N, M] is needed when relu != 0 (masked dy);
+ * dx may be NULL. dW is accumulated with fp32 atomics when the batch is split over CTAs. */
+int dnnb200_tc_linear_bwd(const float* x, const float* w, const float* y, const float* dy, float* dy_scratch,
+                          float* dx, float* dw, float* db, int N, int M, int K, int relu, void* stream);
 /* dx may be NULL; y is the layer OUTPUT (its sign gives ReLU') (K13, K14) */
 int dnnb200_linear_bwd(const float* x, const float* w, const float* y, const float* dy, float* dx,
                        float* dw, float* db, int N, int M, int K, int relu, void* stream);

@@ -103,3 +103,72 @@ def test_network_forward_uses_tensor_cores_by_default_and_fp32_on_request():
         Fn.set_conv_precision("tf32")
     assert _rel(got_fp32, want) < 2e-5
     assert 1e-7 < _rel(got_tf32, want) < 5e-3           # close, but visibly not the fp32 path
+
+
+@pytest.mark.parametrize("N,K,M,relu", [(16, 400, 120, True), (100, 400, 120, True), (1000, 400, 120, False),
+                                        (4096, 400, 120, True), (64, 120, 84, True), (777, 120, 84, False),
+                                        (5000, 120, 84, True)])
+def test_tc_linear_backward_mn_major_operands(N, K, M, relu):
+    """dX and dW as tcgen05 GEMMs fed by TMA boxes of the row-major matrices (MN-major descriptors)."""
+    torch.manual_seed(N + M)
+    x, w, b = torch.randn(N, K), torch.randn(M, K) * K ** -0.5, torch.randn(M) * 0.1
+    dy = torch.randn(N, M)
+    pre = F.linear(x, w, b)
+    y = F.relu(pre) if relu else pre
+    d = dy * (pre > 0) if relu else dy
+    want_dx, want_dw, want_db = d @ w, d.t() @ x, d.sum(0)
+    dx = torch.full((N, K), float("nan"), device="cuda")
+    dw = torch.full((M, K), float("nan"), device="cuda")
+    db = torch.full((M,), float("nan"), device="cuda")
+    native.tc_linear_bwd(x.cuda(), w.cuda(), y.cuda(), dy.cuda(), dx, dw, db, relu)
+    torch.cuda.synchronize()
+    assert torch.isfinite(dx).all() and torch.isfinite(dw).all() and torch.isfinite(db).all()
+    assert _rel(dx, want_dx) < 4e-3, _rel(dx, want_dx)
+    assert _rel(dw, want_dw) < 4e-3, _rel(dw, want_dw)
+    assert _rel(db, want_db) < 1e-4, _rel(db, want_db)
+
+
+def test_autograd_linear_uses_tensor_core_backward_for_large_batches():
+    torch.manual_seed(3)
+    x = torch.randn(512, 400)
+    w = torch.randn(120, 400) * 0.05
+    b = torch.randn(120) * 0.1
+    xr, wr, br = x.clone().requires_grad_(True), w.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    F.relu(F.linear(xr, wr, br)).square().sum().backward()
+    xg, wg, bg = (t.cuda().requires_grad_(True) for t in (x, w, b))
+    assert Fn.get_conv_precision() == "tf32"
+    Fn.linear(xg, wg, bg, relu=True).square().sum().backward()
+    assert _rel(xg.grad, xr.grad) < 6e-3
+    assert _rel(wg.grad, wr.grad) < 6e-3
+    assert _rel(bg.grad, br.grad) < 6e-3
+
+
+def test_mn_major_tf32_operand_address_function():
+    """The only MN-major layout tcgen05.mma reads for 4-byte operands (128-byte swizzle, 32-byte atoms), mapped
+    with a ramp image against an identity: D is the operand exactly as the tensor core sees it (csrc/tc_lab.cu)."""
+    def desc(layout_type, lbo, sbo):
+        return ((lbo >> 4) & 0x3FFF) << 16 | ((sbo >> 4) & 0x3FFF) << 32 | 1 << 46 | layout_type << 61
+
+    def idesc(M, N, a_mn, b_mn):
+        return (1 << 4) | (2 << 7) | (2 << 10) | (a_mn << 15) | (b_mn << 16) | ((N >> 3) << 17) | ((M >> 4) << 24)
+
+    ident = torch.zeros(2 * 2 * 32)                    # B[16][8] = identity, canonical no-swizzle K-major
+    for k in range(8):
+        ident[((k >> 2) * 2 + (k >> 3)) * 32 + (k & 7) * 4 + (k & 3)] = 1.0
+    words = torch.arange(4096)
+    lbo, sbo = 4096, 512
+    m = torch.arange(128).view(-1, 1)
+    k = torch.arange(8).view(1, -1)
+    want = ((m // 32) * lbo + (k // 4) * sbo + (k % 4) * 128 + ((((m % 32) // 8) ^ (k % 4)) * 32) + (m % 8) * 4) // 4
+    got = torch.zeros(128, 8, dtype=torch.long)
+    for shift, mask in ((0, 1023), (10, 1023)):        # two runs: TF32 keeps 10 mantissa bits exactly
+        img = ((words >> shift) & mask).float().cuda()
+        D = native.tc_lab(img, ident.cuda(), desc(1, lbo, sbo), desc(0, 256, 128), idesc(128, 16, 1, 0), 16)
+        torch.cuda.synchronize()
+        got += D[:, :8].cpu().long() << shift
+    assert torch.equal(got, want)
+    # the ordinary 128-byte swizzle (layout type 2) is NOT accepted for an MN-major fp32 operand: it reads zeros
+    D = native.tc_lab((words & 1023).float().cuda() + 1.0, ident.cuda(), desc(2, 4096, 1024), desc(0, 256, 128),
+                      idesc(128, 16, 1, 0), 16)
+    torch.cuda.synchronize()
+    assert float(D[:, :8].abs().max()) == 0.0
