@@ -21,13 +21,16 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent
 CSRC = ROOT / "csrc"
 OUT_DIR = ROOT / "distributed_neural_network_b200" / "_native"
-OBJ_DIR = OUT_DIR / "obj"
-LIB = OUT_DIR / "libdnnb200.so"
+# experiments: DNN_BUILD_TAG=x DNN_BUILD_DEFINES="-DFOO=1 -DBAR=2" python build.py -> libdnnb200_x.so (load it with
+# DNNB200_LIB=<path>); the default build has neither
+_TAG = os.environ.get("DNN_BUILD_TAG", "")
+OBJ_DIR = OUT_DIR / ("obj" + ("_" + _TAG if _TAG else ""))
+LIB = OUT_DIR / ("libdnnb200" + ("_" + _TAG if _TAG else "") + ".so")
 
 NVCC = os.environ.get("NVCC") or shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--use_fast_math", "-Xptxas", "-v",
-          "-I", str(ROOT / "include"), "-I", str(CSRC)]
+          "-I", str(ROOT / "include"), "-I", str(CSRC)] + os.environ.get("DNN_BUILD_DEFINES", "").split()
 
 
 def sources():

@@ -81,14 +81,15 @@ allreduce_kernel(const RankCtx* __restrict__ ctxs, const ArParams prm) {
     v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
   }
   int n = 1;
+  const ExchangeCfg cfg = exchange_cfg(ctl);
   if (world > 1 && !prm.two_shot) {
-    exchange_slice<4>(cx, &xsh, slice, seq, i, in_range, v, &n);
+    exchange_slice<4>(cx, cfg, &xsh, slice, seq, i, in_range, v, &n);
     if (in_range) finish(cx, prm, vr, i, v, n);
   } else if (world > 1 && prm.two_shot == 2) {
-    exchange_slice_nvls<4>(cx, slice, seq, i, in_range, v, &n);   // in-switch reduction (exchange.cuh)
+    exchange_slice_nvls<4>(cx, cfg, slice, seq, i, in_range, v, &n);   // in-switch reduction (exchange.cuh)
     if (in_range) finish(cx, prm, vr, i, v, n);
   } else if (world > 1) {
-    exchange_slice_two_shot<4>(cx, slice, seq, i, in_range, v, &n);
+    exchange_slice_two_shot<4>(cx, cfg, slice, seq, i, in_range, v, &n);
     if (in_range) finish(cx, prm, vr, i, v, n);
   } else {
     if (in_range) finish(cx, prm, vr, i, v, 1);

@@ -36,6 +36,19 @@ struct ExchangeShared {
   unsigned int present;  // bitmask of ranks whose contribution enters the sum
 };
 
+// The two StepCtl fields every exchange needs, read by the caller (the update kernel reads them BEFORE it waits for
+// its predecessor, so that no dependent global load sits between "gradient ready" and the first remote store).
+struct ExchangeCfg {
+  unsigned int configured;        // StepCtl::active_mask
+  unsigned long long timeout_ns;  // StepCtl::timeout_ns
+};
+__device__ __forceinline__ ExchangeCfg exchange_cfg(const StepCtl* ctl) {
+  ExchangeCfg c;
+  c.configured = ctl->active_mask;
+  c.timeout_ns = ctl->timeout_ns;
+  return c;
+}
+
 __device__ __forceinline__ bool seq_reached(unsigned int v, unsigned int seq) {
   return v != 0u && (int)(v - seq) >= 0;
 }
@@ -65,14 +78,14 @@ constexpr size_t kLLStride = 2 * (size_t)kFlatNumel;
 // Values: each thread owns kVec consecutive floats at flat index `i` (kVec = 2 or 4, i % kVec == 0).
 // Returns the sum over present ranks in rank order; *n_present gets the divisor.
 template <int kVec>
-__device__ __forceinline__ void exchange_slice(const RankCtx& cx, ExchangeShared* sh, int slice,
-                                               unsigned int seq, int i, bool in_range,
+__device__ __forceinline__ void exchange_slice(const RankCtx& cx, const ExchangeCfg cfg, ExchangeShared* sh,
+                                               int slice, unsigned int seq, int i, bool in_range,
                                                float (&v)[kVec], int* n_present) {
   static_assert(kVec == 2 || kVec == 4, "vector width");
   const int world = cx.world, rank = cx.rank;
   const int tid = threadIdx.x;
   const unsigned int parity = seq & 1u;
-  const unsigned int configured = cx.ctl->active_mask;
+  const unsigned int configured = cfg.configured;
   const unsigned int* my_flags = cx.flags[rank];
 
   // 1. push my values to every configured peer: one 16-byte LL line per pair of floats.
@@ -92,7 +105,7 @@ __device__ __forceinline__ void exchange_slice(const RankCtx& cx, ExchangeShared
   if (tid == 0) sh->present = configured;
   __syncthreads();
   const float* my_recv = cx.recv[rank];
-  const unsigned long long tmo = cx.ctl->timeout_ns;
+  const unsigned long long tmo = cfg.timeout_ns;
   float acc[kVec];
 #pragma unroll
   for (int k = 0; k < kVec; ++k) acc[k] = 0.f;
@@ -213,14 +226,15 @@ __device__ __forceinline__ bool ll_poll(const float* line, unsigned int seq, flo
 }
 
 template <int kVec>
-__device__ __forceinline__ void exchange_slice_two_shot(const RankCtx& cx, int slice, unsigned int seq, int i,
-                                                        bool in_range, float (&v)[kVec], int* n_present) {
+__device__ __forceinline__ void exchange_slice_two_shot(const RankCtx& cx, const ExchangeCfg cfg, int slice,
+                                                        unsigned int seq, int i, bool in_range, float (&v)[kVec],
+                                                        int* n_present) {
   static_assert(kVec == 2 || kVec == 4, "vector width");
   const int world = cx.world, rank = cx.rank;
   const unsigned int parity = seq & 1u;
-  const unsigned int configured = cx.ctl->active_mask;
+  const unsigned int configured = cfg.configured;
   const int n_cfg = __popc(configured);
-  const unsigned long long tmo = cx.ctl->timeout_ns;
+  const unsigned long long tmo = cfg.timeout_ns;
   *n_present = n_cfg;
   int owner = 0;
   {
@@ -307,12 +321,13 @@ __device__ __forceinline__ void exchange_slice_two_shot(const RankCtx& cx, int s
 // there" to every rank; multimem.ld_reduce returns the switch's sum of all W copies. Static membership (the
 // switch adds every member of the multicast group). Used when the host exposes NVLink multicast.
 template <int kVec>
-__device__ __forceinline__ void exchange_slice_nvls(const RankCtx& cx, int slice, unsigned int seq, int i,
-                                                    bool in_range, float (&v)[kVec], int* n_present) {
+__device__ __forceinline__ void exchange_slice_nvls(const RankCtx& cx, const ExchangeCfg cfg, int slice,
+                                                    unsigned int seq, int i, bool in_range, float (&v)[kVec],
+                                                    int* n_present) {
   static_assert(kVec == 2 || kVec == 4, "vector width");
   const int world = cx.world, rank = cx.rank, tid = threadIdx.x;
   const unsigned int parity = seq & 1u;
-  const unsigned int configured = cx.ctl->active_mask;
+  const unsigned int configured = cfg.configured;
   float* loc = cx.nvls_local;
   float* mc = cx.nvls_mc;
   *n_present = world;
@@ -332,7 +347,7 @@ __device__ __forceinline__ void exchange_slice_nvls(const RankCtx& cx, int slice
   }
   if (tid < world && ((configured >> tid) & 1u)) {
     const unsigned int* f = lflags + (parity * kMaxWorld + tid) * kFlagRow + slice;
-    const unsigned long long tmo = cx.ctl->timeout_ns;
+    const unsigned long long tmo = cfg.timeout_ns;
     unsigned long long t0 = 0;
     unsigned int spins = 0;
     while (ld_acquire_sys(f) != seq) {

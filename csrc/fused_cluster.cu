@@ -346,12 +346,23 @@ __device__ __forceinline__ void fc_dx_partial_push(const float* wsm, const float
 // development aid: thread 0 of every CTA stamps the SM clock at stage boundaries (trace == nullptr in production)
 #define CL_TRACE(k) do { if (trace != nullptr && tid == 0) trace[blockIdx.x * 32 + (k)] = clock64(); } while (0)
 
+// Register budget (experiment switch): 512 threads x 96 registers would leave a quarter of the register file
+// free, exactly one CTA of the update kernel at 256 threads x 64, so that the kernels of consecutive steps can
+// share an SM. (__maxnreg__ and __launch_bounds__ are mutually exclusive.)
+#ifndef DNN_F_MAXNREG
+#define DNN_F_MAXNREG 0
+#endif
 template <int CS>
+#if DNN_F_MAXNREG > 0
+__global__ void __maxnreg__(DNN_F_MAXNREG)
+#else
 __global__ void __launch_bounds__(kCLThreads, 1)
+#endif
 fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict__ x,
                        const long long* __restrict__ labels, float* __restrict__ saved,
                        float* __restrict__ part1, float* __restrict__ part2, float* __restrict__ img_loss,
-                       int* __restrict__ img_correct, int B, float inv_batch, long long* __restrict__ trace) {
+                       int* __restrict__ img_correct, int B, float inv_batch, long long* __restrict__ trace,
+                       const unsigned int* __restrict__ ready_ctr, unsigned int ready_expect) {
   static_assert(CS >= 2 && CS <= 8, "the one-CTA case is fused_step.cu's fwd_bwd_kernel");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   CLSmem& s = *reinterpret_cast<CLSmem*>(smem_raw);
@@ -400,9 +411,25 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       cl_bulk_g2s(s.xd, x + (size_t)im * kImgNumel, kImgNumel * 4, &s.mbar);
     }
   };
-  load_image(img);   // the input batch does not depend on the previous kernel of the stream ...
-  pdl_trigger();     // ... whose successor (the update kernel) may be scheduled from now on,
-  pdl_wait();        // but the weights do: they are written by the previous step's update kernel
+  load_image(img);   // the input batch does not depend on the previous kernel of the stream,
+  // but the weights do: they are written by the previous step's update kernel. Two ways to wait for it:
+  //  * griddepcontrol.wait -- until that GRID has completed and flushed. With peers, its completion includes the
+  //    acknowledgement of its NVLink stores: measured 3.3 us after its last instruction on the rank that pushed last.
+  //  * (steps chained inside one engine call, all weights read by TMA) spin on the counter the update kernel's
+  //    last CTA releases once every CTA has stored its parameters; the grid's drain then overlaps this kernel.
+  // Only thread 0 reads weights (bulk copies; everybody else sees them through the mbarriers they complete), so
+  // only thread 0 waits, and only it lets the successor be scheduled: when the update kernel of THIS step starts,
+  // everything launched before this kernel is complete and visible (it stages its control block before its wait).
+  if (ready_ctr != nullptr) {
+    if (tid == 0) {
+      while ((int)(ld_acquire_gpu(ready_ctr) - ready_expect) < 0) {}
+      asm volatile("fence.proxy.async;" ::: "memory");  // the bulk copies below read through the async proxy
+      pdl_trigger();
+    }
+  } else {
+    pdl_wait();
+    if (tid == 0) pdl_trigger();
+  }
   if (tid == 0) {
     // every weight this CTA needs arrives by TMA bulk copy, issued before anything else: the conv block now,
     // (clusters >= 4) my FC row slices + the FC biases, which land while the conv layers run
@@ -828,7 +855,8 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
 template <int CS>
 static int launch_cluster_t(const float* params, const float* x, const long long* labels, float* saved, float* part1,
                             float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
-                            long long* trace, cudaStream_t stream) {
+                            long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
+                            cudaStream_t stream) {
   static bool attr_set = false;
   auto kern = fwd_bwd_cluster_kernel<CS>;
   const size_t smem = cluster_smem_bytes<CS>();
@@ -855,7 +883,7 @@ static int launch_cluster_t(const float* params, const float* x, const long long
   cfg.numAttrs = 2;
   const float inv_batch = 1.f / (float)B;
   DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, params, x, labels, saved, part1, part2, img_loss, img_correct, B,
-                                    inv_batch, trace));
+                                    inv_batch, trace, CS >= 4 ? ready_ctr : nullptr, ready_expect));
   return kOk;
 }
 
@@ -906,15 +934,16 @@ int max_active_clusters(int cs) {
 
 int launch_fwd_bwd_cluster(int cs, const float* params, const float* x, const long long* labels, float* saved,
                            float* part1, float* part2, float* img_loss, int* img_correct, int B, int num_sms /* = max resident clusters */,
-                           long long* trace, cudaStream_t stream) {
+                           long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
+                           cudaStream_t stream) {
   switch (cs) {
-    case 8: return launch_cluster_t<8>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
-    case 7: return launch_cluster_t<7>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
-    case 6: return launch_cluster_t<6>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
-    case 5: return launch_cluster_t<5>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
-    case 4: return launch_cluster_t<4>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
-    case 3: return launch_cluster_t<3>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
-    case 2: return launch_cluster_t<2>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, stream);
+    case 8: return launch_cluster_t<8>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, ready_ctr, ready_expect, stream);
+    case 7: return launch_cluster_t<7>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, ready_ctr, ready_expect, stream);
+    case 6: return launch_cluster_t<6>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, ready_ctr, ready_expect, stream);
+    case 5: return launch_cluster_t<5>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, ready_ctr, ready_expect, stream);
+    case 4: return launch_cluster_t<4>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, ready_ctr, ready_expect, stream);
+    case 3: return launch_cluster_t<3>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, ready_ctr, ready_expect, stream);
+    case 2: return launch_cluster_t<2>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, ready_ctr, ready_expect, stream);
     default: set_last_error("cluster size %d not supported", cs); return kErrArg;
   }
 }

@@ -504,7 +504,12 @@ fwd_bwd_kernel(const float* __restrict__ params, const float* __restrict__ x,
 // ============================================================================
 // update_kernel
 // ============================================================================
-constexpr int kUpdThreads = kSlice / 2;  // 256 threads, two consecutive floats each
+#ifndef DNN_U_VEC
+#define DNN_U_VEC 2
+#endif
+constexpr int kUVec = DNN_U_VEC;              // consecutive floats per thread (2 or 4)
+constexpr int kUpdThreads = kSlice / kUVec;   // 256 or 128 threads per 512-float slice
+static_assert(kUVec == 2 || kUVec == 4, "update kernel vector width");
 
 // d(loss)/d(param[i]) and param[i+1] summed over the local batch. i is even and both
 // elements lie in the same tensor row (all row lengths are even).
@@ -566,61 +571,114 @@ __device__ __forceinline__ float2 local_grad2(const RankCtx& cx, int i, int B, i
   return g;
 }
 
-// kEmulated: several ranks emulated on one GPU wait on each other inside ONE cooperative launch, so
-// 8 x 122 CTAs must be co-resident (7 per SM => 36 registers). Production (one rank per GPU) is unconstrained.
-template <bool kEmulated>
-__global__ void __launch_bounds__(kUpdThreads, kEmulated ? 7 : 1)
+// kEmulated: several ranks emulated on one GPU wait on each other inside ONE cooperative launch.
+// kMinBlocks (CTAs per SM the register budget must allow):
+//   7  ranks emulated on one GPU: all 8 x 122 CTAs of the cooperative launch must be co-resident
+//   1  one GPU, no exchange: no constraint (fastest gradient reduction)
+//   3  real peers: all 122 CTAs must fit on the 52 SMs the forward/backward kernel (96 CTAs, one per SM, nearly
+//      the whole register file each) leaves free. Otherwise the last CTAs land on SMs that kernel has just left,
+//      and the NEXT step's clusters cannot be placed there until those CTAs have exited -- which, after NVLink
+//      stores, takes ~3 us longer than their last instruction (the stores drain first). Measured at 2 GPUs:
+//      25.3 -> 22.4 us per step; on one GPU the same budget costs 0.7 us, hence two instantiations.
+template <bool kEmulated, int kMinBlocks>
+__global__ void __launch_bounds__(kUpdThreads, kMinBlocks)
 update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slot, int flags,
               float* __restrict__ host_loss) {
   __shared__ ExchangeShared xsh;
-  const RankCtx& cx = ctxs[blockIdx.y];
-  StepCtl* ctl = cx.ctl;
+  __shared__ RankCtx cx;        // this rank's context and ...
+  __shared__ StepCtl ctl_snap;  // ... the host-set fields of its control block, staged BEFORE the dependency wait
   const int slice = blockIdx.x, tid = threadIdx.x;
-  const int i = slice * kSlice + 2 * tid;
+  const int i = slice * kSlice + kUVec * tid;
   const bool in_range = i < kFlatNumel;
-  // programmatic dependent launch: the next step's forward/backward kernel may be scheduled from now on (it
-  // loads its input batch and then waits for us); we wait for OUR predecessor before touching anything it,
-  // or transitively the previous update kernel, has written
-  long long* tr = cx.trace;
-  if (tr && tid == 0) tr[slice * 4 + 0] = (long long)globaltimer_ns();
+  long long t_enter = 0, t_dep = 0;
+  if (tid == 0) t_enter = (long long)globaltimer_ns();
+  // Programmatic dependent launch: the next step's forward/backward kernel may be scheduled from now on (it
+  // loads its input batch and then waits for us). Everything the host configured before this step's
+  // forward/backward kernel -- the context (pointers, peer tables) and lr / momentum / membership / timeout /
+  // exchange variant -- is visible already (that kernel only lets us start after its own dependency wait), so it
+  // is copied to shared memory now: after the wait, nothing but the gradient records themselves is loaded from
+  // global memory before the first remote store goes out.
   if (!(flags & 2)) pdl_trigger();
+  {
+    static_assert(sizeof(RankCtx) % 4 == 0 && sizeof(StepCtl) % 4 == 0, "word copies");
+    const unsigned int* src = reinterpret_cast<const unsigned int*>(ctxs + blockIdx.y);
+    unsigned int* dst = reinterpret_cast<unsigned int*>(&cx);
+    for (int w = tid; w < (int)(sizeof(RankCtx) / 4); w += kUpdThreads) dst[w] = __ldg(src + w);
+  }
+  __syncthreads();
+  StepCtl* ctl = cx.ctl;
+  if (tid < (int)(sizeof(StepCtl) / 4))
+    reinterpret_cast<unsigned int*>(&ctl_snap)[tid] = reinterpret_cast<const volatile unsigned int*>(ctl)[tid];
+  __syncthreads();
+  // parameters and momentum of my elements were written by the PREVIOUS update kernel, which had completed (and
+  // fenced) before this step's forward/backward kernel let us start: fetch them now (from L2, the coherence
+  // point), so that the SGD update after the exchange has no load left in front of its stores
+  const bool grad_only = (flags & 1) != 0;  // tests: leave the local batch gradient in cx.grads, touch nothing else
+  float2 m[kUVec / 2], p[kUVec / 2];
+#pragma unroll
+  for (int k = 0; k < kUVec; k += 2) {
+    m[k / 2] = make_float2(0.f, 0.f);
+    p[k / 2] = make_float2(0.f, 0.f);
+    if (in_range && !grad_only) {
+      m[k / 2] = __ldcg(reinterpret_cast<const float2*>(cx.momentum + i + k));
+      p[k / 2] = __ldcg(reinterpret_cast<const float2*>(cx.params + i + k));
+    }
+  }
   pdl_wait();
-  if (tr && tid == 0) tr[slice * 4 + 1] = (long long)globaltimer_ns();
+  long long* tr = cx.trace;
+  if (tr && tid == 0) t_dep = (long long)globaltimer_ns();
   const unsigned long long step = *reinterpret_cast<volatile unsigned long long*>(&ctl->step);
   const unsigned int seq = (unsigned int)(step + 1ull);
+  if (tr) {
+    // flags bit 2 (value 4): keep the stamps of the last 1024 steps ([step % 1024][slice][8]) instead of one step
+    if (flags & 4) tr += (size_t)(step & 1023ull) * gridDim.x * 8;
+    if (tid == 0) { tr[slice * 8 + 0] = t_enter; tr[slice * 8 + 1] = t_dep; }
+  }
 
-  float v[2] = {0.f, 0.f};
+  float v[kUVec];
+#pragma unroll
+  for (int k = 0; k < kUVec; ++k) v[k] = 0.f;
   if (in_range) {
-    const float2 g = local_grad2(cx, i, B, n_part1);
-    v[0] = g.x; v[1] = g.y;
+#pragma unroll
+    for (int k = 0; k < kUVec; k += 2) {
+      const float2 g = local_grad2(cx, i + k, B, n_part1);
+      v[k] = g.x; v[k + 1] = g.y;
+    }
   }
-  const bool grad_only = (flags & 1) != 0;  // tests: leave the local batch gradient in cx.grads, touch nothing else
   int n = 1;
-  if (tr && tid == 0) tr[slice * 4 + 2] = (long long)globaltimer_ns();
+  if (tr && tid == 0) tr[slice * 8 + 2] = (long long)globaltimer_ns();
   if (cx.world > 1 && !grad_only) {
-    const unsigned int variant = ctl->two_shot;   // 0 one-shot, 1 two-shot, 2 NVLS
-    if (variant == 2u && cx.nvls_mc != nullptr) exchange_slice_nvls<2>(cx, slice, seq, i, in_range, v, &n);
-    else if (variant == 1u) exchange_slice_two_shot<2>(cx, slice, seq, i, in_range, v, &n);
-    else exchange_slice<2>(cx, &xsh, slice, seq, i, in_range, v, &n);
+    const unsigned int variant = ctl_snap.two_shot;   // 0 one-shot, 1 two-shot, 2 NVLS
+    ExchangeCfg cfg;
+    cfg.configured = ctl_snap.active_mask;
+    cfg.timeout_ns = ctl_snap.timeout_ns;
+    if (variant == 2u && cx.nvls_mc != nullptr) exchange_slice_nvls<kUVec>(cx, cfg, slice, seq, i, in_range, v, &n);
+    else if (variant == 1u) exchange_slice_two_shot<kUVec>(cx, cfg, slice, seq, i, in_range, v, &n);
+    else exchange_slice<kUVec>(cx, cfg, &xsh, slice, seq, i, in_range, v, &n);
   }
-  if (tr && tid == 0) tr[slice * 4 + 3] = (long long)globaltimer_ns();
+  if (tr && tid == 0) tr[slice * 8 + 3] = (long long)globaltimer_ns();
 
   if (in_range && grad_only) {
-    if (cx.grads) *reinterpret_cast<float2*>(cx.grads + i) = make_float2(v[0], v[1]);
+    if (cx.grads) {
+#pragma unroll
+      for (int k = 0; k < kUVec; k += 2) *reinterpret_cast<float2*>(cx.grads + i + k) = make_float2(v[k], v[k + 1]);
+    }
   } else if (in_range) {
-    const unsigned int dov = ctl->divisor_override;
+    const unsigned int dov = ctl_snap.divisor_override;
     const float inv_n = 1.f / (float)(dov ? (int)dov : n);
-    const float lr = ctl->lr, mu = ctl->mu;
-    const float g0 = v[0] * inv_n, g1 = v[1] * inv_n;
-    float2 m = *reinterpret_cast<float2*>(cx.momentum + i);
-    float2 p = *reinterpret_cast<float2*>(cx.params + i);
-    m.x = mu * m.x + g0;  // zeroed momentum makes the first step buf = g, as torch.optim.SGD
-    m.y = mu * m.y + g1;
-    p.x -= lr * m.x;
-    p.y -= lr * m.y;
-    *reinterpret_cast<float2*>(cx.momentum + i) = m;
-    *reinterpret_cast<float2*>(cx.params + i) = p;
-    if (cx.grads) *reinterpret_cast<float2*>(cx.grads + i) = make_float2(g0, g1);
+    const float lr = ctl_snap.lr, mu = ctl_snap.mu;
+#pragma unroll
+    for (int k = 0; k < kUVec; k += 2) {
+      const float g0 = v[k] * inv_n, g1 = v[k + 1] * inv_n;
+      float2 mm = m[k / 2], pp = p[k / 2];
+      mm.x = mu * mm.x + g0;  // zeroed momentum makes the first step buf = g, as torch.optim.SGD
+      mm.y = mu * mm.y + g1;
+      pp.x -= lr * mm.x;
+      pp.y -= lr * mm.y;
+      *reinterpret_cast<float2*>(cx.momentum + i + k) = mm;
+      *reinterpret_cast<float2*>(cx.params + i + k) = pp;
+      if (cx.grads) *reinterpret_cast<float2*>(cx.grads + i + k) = make_float2(g0, g1);
+    }
   }
 
   if (slice == 0 && tid < 32) {  // per-step mean loss, fixed summation order
@@ -642,14 +700,20 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
       }
     }
   }
+  if (tr && tid == 0) tr[slice * 8 + 4] = (long long)globaltimer_ns();
   __syncthreads();
   if (tid == 0) {
     __threadfence();
+    if (tr) tr[slice * 8 + 5] = (long long)globaltimer_ns();
     const unsigned int done = atomicAdd(&ctl->ctas_done, 1u);
+    if (tr) tr[slice * 8 + 6] = (long long)globaltimer_ns();
     if (done == gridDim.x - 1) {  // last CTA of this rank: everyone has read `step`
       ctl->ctas_done = 0u;
       __threadfence();
       if (!grad_only) *reinterpret_cast<volatile unsigned long long*>(&ctl->step) = step + 1ull;
+      // "parameters of this step are in place": what the next forward/backward kernel spins on (fused_cluster.cu).
+      // Every CTA fenced its stores before it bumped ctas_done, and this CTA has observed all the bumps.
+      st_release_gpu(&ctl->updates_done, ctl->updates_done + 1u);
     }
   }
 }
@@ -712,7 +776,7 @@ int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int n_part1
   if (n_virtual_ranks > 1) {
     // ranks emulated on ONE device wait on each other: every CTA must be resident
     void* args[] = {(void*)&d_ctxs, (void*)&B, (void*)&n_part1, (void*)&loss_slot, (void*)&flags, (void*)&host_loss};
-    DNN_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)update_kernel<true>, grid, dim3(kUpdThreads), args, 0, stream));
+    DNN_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)update_kernel<true, 7>, grid, dim3(kUpdThreads), args, 0, stream));
   } else {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
@@ -724,7 +788,10 @@ int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int n_part1
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, update_kernel<false>, d_ctxs, B, n_part1, loss_slot, flags, host_loss));
+    if (flags & kUpdFlagPeers)
+      DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, update_kernel<false, 3>, d_ctxs, B, n_part1, loss_slot, flags, host_loss));
+    else
+      DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, update_kernel<false, 1>, d_ctxs, B, n_part1, loss_slot, flags, host_loss));
   }
   return kOk;
 }

@@ -37,7 +37,8 @@ int launch_fwd_bwd(bool train, const float* params, const float* x, const long l
                    int max_ctas, cudaStream_t stream);
 int launch_fwd_bwd_cluster(int cs, const float* params, const float* x, const long long* labels, float* saved,
                            float* part1, float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
-                           long long* trace, cudaStream_t stream);
+                           long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
+                           cudaStream_t stream);
 int max_active_clusters(int cs);
 int launch_pingpong(const RankCtx* d_ctx, int peer, int iters, unsigned int base_seq, long long* d_out_ns,
                     cudaStream_t stream);
@@ -105,6 +106,7 @@ struct dnnb200_engine {
   float *params = nullptr, *momentum = nullptr, *grads = nullptr;
   float *saved = nullptr, *part1 = nullptr, *part2 = nullptr, *img_loss = nullptr;
   long long* trace = nullptr;      // development aid: per-CTA stage timestamps of the cluster kernel
+  unsigned int updates_launched = 0;   // update kernels launched on d_ctx == StepCtl::updates_done once they finish
   int debug_flags = 0;             // OR-ed into the update kernel's flags (bit 1: no early launch of the successor)
   int forced_cluster = 0;          // 0 = pick per batch size
   int max_clusters[9] = {};        // resident clusters of the fwd/bwd kernel per cluster size (index = CS)
@@ -211,23 +213,34 @@ static int cluster_size_for(const dnnb200_engine* e, int B) {
 }
 
 // the forward/backward half of a step; returns the number of conv1 partial rows it produced
-static int fwd_bwd_any(dnnb200_engine* e, const float* x, const long long* y, int B, cudaStream_t s, int* n_part1) {
+// chained: the previous operation this engine put on the stream is the update kernel of the previous step and
+// nothing else came between (inner iterations of the multi-step calls). Only then may the kernel wait on the
+// update counter instead of on the completion of the previous grid (fused_cluster.cu).
+static int fwd_bwd_any(dnnb200_engine* e, const float* x, const long long* y, int B, cudaStream_t s, int* n_part1,
+                       bool chained = false) {
   const int cs = cluster_size_for(e, B);
   *n_part1 = B;  // clusters reduce their conv1 partials to one row per image before they write them
   if (cs == 1)
     return launch_fwd_bwd(true, e->params, x, y, e->saved, e->part1, e->part2, e->img_loss, e->img_correct, nullptr,
                           B, e->num_sms, s);
   return launch_fwd_bwd_cluster(cs, e->params, x, y, e->saved, e->part1, e->part2, e->img_loss, e->img_correct, B,
-                                e->max_clusters[cs] > 0 ? e->max_clusters[cs] : 1, e->trace, s);
+                                e->max_clusters[cs] > 0 ? e->max_clusters[cs] : 1, e->trace,
+                                chained && !(e->debug_flags & 8) ? &e->ctl->updates_done : nullptr, e->updates_launched, s);
 }
 
-static int step_kernels(dnnb200_engine* e, const float* x, const long long* y, int B, int flags, cudaStream_t s) {
+static inline int peers_flag(const dnnb200_engine* e) {
+  return (e->h_ctx.world > 1 && !(e->debug_flags & 32)) ? (int)kUpdFlagPeers : 0;   // debug bit 32: A/B switch
+}
+
+static int step_kernels(dnnb200_engine* e, const float* x, const long long* y, int B, int flags, cudaStream_t s,
+                        bool chained = false) {
   int n_part1 = B;
-  int rc = fwd_bwd_any(e, x, y, B, s, &n_part1);
+  int rc = fwd_bwd_any(e, x, y, B, s, &n_part1, chained);
   if (rc) return rc;
   rc = launch_update(e->d_ctx, 1, B, n_part1, (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask),
-                     flags | e->debug_flags, nullptr, s);
+                     flags | e->debug_flags | peers_flag(e), nullptr, s);
   if (rc) return rc;
+  e->updates_launched += 1u;
   e->launches += 2;
   return kOk;
 }
@@ -571,7 +584,7 @@ int dnnb200_engine_train_device(dnnb200_engine* e, const float* x, const int64_t
   DNN_ARG_CHECK(B >= 1 && B <= e->max_batch, "engine_train_device: batch %d exceeds max_batch %d", B, e->max_batch);
   for (int t = 0; t < nsteps; ++t) {
     int rc = step_kernels(e, x + (size_t)t * B * kImgNumel, (const long long*)y + (size_t)t * B, B, 0,
-                          (cudaStream_t)stream);
+                          (cudaStream_t)stream, /*chained=*/t > 0);
     if (rc) return rc;
     e->steps_launched += 1;
   }
@@ -627,12 +640,13 @@ int dnnb200_engine_train_host(dnnb200_engine* e, const float* h_x, const int64_t
     for (int k = 0; k < n; ++k) {
       const int slot = gslot * G + k, t = t0 + k;
       int n_part1 = B;
-      rc = fwd_bwd_any(e, e->d_x[slot], e->d_y[slot], B, s, &n_part1);
+      rc = fwd_bwd_any(e, e->d_x[slot], e->d_y[slot], B, s, &n_part1, /*chained=*/k > 0);
       if (rc) return rc;
       // The step's mean loss is written by the update kernel itself into h_losses[t] (device->host, 4 bytes).
       const int lslot = (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask);
-      rc = launch_update(e->d_ctx, 1, B, n_part1, lslot, 0, d_losses ? d_losses + t : nullptr, s);
+      rc = launch_update(e->d_ctx, 1, B, n_part1, lslot, e->debug_flags | peers_flag(e), d_losses ? d_losses + t : nullptr, s);
       if (rc) return rc;
+      e->updates_launched += 1u;
       e->launches += 2;
       e->steps_launched += 1;
     }
@@ -739,7 +753,7 @@ int dnnb200_vr_step(dnnb200_engine** engines, int n, const float* const* xs, con
   cudaStreamSynchronize(s);
   cudaFree(d);
   if (rc) return rc;
-  for (auto* e : live) { e->launches += 1; e->steps_launched += 1; }
+  for (auto* e : live) { e->launches += 1; e->steps_launched += 1; e->updates_launched += 1u; }
   return kOk;
 }
 

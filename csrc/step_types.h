@@ -17,6 +17,15 @@ static_assert(kLeaveSlot < kFlagRow, "flag row too small");
 // {value, seq, value, seq} (exchange.cuh), i.e. 2*kFlatNumel floats per (parity, source).
 // Parity = seq & 1, so the pushes of step t+1 never land on data a slow reader still sums for step t.
 
+// flags argument of the update kernel (bits 0..2: kernel behaviour; bit 4: host-side kernel selection)
+enum UpdateFlags : int {
+  kUpdFlagGradOnly = 1,    // leave the local batch gradient in RankCtx::grads, touch nothing else (tests)
+  kUpdFlagNoTrigger = 2,   // do not let the successor start early
+  kUpdFlagTraceRing = 4,   // trace buffer keeps the last 1024 steps
+  kUpdFlagPeers = 16,      // this rank exchanges with real peers: use the instantiation that fits beside the
+                           // forward/backward kernel (see update_kernel)
+};
+
 enum StepStatus : unsigned int {
   kStatusOk = 0,
   kStatusTimeout = 1u,  // bit 0: some peer was waited for longer than timeout_ns
@@ -34,7 +43,8 @@ struct StepCtl {
   unsigned int status;      // StepStatus bits, sticky until the host clears them
   unsigned int active_mask; // ranks configured into the exchange (bit r = rank r)
   unsigned int two_shot;          // fused exchange variant: 0 one-shot (membership-safe), 1 two-shot (static membership)
-  unsigned int pad0_;
+  unsigned int updates_done;      // update kernels completed on this rank, ever (never reset): the next step's
+                                  // forward/backward kernel spins on it instead of waiting for grid completion
   unsigned int divisor_override;  // 0: divide by the ranks present; else by this (parent/children parity mode:
                                   // the non-training parent contributes zeros and the divisor is W-1)
 };

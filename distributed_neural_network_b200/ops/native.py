@@ -18,7 +18,8 @@ from typing import Optional, Sequence
 
 import torch
 
-_LIB_PATH = Path(__file__).resolve().parent.parent / "_native" / "libdnnb200.so"
+_LIB_PATH = Path(os.environ.get("DNNB200_LIB") or
+                 Path(__file__).resolve().parent.parent / "_native" / "libdnnb200.so")
 _lib: Optional[C.CDLL] = None
 _load_error: Optional[str] = None
 
@@ -41,7 +42,7 @@ class Ctl(C.Structure):
         ("status", C.c_uint),
         ("active_mask", C.c_uint),
         ("two_shot", C.c_uint),
-        ("pad0_", C.c_uint),
+        ("updates_done", C.c_uint),
         ("divisor_override", C.c_uint),
     ]
 
@@ -319,7 +320,7 @@ class Engine:
         _check(require().dnnb200_engine_set_debug_flags(self._h, flags))
 
     def set_update_trace(self, trace: Optional[torch.Tensor]) -> None:
-        """int64 CUDA tensor [122*4]: update-kernel timestamps per slice (development aid)."""
+        """int64 CUDA tensor [122*8] (or [1024*122*8] with debug flag 4): update-kernel timestamps per slice (development aid)."""
         self._utrace = trace
         _check(require().dnnb200_engine_set_update_trace(self._h, _p(trace)))
 

@@ -105,7 +105,7 @@ typedef struct dnnb200_ctl {
   unsigned int status;
   unsigned int active_mask;
   unsigned int two_shot;
-  unsigned int pad0_;
+  unsigned int updates_done;
   unsigned int divisor_override;
 } dnnb200_ctl;
 
