@@ -225,7 +225,7 @@ def run_ours(args) -> int:
                     "h2d_bytes_per_step": B * 3 * 32 * 32 * 4 + B * 8, "d2h_bytes_per_step": 4,
                     "ms_per_step": round(e2e_max * 1e3 / K, 6),
                     "how": "Engine.train_host: per step cudaMemcpyAsync of that step's images+labels from pinned host "
-                           "memory (16-slot device ring, copy stream), 2 kernels, and the update kernel stores the step's mean "
+                           "memory (32-slot device ring, copy stream), 2 kernels, and the update kernel stores the step's mean "
                            "loss into the caller's pinned host buffer (device->host over PCIe); wall clock with "
                            "synchronize on both sides, max over ranks",
                     "mean_loss_read_back": round(max(s["loss"] for s in stats), 4)},

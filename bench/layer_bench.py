@@ -9,6 +9,7 @@ import torch.nn.functional as F
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 from distributed_neural_network_b200 import Network  # noqa: E402
 from distributed_neural_network_b200.ops import flat as L  # noqa: E402
+from distributed_neural_network_b200.ops import functional as Fn  # noqa: E402
 from distributed_neural_network_b200.ops import native  # noqa: E402
 
 
@@ -47,6 +48,34 @@ def main():
             out[f"{name}_fwd_N{N}_tcgen05_tma_us"] = round(t_us(lambda: native.tc_linear_fwd(x, w, b, y, True)), 2)
             out[f"{name}_fwd_N{N}_ffma_us"] = round(t_us(lambda: native.linear_fwd(x, w, b, y, True)), 2)
             out[f"{name}_fwd_N{N}_torch_cublas_us"] = round(t_us(lambda: F.relu(F.linear(x, w, b))), 2)
+            dy = torch.randn(N, M, device="cuda")
+            dx, dw, db = torch.empty_like(x), torch.empty_like(w), torch.empty(M, device="cuda")
+            out[f"{name}_bwd_N{N}_tcgen05_tma_us"] = round(t_us(lambda: native.tc_linear_bwd(x, w, y, dy, dx, dw, db, True)), 2)
+            out[f"{name}_bwd_N{N}_ffma_us"] = round(t_us(lambda: native.linear_bwd(x, w, y, dy, dx, dw, db, True)), 2)
+
+            def torch_bwd():
+                d = dy * (y > 0)
+                return d @ w, d.t() @ x, d.sum(0)
+            out[f"{name}_bwd_N{N}_torch_cublas_us"] = round(t_us(torch_bwd), 2)
+    # one forward+backward of the whole model through autograd at large batches: our layer kernels vs PyTorch ops
+    for N in (1024, 8192):
+        m = Network().cuda()
+        x = torch.randn(N, 3, 32, 32, device="cuda")
+        y = torch.randint(0, 10, (N,), device="cuda")
+
+        def ours():
+            m.zero_grad()
+            Fn.cross_entropy(m(x), y).backward()
+
+        def eager():
+            m.zero_grad()
+            h = F.max_pool2d(F.relu(F.conv2d(x, m.conv1.weight, m.conv1.bias)), 2, 2)
+            h = F.max_pool2d(F.relu(F.conv2d(h, m.conv2.weight, m.conv2.bias)), 2, 2).flatten(1)
+            h = F.relu(F.linear(h, m.fc1.weight, m.fc1.bias))
+            h = F.relu(F.linear(h, m.fc2.weight, m.fc2.bias))
+            F.cross_entropy(F.linear(h, m.fc3.weight, m.fc3.bias), y).backward()
+        out[f"autograd_fwd_bwd_N{N}_layer_kernels_us"] = round(t_us(ours, 20, 3), 1)
+        out[f"autograd_fwd_bwd_N{N}_torch_eager_us"] = round(t_us(eager, 20, 3), 1)
     # eval of 10 000 test images (reference eval loop semantics), batch 16
     m = Network().cuda()
     eng = native.Engine(m.flat_params, torch.zeros(L.FLAT_NUMEL, device="cuda"), None, 16, 0.001, 0.9)

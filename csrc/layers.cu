@@ -66,21 +66,24 @@ conv_relu_pool_fwd_kernel(const float* __restrict__ x, const float* __restrict__
 }
 
 // wgrad + bgrad over the pooled grid (K16/K17 wgrad with K14/K15 folded in).
-// One CTA per (o, c); each thread keeps the 25 taps and walks a strided subset of (n, pooled pixel).
+// One CTA per (o, c) and batch chunk (blockIdx.y); each thread keeps the 25 taps and walks a strided subset of
+// (n, pooled pixel) of its chunk. With one chunk the sums are stored (fixed order); with several they are added
+// to a zeroed dw/db with fp32 atomics -- large batches would otherwise run on Co*Ci (18 for conv1) CTAs only.
 __global__ void __launch_bounds__(256)
 conv_relu_pool_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ y,
                             const unsigned char* __restrict__ idx, const float* __restrict__ dy,
                             float* __restrict__ dw, float* __restrict__ db, int N, int Ci, int H, int W,
-                            int Co) {
+                            int Co, int imgs_per_chunk) {
   const int o = blockIdx.x / Ci, c = blockIdx.x - o * Ci;
   const int Hp = (H - 4) / 2, Wp = (W - 4) / 2, per_img = Hp * Wp;
   float acc[25];
 #pragma unroll
   for (int t = 0; t < 25; ++t) acc[t] = 0.f;
   float bsum = 0.f;
-  const long long total = (long long)N * per_img;
+  const int n_lo = blockIdx.y * imgs_per_chunk, n_hi = min(N, n_lo + imgs_per_chunk);
+  const long long total = (long long)(n_hi - n_lo) * per_img;
   for (long long t = threadIdx.x; t < total; t += blockDim.x) {
-    const int n = (int)(t / per_img), pp = (int)(t - (long long)n * per_img);
+    const int n = n_lo + (int)(t / per_img), pp = (int)(t % per_img);
     const size_t oi = ((size_t)(n * Co + o)) * per_img + pp;
     const float g = y[oi] > 0.f ? dy[oi] : 0.f;
     if (g == 0.f) continue;
@@ -108,8 +111,13 @@ conv_relu_pool_wgrad_kernel(const float* __restrict__ x, const float* __restrict
   if (threadIdx.x < 26) {
     float s = 0.f;
     for (int wv = 0; wv < (int)(blockDim.x >> 5); ++wv) s += red[wv][threadIdx.x];
-    if (threadIdx.x < 25) dw[(o * Ci + c) * 25 + threadIdx.x] = s;
-    else if (c == 0) db[o] = s;
+    if (gridDim.y == 1) {
+      if (threadIdx.x < 25) dw[(o * Ci + c) * 25 + threadIdx.x] = s;
+      else if (c == 0) db[o] = s;
+    } else {
+      if (threadIdx.x < 25) atomicAdd(dw + (o * Ci + c) * 25 + threadIdx.x, s);
+      else if (c == 0) atomicAdd(db + o, s);
+    }
   }
 }
 
@@ -190,33 +198,40 @@ linear_dx_kernel(const float* __restrict__ w, const float* __restrict__ y, const
 }
 
 // dw[m,k] = sum_n dy'[n,m] x[n,k];  db[m] = sum_n dy'[n,m]
+// blockIdx.y = batch chunk: one chunk stores (fixed order), several add to a zeroed dw/db with fp32 atomics
 __global__ void __launch_bounds__(256)
 linear_dw_kernel(const float* __restrict__ x, const float* __restrict__ y, const float* __restrict__ dy,
-                 float* __restrict__ dw, float* __restrict__ db, int N, int M, int K, int relu) {
+                 float* __restrict__ dw, float* __restrict__ db, int N, int M, int K, int relu, int rows_per_chunk) {
   const long long total = (long long)M * K;
+  const int n_lo = blockIdx.y * rows_per_chunk, n_hi = min(N, n_lo + rows_per_chunk);
   for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total;
        t += (long long)gridDim.x * blockDim.x) {
     const int m = (int)(t / K), k = (int)(t - (long long)m * K);
     float acc = 0.f, bacc = 0.f;
-    for (int n = 0; n < N; ++n) {
+    for (int n = n_lo; n < n_hi; ++n) {
       float d = dy[(size_t)n * M + m];
       if (relu && !(y[(size_t)n * M + m] > 0.f)) d = 0.f;
       acc += d * __ldg(x + (size_t)n * K + k);
       bacc += d;
     }
-    dw[t] = acc;
-    if (k == 0) db[m] = bacc;
+    if (gridDim.y == 1) {
+      dw[t] = acc;
+      if (k == 0) db[m] = bacc;
+    } else {
+      atomicAdd(dw + t, acc);
+      if (k == 0) atomicAdd(db + m, bacc);
+    }
   }
 }
 
 // ---------------------------------------------------------------------------
 // softmax cross-entropy (mean) forward + backward in one pass (K11, K12)
-// single CTA, one warp per row, fixed summation order => deterministic loss
+// single CTA (32 warps), one warp per row, fixed summation order => deterministic loss
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 softmax_xent_kernel(const float* __restrict__ logits, const long long* __restrict__ target,
                     float* __restrict__ loss, float* __restrict__ dlogits, int N, int C) {
-  __shared__ float s_part[8];
+  __shared__ float s_part[32];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
   const float invN = 1.f / (float)N;
   float part = 0.f;
@@ -283,8 +298,19 @@ int launch_tc_conv2_dgrad(const float* w, const float* y, const unsigned char* i
 int launch_conv_relu_pool_bwd(const float* x, const float* w, const float* y, const unsigned char* idx,
                               const float* dy, float* dx, float* dw, float* db, int N, int Ci, int H, int W,
                               int Co, int tensor_core_dgrad, cudaStream_t s) {
-  conv_relu_pool_wgrad_kernel<<<Co * Ci, 256, 0, s>>>(x, y, idx, dy, dw, db, N, Ci, H, W, Co);
-  DNN_CUDA_CHECK(cudaGetLastError());
+  {
+    // enough (o, c, batch chunk) CTAs for two waves; small batches keep one chunk and the fixed summation order
+    int chunks = N >= 64 ? (2 * 148 + Co * Ci - 1) / (Co * Ci) : 1;
+    if (chunks > N / 8) chunks = N / 8 > 0 ? N / 8 : 1;
+    const int per = (N + chunks - 1) / chunks;
+    chunks = (N + per - 1) / per;
+    if (chunks > 1) {
+      DNN_CUDA_CHECK(cudaMemsetAsync(dw, 0, (size_t)Co * Ci * 25 * sizeof(float), s));
+      DNN_CUDA_CHECK(cudaMemsetAsync(db, 0, (size_t)Co * sizeof(float), s));
+    }
+    conv_relu_pool_wgrad_kernel<<<dim3(Co * Ci, chunks), 256, 0, s>>>(x, y, idx, dy, dw, db, N, Ci, H, W, Co, per);
+    DNN_CUDA_CHECK(cudaGetLastError());
+  }
   if (dx && tensor_core_dgrad && Ci == 6 && H == 14 && W == 14 && Co == 16)
     return launch_tc_conv2_dgrad(w, y, idx, dy, dx, N, s);   // tcgen05 implicit GEMM (TF32)
   if (dx) {
@@ -308,14 +334,25 @@ int launch_linear_bwd(const float* x, const float* w, const float* y, const floa
     linear_dx_kernel<<<grid_for((long long)N * K, 256), 256, 0, s>>>(w, y, dy, dx, N, M, K, relu);
     DNN_CUDA_CHECK(cudaGetLastError());
   }
-  linear_dw_kernel<<<grid_for((long long)M * K, 256), 256, 0, s>>>(x, y, dy, dw, db, N, M, K, relu);
-  DNN_CUDA_CHECK(cudaGetLastError());
+  {
+    const int gx = grid_for((long long)M * K, 256);
+    int chunks = N >= 256 ? (2 * 148 + gx - 1) / gx : 1;
+    if (chunks > N / 32) chunks = N / 32 > 0 ? N / 32 : 1;
+    const int per = (N + chunks - 1) / chunks;
+    chunks = (N + per - 1) / per;
+    if (chunks > 1) {
+      DNN_CUDA_CHECK(cudaMemsetAsync(dw, 0, (size_t)M * K * sizeof(float), s));
+      DNN_CUDA_CHECK(cudaMemsetAsync(db, 0, (size_t)M * sizeof(float), s));
+    }
+    linear_dw_kernel<<<dim3(gx, chunks), 256, 0, s>>>(x, y, dy, dw, db, N, M, K, relu, per);
+    DNN_CUDA_CHECK(cudaGetLastError());
+  }
   return kOk;
 }
 
 int launch_softmax_xent(const float* logits, const long long* target, float* loss, float* dlogits, int N, int C,
                         cudaStream_t s) {
-  softmax_xent_kernel<<<1, 256, 0, s>>>(logits, target, loss, dlogits, N, C);
+  softmax_xent_kernel<<<1, N >= 256 ? 1024 : 256, 0, s>>>(logits, target, loss, dlogits, N, C);
   DNN_CUDA_CHECK(cudaGetLastError());
   return kOk;
 }

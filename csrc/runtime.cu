@@ -126,8 +126,8 @@ struct dnnb200_engine {
   unsigned long long steps_launched = 0;  // host mirror: update launches (loss ring slot)
   int num_sms = 148;
   // host-fed ring
-  static constexpr int kRing = 16;   // device input slots
-  static constexpr int kGroup = 4;   // steps per event group (stream events break the kernels' programmatic overlap)
+  static constexpr int kRing = 32;   // device input slots
+  static constexpr int kGroup = 8;   // steps per event group (stream events break the kernels' programmatic overlap)
   cudaStream_t copy_stream = nullptr, d2h_stream = nullptr;
   cudaEvent_t slot_ready[kRing] = {}, slot_free[kRing] = {}, step_done[kRing] = {};
   float* d_x[kRing] = {};

@@ -100,6 +100,33 @@ def test_train_host_pipeline_equals_step_loop():
     ea.close(); eb.close()
 
 
+def test_chained_steps_equal_single_steps_and_respect_foreign_writes():
+    """Inside one train_device call the forward/backward kernel of step t+1 waits on the update counter instead
+    of on the completion of step t's update grid; the first step of every call must still honour whatever the
+    stream did in between (here: a PyTorch kernel that rescales the parameters)."""
+    torch.manual_seed(11)
+    base = Network()
+    a, b = copy.deepcopy(base).cuda(), copy.deepcopy(base).cuda()
+    steps, B = 40, 16
+    x = torch.randn(steps, B, 3, 32, 32, device="cuda")
+    y = torch.randint(0, 10, (steps, B), device="cuda")
+    ea = native.Engine(a.flat_params, torch.zeros(L.FLAT_NUMEL, device="cuda"), None, 16, 0.01, 0.9)
+    eb = native.Engine(b.flat_params, torch.zeros(L.FLAT_NUMEL, device="cuda"), None, 16, 0.01, 0.9)
+    for rnd in range(3):
+        ea.train_device(x, y)                       # 40 chained steps
+        a.flat_params.mul_(0.97)                    # foreign kernel on the same stream, no synchronisation
+        for t in range(steps):
+            eb.step(x[t], y[t])                     # 40 stand-alone steps (grid-completion dependency)
+        b.flat_params.mul_(0.97)
+    torch.cuda.synchronize()
+    assert torch.equal(a.flat_params, b.flat_params)
+    ca, cb = ea.read_ctl(), eb.read_ctl()
+    assert ca.step == cb.step == 3 * steps
+    assert ca.updates_done == cb.updates_done == 3 * steps
+    assert ca.loss_sum == cb.loss_sum
+    ea.close(); eb.close()
+
+
 @pytest.mark.parametrize("N,bs", [(16, 16), (1000, 16), (37, 8)])
 def test_eval_matches_reference_semantics(N, bs):
     torch.manual_seed(N)
