@@ -302,7 +302,9 @@ int launch_tc_linear_bwd(const float* x, const float* w, const float* y, const f
     if (rc) return rc;
     const int ktiles = (K + 127) / 128;
     const int blocks = (N + 31) / 32;
-    int splits = blocks / 8;                               // at least 8 reduction blocks (256 rows) per CTA
+    // at least 8 reduction blocks (256 rows) per CTA; swept 4..64 (bench/sweep_dw.sh): 4-16 are within 3 % of each
+    // other, beyond that the streaming phase loses its parallelism
+    int splits = blocks / 8;
     if (splits > 148 / ktiles) splits = 148 / ktiles;
     if (splits < 1) splits = 1;
     const int rows_per_split = ((blocks + splits - 1) / splits) * 32;
