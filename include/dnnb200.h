@@ -139,10 +139,14 @@ int dnnb200_engine_cluster_info(const dnnb200_engine* e, int B, int* chosen, int
 /* development aid: d_trace[cta*16 + k] receives the SM clock at stage boundary k of the clustered
  * forward/backward kernel (NULL switches it off) */
 int dnnb200_engine_set_trace(dnnb200_engine* e, long long* d_trace);
-/* same for the update kernel: d_trace[slice*4 + {0,1,2,3}] = globaltimer (ns) at entry, after the dependency
- * wait, after the local gradient, after the exchange */
+/* same for the update kernel: d_trace[slice*8 + k] = globaltimer (ns) at k = 0 entry, 1 after the dependency wait,
+ * 2 after the local gradient, 3 after the exchange, 4 after the SGD stores, 5 after the fence, 6 after the
+ * last-CTA counter; [122*8] words, or [1024*122*8] with debug flag 4 (ring over the last 1024 steps) */
 int dnnb200_engine_set_update_trace(dnnb200_engine* e, long long* d_trace);
-/* development aid: bit 1 = the update kernel does not trigger the early launch of the next kernel */
+/* development aid / A-B switches, OR-ed: 2 = the update kernel does not trigger the early launch of the next
+ * kernel; 4 = the update trace is a ring over the last 1024 steps; 8 = chained steps wait for the completion of
+ * the previous update GRID instead of its update counter; 32 = with peers, use the unconstrained update kernel
+ * instead of the one that fits three CTAs per SM */
 int dnnb200_engine_set_debug_flags(dnnb200_engine* e, int flags);
 
 /* one optimizer step on a device-resident batch: fwd/bwd kernel + update kernel
