@@ -511,13 +511,18 @@ constexpr int kUVec = DNN_U_VEC;              // consecutive floats per thread (
 constexpr int kUpdThreads = kSlice / kUVec;   // 256 or 128 threads per 512-float slice
 static_assert(kUVec == 2 || kUVec == 4, "update kernel vector width");
 
+#ifndef DNN_GRAD_UNROLL
+#define DNN_GRAD_UNROLL 16
+#endif
+constexpr int kGradUnroll = DNN_GRAD_UNROLL;   // batch loop: a whole batch of 16 has all its loads in flight at once
+
 // d(loss)/d(param[i]) and param[i+1] summed over the local batch. i is even and both
 // elements lie in the same tensor row (all row lengths are even).
 __device__ __forceinline__ float2 local_grad2(const RankCtx& cx, int i, int B, int n_part1) {
   float2 g = make_float2(0.f, 0.f);
   if (i < kOffW2) {
     const float* p = cx.part1 + i;
-#pragma unroll 8
+#pragma unroll kGradUnroll
     for (int b = 0; b < n_part1; ++b) {
       const float2 t = __ldg(reinterpret_cast<const float2*>(p + (size_t)b * kOffW2));
       g.x += t.x; g.y += t.y;
@@ -526,7 +531,7 @@ __device__ __forceinline__ float2 local_grad2(const RankCtx& cx, int i, int B, i
   }
   if (i < kConvPrefix) {
     const float* p = cx.part2 + (i - kOffW2);
-#pragma unroll 8
+#pragma unroll kGradUnroll
     for (int b = 0; b < B; ++b) {
       const float2 t = __ldg(reinterpret_cast<const float2*>(p + (size_t)b * (kConvPrefix - kOffW2)));
       g.x += t.x; g.y += t.y;
@@ -555,13 +560,13 @@ __device__ __forceinline__ float2 local_grad2(const RankCtx& cx, int i, int B, i
   const float* sv = cx.saved;
   if (is_bias) {
     // j even, j+1 in range for all three biases (120, 84, 10 are even)
-#pragma unroll 8
+#pragma unroll kGradUnroll
     for (int b = 0; b < B; ++b) {
       const float2 d = __ldg(reinterpret_cast<const float2*>(sv + (size_t)b * kSavStride + off_d + j));
       g.x += d.x; g.y += d.y;
     }
   } else {
-#pragma unroll 8
+#pragma unroll kGradUnroll
     for (int b = 0; b < B; ++b) {
       const float d = __ldg(sv + (size_t)b * kSavStride + off_d + j);
       const float2 a = __ldg(reinterpret_cast<const float2*>(sv + (size_t)b * kSavStride + off_a + k));
@@ -627,12 +632,38 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
   pdl_wait();
   long long* tr = cx.trace;
   if (tr && tid == 0) t_dep = (long long)globaltimer_ns();
-  const unsigned long long step = *reinterpret_cast<volatile unsigned long long*>(&ctl->step);
+  // the previous update kernel stored `step` before it released the counter our predecessor waited on, and the
+  // host only changes it with stream-ordered kernels before that predecessor: the staged copy is current
+  const unsigned long long step = ctl_snap.step;
   const unsigned int seq = (unsigned int)(step + 1ull);
   if (tr) {
     // flags bit 2 (value 4): keep the stamps of the last 1024 steps ([step % 1024][slice][8]) instead of one step
     if (flags & 4) tr += (size_t)(step & 1023ull) * gridDim.x * 8;
     if (tid == 0) { tr[slice * 8 + 0] = t_enter; tr[slice * 8 + 1] = t_dep; }
+  }
+
+  // Per-step mean loss (fixed summation order), by the last warp of the last slice: its elements lie beyond the
+  // end of the parameter vector, so it has nothing else to do, and the bookkeeping (a read-modify-write of the
+  // control block, a 4-byte store to the caller's pinned host buffer) runs beside the gradient reduction instead
+  // of behind it. (It used to sit on thread 0 of slice 0, 0.8 us on the step's critical path.)
+  static_assert(kFlatNumel - (kNumSlices - 1) * kSlice <= (kUpdThreads - 32) * kUVec, "last warp of last slice idle");
+  if (slice == (int)gridDim.x - 1 && tid >= kUpdThreads - 32) {
+    const int lane = tid & 31;
+    float a = 0.f;
+    for (int b = lane; b < B; b += 32) a += cx.img_loss[b];
+    a = warp_sum(a);
+    if (lane == 0) {
+      const float mean = a / (float)B;
+      cx.loss_ring[loss_slot & cx.loss_ring_mask] = mean;
+      // the step's result goes straight to the caller's pinned host buffer: a 4-byte store over PCIe, no
+      // copy-engine operation and no extra stream dependency on the step path (visible to the host once the
+      // stream has been synchronised)
+      if (host_loss != nullptr) *reinterpret_cast<volatile float*>(host_loss) = mean;
+      if (!grad_only) {
+        ctl->loss_sum += mean;
+        ctl->loss_steps += 1u;
+      }
+    }
   }
 
   float v[kUVec];
@@ -681,25 +712,6 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
     }
   }
 
-  if (slice == 0 && tid < 32) {  // per-step mean loss, fixed summation order
-    float a = 0.f;
-    for (int b = tid; b < B; b += 32) a += cx.img_loss[b];
-    a = warp_sum(a);
-    if (tid == 0) {
-      const float mean = a / (float)B;
-      cx.loss_ring[loss_slot & cx.loss_ring_mask] = mean;
-      if (host_loss != nullptr) {
-        // the step's result goes straight to the caller's pinned host buffer: a 4-byte store over PCIe,
-        // no copy-engine operation and no extra stream dependency on the step path
-        *reinterpret_cast<volatile float*>(host_loss) = mean;
-        __threadfence_system();
-      }
-      if (!grad_only) {
-        ctl->loss_sum += mean;
-        ctl->loss_steps += 1u;
-      }
-    }
-  }
   if (tr && tid == 0) tr[slice * 8 + 4] = (long long)globaltimer_ns();
   __syncthreads();
   if (tid == 0) {
@@ -709,11 +721,11 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
     if (tr) tr[slice * 8 + 6] = (long long)globaltimer_ns();
     if (done == gridDim.x - 1) {  // last CTA of this rank: everyone has read `step`
       ctl->ctas_done = 0u;
-      __threadfence();
       if (!grad_only) *reinterpret_cast<volatile unsigned long long*>(&ctl->step) = step + 1ull;
       // "parameters of this step are in place": what the next forward/backward kernel spins on (fused_cluster.cu).
-      // Every CTA fenced its stores before it bumped ctas_done, and this CTA has observed all the bumps.
-      st_release_gpu(&ctl->updates_done, ctl->updates_done + 1u);
+      // Every CTA fenced its stores before it bumped ctas_done, and this CTA has observed all the bumps; the
+      // release also orders the two stores above (one fence on this path, not three).
+      st_release_gpu(&ctl->updates_done, ctl_snap.updates_done + 1u);
     }
   }
 }
