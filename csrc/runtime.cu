@@ -228,6 +228,13 @@ static int fwd_bwd_any(dnnb200_engine* e, const float* x, const long long* y, in
                                 chained && !(e->debug_flags & 8) ? &e->ctl->updates_done : nullptr, e->updates_launched, s);
 }
 
+// The counter value a chained step waits for is a kernel ARGUMENT: baked into a CUDA graph it would be stale on
+// every replay, so steps recorded by a stream capture keep the grid-completion dependency.
+static inline bool stream_capturing(cudaStream_t s) {
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  return cudaStreamIsCapturing(s, &st) == cudaSuccess && st != cudaStreamCaptureStatusNone;
+}
+
 static inline int peers_flag(const dnnb200_engine* e) {
   return (e->h_ctx.world > 1 && !(e->debug_flags & 32)) ? (int)kUpdFlagPeers : 0;   // debug bit 32: A/B switch
 }
@@ -582,9 +589,10 @@ int dnnb200_engine_step(dnnb200_engine* e, const float* x, const int64_t* y, int
 int dnnb200_engine_train_device(dnnb200_engine* e, const float* x, const int64_t* y, int B, int nsteps, void* stream) {
   DNN_ARG_CHECK(e && x && y, "engine_train_device: null argument");
   DNN_ARG_CHECK(B >= 1 && B <= e->max_batch, "engine_train_device: batch %d exceeds max_batch %d", B, e->max_batch);
+  const bool may_chain = !stream_capturing((cudaStream_t)stream);
   for (int t = 0; t < nsteps; ++t) {
     int rc = step_kernels(e, x + (size_t)t * B * kImgNumel, (const long long*)y + (size_t)t * B, B, 0,
-                          (cudaStream_t)stream, /*chained=*/t > 0);
+                          (cudaStream_t)stream, /*chained=*/may_chain && t > 0);
     if (rc) return rc;
     e->steps_launched += 1;
   }
