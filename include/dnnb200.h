@@ -156,7 +156,7 @@ int dnnb200_engine_step(dnnb200_engine* e, const float* x, const int64_t* y, int
  * no per-step Python (the whole dataset fits in HBM many times over) */
 int dnnb200_engine_train_device(dnnb200_engine* e, const float* x, const int64_t* y, int B, int nsteps, void* stream);
 /* nsteps steps fed from PINNED host memory: per step an async H2D copy of that step's
- * inputs (16-slot device ring on a copy stream, events every 4 steps) and the two kernels; the update kernel writes
+ * inputs (32-slot device ring on a copy stream, events every 8 steps) and the two kernels; the update kernel writes
  * the step's mean loss straight into h_losses[t] (pinned host memory, 4 bytes device->host per
  * step). Returns after everything is enqueued; the caller synchronises `stream` before reading
  * h_losses. */
