@@ -172,3 +172,34 @@ def test_mpiexec_front_end_runs_the_documented_command_line(tmp_path):
     assert (tmp_path / "log" / "bs8_log_epochs1_proc2_parent.txt").exists()
     sd = torch.load(tmp_path / "model.pt", weights_only=True)
     assert len(sd) == 10
+
+
+def test_single_proc_and_model_replication_entry_points(tmp_path):
+    """The other two reference command lines (single_proc_train.py:16-107, model_replication_train.py:153-160)."""
+    common = ["--synthetic", "--train-size", "64", "--test-size", "16", "--device", "cpu", "--epochs", "1"]
+    out = subprocess.run([sys.executable, str(ROOT / "single_proc_train.py"), "--batch-size", "4", *common,
+                          "--jsonl", str(tmp_path / "single.jsonl")], capture_output=True, text=True, cwd=ROOT,
+                         timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    rec = json.loads((tmp_path / "single.jsonl").read_text().splitlines()[-1])
+    assert rec["epoch"] == 0 and rec["train_loss"] > 0 and 0.0 <= rec["val_acc"] <= 100.0
+    out = subprocess.run([str(ROOT / "bin" / "mpiexec"), "-n", "3", sys.executable,
+                          str(ROOT / "model_replication_train.py"), "--batch-size", "8", *common],
+                         capture_output=True, text=True, cwd=ROOT, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert "Validation loss of updated master model" in out.stdout
+
+
+def test_run_training_sh_issues_the_reference_sweep(tmp_path):
+    """run_training.sh:1-4 -- batch sizes 1..64 at 4 processes (and, new, 8) -- checked with a recording mpiexec."""
+    fake = tmp_path / "mpiexec"
+    fake.write_text("#!/bin/sh\nprintf '%%s\\n' \"$*\" >> \"%s\"\n" % (tmp_path / "calls.txt"))
+    fake.chmod(0o755)
+    env = dict(os.environ, PATH=f"{tmp_path}:{os.environ['PATH']}")
+    out = subprocess.run(["sh", str(ROOT / "run_training.sh"), "--synthetic"], capture_output=True, text=True, cwd=ROOT,
+                         env=env, timeout=60)
+    assert out.returncode == 0, out.stderr
+    calls = (tmp_path / "calls.txt").read_text().splitlines()
+    want = [f"-n {n} python data_parallelism_train.py --nb-proc {n} --batch-size {bs} --synthetic"
+            for n in (4, 8) for bs in (1, 2, 4, 8, 16, 32, 64)]
+    assert calls == want
