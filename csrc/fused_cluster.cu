@@ -411,7 +411,19 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       cl_bulk_g2s(s.xd, x + (size_t)im * kImgNumel, kImgNumel * 4, &s.mbar);
     }
   };
+  // dense CHW image -> padded rows (36 floats, 16-byte aligned) for the conv1 patch loads
+  auto relayout_image = [&]() {
+    for (int i = tid; i < kImgNumel / 4; i += kCLThreads) {
+      const float4 v = reinterpret_cast<const float4*>(s.xd)[i];
+      const int e = i * 4, c = e >> 10, h = (e >> 5) & 31, w = e & 31;
+      *reinterpret_cast<float4*>(s.x + c * kXCh + h * kXRow + w) = v;
+    }
+  };
   load_image(img);   // the input batch does not depend on the previous kernel of the stream,
+  if (img < B) {     // ... so the first image is landed AND re-laid out before the dependency is even looked at
+    cl_mbar_wait(&s.mbar, phase);
+    relayout_image();
+  }
   // but the weights do: they are written by the previous step's update kernel. Two ways to wait for it:
   //  * griddepcontrol.wait -- until that GRID has completed and flushed. With peers, its completion includes the
   //    acknowledgement of its NVLink stores: measured 3.3 us after its last instruction on the rank that pushed last.
@@ -475,13 +487,11 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       cl_mbar_expect_tx(&s.sbar[kBarG2], (kPre ? CS : 1) * kFlat * 4);
       if (r == 0) cl_mbar_expect_tx(&s.sbar[kBarW1], CS * kW1Row * 4);
     }
-    cl_mbar_wait(&s.mbar, phase);  // image landed
-    cl_mbar_wait(&s.cbar, 0);      // conv weights landed (first image; complete ever after)
-    for (int i = tid; i < kImgNumel / 4; i += kCLThreads) {  // dense -> padded rows (36 floats, 16-byte aligned)
-      const float4 v = reinterpret_cast<const float4*>(s.xd)[i];
-      const int e = i * 4, c = e >> 10, h = (e >> 5) & 31, w = e & 31;
-      *reinterpret_cast<float4*>(s.x + c * kXCh + h * kXRow + w) = v;
+    if (!first_img) {
+      cl_mbar_wait(&s.mbar, phase);  // image landed
+      relayout_image();
     }
+    cl_mbar_wait(&s.cbar, 0);      // conv weights landed (first image; complete ever after)
     __syncthreads();
     CL_TRACE(2);
 
