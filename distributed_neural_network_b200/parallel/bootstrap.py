@@ -16,7 +16,6 @@ from __future__ import annotations
 
 import datetime
 import os
-import pickle
 from typing import Any, List, Optional, Tuple
 
 _RANK_VARS = ("RANK", "OMPI_COMM_WORLD_RANK", "PMI_RANK", "PMIX_RANK", "SLURM_PROCID")
