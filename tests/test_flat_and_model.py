@@ -92,3 +92,26 @@ def test_top_level_import_path():
     sys.path.insert(0, str(ROOT))
     mod = importlib.import_module("models.model")
     assert mod.Network is Network
+
+
+def test_header_and_library_export_the_same_c_abi():
+    """include/dnnb200.h is the contract: every function it declares is exported by the built library, and the
+    library exports no dnnb200_* symbol the header does not declare."""
+    import re
+    import subprocess
+    from pathlib import Path
+
+    from distributed_neural_network_b200.ops import native
+
+    root = Path(__file__).resolve().parent.parent
+    lib_path = native.lib_path()
+    if not Path(lib_path).exists():
+        pytest.skip("native library not built")
+    header = (root / "include" / "dnnb200.h").read_text()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    declared = set(re.findall(r"\b(dnnb200_[a-z0-9_]+)\s*\(", header))
+    out = subprocess.run(["nm", "-D", "--defined-only", str(lib_path)], capture_output=True, text=True, check=True).stdout
+    exported = {ln.split()[-1] for ln in out.splitlines() if ln.split() and ln.split()[-1].startswith("dnnb200_")}
+    assert declared, "no declarations parsed from the header"
+    assert declared - exported == set(), f"declared but not exported: {sorted(declared - exported)}"
+    assert exported - declared == set(), f"exported but not declared: {sorted(exported - declared)}"
