@@ -115,3 +115,26 @@ def test_header_and_library_export_the_same_c_abi():
     assert declared, "no declarations parsed from the header"
     assert declared - exported == set(), f"declared but not exported: {sorted(declared - exported)}"
     assert exported - declared == set(), f"exported but not declared: {sorted(exported - declared)}"
+
+
+def test_python_mirror_of_the_control_block_matches_the_header():
+    import ctypes
+    import re
+    from pathlib import Path
+
+    from distributed_neural_network_b200.ops import native
+
+    header = (Path(__file__).resolve().parent.parent / "include" / "dnnb200.h").read_text()
+    body = re.search(r"typedef struct dnnb200_ctl \{(.*?)\} dnnb200_ctl;", header, flags=re.S).group(1)
+    ctype = {"unsigned long long": ctypes.c_ulonglong, "float": ctypes.c_float, "unsigned int": ctypes.c_uint}
+    want = []
+    for decl in body.split(";"):
+        decl = decl.strip()
+        if not decl:
+            continue
+        m = re.match(r"(unsigned long long|unsigned int|float)\s+(.*)", decl)
+        assert m, decl
+        for name in m.group(2).split(","):
+            want.append((name.strip(), ctype[m.group(1)]))
+    assert [(n, t) for n, t in native.Ctl._fields_] == want
+    assert ctypes.sizeof(native.Ctl) == 56
