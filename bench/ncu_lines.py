@@ -35,7 +35,7 @@ def main():
     tot_s = sum(x[0] for x in lines) or 1
     tot_i = sum(x[1] for x in lines) or 1
     print(f"total samples {tot_s}, total warp-instructions {tot_i}")
-    for s, i, f, ln, src, st, bank in sorted(lines, reverse=True)[:top]:
+    for s, i, f, ln, src, st, bank in sorted(lines, key=lambda x: (x[0], x[1]), reverse=True)[:top]:
         tops = ",".join(f"{k}:{v}" for k, v in sorted(st.items(), key=lambda kv: -kv[1])[:3])
         print(f"{100*s/tot_s:5.1f}% smp {100*i/tot_i:5.1f}% ins  {f}:{ln:>4}  bankx={bank:>6} [{tops}]  {src}")
 
