@@ -478,6 +478,8 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
   CL_TRACE(1);
 
   for (; img < B; img += n_clusters) {
+    // the label is only needed by the softmax, six stages from here: fetch it now, off that stage's critical path
+    const int label = (int)__ldg(labels + img);
     if (tid == 0) {  // arm this image's all-gathers: bytes each one will deliver into THIS CTA
       cl_mbar_expect_tx(&s.sbar[kBarP1], 1176 * 8);
       cl_mbar_expect_tx(&s.sbar[kBarP2], 400 * 8);
@@ -643,7 +645,6 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     }
     __syncthreads();
     if (warp == 0) {
-      const int label = (int)__ldg(labels + img);
       const float z = lane < 10 ? s.logits[lane] : -INFINITY;
       const float m = warp_max(z);
       const float e = lane < 10 ? __expf(z - m) : 0.f;
@@ -817,21 +818,24 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
         }
         float* dst = sred + pg * 450 + o * 75 + c * 25 + kh * 5;
         dst[0] = a0; dst[1] = a1; dst[2] = a2; dst[3] = a3; dst[4] = a4;
-      } else if (warp == 15) {
-        for (int o = 0; o < 6; ++o) {   // bias partial straight to CTA 0
-          float a = 0.f;
-          for (int q = q0 + lane; q < q1; q += 32) a += s.g1[o * 196 + q];
-          a = warp_sum(a);
-          if (lane == 0)
-            cl_st_async(R.base[0] + kRxW1 + 4u * (uint32_t)(r * kW1Row + 450 + o), __float_as_uint(a),
-                        R.base[0] + CL_BAR(kBarW1));
-        }
+      } else if (warp == 15 && lane < 30) {
+        // bias partial: (channel, pixel group of 5) per lane, same two-step shape as the weights. (Six warp-wide
+        // reductions one after the other in this warp used to be what the barrier below waited for.)
+        const int o = lane / 5, pg = lane - o * 5;
+        float a = 0.f;
+        for (int q = q0 + pg; q < q1; q += 5) a += s.g1[o * 196 + q];
+        sred[5 * 450 + pg * 6 + o] = a;
       }
       __syncthreads();
-      if (tid < 450) {
+      if (tid < kW1Row) {   // 450 weight taps + 6 biases: add the five pixel groups, send the partial to CTA 0
         float a = 0.f;
+        if (tid < 450) {
 #pragma unroll
-        for (int pg = 0; pg < 5; ++pg) a += sred[pg * 450 + tid];
+          for (int pg = 0; pg < 5; ++pg) a += sred[pg * 450 + tid];
+        } else {
+#pragma unroll
+          for (int pg = 0; pg < 5; ++pg) a += sred[5 * 450 + pg * 6 + (tid - 450)];
+        }
         cl_st_async(R.base[0] + kRxW1 + 4u * (uint32_t)(r * kW1Row + tid), __float_as_uint(a),
                     R.base[0] + CL_BAR(kBarW1));
       }
