@@ -176,7 +176,8 @@ def test_mpiexec_front_end_runs_the_documented_command_line(tmp_path):
 
 def test_single_proc_and_model_replication_entry_points(tmp_path):
     """The other two reference command lines (single_proc_train.py:16-107, model_replication_train.py:153-160)."""
-    common = ["--synthetic", "--train-size", "64", "--test-size", "16", "--device", "cpu", "--epochs", "1"]
+    common = ["--synthetic", "--train-size", "64", "--test-size", "16", "--device", "cpu", "--epochs", "1",
+              "--log-dir", str(tmp_path / "log")]
     out = subprocess.run([sys.executable, str(ROOT / "single_proc_train.py"), "--batch-size", "4", *common,
                           "--jsonl", str(tmp_path / "single.jsonl")], capture_output=True, text=True, cwd=ROOT,
                          timeout=300)
