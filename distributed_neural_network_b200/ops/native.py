@@ -6,6 +6,12 @@ in ``include/dnnb200.h``. Tensors are passed as raw device pointers and the
 kernels are enqueued on PyTorch's current CUDA stream, so they compose with
 torch ops, events and CUDA graphs.
 
+What it stands in for in the reference: ``Engine.step / train_device / train_host`` are the body of
+``run_child`` (data_parallelism_train.py:185-213: forward, loss, backward, SGD step per batch) and, with a peer
+group attached, also ``run_parent``'s parameter exchange (data_parallelism_train.py:219-254) folded into every
+step; ``Engine.evaluate`` is ``eval`` (data_parallelism_train.py:157-183); ``Engine.allreduce`` is the once-per-epoch
+state_dict average of the parity modes (data_parallelism_train.py:226-244).
+
 There is deliberately no fallback here: on a CUDA tensor a missing library is
 an error (``require()``), so a GPU run can never silently measure eager PyTorch.
 """

@@ -6,6 +6,7 @@ needs the CUDA VMM API and a file-descriptor exchange between processes; ``torch
 already does exactly that, so it is used for the allocation and rendezvous only -- the kernels that use the
 addresses are ours (csrc/allreduce.cu). Availability is probed at run time (north star: "an NVLS-multicast path
 where the host exposes it"); when anything is missing the caller keeps the peer-memory variants.
+No counterpart in the reference, whose only collective is the rank-0 star of data_parallelism_train.py:226-244.
 """
 from __future__ import annotations
 
