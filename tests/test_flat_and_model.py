@@ -138,3 +138,36 @@ def test_python_mirror_of_the_control_block_matches_the_header():
             want.append((name.strip(), ctype[m.group(1)]))
     assert [(n, t) for n, t in native.Ctl._fields_] == want
     assert ctypes.sizeof(native.Ctl) == 56
+
+
+def test_header_is_plain_c_and_links_from_a_c_program(tmp_path):
+    """include/dnnb200.h must be usable from C (the ABI is extern "C", integer status codes): compile a C99
+    program with -pedantic against it, link the in-tree library, and run the one entry point that needs no GPU."""
+    import shutil
+    import subprocess
+    from pathlib import Path
+
+    from distributed_neural_network_b200.ops import flat, native
+
+    root = Path(__file__).resolve().parent.parent
+    lib_dir = Path(native.lib_path()).parent
+    if shutil.which("gcc") is None or not Path(native.lib_path()).exists():
+        pytest.skip("needs gcc and the built library")
+    src = tmp_path / "abi_check.c"
+    src.write_text(
+        '#include <stdint.h>\n#include <stdio.h>\n#include "dnnb200.h"\n'
+        "int main(void) {\n"
+        "  int offs[10], numel, slice, nslices;\n"
+        "  if (dnnb200_layout(offs, &numel, &slice, &nslices) != 0) return 1;\n"
+        '  printf("%d %d %d %d %d\\n", numel, slice, nslices, offs[9], dnnb200_version());\n'
+        "  return 0;\n}\n")
+    exe = tmp_path / "abi_check"
+    cc = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", f"-I{root / 'include'}", str(src),
+                         f"-L{lib_dir}", "-ldnnb200", f"-Wl,-rpath,{lib_dir}", "-o", str(exe)],
+                        capture_output=True, text=True)
+    assert cc.returncode == 0, cc.stderr
+    out = subprocess.run([str(exe)], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 0, out.stderr
+    numel, slice_, nslices, last_off, version = map(int, out.stdout.split())
+    assert numel == flat.FLAT_NUMEL and last_off == list(flat.PARAM_OFFSETS.values())[-1]
+    assert slice_ * nslices >= numel and version >= 100
