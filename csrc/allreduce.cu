@@ -73,7 +73,7 @@ allreduce_kernel(const RankCtx* __restrict__ ctxs, const ArParams prm) {
   const bool in_range = i < prm.n;
   const unsigned long long step = *reinterpret_cast<volatile unsigned long long*>(&ctl->step);
   const unsigned int seq = (unsigned int)(step + 1ull);
-  const int world = cx.world, rank = cx.rank;
+  const int world = cx.world;
 
   float v[4] = {0.f, 0.f, 0.f, 0.f};
   if (in_range) {
