@@ -1,4 +1,4 @@
-"""An executable model of the one-shot exchange protocol of csrc/exchange.cuh, run under random interleavings.
+"""An executable model of the exchange protocols of csrc/exchange.cuh (one-shot, two-shot), run under random interleavings.
 
 compute-sanitizer cannot see a race between GPUs, and it is closed on the development pool anyway;
 what CAN be checked on a CPU is the protocol itself. The model keeps exactly the state the kernels keep --
@@ -139,6 +139,69 @@ def test_ranks_leaving_mid_run_survivors_agree(W):
         leavers = rng.sample(range(W), k=rng.randint(1, W - 1))
         leave_at = {r: rng.randint(1, 5) for r in leavers}
         check(run(W, steps=7, leave_at=leave_at, seed=1000 + seed))
+
+
+def rank_program_two_shot(w: World, r: int):
+    """The two-shot variant (static membership): slice s is owned by rank s % W; the others send their value only to
+    the owner (source slot = sender), the owner adds in rank order and sends the SUM to everybody through its own
+    source slot, which nobody else uses for that slice."""
+    W = w.W
+    for step in range(w.steps):
+        seq = step + 1
+        parity = seq & 1
+        for s in range(S):                              # hop 1: contributions to the owners
+            owner = s % W
+            if owner != r:
+                w.recv[owner][parity][r][s] = (payload(r, step, s), seq)
+                yield
+        for s in range(S):
+            owner = s % W
+            if owner == r:                              # owner: gather, add in rank order, broadcast
+                vals = {}
+                pending = [q for q in range(W) if q != r]
+                while pending:
+                    for q in list(pending):
+                        val, sq = w.recv[r][parity][q][s]
+                        yield
+                        if sq == seq:
+                            assert val == payload(q, step, s), "a line of another step was accepted"
+                            vals[q] = val
+                            pending.remove(q)
+                total = 0.0
+                for q in range(W):
+                    total += payload(r, step, s) if q == r else vals[q]
+                for p in range(W):
+                    if p != r:
+                        w.recv[p][parity][r][s] = (total, seq)
+                        yield
+                w.results[(r, step, s)] = (total, W)
+            else:                                       # everybody else: wait for the owner's sum
+                while True:
+                    val, sq = w.recv[r][parity][owner][s]
+                    yield
+                    if sq == seq:
+                        w.results[(r, step, s)] = (val, W)
+                        break
+
+
+@pytest.mark.parametrize("W", [2, 4, 8])
+def test_two_shot_all_interleavings_agree(W):
+    for seed in range(60):
+        rng = random.Random(seed)
+        w = World(W, 5, {})
+        progs = {r: rank_program_two_shot(w, r) for r in range(W)}
+        budget = 2_000_000
+        while progs:
+            r = rng.choice(list(progs))
+            for _ in range(rng.choice((1, 1, 2, 5, 40))):
+                try:
+                    next(progs[r])
+                except StopIteration:
+                    del progs[r]
+                    break
+                budget -= 1
+                assert budget > 0, "livelock"
+        check(w)
 
 
 def test_the_model_catches_a_protocol_without_parity():
