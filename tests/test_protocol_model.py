@@ -233,3 +233,78 @@ def test_the_model_catches_a_protocol_without_parity():
         except AssertionError:
             broken += 1
     assert broken > 0
+
+
+# ---------------------------------------------------------------------------------------------------------
+# The step-to-step dependency of chained steps: the forward/backward kernel of step t+1 waits on
+# a counter the update kernel's last CTA releases, not on the completion of the update grid.
+# ---------------------------------------------------------------------------------------------------------
+def _run_chained(steps, n_f, n_u, seed, f_waits=True):
+    """F CTAs read ALL parameter slices and write their records; U CTAs read ALL records and write ONE slice.
+    Grids: U(t) may start only when F(t) has completed (griddepcontrol.wait in the update kernel); F(t+1) CTAs are
+    launched as soon as every U(t) CTA has started (programmatic launch) and gate themselves on the counter."""
+    rng = random.Random(seed)
+    params = [0] * n_u            # version of each slice = number of updates applied
+    records = [-1] * n_f          # records[i] = step whose forward/backward wrote it
+    counter = [0]
+    done = [0]
+    state = {"f_done": [0] * (steps + 1), "u_started": [0] * (steps + 1)}
+
+    def f_cta(t, i):
+        while state["u_started"][t - 1] < n_u and t > 0:      # not launched before all U(t-1) CTAs have started
+            yield
+        if f_waits:
+            while counter[0] < t:                               # ld.acquire.gpu spin (thread 0)
+                yield
+        for k in range(n_u):                                    # TMA of the weights
+            assert params[k] == t, f"F({t}) read slice {k} at version {params[k]}"
+            yield
+        records[i] = t
+        yield
+        state["f_done"][t] += 1
+
+    def u_cta(t, k):
+        state["u_started"][t] += 1
+        while state["f_done"][t] < n_f:                         # griddepcontrol.wait: F(t) complete
+            yield
+        for i in range(n_f):
+            assert records[i] == t, f"U({t}) read record {i} of step {records[i]}"
+            yield
+        params[k] = t + 1
+        yield
+        done[0] += 1
+        if done[0] == n_u:                                      # last CTA out: reset, then release the counter
+            done[0] = 0
+            counter[0] = t + 1
+
+    progs = []
+    for t in range(steps):
+        progs += [f_cta(t, i) for i in range(n_f)] + [u_cta(t, k) for k in range(n_u)]
+    # the stream launches grids in order, but CTAs of already-launched grids interleave freely: keep a window
+    live, nxt, budget = [], 0, 1_000_000
+    while live or nxt < len(progs):
+        while nxt < len(progs) and len(live) < 3 * (n_f + n_u):
+            live.append(progs[nxt]); nxt += 1
+        g = rng.choice(live)
+        try:
+            next(g)
+        except StopIteration:
+            live.remove(g)
+        budget -= 1
+        assert budget > 0, "deadlock in the chained-step model"
+    assert params == [steps] * n_u and counter[0] == steps
+
+
+def test_chained_step_counter_dependency_is_sufficient():
+    for seed in range(150):
+        _run_chained(steps=5, n_f=4, n_u=5, seed=seed)
+
+
+def test_chained_step_model_fails_without_the_counter_wait():
+    failures = 0
+    for seed in range(60):
+        try:
+            _run_chained(steps=4, n_f=4, n_u=5, seed=seed, f_waits=False)
+        except AssertionError:
+            failures += 1
+    assert failures > 0
