@@ -2,7 +2,9 @@
 where does the step time of a multi-GPU run go -- compute jitter between ranks or the exchange itself?
 
 Run under torchrun; every rank writes gpurun_out/jitter_w{world}_r{rank}.npy with one row per step:
-[dependency wait passed, last local gradient done, last exchange done, first CTA entered] (ns, that GPU's globaltimer).
+[dependency wait passed, last local gradient done, last exchange done, first CTA entered, SGD stored, fence
+passed, counter bumped] (ns, that GPU's globaltimer). Environment: DNN_DEBUG_FLAGS (engine A/B switches), DNN_EXCHANGE
+(one-shot | two-shot), DNN_CLUSTER (cluster size of the forward/backward kernel).
 """
 import os
 import sys
@@ -21,6 +23,8 @@ def main():
     tr = Trainer(TrainConfig(batch_size=B, sync_mode="step-allreduce" if world > 1 else "none", synthetic=True, quiet=True,
                              seed=1, device="cuda", peer_timeout_s=60.0))
     eng = tr.engine
+    if os.environ.get("DNN_CLUSTER"):                       # CTAs per image in the forward/backward kernel (default: auto = 6)
+        eng.set_cluster_size(int(os.environ["DNN_CLUSTER"]))
     variant = os.environ.get("DNN_EXCHANGE", "")
     if world > 1 and variant:
         eng.set_exchange_variant({"one-shot": 0, "two-shot": 1}[variant])
