@@ -10,13 +10,24 @@ Metric and config are the ones BASELINE.json names: data-parallel CNN (models/mo
 16 per GPU (weak scaling), CIFAR-10-shaped synthetic data, random-init weights, a full optimizer
 step (forward, loss, backward, gradient exchange, SGD-momentum) inside the timed region.
 
-Two numbers per run:
+Numbers per run:
   value  device-timed (CUDA events around exactly K steps, max over ranks). Inputs come from a
          device-resident pool of distinct batches that is larger than the 126 MB L2 and is cycled,
          so no step re-reads its inputs from cache; the 248 KB of weights legitimately stay hot.
   e2e    the same K steps through the public host-fed API (`Engine.train_host`): every step's
          inputs are copied host->device from pinned memory and the step's loss is copied
          device->host; wall-clock, sync on both sides, max over ranks.
+  allreduce_us / exchange_roofline_frac (N > 1)
+         the other half of BASELINE.json's metric: exposed gradient exchange per step (from the
+         update kernel's own time stamps, in a separate traced pass of the same steps) and the
+         fraction of the NVLink roofline (bytes per direction at 900 GB/s) it reaches.
+
+How the timed region is aligned (the whole region is 0.4 ms at the driver's 20 steps, so start-up
+skew between ranks would BE the measurement): everything that touches Python imports, NVML or
+the allocator happens before the barrier; after barrier + synchronize every rank enqueues, in one
+burst with no host work in between, A untimed steps, the start event, the K timed steps and the
+stop event. The exchange inside the untimed steps is the device-side barrier: when the start
+event fires, all GPUs are within a few microseconds of each other and the launch queue is deep.
 One JSON line on stdout (rank 0).
 """
 from __future__ import annotations
@@ -29,6 +40,8 @@ import sys
 import threading
 import time
 from pathlib import Path
+
+import numpy as np
 
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
@@ -48,8 +61,10 @@ class ClockSampler:
                0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
                0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
 
-    def __init__(self, cuda_index: int):
+    def __init__(self, cuda_index: int, period_s: float = 0.0005):
         self.samples, self.reasons, self.max_mhz, self.ok = [], set(), None, False
+        self.period_s = period_s
+        self.t_lo = self.t_hi = None      # perf_counter window of the region the samples are reported for
         self._stop = threading.Event()
         self._t = None
         try:
@@ -72,17 +87,15 @@ class ClockSampler:
         nv = self._nv
         while not self._stop.is_set():
             try:
-                self.samples.append(int(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+                mhz = int(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
                 try:
                     bits = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self._h))
                 except Exception:
                     bits = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
-                for b, name in self.REASONS.items():
-                    if bits & b and name != "gpu_idle":
-                        self.reasons.add(name)
+                self.samples.append((time.perf_counter(), mhz, bits))
             except Exception:
                 pass
-            time.sleep(0.005)
+            time.sleep(self.period_s)
 
     def __enter__(self):
         if self.ok:
@@ -95,12 +108,25 @@ class ClockSampler:
         if self._t:
             self._t.join()
 
+    def window(self, t_lo: float, t_hi: float):
+        self.t_lo, self.t_hi = t_lo, t_hi
+
     def summary(self):
+        """Median SM clock and the union of throttle reasons over the samples taken while the GPU worked on the
+        burst (untimed alignment steps + the timed steps); `samples_timed` of them fall between the host's
+        enqueue of the start event and the end of the final synchronize."""
         if not self.ok or not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "note": "no NVML samples"}
-        s = sorted(self.samples)
-        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(s)}
+        inside = [x for x in self.samples if self.t_lo is None or self.t_lo <= x[0] <= self.t_hi]
+        use = inside or self.samples
+        mhz = sorted(x[1] for x in use)
+        reasons = set()
+        for _, _, bits in use:
+            for b, name in self.REASONS.items():
+                if bits & b and name != "gpu_idle":
+                    reasons.add(name)
+        return {"sm_mhz": mhz[len(mhz) // 2], "sm_min_mhz": mhz[0], "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(reasons), "samples": len(use), "period_ms": self.period_s * 1e3}
 
 
 # --------------------------------------------------------------------------- our arm
@@ -108,7 +134,9 @@ def run_ours(args) -> int:
     import torch
 
     from distributed_neural_network_b200.ops import native
-    from distributed_neural_network_b200.trainer import TrainConfig, Trainer
+    from distributed_neural_network_b200.utils.tracing import nvtx_range
+    from distributed_neural_network_b200.trainer import (NVLINK_BYTES_PER_S, TrainConfig, Trainer,
+                                                         exchange_bytes_per_direction)
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -118,7 +146,8 @@ def run_ours(args) -> int:
             cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                    "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 500), __file__,
                    "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup),
-                   "--batch", str(args.batch), "--exchange", args.exchange]
+                   "--batch", str(args.batch), "--exchange", args.exchange, "--prep", str(args.prep),
+                   "--align", str(args.align), "--pool", str(args.pool)]
             return subprocess.call(cmd)
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     if not torch.cuda.is_available():
@@ -134,7 +163,10 @@ def run_ours(args) -> int:
     eng, comm = trainer.engine, trainer.comm
     dev = trainer.device
     variant = trainer._exchange_variant() if world > 1 else 0
-    two_shot = variant == 1
+    variant_name = {0: "one-shot push, 16-byte LL lines (value, seq, value, seq)",
+                    1: "two-shot (owner-reduce + broadcast), 16-byte LL lines",
+                    2: "NVLS in-switch reduction (multimem.ld_reduce)",
+                    3: "one-shot push, 128-byte lines (31 values + 1 flag word per warp-wide store)"}[variant]
 
     # ---- data: pools of distinct synthetic batches, larger than L2 -------------------------------
     pool = args.pool
@@ -145,61 +177,116 @@ def run_ours(args) -> int:
     dx, dy = hx.to(dev), hy.to(dev)
     pool_bytes = dx.numel() * 4
 
+    cur = {"d": 0, "h": 0}                      # the pools are walked round-robin ACROSS calls, so a batch is
+                                                # re-read only after the other pool-1 batches (> L2) went by
     def run_device(n):
-        done = 0
-        while done < n:
-            c = min(pool, n - done)
-            eng.train_device(dx[:c], dy[:c])
-            done += c
+        while n > 0:
+            c = min(pool - cur["d"], n)
+            eng.train_device(dx[cur["d"]:cur["d"] + c], dy[cur["d"]:cur["d"] + c])
+            cur["d"] = (cur["d"] + c) % pool
+            n -= c
 
     def run_host(n):
-        done = 0
-        while done < n:
-            c = min(pool, n - done)
-            eng.train_host(hx[:c], hy[:c], hl[:c])
-            done += c
+        while n > 0:
+            c = min(pool - cur["h"], n)
+            eng.train_host(hx[cur["h"]:cur["h"] + c], hy[cur["h"]:cur["h"] + c], hl[cur["h"]:cur["h"] + c])
+            cur["h"] = (cur["h"] + c) % pool
+            n -= c
+
+    # ---- preparation: everything slow happens BEFORE the barrier ----------------------------------
+    A = max(W, args.align)                      # untimed steps enqueued directly in front of the timed ones
+    prep = max(W, args.prep)                    # loads every kernel of the path, runs full engine calls
+    clk = ClockSampler(torch.cuda.current_device())          # NVML init + handle lookup: milliseconds
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    utrace = torch.zeros(1024 * 122 * 8, dtype=torch.int64, device=dev) if world > 1 else None
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    run_device(prep)
+    run_host(prep)
+    e0.record(); e1.record()                    # first use of an event allocates it
+    flush.zero_()                               # 256 MiB written: whatever the upload or the warm-up left in L2 is gone
+    torch.cuda.synchronize()
 
     # ---- device-timed region -------------------------------------------------------------------
-    run_device(W)
-    torch.cuda.synchronize()
-    comm.barrier()
-    torch.cuda.synchronize()
-    l0 = eng.launches
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(torch.cuda.current_device()) as clk:
+    with clk, nvtx_range("bench/device-timed"):
+        comm.barrier()
+        torch.cuda.synchronize()
+        l0 = eng.launches
+        t_burst = time.perf_counter()
+        run_device(A)                           # untimed; its exchanges align the GPUs of all ranks on the device
         e0.record()
         run_device(K)
         e1.record()
         torch.cuda.synchronize()
+        clk.window(t_burst, time.perf_counter())
     comm.barrier()
-    launches = eng.launches - l0
+    launches = eng.launches - l0 - 2 * A
     ms = e0.elapsed_time(e1)
     ctl = eng.read_ctl()
 
     # ---- end-to-end region (pinned host -> device every step, loss -> host every step) -----------
-    run_host(W)
-    torch.cuda.synchronize()
     comm.barrier()
-    torch.cuda.synchronize()
+    torch.cuda.nvtx.range_push("bench/end-to-end")
+    run_host(A)                                 # the last of these ends at the same moment on every GPU ...
+    torch.cuda.synchronize()                    # ... so every host leaves this synchronize within microseconds
     t0 = time.perf_counter()
     run_host(K)
     torch.cuda.synchronize()
     t1 = time.perf_counter()
+    torch.cuda.nvtx.range_pop()
     comm.barrier()
     e2e_s = t1 - t0
-    last = min(pool, K)
-    loss_mean = float(hl[:last].mean())
+    loss_mean = float(hl[:min(pool, prep + A + K)].mean())
+
+    # ---- exchange time per step, from the update kernel's own stamps (separate traced pass) -----------
+    xch = None
+    if world > 1:
+        n_tr = min(1024, max(K, 256))
+        eng.set_update_trace(utrace)
+        eng.set_debug_flags(4)                  # ring mode: keep the stamps of the last 1024 steps
+        comm.barrier()
+        run_device(A + n_tr)
+        torch.cuda.synchronize()
+        eng.set_debug_flags(0)
+        eng.set_update_trace(None)
+        end = int(eng.read_ctl().step)
+        u = utrace.view(1024, 122, 8).cpu().numpy()
+        idx = [(end - n_tr + k) % 1024 for k in range(n_tr)]
+        grad_done = u[idx, :, 2].max(axis=1)    # last slice has its local batch gradient
+        xch_done = u[idx, :, 3].max(axis=1)     # last slice has the sum of all ranks
+        wait = np.sort((xch_done - grad_done) / 1e3)
+        xch = {"median_us": float(wait[len(wait) // 2]), "p90_us": float(wait[int(len(wait) * 0.9)]),
+               "mean_us": float(wait.mean()), "steps": n_tr}
+        comm.barrier()
 
     stats = comm.allgather({"ms": ms, "e2e_s": e2e_s, "launches": launches, "clk": clk.summary(),
-                            "status": int(ctl.status), "loss": loss_mean})
+                            "status": int(ctl.status), "loss": loss_mean, "xch": xch})
     if rank == 0:
         ms_max = max(s["ms"] for s in stats)
         e2e_max = max(s["e2e_s"] for s in stats)
         value = world * B * K / (ms_max / 1e3)
         e2e_value = world * B * K / e2e_max
         cs, _ = eng.cluster_info(B)
+        # the other half of the metric: exposed exchange per step and its NVLink roofline
+        xout = {}
+        if world > 1:
+            per_dir = exchange_bytes_per_direction(variant, world)
+            t_roof_us = per_dir / NVLINK_BYTES_PER_S * 1e6
+            xs = [s_["xch"] for s_ in stats]
+            med = max(x["median_us"] for x in xs)
+            xout = {"allreduce_us": round(med, 3),
+                    "allreduce_us_p90": round(max(x["p90_us"] for x in xs), 3),
+                    "exchange_roofline_frac": round(t_roof_us / med, 4) if med > 0 else None,
+                    "exchange": {"bytes_per_direction_per_gpu": per_dir, "roofline_us_at_900GBps": round(t_roof_us, 3),
+                                 "definition": "per step: (last slice holds the sum of all ranks) - (last slice holds its "
+                                               "local batch gradient), globaltimer stamps of the update kernel; median over "
+                                               f"{xs[0]['steps']} traced steps run after the timed region, max over ranks; "
+                                               "compute at peak is negligible, so the roofline is the NVLink time",
+                                 "per_rank_median_us": [round(x["median_us"], 3) for x in xs]}}
         out = {
-            "metric": METRIC, "value": round(value, 1), "unit": "images/s", "n_gpus": world, "steps": K, "warmup": W,
+            "metric": METRIC, "value": round(value, 1), "unit": "images/s", "n_gpus": world, "steps": K,
+            "warmup": prep + A, "warmup_requested": args.warmup,
+            "warmup_note": f"{prep} steps before the barrier (kernels loaded, full engine calls) + {A} untimed steps "
+                           "enqueued in the same burst as the timed ones (device-side alignment of the ranks)",
             "ms_per_step": round(ms_max / K, 6), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": round(value / BASELINE_IMG_S, 2),
             "baseline_ref": "3949 img/s: reference's best committed aggregate (3 procs = 2 children, bs16, 8-core CPU; "
@@ -210,22 +297,24 @@ def run_ours(args) -> int:
                        "global_batch": world * B, "per_gpu_batch": B, "seq_len": None,
                        "parallelism": f"dp{world}", "optimizer": "SGD lr=0.001 momentum=0.9 (inside the timed step)",
                        "exchange": "none (1 GPU)" if world == 1 else
-                                   ("NVLS in-switch reduction (multimem.ld_reduce), fused into the update kernel"
-                                    if variant == 2 else
-                                    ("two-shot (owner-reduce + broadcast)" if two_shot else "one-shot push") +
-                                    " all-reduce over NVLink peer memory with 16-byte LL lines, fused into the update kernel"),
+                                   variant_name + " over NVLink peer memory, fused into the update kernel; chosen " +
+                                   ("by --exchange" if args.exchange != "auto" else
+                                    "by the start-up measurement of every usable variant (exchange_table)"),
                        "l2": f"inputs cycle through a pool of {pool} distinct batches = {pool_bytes >> 20} MiB on the "
-                             f"device (> 126 MB L2); no explicit flush",
+                             f"device (> 126 MB L2), walked round-robin across all calls; 256 MiB written to flush L2 "
+                             f"after the warm-up, before the burst",
                        "cluster_size": cs, "kernels_per_step": 2},
             "clocks": stats[0]["clk"] if world == 1 else
                       {"sm_mhz": min((s["clk"]["sm_mhz"] or 0) for s in stats), "sm_max_mhz": stats[0]["clk"]["sm_max_mhz"],
                        "reasons": sorted({r for s in stats for r in s["clk"]["reasons"]}),
+                       "samples": min(s["clk"].get("samples", 0) for s in stats),
                        "per_rank_sm_mhz": [s["clk"]["sm_mhz"] for s in stats]},
             "e2e": {"value": round(e2e_value, 1), "unit": "images/s",
                     "h2d_bytes_per_step": B * 3 * 32 * 32 * 4 + B * 8, "d2h_bytes_per_step": 4,
                     "ms_per_step": round(e2e_max * 1e3 / K, 6),
-                    "how": "Engine.train_host: per step cudaMemcpyAsync of that step's images+labels from pinned host "
-                           "memory (32-slot device ring, copy stream), 2 kernels, and the update kernel stores the step's mean "
+                    "how": "Engine.train_host: every step's images+labels are copied from pinned host memory inside the "
+                           "region (cudaMemcpyAsync on a copy stream into a 32-slot device ring, the steps of a group of "
+                           "<= 8 sharing one copy), 2 kernels per step, and the update kernel stores each step's mean "
                            "loss into the caller's pinned host buffer (device->host over PCIe); wall clock with "
                            "synchronize on both sides, max over ranks",
                     "mean_loss_read_back": round(max(s["loss"] for s in stats), 4)},
@@ -235,6 +324,9 @@ def run_ours(args) -> int:
             "peer_timeouts": [s["status"] for s in stats],
             "impl": "ours",
         }
+        out.update(xout)
+        if trainer.exchange_table:
+            out["exchange_table"] = trainer.exchange_table
         print(json.dumps(out), flush=True)
     trainer.close()
     comm.close()
@@ -308,6 +400,16 @@ def run_reference(args) -> int:
                                "the reference script itself runs unmodified from baseline/_ref"},
            "timing": "wall clock inside each child from receiving the weights to sending them back (its whole epoch "
                      "of K steps), max over children; a CPU program has no device timeline",
+           # The reference's only timeline IS end to end: the child's epoch from the arrival of the weights to their
+           # departure includes its DataLoader (worker process, uint8 -> float transform, collation), forward, loss,
+           # backward, optimizer step and loss.item() of every step (data_parallelism_train.py:190-207). Nothing moves
+           # between host and device because the reference's distributed path never leaves the CPU.
+           "e2e": {"value": round(value, 1), "unit": "images/s", "ms_per_step": round(t_max * 1e3 / K, 4),
+                   "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                   "how": "wall clock recv->send of the child's epoch incl. the reference's DataLoader + transform, "
+                          "max over children (same region as `value`: a CPU program has no separate device time)"},
+           "clocks": {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "note": "CPU program: no GPU clocks apply"},
+           "gpu_launches": 0,
            "impl": "reference"}
     print(json.dumps(out), flush=True)
     return 0
@@ -320,9 +422,12 @@ def main() -> int:
     ap.add_argument("--warmup", type=int, default=200)
     ap.add_argument("--batch", type=int, default=PER_GPU_BATCH, help="per-GPU batch (the headline config is 16)")
     ap.add_argument("--pool", type=int, default=1024, help="distinct batches cycled through (1024 x 16 = 201 MB > L2)")
+    ap.add_argument("--prep", type=int, default=512, help="untimed steps before the barrier (at least --warmup)")
+    ap.add_argument("--align", type=int, default=128,
+                    help="untimed steps enqueued directly in front of the timed ones (at least --warmup)")
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
-    ap.add_argument("--exchange", choices=["auto", "one-shot", "two-shot", "nvls"], default="auto",
-                    help="gradient exchange variant (auto: by world size, from the measured table in profiles/)")
+    ap.add_argument("--exchange", choices=["auto", "one-shot", "one-shot-128", "two-shot", "nvls"], default="auto",
+                    help="gradient exchange variant (auto: every usable variant is timed at start-up, the fastest runs)")
     ap.add_argument("--ref-max-steps", type=int, default=400)
     ap.add_argument("--ref-timeout", type=float, default=1500.0)
     a = ap.parse_args()

@@ -2,7 +2,7 @@
 // the 1/W scale and the SGD-momentum update.
 //
 // Used (a) by the layer-at-a-time / autograd path, where gradients already sit in
-// Network._flat_grad, launched per bucket on a side stream; (b) in the
+// Network._flat_grad (one launch for the whole flat vector, after backward); (b) in the
 // reference-parity "epoch-average" and "replication" modes, where the vector is
 // the PARAMETER buffer and the op is a plain mean (reference:
 // data_parallelism_train.py:238-240, model_replication_train.py:134-136 -- R1);
@@ -18,8 +18,8 @@
 //              Ownership needs a static membership, so ranks must not leave
 //              between the host's membership updates while this variant is used.
 //
-// The fused step path (fused_step.cu: update_kernel) embeds the one-shot variant
-// directly behind its wgrad tiles.
+// The fused step path (fused_step.cu: update_kernel) embeds the same variants
+// (exchange.cuh) directly behind its weight-gradient reduction.
 #include <cuda_runtime.h>
 
 #include "common.cuh"
@@ -41,7 +41,7 @@ struct ArParams {
   float* out[kMaxWorld];
   int n;         // elements (multiple of 4, <= kFlatNumel)
   int mode;      // ArMode
-  int two_shot;  // variant: 0 one-shot, 1 two-shot, 2 NVLS (multimem.ld_reduce in the NVSwitch)
+  int two_shot;  // variant: 0 one-shot, 1 two-shot, 2 NVLS (multimem.ld_reduce in the NVSwitch), 3 one-shot with 128-byte lines
 };
 
 __device__ __forceinline__ void finish(const RankCtx& cx, const ArParams& prm, int vr, int i, const float (&v)[4],
@@ -85,11 +85,15 @@ allreduce_kernel(const RankCtx* __restrict__ ctxs, const ArParams prm) {
   if (world > 1 && !prm.two_shot) {
     exchange_slice<4>(cx, cfg, &xsh, slice, seq, i, in_range, v, &n);
     if (in_range) finish(cx, prm, vr, i, v, n);
+  } else if (world > 1 && prm.two_shot == 3) {
+    const int left = prm.n - slice * kSlice;
+    exchange_slice_ll128<4>(cx, cfg, &xsh, slice, seq, left < kSlice ? left : kSlice, v, &n);  // one-shot, 128-byte lines
+    if (in_range) finish(cx, prm, vr, i, v, n);
   } else if (world > 1 && prm.two_shot == 2) {
-    exchange_slice_nvls<4>(cx, cfg, slice, seq, i, in_range, v, &n);   // in-switch reduction (exchange.cuh)
+    exchange_slice_nvls<4>(cx, cfg, &xsh, slice, seq, i, in_range, v, &n);   // in-switch reduction (exchange.cuh)
     if (in_range) finish(cx, prm, vr, i, v, n);
   } else if (world > 1) {
-    exchange_slice_two_shot<4>(cx, cfg, slice, seq, i, in_range, v, &n);
+    exchange_slice_two_shot<4>(cx, cfg, &xsh, slice, seq, i, in_range, v, &n);
     if (in_range) finish(cx, prm, vr, i, v, n);
   } else {
     if (in_range) finish(cx, prm, vr, i, v, 1);
@@ -129,6 +133,60 @@ __global__ void pingpong_kernel(const RankCtx* __restrict__ cxp, int peer, int i
     }
   }
   *out_ns = (long long)(globaltimer_ns() - t0);
+}
+
+// ---- 128-byte line probe: is a warp-wide 128-byte store ever seen torn by the peer's warp-wide load? -------------
+// Both ranks run this kernel at the same time. Every warp owns one line slot of the receive area (slice =
+// blockIdx.x, line = warp) and plays ping-pong with the same warp of the peer: 31 words derived from
+// (sequence, slice, line, lane) + the sequence number as flag word, written with ONE st per lane. The receiver
+// spins until the flag word carries the sequence number and then checks that the 31 values returned by that
+// very load belong to it too. A line delivered in pieces shows up as values of the previous round under the
+// new flag. out[0] = mismatching words, out[1] = ns for all rounds, out[2] = 1 if a wait was given up (2 s).
+__device__ __forceinline__ unsigned int line_pattern(unsigned int seq, int slice, int line, int lane) {
+  return (seq * 2654435761u) ^ (unsigned int)(slice * 7919 + line * 131 + lane + 1);
+}
+__global__ void __launch_bounds__(256)
+ll128_probe_kernel(const RankCtx* __restrict__ cxp, int peer, int iters, unsigned int base_seq,
+                   unsigned long long* __restrict__ out) {
+  const RankCtx& cx = *cxp;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, slice = blockIdx.x;
+  const bool first = cx.rank < peer;
+  const unsigned long long t_start = globaltimer_ns();
+  unsigned long long bad = 0ull;
+  bool gave_up = false;
+  for (int it = 0; it < iters && !gave_up; ++it) {
+    const unsigned int seq = base_seq + (unsigned int)it, parity = seq & 1u;
+    const size_t slot = (size_t)slice * kSlice128 + (size_t)warp * 32 + lane;
+    float* theirs = cx.recv[peer] + (size_t)(parity * cx.world + cx.rank) * kLLStride + slot;
+    const float* mine = cx.recv[cx.rank] + (size_t)(parity * cx.world + peer) * kLLStride + slot;
+    const unsigned int word = lane == kLineData ? seq : line_pattern(seq, slice, warp, lane);
+    if (first) st_line_word(theirs, word);
+    unsigned int got;
+    const unsigned long long t0 = globaltimer_ns();
+    unsigned int spins = 0;
+    for (;;) {
+      got = ld_line_word(mine);
+      if (__shfl_sync(0xffffffffu, got, kLineData) == seq) break;
+      if ((++spins & 0xfffu) == 0u && __shfl_sync(0xffffffffu, globaltimer_ns() - t0 > 2000000000ull ? 1 : 0, 0)) {
+        gave_up = true;
+        break;
+      }
+    }
+    if (!gave_up && lane < kLineData && got != line_pattern(seq, slice, warp, lane)) ++bad;
+    if (!first) st_line_word(theirs, word);
+  }
+  if (bad) atomicAdd(out, bad);
+  if (gave_up && lane == 0) out[2] = 1ull;
+  if (blockIdx.x == 0 && threadIdx.x == 0) out[1] = globaltimer_ns() - t_start;
+}
+
+int launch_ll128_probe(const RankCtx* d_ctx, int peer, int iters, int n_ctas, unsigned int base_seq,
+                       unsigned long long* d_out3, cudaStream_t stream) {
+  DNN_ARG_CHECK(n_ctas >= 1 && n_ctas <= kNumSlices, "ll128_probe: 1..%d CTAs", kNumSlices);
+  DNN_CUDA_CHECK(cudaMemsetAsync(d_out3, 0, 3 * sizeof(unsigned long long), stream));
+  ll128_probe_kernel<<<n_ctas, 256, 0, stream>>>(d_ctx, peer, iters, base_seq, d_out3);
+  DNN_CUDA_CHECK(cudaGetLastError());
+  return kOk;
 }
 
 int launch_pingpong(const RankCtx* d_ctx, int peer, int iters, unsigned int base_seq, long long* d_out_ns,

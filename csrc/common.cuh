@@ -35,6 +35,25 @@ void set_last_error(const char* fmt, ...);
     }                                          \
   } while (0)
 
+// Kernel function attributes (cudaFuncSetAttribute) belong to the DEVICE that is current when they are set, so
+// "done once per process" is wrong as soon as a process drives a second GPU: its launches with more than 48 KB of
+// dynamic shared memory would fail. One of these per kernel remembers which devices have been configured.
+struct PerDeviceOnce {
+  static constexpr int kMaxDevices = 64;
+  volatile unsigned char done[kMaxDevices] = {};
+};
+template <class Kernel>
+inline int ensure_max_dynamic_smem(PerDeviceOnce& once, Kernel kern, size_t bytes) {
+  int dev = 0;
+  DNN_CUDA_CHECK(cudaGetDevice(&dev));
+  const bool tracked = dev >= 0 && dev < PerDeviceOnce::kMaxDevices;
+  if (tracked && once.done[dev]) return kOk;
+  // (two threads racing here both set the same value: harmless)
+  DNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  if (tracked) once.done[dev] = 1;
+  return kOk;
+}
+
 #ifdef __CUDACC__
 
 __device__ __forceinline__ float warp_sum(float v) {

@@ -32,8 +32,15 @@
 
 namespace dnnb200 {
 
+// 128-byte lines (one-shot-128): a slice of kSlice floats travels as kLines128 lines of 31 values + 1 flag word
+constexpr int kLineData = 31;
+constexpr int kLines128 = (kSlice + kLineData - 1) / kLineData;   // 17
+constexpr int kSlice128 = kLines128 * 32;                         // 544 words per (slice, source) in the receive area
+
 struct ExchangeShared {
   unsigned int present;  // bitmask of ranks whose contribution enters the sum
+  alignas(16) float in[kLines128 * kLineData + 1];   // 128-byte-line variant: my slice, re-laid out line by line
+  alignas(16) float out[kLines128 * kLineData + 1];  //   and the sum over the ranks
 };
 
 // The two StepCtl fields every exchange needs, read by the caller (the update kernel reads them BEFORE it waits for
@@ -203,6 +210,147 @@ __device__ __forceinline__ void exchange_slice(const RankCtx& cx, const Exchange
   *n_present = __popc(present);
 }
 
+// ---- one-shot with 128-byte lines ------------------------------------------------------------------
+// The 16-byte LL lines above spend half of every NVLink byte on sequence numbers; at 8 GPUs the one-shot push
+// then moves 7 x 497 KB per GPU and loses to two-shot. Here a line is 128 bytes: 31 values + ONE flag word,
+// written by one warp-wide store instruction (32 lanes x 4 bytes, one fully covered 128-byte transaction) and
+// read back by one warp-wide load. A 128-byte aligned write travels over NVLink and lands in the peer's L2 as
+// one unit -- the property NCCL's LL128 protocol is built on -- so a reader whose load returns the flag word
+// of this step also holds the 31 values of this step. 1/32 of the bytes is overhead instead of 1/2:
+// 7 x 265 KB per GPU at 8 GPUs, still ONE latency hop, and membership-safe like the 16-byte one-shot
+// (leave markers, timeout, the CTA agrees on one set of contributors, rank-ordered sum => identical bits).
+// The thread-owned values are re-laid out line by line through shared memory (sh->in / sh->out).
+// tests/test_gpu_multiproc.py::test_ll128_lines_are_never_torn hammers the atomicity assumption over NVLink.
+__device__ __forceinline__ void st_line_word(float* p, unsigned int w) {
+  asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(w) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_line_word(const float* p) {
+  unsigned int w;
+  asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(w) : "l"(p) : "memory");
+  return w;
+}
+
+// kThreads = threads of the CTA (kSlice / kVec). n_valid = how many of the slice's kSlice values exist (the last
+// slice of a vector is short): only the lines that carry one of them travel.
+template <int kVec>
+__device__ __forceinline__ void exchange_slice_ll128(const RankCtx& cx, const ExchangeCfg cfg, ExchangeShared* sh,
+                                                     int slice, unsigned int seq, int n_valid, float (&v)[kVec],
+                                                     int* n_present) {
+  static_assert(kVec == 2 || kVec == 4, "vector width");
+  constexpr int kWarps = kSlice / kVec / 32;
+  const int world = cx.world, rank = cx.rank;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const unsigned int parity = seq & 1u;
+  const unsigned int configured = cfg.configured;
+  const unsigned long long tmo = cfg.timeout_ns;
+  const unsigned int* my_flags = cx.flags[rank];
+  const int n_lines = (n_valid + kLineData - 1) / kLineData;
+  const size_t area = (size_t)slice * kSlice128;   // word offset of this slice inside a (parity, source) block
+
+  // 1. my values, line layout: word w of the slice sits at in[w] (lines are consecutive runs of 31)
+#pragma unroll
+  for (int k = 0; k < kVec; ++k) sh->in[kVec * tid + k] = v[k];
+  if (tid == 0) sh->present = configured;
+  __syncthreads();
+
+  // 2. push: one warp-wide store per (line, peer)
+  for (int L = warp; L < n_lines; L += kWarps) {
+    const int w = L * kLineData + lane;
+    const unsigned int word = lane == kLineData ? seq : (w < kSlice ? __float_as_uint(sh->in[w]) : 0u);
+    for (int p = 0; p < world; ++p) {
+      if (p == rank || !((configured >> p) & 1u)) continue;
+      st_line_word(cx.recv[p] + ((size_t)(parity * world + rank) * kLLStride + area + (size_t)L * 32 + lane), word);
+    }
+  }
+
+  // 3. gather my lines from my own receive area; all pending peers of a line are polled as one batch of loads
+  const float* my_recv = cx.recv[rank];
+  unsigned int absent_warp = 0u;   // warp-uniform
+  unsigned int used_any = 0u;      // union over my lines of the sets that entered their sums
+  for (int L = warp; L < n_lines; L += kWarps) {
+    const int w = L * kLineData + lane;
+    const float mine = (lane < kLineData && w < kSlice) ? sh->in[w] : 0.f;
+    float acc = 0.f;
+    unsigned int absent = absent_warp;
+    for (int g0 = 0; g0 < world; g0 += 8) {
+      unsigned int t[8];
+      unsigned int pending = (configured >> g0) & 0xffu & ~(absent >> g0);
+      if (rank >= g0 && rank < g0 + 8) pending &= ~(1u << (rank - g0));
+      if (world - g0 < 8) pending &= (1u << (world - g0)) - 1u;
+      unsigned int spins = 0;
+      unsigned long long t0 = 0;
+      while (pending) {
+        unsigned int arrived = 0u;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          if ((pending >> j) & 1u) {
+            t[j] = ld_line_word(my_recv + ((size_t)(parity * world + g0 + j) * kLLStride + area + (size_t)L * 32 + lane));
+            if (__shfl_sync(0xffffffffu, t[j], kLineData) == seq) arrived |= 1u << j;
+          }
+        }
+        pending &= ~arrived;
+        if (!pending) break;
+        if ((++spins & 0x3fu) != 0u) continue;
+        // something is late: has it left (announced), or is it time to give up? (all lanes take the same path)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          if (!((pending >> j) & 1u)) continue;
+          const unsigned int l = ld_acquire_sys(my_flags + (g0 + j) * kFlagRow + kLeaveSlot);
+          if (l != 0u && (int)(seq - l) >= 0) {
+            // a peer that left pushed every line of its last step BEFORE it wrote the marker: one more look settles it
+            t[j] = ld_line_word(my_recv + ((size_t)(parity * world + g0 + j) * kLLStride + area + (size_t)L * 32 + lane));
+            if (__shfl_sync(0xffffffffu, t[j], kLineData) != seq) absent |= 1u << (g0 + j);
+            pending &= ~(1u << j);
+          }
+        }
+        if (pending && tmo != 0ull) {
+          const unsigned long long now = globaltimer_ns();
+          if (t0 == 0ull) t0 = now;
+          else if (__shfl_sync(0xffffffffu, (now - t0 > tmo) ? 1 : 0, 0)) {
+            if (lane == 0) atomicOr(&cx.ctl->status, kStatusTimeout | (pending << (8 + g0)));
+            absent |= pending << g0;
+            pending = 0u;
+          }
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {   // rank-ordered sum, my own contribution at its rank position
+        const int pr = g0 + j;
+        if (pr >= world || !((configured >> pr) & 1u)) continue;
+        if (pr == rank) acc += mine;
+        else if (!((absent >> pr) & 1u)) acc += __uint_as_float(t[j]);
+      }
+    }
+    if (lane < kLineData) sh->out[w] = acc;
+    used_any |= configured & ~absent;
+    absent_warp |= absent;   // a rank that is gone for one line of this step is gone for all of them
+  }
+  // 4. the CTA agrees on ONE set of contributors (a rank pushes all lines of a step or none, so views only differ
+  //    when a timeout races with late data): union of everybody's "absent"; a warp that summed a larger set for
+  //    any of its lines redoes them from the receive area (the lines of the ranks that stay in have all arrived)
+  if (absent_warp && lane == 0) atomicAnd(&sh->present, ~absent_warp);
+  __syncthreads();
+  const unsigned int present = sh->present;
+  if (used_any & ~present) {   // warp-uniform
+    for (int L = warp; L < n_lines; L += kWarps) {
+      const int w = L * kLineData + lane;
+      float acc = 0.f;
+      for (int p = 0; p < world; ++p) {
+        if (!((present >> p) & 1u)) continue;
+        if (p == rank) acc += (lane < kLineData && w < kSlice) ? sh->in[w] : 0.f;
+        else acc += __uint_as_float(ld_line_word(my_recv + ((size_t)(parity * world + p) * kLLStride + area + (size_t)L * 32 + lane)));
+      }
+      if (lane < kLineData) sh->out[w] = acc;
+    }
+  }
+  __syncthreads();
+  if (kVec * tid < n_valid) {
+#pragma unroll
+    for (int k = 0; k < kVec; ++k) v[k] = sh->out[kVec * tid + k];
+  }
+  *n_present = __popc(present);
+}
+
 // ---- two-shot variant ------------------------------------------------------------------------
 // Slice s is owned by the (s mod n)-th configured rank. Everybody else sends its values for s only to
 // the owner (LL lines, src slot = sender); the owner adds the n contributions in rank order and sends
@@ -210,7 +358,14 @@ __device__ __forceinline__ void exchange_slice(const RankCtx& cx, const Exchange
 // 2(n-1)/n x the vector per GPU instead of (n-1) x: wins from about 4 GPUs on (measured table in
 // profiles/). All ranks end up with the same bits because all use the owner's sum.
 // Ownership is static: this variant is only valid while no configured rank leaves (the host picks the
-// one-shot variant whenever the failure drill can drop ranks); a silent owner trips the timeout.
+// one-shot variant whenever the failure drill can drop ranks).
+// What a stall does (timeout_ns != 0), so that nobody ever applies garbage:
+//   * a contribution that does not reach the OWNER in time is left out, for the whole slice (the CTA agrees on
+//     one set, like the one-shot path); the owner scales the sum by n_configured / n_arrived before it sends it,
+//     so every rank still divides by n_configured and all of them apply the same mean over the ranks that arrived;
+//   * a rank whose OWNER stays silent keeps its own local gradient for the slice (divisor 1: a local SGD step).
+//     Its replica then differs from the others in that slice until the host re-averages (Trainer._resync_state).
+// Either way StepCtl::status carries kStatusTimeout and the mask of the ranks given up on.
 __device__ __forceinline__ bool ll_poll(const float* line, unsigned int seq, float* a, float* b,
                                         unsigned long long tmo) {
   unsigned int spins = 0;
@@ -226,9 +381,9 @@ __device__ __forceinline__ bool ll_poll(const float* line, unsigned int seq, flo
 }
 
 template <int kVec>
-__device__ __forceinline__ void exchange_slice_two_shot(const RankCtx& cx, const ExchangeCfg cfg, int slice,
-                                                        unsigned int seq, int i, bool in_range, float (&v)[kVec],
-                                                        int* n_present) {
+__device__ __forceinline__ void exchange_slice_two_shot(const RankCtx& cx, const ExchangeCfg cfg, ExchangeShared* sh,
+                                                        int slice, unsigned int seq, int i, bool in_range,
+                                                        float (&v)[kVec], int* n_present) {
   static_assert(kVec == 2 || kVec == 4, "vector width");
   const int world = cx.world, rank = cx.rank;
   const unsigned int parity = seq & 1u;
@@ -242,24 +397,35 @@ __device__ __forceinline__ void exchange_slice_two_shot(const RankCtx& cx, const
     for (int p = 0; p < world; ++p)
       if ((configured >> p) & 1u) { if (k == 0) { owner = p; break; } --k; }
   }
-  if (!in_range || !((configured >> rank) & 1u)) return;
+  if (!((configured >> rank) & 1u)) return;   // (whole CTA: rank is uniform)
   const float* my_recv = cx.recv[rank];
   if (rank != owner) {
+    if (!in_range) return;
     float* dst = cx.recv[owner] + ((size_t)(parity * world + rank) * kLLStride + 2 * (size_t)i);
 #pragma unroll
     for (int k = 0; k < kVec; k += 2) st_ll(dst + 2 * k, v[k], v[k + 1], seq);
     const float* src = my_recv + ((size_t)(parity * world + owner) * kLLStride + 2 * (size_t)i);
+    float got[kVec];
+    bool ok = true;
 #pragma unroll
-    for (int k = 0; k < kVec; k += 2)
-      if (!ll_poll(src + 2 * k, seq, &v[k], &v[k + 1], tmo))
-        atomicOr(&cx.ctl->status, kStatusTimeout | (1u << (8 + owner)));
+    for (int k = 0; k < kVec; k += 2) ok = ll_poll(src + 2 * k, seq, &got[k], &got[k + 1], tmo) && ok;
+    if (ok) {
+#pragma unroll
+      for (int k = 0; k < kVec; ++k) v[k] = got[k];
+    } else {   // silent owner: keep my own gradient for these elements, as a local step
+      atomicOr(&cx.ctl->status, kStatusTimeout | (1u << (8 + owner)));
+      *n_present = 1;
+    }
   } else {
+    if (threadIdx.x == 0) sh->present = configured;
+    __syncthreads();
+    unsigned int absent = 0u;
     float acc[kVec];
 #pragma unroll
     for (int k = 0; k < kVec; ++k) acc[k] = 0.f;
     for (int g0 = 0; g0 < world; g0 += 8) {   // all pending contributions are polled as one batch of loads
       float t[8][kVec];
-      unsigned int pending = (configured >> g0) & 0xffu;
+      unsigned int pending = in_range ? ((configured >> g0) & 0xffu) : 0u;
       if (rank >= g0 && rank < g0 + 8) pending &= ~(1u << (rank - g0));
       if (world - g0 < 8) pending &= (1u << (world - g0)) - 1u;
       unsigned int spins = 0;
@@ -282,12 +448,7 @@ __device__ __forceinline__ void exchange_slice_two_shot(const RankCtx& cx, const
           if (t0 == 0ull) t0 = now;
           else if (now - t0 > tmo) {
             atomicOr(&cx.ctl->status, kStatusTimeout | (pending << (8 + g0)));
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-              if ((pending >> j) & 1u) {
-#pragma unroll
-                for (int k = 0; k < kVec; ++k) t[j][k] = 0.f;
-              }
+            absent |= pending << g0;
             pending = 0u;
           }
         }
@@ -299,11 +460,39 @@ __device__ __forceinline__ void exchange_slice_two_shot(const RankCtx& cx, const
         if (pr == rank) {
 #pragma unroll
           for (int k = 0; k < kVec; ++k) acc[k] += v[k];
-        } else {
+        } else if (in_range && !((absent >> pr) & 1u)) {
 #pragma unroll
           for (int k = 0; k < kVec; ++k) acc[k] += t[j][k];
         }
       }
+    }
+    // one set of contributors for the whole slice: the union of what any thread gave up on (normally nothing)
+    if (absent) atomicAnd(&sh->present, ~absent);
+    __syncthreads();
+    const unsigned int present = sh->present;
+    if (!in_range) return;
+    if (present != (configured & ~absent)) {   // somebody else dropped a rank whose line I did receive: redo the sum
+#pragma unroll
+      for (int k = 0; k < kVec; ++k) acc[k] = 0.f;
+      for (int p = 0; p < world; ++p) {
+        if (!((present >> p) & 1u)) continue;
+        if (p == rank) {
+#pragma unroll
+          for (int k = 0; k < kVec; ++k) acc[k] += v[k];
+        } else {
+          const float* src = my_recv + ((size_t)(parity * world + p) * kLLStride + 2 * (size_t)i);
+          float t2[kVec];
+#pragma unroll
+          for (int k = 0; k < kVec; k += 2) (void)ld_ll(src + 2 * k, seq, &t2[k], &t2[k + 1]);
+#pragma unroll
+          for (int k = 0; k < kVec; ++k) acc[k] += t2[k];
+        }
+      }
+    }
+    if (present != configured) {   // everyone divides by n_cfg: make that the mean over the ranks that arrived
+      const float fix = (float)n_cfg / (float)__popc(present);
+#pragma unroll
+      for (int k = 0; k < kVec; ++k) acc[k] *= fix;
     }
     for (int p = 0; p < world; ++p) {
       if (p == rank || !((configured >> p) & 1u)) continue;
@@ -320,10 +509,12 @@ __device__ __forceinline__ void exchange_slice_two_shot(const RankCtx& cx, const
 // Each rank parks its values in its own symmetric buffer; ONE multimem.st publishes "slice s of rank r is
 // there" to every rank; multimem.ld_reduce returns the switch's sum of all W copies. Static membership (the
 // switch adds every member of the multicast group). Used when the host exposes NVLink multicast.
+// A member that does not publish its slice in time cannot be left out of the switch's sum, so the whole slice
+// falls back to this rank's own gradient (divisor 1, a local step) and StepCtl::status says so.
 template <int kVec>
-__device__ __forceinline__ void exchange_slice_nvls(const RankCtx& cx, const ExchangeCfg cfg, int slice,
-                                                    unsigned int seq, int i, bool in_range, float (&v)[kVec],
-                                                    int* n_present) {
+__device__ __forceinline__ void exchange_slice_nvls(const RankCtx& cx, const ExchangeCfg cfg, ExchangeShared* sh,
+                                                    int slice, unsigned int seq, int i, bool in_range,
+                                                    float (&v)[kVec], int* n_present) {
   static_assert(kVec == 2 || kVec == 4, "vector width");
   const int world = cx.world, rank = cx.rank, tid = threadIdx.x;
   const unsigned int parity = seq & 1u;
@@ -331,6 +522,7 @@ __device__ __forceinline__ void exchange_slice_nvls(const RankCtx& cx, const Exc
   float* loc = cx.nvls_local;
   float* mc = cx.nvls_mc;
   *n_present = world;
+  if (tid == 0) sh->present = 1u;   // here: "every member published in time"
   if (in_range) {
     float* dst = loc + (size_t)parity * kFlatNumel + i;
     if (kVec == 4) *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
@@ -354,11 +546,19 @@ __device__ __forceinline__ void exchange_slice_nvls(const RankCtx& cx, const Exc
       if (tmo != 0ull && (++spins & 0x3ffu) == 0u) {
         const unsigned long long now = globaltimer_ns();
         if (t0 == 0ull) t0 = now;
-        else if (now - t0 > tmo) { atomicOr(&cx.ctl->status, kStatusTimeout | (1u << (8 + tid))); break; }
+        else if (now - t0 > tmo) {
+          atomicOr(&cx.ctl->status, kStatusTimeout | (1u << (8 + tid)));
+          sh->present = 0u;
+          break;
+        }
       }
     }
   }
   __syncthreads();
+  if (sh->present == 0u) {
+    *n_present = 1;
+    return;
+  }
   if (in_range) {
     const float* src = mc + (size_t)parity * kFlatNumel + i;
     if (kVec == 4) {

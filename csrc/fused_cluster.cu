@@ -1,5 +1,5 @@
 // fwd_bwd_cluster_kernel: the forward/backward half of the training step with each
-// IMAGE spread over a thread-block cluster of CS CTAs (CS = 1, 2, 4 or 8).
+// IMAGE spread over a thread-block cluster of CS CTAs (CS = 2..8; one CTA per image is fused_step.cu).
 //
 // Why: at the reference's batch sizes (1..64 per rank, data_parallelism_train.py:263,
 // run_training.sh) one CTA per image leaves most of the 148 SMs idle and makes the step a
@@ -871,13 +871,10 @@ static int launch_cluster_t(const float* params, const float* x, const long long
                             float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
                             long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
                             cudaStream_t stream) {
-  static bool attr_set = false;
+  static PerDeviceOnce attr_set;
   auto kern = fwd_bwd_cluster_kernel<CS>;
   const size_t smem = cluster_smem_bytes<CS>();
-  if (!attr_set) {
-    DNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
-  }
+  if (int rc = ensure_max_dynamic_smem(attr_set, kern, smem)) return rc;
   const int n_clusters = B < max_clusters ? B : max_clusters;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(n_clusters * CS);

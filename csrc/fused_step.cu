@@ -683,8 +683,12 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
     ExchangeCfg cfg;
     cfg.configured = ctl_snap.active_mask;
     cfg.timeout_ns = ctl_snap.timeout_ns;
-    if (variant == 2u && cx.nvls_mc != nullptr) exchange_slice_nvls<kUVec>(cx, cfg, slice, seq, i, in_range, v, &n);
-    else if (variant == 1u) exchange_slice_two_shot<kUVec>(cx, cfg, slice, seq, i, in_range, v, &n);
+    if (variant == 2u && cx.nvls_mc != nullptr) exchange_slice_nvls<kUVec>(cx, cfg, &xsh, slice, seq, i, in_range, v, &n);
+    else if (variant == 1u) exchange_slice_two_shot<kUVec>(cx, cfg, &xsh, slice, seq, i, in_range, v, &n);
+    else if (variant == 3u) {
+      const int left = kFlatNumel - slice * kSlice;
+      exchange_slice_ll128<kUVec>(cx, cfg, &xsh, slice, seq, left < kSlice ? left : kSlice, v, &n);
+    }
     else exchange_slice<kUVec>(cx, cfg, &xsh, slice, seq, i, in_range, v, &n);
   }
   if (tr && tid == 0) tr[slice * 8 + 3] = (long long)globaltimer_ns();
@@ -763,18 +767,15 @@ __global__ void eval_reduce_kernel(const float* __restrict__ img_loss, const int
 }
 
 // ============================================================================
-// host launchers (used by engine.cpp and by the C ABI in api.cpp)
+// host launchers (used by runtime.cu and noalloc.cu)
 // ============================================================================
 int launch_fwd_bwd(bool train, const float* params, const float* x, const long long* labels,
                    float* saved, float* part1, float* part2, float* img_loss, int* img_correct,
                    float* logits_out, int B, int max_ctas, cudaStream_t stream) {
-  static bool attr_set[2] = {false, false};
+  static PerDeviceOnce attr_set[2];
   const size_t smem = sizeof(FBSmem);
   auto kern = train ? fwd_bwd_kernel<true> : fwd_bwd_kernel<false>;
-  if (!attr_set[train ? 1 : 0]) {
-    DNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set[train ? 1 : 0] = true;
-  }
+  if (int rc = ensure_max_dynamic_smem(attr_set[train ? 1 : 0], kern, smem)) return rc;
   const int grid = B < max_ctas ? B : max_ctas;
   kern<<<grid, kFBThreads, smem, stream>>>(params, x, labels, saved, part1, part2, img_loss, img_correct,
                                            logits_out, B, 1.f / (float)B);

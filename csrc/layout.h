@@ -1,5 +1,5 @@
 // Flat parameter layout of the CIFAR-10 CNN, shared by every kernel.
-// Mirrors distributed_neural_network_b200/ops/flat.py (tests/test_flat.py checks
+// Mirrors distributed_neural_network_b200/ops/flat.py (tests/test_flat_and_model.py checks
 // that both agree). Tensor order/shapes: reference models/model.py:13-18.
 #pragma once
 

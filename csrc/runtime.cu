@@ -42,6 +42,8 @@ int launch_fwd_bwd_cluster(int cs, const float* params, const float* x, const lo
 int max_active_clusters(int cs);
 int launch_pingpong(const RankCtx* d_ctx, int peer, int iters, unsigned int base_seq, long long* d_out_ns,
                     cudaStream_t stream);
+int launch_ll128_probe(const RankCtx* d_ctx, int peer, int iters, int n_ctas, unsigned int base_seq,
+                       unsigned long long* d_out3, cudaStream_t stream);
 int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int n_part1, int loss_slot, int flags,
                   float* host_loss, cudaStream_t stream);
 int launch_eval_reduce(const float* img_loss, const int* img_correct, int N, int bs, double* out, cudaStream_t stream);
@@ -130,10 +132,11 @@ struct dnnb200_engine {
   static constexpr int kGroup = 8;   // steps per event group (stream events break the kernels' programmatic overlap)
   cudaStream_t copy_stream = nullptr, d2h_stream = nullptr;
   cudaEvent_t slot_ready[kRing] = {}, slot_free[kRing] = {}, step_done[kRing] = {};
-  float* d_x[kRing] = {};
-  long long* d_y[kRing] = {};
+  float* ring_x = nullptr;        // [kRing / kGroup] group regions of kGroup * max_batch images; a call packs its steps at its own batch size
+  long long* ring_y = nullptr;    // [kRing][max_batch]
   bool ring_ready = false;
   unsigned long long ring_uses = 0;
+  unsigned int pingpong_seq = 1000;
 };
 
 namespace dnnb200 {
@@ -147,11 +150,7 @@ static int push_ctx(dnnb200_engine* e, cudaStream_t s) {
   return kOk;
 }
 
-static int group_create(int rank, int world, dnnb200_group** out, void* h_handle64) {
-  DNN_ARG_CHECK(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world, "group: bad rank/world %d/%d", rank,
-                world);
-  dnnb200_group* g = new (std::nothrow) dnnb200_group();
-  DNN_ARG_CHECK(g != nullptr, "group: out of host memory");
+static int group_fill(dnnb200_group* g, int rank, int world, void* h_handle64) {
   g->rank = rank;
   g->world = world;
   DNN_CUDA_CHECK(cudaGetDevice(&g->device));
@@ -165,6 +164,21 @@ static int group_create(int rank, int world, dnnb200_group** out, void* h_handle
     cudaIpcMemHandle_t h;
     DNN_CUDA_CHECK(cudaIpcGetMemHandle(&h, g->base));
     memcpy(h_handle64, &h, sizeof(h));
+  }
+  return kOk;
+}
+
+static int group_create(int rank, int world, dnnb200_group** out, void* h_handle64) {
+  DNN_ARG_CHECK(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world, "group: bad rank/world %d/%d", rank,
+                world);
+  DNN_ARG_CHECK(out != nullptr, "group: null output pointer");
+  dnnb200_group* g = new (std::nothrow) dnnb200_group();
+  DNN_ARG_CHECK(g != nullptr, "group: out of host memory");
+  const int rc = group_fill(g, rank, world, h_handle64);
+  if (rc) {                       // nothing half-built survives a failure (the error text is already set)
+    if (g->base) cudaFree(g->base);
+    delete g;
+    return rc;
   }
   *out = g;
   return kOk;
@@ -188,16 +202,45 @@ static int engine_refresh_peers(dnnb200_engine* e, cudaStream_t s) {
   return push_ctx(e, s);
 }
 
-static int ensure_ring(dnnb200_engine* e) {
-  if (e->ring_ready) return kOk;
+static void free_ring(dnnb200_engine* e) {   // tolerates a ring that was only partly created
+  for (int i = 0; i < dnnb200_engine::kRing; ++i) {
+    if (e->slot_ready[i]) cudaEventDestroy(e->slot_ready[i]);
+    if (e->slot_free[i]) cudaEventDestroy(e->slot_free[i]);
+    if (e->step_done[i]) cudaEventDestroy(e->step_done[i]);
+    e->slot_ready[i] = e->slot_free[i] = e->step_done[i] = nullptr;
+  }
+  cudaFree(e->ring_x);
+  cudaFree(e->ring_y);
+  e->ring_x = nullptr;
+  e->ring_y = nullptr;
+  if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
+  if (e->d2h_stream) cudaStreamDestroy(e->d2h_stream);
+  e->copy_stream = e->d2h_stream = nullptr;
+  e->ring_ready = false;
+}
+
+static int create_ring(dnnb200_engine* e) {
   DNN_CUDA_CHECK(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
   DNN_CUDA_CHECK(cudaStreamCreateWithFlags(&e->d2h_stream, cudaStreamNonBlocking));
   for (int i = 0; i < dnnb200_engine::kRing; ++i) {
     DNN_CUDA_CHECK(cudaEventCreateWithFlags(&e->slot_ready[i], cudaEventDisableTiming));
     DNN_CUDA_CHECK(cudaEventCreateWithFlags(&e->slot_free[i], cudaEventDisableTiming));
     DNN_CUDA_CHECK(cudaEventCreateWithFlags(&e->step_done[i], cudaEventDisableTiming));
-    DNN_CUDA_CHECK(cudaMalloc(&e->d_x[i], (size_t)e->max_batch * kImgNumel * sizeof(float)));
-    DNN_CUDA_CHECK(cudaMalloc(&e->d_y[i], (size_t)e->max_batch * sizeof(long long)));
+  }
+  // ONE allocation for all slots: the inputs of consecutive steps are consecutive in the caller's pinned buffer and
+  // in the ring, so a whole group of steps is moved by one copy for the images and one for the labels
+  DNN_CUDA_CHECK(cudaMalloc(&e->ring_x, (size_t)dnnb200_engine::kRing * e->max_batch * kImgNumel * sizeof(float)));
+  DNN_CUDA_CHECK(cudaMalloc(&e->ring_y, (size_t)dnnb200_engine::kRing * e->max_batch * sizeof(long long)));
+  return kOk;
+}
+
+static int ensure_ring(dnnb200_engine* e) {
+  if (e->ring_ready) return kOk;
+  const int rc = create_ring(e);
+  if (rc) {          // a retry must not find (and leak) the slots of a failed attempt
+    free_ring(e);
+    cudaGetLastError();
+    return rc;
   }
   e->ring_ready = true;
   return kOk;
@@ -381,12 +424,8 @@ int dnnb200_group_destroy(dnnb200_group* g) {
 }
 
 // ---- engine ---------------------------------------------------------------------
-int dnnb200_engine_create(float* params, float* momentum, float* grads, int max_batch, float lr, float mu,
-                          dnnb200_engine** out) {
-  DNN_ARG_CHECK(params && momentum && out, "engine_create: null argument");
-  DNN_ARG_CHECK(max_batch >= 1 && max_batch <= 65536, "engine_create: max_batch out of range");
-  dnnb200_engine* e = new (std::nothrow) dnnb200_engine();
-  DNN_ARG_CHECK(e != nullptr, "engine_create: out of host memory");
+static int engine_fill(dnnb200_engine* e, float* params, float* momentum, float* grads, int max_batch, float lr,
+                       float mu) {
   DNN_CUDA_CHECK(cudaGetDevice(&e->device));
   cudaDeviceProp prop;
   DNN_CUDA_CHECK(cudaGetDeviceProperties(&prop, e->device));
@@ -429,8 +468,26 @@ int dnnb200_engine_create(float* params, float* momentum, float* grads, int max_
   e->h_ctx.loss_ring = e->loss_ring;
   e->h_ctx.loss_ring_mask = e->loss_ring_mask;
   e->h_ctx.ctl = e->ctl;
-  int rc = engine_refresh_peers(e, nullptr);
-  if (rc) return rc;
+  return engine_refresh_peers(e, nullptr);
+}
+
+int dnnb200_engine_destroy(dnnb200_engine* e);
+
+int dnnb200_engine_create(float* params, float* momentum, float* grads, int max_batch, float lr, float mu,
+                          dnnb200_engine** out) {
+  DNN_ARG_CHECK(params && momentum && out, "engine_create: null argument");
+  DNN_ARG_CHECK(max_batch >= 1 && max_batch <= 65536, "engine_create: max_batch out of range");
+  dnnb200_engine* e = new (std::nothrow) dnnb200_engine();
+  DNN_ARG_CHECK(e != nullptr, "engine_create: out of host memory");
+  const int rc = engine_fill(e, params, momentum, grads, max_batch, lr, mu);
+  if (rc) {   // e.g. out of device memory at a large max_batch: give back what was allocated so far
+    char keep[sizeof(g_err)];
+    memcpy(keep, g_err, sizeof(keep));
+    dnnb200_engine_destroy(e);
+    cudaGetLastError();
+    memcpy(g_err, keep, sizeof(keep));
+    return rc;
+  }
   *out = e;
   return kOk;
 }
@@ -441,14 +498,8 @@ int dnnb200_engine_destroy(dnnb200_engine* e) {
   cudaFree(e->saved); cudaFree(e->part1); cudaFree(e->part2); cudaFree(e->img_loss); cudaFree(e->img_correct);
   cudaFree(e->eval_loss); cudaFree(e->eval_correct); cudaFree(e->d_eval_out);
   cudaFree(e->ctl); cudaFree(e->loss_ring); cudaFree(e->d_ctx);
-  cudaFreeHost(e->h_ctx_pinned);
-  if (e->ring_ready) {
-    for (int i = 0; i < dnnb200_engine::kRing; ++i) {
-      cudaEventDestroy(e->slot_ready[i]); cudaEventDestroy(e->slot_free[i]); cudaEventDestroy(e->step_done[i]);
-      cudaFree(e->d_x[i]); cudaFree(e->d_y[i]);
-    }
-    cudaStreamDestroy(e->copy_stream); cudaStreamDestroy(e->d2h_stream);
-  }
+  if (e->h_ctx_pinned) cudaFreeHost(e->h_ctx_pinned);
+  free_ring(e);
   delete e;
   return kOk;
 }
@@ -485,7 +536,8 @@ int dnnb200_engine_set_membership(dnnb200_engine* e, unsigned int active_mask, u
 
 int dnnb200_engine_set_exchange_variant(dnnb200_engine* e, int two_shot, void* stream) {
   DNN_ARG_CHECK(e, "null engine");
-  DNN_ARG_CHECK(two_shot >= 0 && two_shot <= 2, "exchange variant must be 0 (one-shot), 1 (two-shot) or 2 (NVLS)");
+  DNN_ARG_CHECK(two_shot >= 0 && two_shot <= 3,
+                "exchange variant must be 0 (one-shot), 1 (two-shot), 2 (NVLS) or 3 (one-shot, 128-byte lines)");
   DNN_ARG_CHECK(two_shot != 2 || e->h_ctx.nvls_mc != nullptr, "the NVLS variant needs dnnb200_engine_attach_nvls first");
   ctl_set_variant_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(e->ctl, (unsigned int)two_shot);
   DNN_CUDA_CHECK(cudaGetLastError());
@@ -539,14 +591,36 @@ int dnnb200_engine_set_trace(dnnb200_engine* e, long long* d_trace) {
 int dnnb200_engine_pingpong(dnnb200_engine* e, int peer, int iters, double* h_one_way_us, void* stream) {
   DNN_ARG_CHECK(e && h_one_way_us && e->group && e->group->world > 1, "pingpong needs an attached group of >= 2 ranks");
   DNN_ARG_CHECK(peer >= 0 && peer < e->group->world && peer != e->group->rank && iters > 0, "pingpong: bad peer/iters");
-  static unsigned int seq = 1000;   // every call uses fresh sequence numbers (both ranks call in lockstep)
-  int rc = launch_pingpong(e->d_ctx, peer, iters, seq, reinterpret_cast<long long*>(e->d_eval_out), (cudaStream_t)stream);
-  seq += (unsigned int)iters;
+  // every call uses fresh sequence numbers (both ranks call in lockstep, so their engines count alike)
+  int rc = launch_pingpong(e->d_ctx, peer, iters, e->pingpong_seq, reinterpret_cast<long long*>(e->d_eval_out),
+                           (cudaStream_t)stream);
+  e->pingpong_seq += (unsigned int)iters;
   if (rc) return rc;
   long long ns = 0;
   DNN_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
   DNN_CUDA_CHECK(cudaMemcpy(&ns, e->d_eval_out, sizeof(ns), cudaMemcpyDeviceToHost));
   *h_one_way_us = (double)ns / 1e3 / (2.0 * iters);
+  e->launches += 1;
+  return kOk;
+}
+
+int dnnb200_engine_ll128_probe(dnnb200_engine* e, int peer, int iters, int n_ctas, unsigned long long* h_out3,
+                               void* stream) {
+  DNN_ARG_CHECK(e && h_out3 && e->group && e->group->world > 1, "ll128_probe needs an attached group of >= 2 ranks");
+  DNN_ARG_CHECK(peer >= 0 && peer < e->group->world && peer != e->group->rank && iters > 0, "ll128_probe: bad peer/iters");
+  cudaStream_t s = (cudaStream_t)stream;
+  unsigned long long* d_out = nullptr;
+  DNN_CUDA_CHECK(cudaMalloc(&d_out, 3 * sizeof(unsigned long long)));
+  // sequence numbers far above anything a training run reaches, so a leftover flag word can never be taken for a step's
+  int rc = launch_ll128_probe(e->d_ctx, peer, iters, n_ctas, 0x40000000u + e->pingpong_seq, d_out, s);
+  e->pingpong_seq += (unsigned int)iters;
+  if (rc == kOk) {
+    cudaError_t ce = cudaStreamSynchronize(s);
+    if (ce == cudaSuccess) ce = cudaMemcpy(h_out3, d_out, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    if (ce != cudaSuccess) { set_last_error("ll128_probe: %s", cudaGetErrorString(ce)); rc = kErrCuda; }
+  }
+  cudaFree(d_out);
+  if (rc) return rc;
   e->launches += 1;
   return kOk;
 }
@@ -630,25 +704,31 @@ int dnnb200_engine_train_host(dnnb200_engine* e, const float* h_x, const int64_t
   // pinned host memory is addressable from the device (unified addressing): resolve the device view once
   float* d_losses = nullptr;
   if (h_losses) DNN_CUDA_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&d_losses), h_losses, 0));
-  // Steps are enqueued in groups of kGroup: each step still gets its own H2D copies, but the cross-stream events
-  // (inputs ready / slots free) are recorded once per group, so that inside a group nothing sits between the
-  // kernels in the stream and their programmatic dependent launches overlap.
+  // Steps are enqueued in groups of up to kGroup: the inputs of a group's steps travel in one H2D copy for the
+  // images and one for the labels (every step's inputs are still copied, inside the call, just not one DMA
+  // descriptor per step), and the cross-stream events (inputs ready / slots free) are recorded once per group, so
+  // that inside a group nothing sits between the kernels in the stream and their programmatic dependent launches
+  // overlap. The FIRST group of a call is short: the GPU starts on step 0 after two steps' worth of PCIe time
+  // instead of eight, which is most of the fixed cost of a short call.
   constexpr int G = dnnb200_engine::kGroup;
-  for (int t0 = 0; t0 < nsteps; t0 += G) {
-    const int n = nsteps - t0 < G ? nsteps - t0 : G;
+  const bool may_chain = !stream_capturing(s);   // same rule as train_device: a captured counter value would be stale
+  for (int t0 = 0; t0 < nsteps;) {
+    const int cap = t0 == 0 ? 2 : G;
+    const int n = nsteps - t0 < cap ? nsteps - t0 : cap;
     const int gslot = (int)((e->ring_uses / G) % (R / G));        // group index in the ring
     if (e->ring_uses >= (unsigned long long)R) DNN_CUDA_CHECK(cudaStreamWaitEvent(e->copy_stream, e->slot_free[gslot], 0));
-    for (int k = 0; k < n; ++k) {
-      const int slot = gslot * G + k, t = t0 + k;
-      DNN_CUDA_CHECK(cudaMemcpyAsync(e->d_x[slot], h_x + (size_t)t * B * kImgNumel, xb, cudaMemcpyHostToDevice, e->copy_stream));
-      DNN_CUDA_CHECK(cudaMemcpyAsync(e->d_y[slot], h_y + (size_t)t * B, yb, cudaMemcpyHostToDevice, e->copy_stream));
-    }
+    // a group's region has a fixed place (so the slot_free event of that place guards it whatever batch sizes the
+    // calls use); inside it the steps are packed at this call's batch size
+    float* gx = e->ring_x + (size_t)gslot * G * e->max_batch * kImgNumel;
+    long long* gy = e->ring_y + (size_t)gslot * G * e->max_batch;
+    DNN_CUDA_CHECK(cudaMemcpyAsync(gx, h_x + (size_t)t0 * B * kImgNumel, (size_t)n * xb, cudaMemcpyHostToDevice, e->copy_stream));
+    DNN_CUDA_CHECK(cudaMemcpyAsync(gy, h_y + (size_t)t0 * B, (size_t)n * yb, cudaMemcpyHostToDevice, e->copy_stream));
     DNN_CUDA_CHECK(cudaEventRecord(e->slot_ready[gslot], e->copy_stream));
     DNN_CUDA_CHECK(cudaStreamWaitEvent(s, e->slot_ready[gslot], 0));
     for (int k = 0; k < n; ++k) {
-      const int slot = gslot * G + k, t = t0 + k;
+      const int t = t0 + k;
       int n_part1 = B;
-      rc = fwd_bwd_any(e, e->d_x[slot], e->d_y[slot], B, s, &n_part1, /*chained=*/k > 0);
+      rc = fwd_bwd_any(e, gx + (size_t)k * B * kImgNumel, gy + (size_t)k * B, B, s, &n_part1, /*chained=*/may_chain && k > 0);
       if (rc) return rc;
       // The step's mean loss is written by the update kernel itself into h_losses[t] (device->host, 4 bytes).
       const int lslot = (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask);
@@ -659,7 +739,8 @@ int dnnb200_engine_train_host(dnnb200_engine* e, const float* h_x, const int64_t
       e->steps_launched += 1;
     }
     DNN_CUDA_CHECK(cudaEventRecord(e->slot_free[gslot], s));
-    e->ring_uses += G;   // a short last group still consumes a whole group of slots
+    e->ring_uses += G;   // a short group still consumes a whole group of slots
+    t0 += n;
   }
   return kOk;
 }

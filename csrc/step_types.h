@@ -1,5 +1,5 @@
 // Device-visible structs shared by the fused step kernels, the stand-alone
-// all-reduce kernel and the host runtime (engine.cpp / peer_group.cpp).
+// all-reduce kernel and the host runtime (runtime.cu).
 #pragma once
 #include <stdint.h>
 #include "layout.h"
@@ -42,7 +42,8 @@ struct StepCtl {
   unsigned int ctas_done;   // last-CTA-out counter of the update kernel
   unsigned int status;      // StepStatus bits, sticky until the host clears them
   unsigned int active_mask; // ranks configured into the exchange (bit r = rank r)
-  unsigned int two_shot;          // fused exchange variant: 0 one-shot (membership-safe), 1 two-shot (static membership)
+  unsigned int two_shot;          // fused exchange variant: 0 one-shot with 16-byte lines, 3 one-shot with 128-byte lines
+                                  // (both membership-safe), 1 two-shot, 2 NVLS (both need a static membership)
   unsigned int updates_done;      // update kernels completed on this rank, ever (never reset): the next step's
                                   // forward/backward kernel spins on it instead of waiting for grid completion
   unsigned int divisor_override;  // 0: divide by the ranks present; else by this (parent/children parity mode:

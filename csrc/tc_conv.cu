@@ -330,12 +330,8 @@ tc_conv2_dgrad_kernel(const float* __restrict__ w, const float* __restrict__ y, 
 
 int launch_tc_conv2_dgrad(const float* w, const float* y, const unsigned char* idx, const float* dy, float* dx, int N,
                           cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    DNN_CUDA_CHECK(cudaFuncSetAttribute(tc_conv2_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)DgradCfg::kSmemBytes));
-    attr_set = true;
-  }
+  static PerDeviceOnce attr_set;
+  if (int rc = ensure_max_dynamic_smem(attr_set, tc_conv2_dgrad_kernel, DgradCfg::kSmemBytes)) return rc;
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -349,12 +345,9 @@ template <int CI, int HIN, int CO>
 static int launch_tc_conv_t(const float* x, const float* w, const float* b, float* y, unsigned char* idx, int N,
                             cudaStream_t s) {
   using C = ConvCfg<CI, HIN, CO>;
-  static bool attr_set = false;
+  static PerDeviceOnce attr_set;
   auto kern = tc_conv_relu_pool_fwd_kernel<CI, HIN, CO>;
-  if (!attr_set) {
-    DNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::kSmemBytes));
-    attr_set = true;
-  }
+  if (int rc = ensure_max_dynamic_smem(attr_set, kern, C::kSmemBytes)) return rc;
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -377,11 +370,8 @@ int launch_tc_conv_relu_pool_fwd(const float* x, const float* w, const float* b,
 int launch_tc_gemm_probe(const float* A, const float* B, float* D, int K, cudaStream_t s) {
   DNN_ARG_CHECK(K >= 8 && K % 8 == 0 && K <= 256, "tc_gemm_probe: K must be a multiple of 8 in [8, 256]");
   const size_t smem = (size_t)(K / 4) * (128 + 16) * 16;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DNN_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-    attr_set = true;
-  }
+  static PerDeviceOnce attr_set;
+  if (int rc = ensure_max_dynamic_smem(attr_set, tc_gemm_probe_kernel, 160 * 1024)) return rc;
   tc_gemm_probe_kernel<<<1, 128, smem, s>>>(A, B, D, K);
   DNN_CUDA_CHECK(cudaGetLastError());
   return kOk;

@@ -123,13 +123,10 @@ tc_linear_fwd_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_co
 template <int BN>
 static int launch_tc_linear_t(const float* x, const float* w, const float* b, float* y, int N, int M, int K, int relu,
                               cudaStream_t s) {
-  static bool attr_set = false;
+  static PerDeviceOnce attr_set;
   auto kern = tc_linear_fwd_kernel<BN>;
   const size_t smem = sizeof(LinSmem<BN>) + 1024;
-  if (!attr_set) {
-    DNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
-  }
+  if (int rc0 = ensure_max_dynamic_smem(attr_set, kern, smem)) return rc0;
   CUtensorMap tw, tx;
   int rc = make_tmap_2d(&tw, w, M, K, kLinM);
   if (rc) return rc;

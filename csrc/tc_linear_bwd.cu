@@ -251,13 +251,10 @@ tc_linear_dw_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_co
 // ---------------------------------------------------------------------------------------------
 template <int BN>
 static int launch_dx_t(const CUtensorMap& tw, const float* dyp, float* dx, int N, int M, int K, cudaStream_t s) {
-  static bool attr_set = false;
+  static PerDeviceOnce attr_set;
   auto kern = tc_linear_dx_kernel<BN>;
   const size_t smem = sizeof(DxSmem<BN>) + 1024;
-  if (!attr_set) {
-    DNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
-  }
+  if (int rc0 = ensure_max_dynamic_smem(attr_set, kern, smem)) return rc0;
   CUtensorMap tdy;
   const int rc = make_tmap_2d(&tdy, dyp, N, M, BN);
   if (rc) return rc;
@@ -289,12 +286,9 @@ int launch_tc_linear_bwd(const float* x, const float* w, const float* y, const f
   }
 
   {
-    static bool attr_set = false;
+    static PerDeviceOnce attr_set;
     const size_t smem = sizeof(DwSmem) + 1024;
-    if (!attr_set) {
-      DNN_CUDA_CHECK(cudaFuncSetAttribute(tc_linear_dw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      attr_set = true;
-    }
+    if (int rc0 = ensure_max_dynamic_smem(attr_set, tc_linear_dw_kernel, smem)) return rc0;
     CUtensorMap tdy, tx;
     int rc = make_tmap_2d(&tdy, dmat, N, M, 32, /*mn_major=*/true);
     if (rc) return rc;

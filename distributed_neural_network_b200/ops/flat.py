@@ -6,7 +6,7 @@ see a single contiguous vector. Every tensor starts on a 128-byte boundary
 (32 floats) so kernels can use 16-byte vector loads; the gaps stay zero forever
 (their gradient and momentum are never written).
 
-The same table is compiled into csrc/layout.h -- tests/test_flat.py checks that
+The same table is compiled into csrc/layout.h -- tests/test_flat_and_model.py checks that
 the two agree.
 """
 from __future__ import annotations

@@ -53,6 +53,16 @@ class Ctl(C.Structure):
     ]
 
 
+EXCHANGE_VARIANTS = {"one-shot": 0, "two-shot": 1, "nvls": 2, "one-shot-128": 3}
+
+
+def variant_id(v) -> int:
+    """Exchange variant as the C ABI numbers it (include/dnnb200.h); accepts the name, the number or a bool."""
+    if isinstance(v, str):
+        return EXCHANGE_VARIANTS[v]
+    return int(v)
+
+
 def lib_path() -> Path:
     return _LIB_PATH
 
@@ -287,10 +297,9 @@ class Engine:
                                                        _stream()))
 
     def set_exchange_variant(self, variant) -> None:
-        """Fused exchange: 0/False one-shot (tolerates ranks leaving), 1/True two-shot, 2/"nvls" in-switch reduction
-        (the last two need a static membership)."""
-        v = 2 if variant == "nvls" else int(variant)
-        _check(require().dnnb200_engine_set_exchange_variant(self._h, v, _stream()))
+        """Fused exchange: 0/False/"one-shot" (16-byte lines) and 3/"one-shot-128" (128-byte lines) tolerate ranks
+        leaving; 1/True/"two-shot" and 2/"nvls" (in-switch reduction) need a static membership."""
+        _check(require().dnnb200_engine_set_exchange_variant(self._h, variant_id(variant), _stream()))
 
     def set_divisor(self, divisor: int) -> None:
         """0 = divide exchanged sums by the ranks present; n = divide by n."""
@@ -378,10 +387,18 @@ class Engine:
         return float(out[0]), int(out[1])
 
     def allreduce(self, inp: torch.Tensor, out: Optional[torch.Tensor], mode: int = 0, two_shot=False) -> None:
-        """``two_shot``: False/0 one-shot, True/1 two-shot, 2 or "nvls" the in-switch (multimem) variant."""
+        """``two_shot`` names the variant: False/0 one-shot, True/1 two-shot, 2/"nvls" in-switch (multimem),
+        3/"one-shot-128" one-shot with 128-byte lines."""
         _f32(inp, "in")
-        variant = 2 if two_shot == "nvls" else int(two_shot)
-        _check(require().dnnb200_engine_allreduce(self._h, _p(inp), _p(out), inp.numel(), mode, variant, _stream()))
+        _check(require().dnnb200_engine_allreduce(self._h, _p(inp), _p(out), inp.numel(), mode, variant_id(two_shot),
+                                                  _stream()))
+
+    def ll128_probe(self, peer: int, iters: int = 2000, n_ctas: int = 32):
+        """Ping-pong of 128-byte lines with rank ``peer`` (which must call it too): returns (torn words -- must be 0,
+        microseconds per round trip, gave_up)."""
+        out = (C.c_ulonglong * 3)()
+        _check(require().dnnb200_engine_ll128_probe(self._h, peer, iters, n_ctas, out, _stream()))
+        return int(out[0]), float(out[1]) / 1e3 / iters, bool(out[2])
 
     def attach_nvls(self, local_buf: torch.Tensor, multicast_ptr: int) -> None:
         _f32(local_buf, "local_buf")
@@ -417,4 +434,4 @@ def vr_allreduce(engines: Sequence[Engine], ins: Sequence[Optional[torch.Tensor]
     eh = (C.c_void_p * n)(*[e._h for e in engines])
     ip = (C.c_void_p * n)(*[(t.data_ptr() if t is not None else 0) for t in ins])
     op = (C.c_void_p * n)(*[(t.data_ptr() if t is not None else 0) for t in outs])
-    _check(require().dnnb200_vr_allreduce(eh, n, ip, op, count, mode, int(two_shot), _stream()))
+    _check(require().dnnb200_vr_allreduce(eh, n, ip, op, count, mode, variant_id(two_shot), _stream()))

@@ -15,7 +15,7 @@ from __future__ import annotations
 
 import time
 from dataclasses import dataclass, field
-from typing import Optional, Set
+from typing import Dict, Optional, Set, Tuple
 
 import numpy as np
 
@@ -55,9 +55,18 @@ class Membership:
             return True
         return False
 
-    def donor(self) -> int:
-        """The rank a returning member copies its state from."""
-        return min(self.active)
+    def donor(self, progress: Optional[Dict[int, Tuple[bool, int]]] = None) -> int:
+        """The rank a returning member copies its state from.
+
+        ``progress`` maps rank -> (dropped this epoch, steps it completed this epoch). A rank that stayed for the
+        whole epoch wins; if EVERY trainer dropped out at some point, the one that trained longest does (so the
+        epoch's progress is kept, not the state of whoever happens to have the lowest rank number)."""
+        if not progress:
+            return min(self.active)
+        cands = [r for r in progress if r in self.active or progress[r][0]]
+        stayed = [r for r in cands if not progress[r][0]]
+        pool = stayed or cands
+        return min(pool, key=lambda r: (-progress[r][1], r))
 
 
 @dataclass

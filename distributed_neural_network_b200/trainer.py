@@ -43,6 +43,7 @@ from .parallel.membership import FailureSimulator, Membership
 from .utils import checkpoint as ckpt
 from .utils import data as D
 from .utils import logs
+from .utils.tracing import nvtx_range
 
 
 @dataclass
@@ -68,7 +69,11 @@ class TrainConfig:
     save: Optional[str] = None
     resume: Optional[str] = None
     input_pipeline: str = "device"    # device: dataset resident in HBM; host: per-step H2D from pinned memory
-    allreduce_variant: str = "auto"        # auto | one-shot | two-shot (see _exchange_two_shot)
+    allreduce_variant: str = "auto"        # auto (measured at start-up) | one-shot | one-shot-128 | two-shot | nvls
+    calibrate_exchange: bool = True        # auto: time every usable variant on this world size and take the fastest
+    calibrate_steps: int = 300
+    exchange_timing: bool = True           # per-epoch "allreduce_us" in the JSONL (the reference books its
+                                           # mpi_communication_time_children, data_parallelism_train.py:209-213)
     peer_timeout_s: float = 30.0
     eval_batch_size: Optional[int] = None  # the reference evaluates with --batch-size too (Q11)
     neptune: bool = False
@@ -79,6 +84,21 @@ class TrainConfig:
             raise ValueError(f"unknown sync mode {self.sync_mode!r}")
         self.lr, self.momentum = float(self.lr), float(self.momentum)   # the reference forgets the casts (Q5)
         self.batch_size, self.epochs = int(self.batch_size), int(self.epochs)
+
+
+def exchange_bytes_per_direction(variant: int, world: int) -> int:
+    """Bytes one GPU sends (= receives) over NVLink per step for the flat gradient, per exchange variant: the
+    numerator of the exchange roofline (bytes over NVLink at 900 GB/s per direction, BASELINE.json)."""
+    vec = L.FLAT_NUMEL * 4
+    if world <= 1:
+        return 0
+    return {0: (world - 1) * vec * 2,                    # one-shot, 16-byte lines carry 8 bytes of payload
+            1: 2 * (world - 1) * vec * 2 // world,       # two-shot: reduce-scatter + all-gather, 16-byte lines
+            2: (world - 1) * vec,                        # NVLS: every peer's ld_reduce pulls my vector once
+            3: (world - 1) * 122 * 17 * 128}[int(variant)]   # one-shot, 128-byte lines (31 values + flag), 17 per slice
+
+
+NVLINK_BYTES_PER_S = 900e9   # per direction per GPU (NVLink 5)
 
 
 def reference_global_avg_loss(total_losses: float, n_children: int) -> float:
@@ -124,6 +144,10 @@ class Trainer:
         self.group: Optional[native.Group] = None
         self.first_step = True
         self.nvls_ok = False
+        self._utrace: Optional[torch.Tensor] = None
+        self.last_exchange_us: Optional[float] = None  # median exposed exchange per step over the epoch's last steps
+        self.exchange_choice: Optional[str] = None     # measured winner (calibrate_exchange)
+        self.exchange_table: Dict = {}
         if self.device.type == "cuda":
             self.engine = native.Engine(self.model.flat_params, self.momentum, None, max(cfg.batch_size, 1),
                                         cfg.lr, cfg.momentum)
@@ -144,7 +168,11 @@ class Trainer:
                                         self.rank)
         self.dropped = False
         self.saw_timeout = False
+        self.steps_this_epoch = 0
         self.history: List[Dict] = []
+        if (self.engine is not None and self.world > 1 and cfg.sync_mode == "step-allreduce"
+                and cfg.allreduce_variant == "auto" and cfg.calibrate_exchange and not cfg.reference_topology):
+            self.calibrate_exchange()
 
     # ------------------------------------------------------------------ setup helpers
     def _pick_device(self) -> torch.device:
@@ -168,38 +196,106 @@ class Trainer:
         if self.device.type == "cuda":
             torch.cuda.synchronize()
 
+    def _can_drop(self) -> bool:
+        return self.cfg.failure_mode == "drop" and self.cfg.failure_probability > 0
+
+    def _usable_variants(self) -> List[str]:
+        """Exchange variants this run may use. The one-shot forms tolerate ranks leaving mid-epoch (leave markers);
+        two-shot has static slice ownership and the NVSwitch adds EVERY member of the multicast group, so both need
+        a membership that cannot change (no drop-mode failure drill, every rank a stepping trainer for NVLS)."""
+        names = ["one-shot", "one-shot-128"]
+        if not self._can_drop():
+            names.append("two-shot")
+            if self.nvls_ok and len(self.membership.active) == self.world:
+                names.append("nvls")
+        return names
+
     def _exchange_variant(self) -> int:
-        """0 one-shot, 1 two-shot, 2 NVLS for the exchange fused into the update kernel."""
-        can_drop = self.cfg.failure_mode == "drop" and self.cfg.failure_probability > 0
-        # the switch adds EVERY member of the multicast group: all ranks must be stepping trainers
-        if (self.cfg.allreduce_variant == "nvls" and self.nvls_ok and not can_drop
-                and len(self.membership.active) == self.world):
-            return 2
-        return 1 if self._exchange_two_shot() else 0
+        """Variant of the exchange fused into the update kernel (numbering of include/dnnb200.h: 0 one-shot, 1 two-shot,
+        2 NVLS, 3 one-shot with 128-byte lines)."""
+        v = self.cfg.allreduce_variant
+        usable = self._usable_variants()
+        if v != "auto":
+            if v == "nvls" and not self.nvls_ok:
+                raise RuntimeError("--allreduce-variant nvls: NVLink multicast is not available to this job")
+            return native.variant_id(v if v in usable else "one-shot")
+        if self.exchange_choice in usable:
+            return native.variant_id(self.exchange_choice)
+        # not measured (calibration switched off): one hop while the 128-byte lines keep the traffic below the
+        # link time of the other ranks, measured winner of profiles/exchange_table_n*.json
+        return native.variant_id("one-shot-128")
 
     def _exchange_two_shot(self) -> bool:
-        """Variant of the fused gradient exchange. One-shot (everyone pushes to everyone) has one latency hop
-        but moves (W-1) x the vector per GPU; two-shot (slice owners reduce, then broadcast) has two hops and
-        moves 2(W-1)/W x. Measured on 8xB200 (profiles/): one-shot wins at 2 GPUs, they tie at 4, two-shot wins at 8.
-        Two-shot needs a static membership, so the failure drill that drops ranks always uses one-shot."""
-        v = self.cfg.allreduce_variant
-        can_drop = self.cfg.failure_mode == "drop" and self.cfg.failure_probability > 0
-        if v == "two-shot":
-            return not can_drop
-        if v == "one-shot" or can_drop:
-            return False
-        return len(self.membership.active) >= 6
+        return self._exchange_variant() == 1
 
     def _standalone_variant(self):
-        """Variant of the stand-alone all-reduce (parameter averaging): 0 one-shot, 1 two-shot, 2 NVLS."""
+        """Variant of the stand-alone all-reduce (parameter averaging once per epoch; not on the step path)."""
         v = self.cfg.allreduce_variant
         if v == "nvls":
             if not self.nvls_ok:
                 raise RuntimeError("--allreduce-variant nvls: NVLink multicast is not available to this job")
             return 2
-        if v == "two-shot" or (v == "auto" and self.world >= 6):
-            return 1
-        return 0
+        if v == "auto":
+            return native.variant_id(self.exchange_choice) if self.exchange_choice in ("one-shot", "one-shot-128",
+                                                                                       "two-shot") else 3
+        return native.variant_id(v)
+
+    @torch.no_grad()
+    def calibrate_exchange(self, steps: Optional[int] = None) -> Dict:
+        """Measure, on THIS world size and batch size, every usable exchange variant inside the real step
+        (forward/backward + update kernel, device-timed, max over ranks) and keep the fastest. The message is
+        the 248 KB flat gradient whatever the batch size, so it is latency-bound and the best variant depends on
+        the number of ranks, not on a formula: the table is measured, not assumed. Collective: every rank calls
+        it at the same point. Parameters and momentum are restored afterwards; only the step counter moves on."""
+        if self.engine is None or self.world == 1:
+            return {}
+        steps = int(steps or self.cfg.calibrate_steps)
+        B, eng = self.cfg.batch_size, self.engine
+        with nvtx_range("calibrate/exchange variants"):
+            return self._calibrate_exchange(steps, B, eng)
+
+    def _calibrate_exchange(self, steps: int, B: int, eng) -> Dict:
+        keep_p, keep_m = self.model.flat_params.detach().clone(), self.momentum.clone()
+        g = torch.Generator(device="cpu").manual_seed(4242 + self.rank)
+        nb = 64
+        x = (torch.rand((nb, B, 3, 32, 32), generator=g) * 2 - 1).to(self.device)
+        y = torch.randint(0, 10, (nb, B), generator=g).to(self.device)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        table: Dict[str, float] = {}
+        self.engine.set_membership(self.membership.mask, int(self.cfg.peer_timeout_s * 1e9))
+        stepping = self.is_trainer and self.rank in self.membership.active   # a parent that never trains only listens
+        for name in (self._usable_variants() if stepping else []):
+            eng.set_exchange_variant(name)
+            eng.train_device(x, y)                       # warm-up; also the device-side alignment of the ranks
+            e0.record()
+            done = 0
+            while done < steps:
+                c = min(nb, steps - done)
+                eng.train_device(x[:c], y[:c])
+                done += c
+            e1.record()
+            torch.cuda.synchronize()
+            table[name] = e0.elapsed_time(e1) * 1e3 / steps
+        per_rank = [t for t in self.comm.allgather(table) if t]
+        worst = {k: max(t[k] for t in per_rank) for k in per_rank[0]}    # a step is as slow as its slowest rank
+        self.exchange_choice = min(worst, key=worst.get)
+        self.exchange_table = {"world": self.world, "batch_size": B, "steps": steps, "message_bytes": L.FLAT_NUMEL * 4,
+                               "us_per_step_max_over_ranks": {k: round(v, 3) for k, v in worst.items()},
+                               "chosen": self.exchange_choice}
+        ctl = eng.read_ctl()
+        if ctl.status & 1:
+            self.saw_timeout = True
+        self.model.flat_params.copy_(keep_p)
+        self.momentum.copy_(keep_m)
+        eng.reset_loss()
+        self._sync()
+        self.comm.barrier()
+        self._apply_membership()
+        if self.rank == 0:
+            self.jsonl.write(event="exchange_calibration", **self.exchange_table)
+            self._log(f"exchange variants, us/step at {self.world} ranks: {self.exchange_table['us_per_step_max_over_ranks']}"
+                      f" -> {self.exchange_choice}")
+        return self.exchange_table
 
     def _apply_membership(self, local_only: bool = False) -> None:
         """Program the exchange kernels: who is in the sum, how long to wait for a silent peer."""
@@ -271,15 +367,32 @@ class Trainer:
         steps = len(shard) // B
         x, y, tail_xy = D.epoch_tensor(shard, B, shuffle=True, generator=self.gen)
         run_steps = steps if drop_at is None else min(steps, drop_at)
+        # exchange timing: the update kernel stamps the LAST steps of the epoch (at most 256), the rest runs untraced
+        n_tail = min(run_steps, 256) if (self.cfg.exchange_timing and not local_sgd and self.world > 1
+                                         and self.cfg.input_pipeline != "host") else 0
         if self.cfg.input_pipeline == "host":
-            # per-step H2D copies from pinned memory through the engine's 4-slot ring
+            # per-step H2D copies from pinned memory through the engine's 32-slot ring
             if run_steps:
                 eng.train_host(x[:run_steps].pin_memory(), y[:run_steps].pin_memory(), None)
         elif run_steps:
-            eng.train_device(x[:run_steps], y[:run_steps])
+            if run_steps > n_tail:
+                eng.train_device(x[:run_steps - n_tail], y[:run_steps - n_tail])
+            if n_tail:
+                if self._utrace is None:
+                    self._utrace = torch.zeros(1024 * 122 * 8, dtype=torch.int64, device=self.device)
+                eng.set_update_trace(self._utrace)
+                eng.set_debug_flags(4)
+                eng.train_device(x[run_steps - n_tail:run_steps], y[run_steps - n_tail:run_steps])
+                eng.set_debug_flags(0)
+                eng.set_update_trace(None)
+                end = int(eng.read_ctl().step)
+                u = self._utrace.view(1024, 122, 8)[[(end - n_tail + k) % 1024 for k in range(n_tail)]].cpu().numpy()
+                wait = np.sort((u[:, :, 3].max(axis=1) - u[:, :, 2].max(axis=1)) / 1e3)
+                self.last_exchange_us = float(wait[len(wait) // 2])
         if tail_xy is not None and drop_at is None:
             # the trailing short batch, as DataLoader(drop_last=False) yields it
             eng.step(tail_xy[0].to(self.device), tail_xy[1].to(self.device))
+        self.steps_this_epoch = run_steps
         if drop_at is not None:
             eng.leave()
             self.dropped = True
@@ -317,6 +430,7 @@ class Trainer:
                 g = model.flat_grads
             Fn.sgd_momentum_(model.flat_params.data, g, self.momentum, cfg.lr, cfg.momentum, self.first_step)
             self.first_step = False
+        self.steps_this_epoch = nb
         if drop_at is not None:
             self.dropped = True
         return total, nb
@@ -378,7 +492,8 @@ class Trainer:
         """Membership epoch: agree on who is present; returning ranks adopt a survivor's state."""
         if self.world == 1:
             return
-        status = self.comm.allgather({"rank": self.rank, "dropped": self.dropped, "timeout": self.saw_timeout})
+        status = self.comm.allgather({"rank": self.rank, "dropped": self.dropped, "timeout": self.saw_timeout,
+                                      "steps": self.steps_this_epoch, "trainer": self.is_trainer})
         if any(s["timeout"] for s in status) and self.cfg.sync_mode == "step-allreduce":
             # A peer was given up on mid-epoch (unannounced stall): different ranks may have summed different sets
             # for some slices, so the replicas can differ in the last bits. Re-establish identical replicas by
@@ -386,24 +501,32 @@ class Trainer:
             self._log(f"[rank {self.rank}] re-synchronising replicas after a peer timeout")
             self._resync_state()
             self.saw_timeout = False
-        came_back = [s["rank"] for s in status if s["dropped"]]
+        dropped = [s["rank"] for s in status if s["dropped"]]
+        if not dropped:
+            return
+        # whose state survives: a trainer that stayed all epoch, else (everybody dropped) the one that trained longest
+        donor = self.membership.donor({s["rank"]: (s["dropped"], s["steps"]) for s in status if s["trainer"]})
+        if donor in dropped:
+            self._log(f"[rank {self.rank}] every trainer dropped out this epoch; rank {donor} trained longest and "
+                      f"becomes the donor")
+        came_back = [r for r in dropped if r != donor]
         for r in came_back:
             self.membership.leave(r)
-        if not came_back:
-            return
-        donor = self.membership.donor()
         state = None
         if self.rank == donor:
             step = self.engine.read_ctl().step if self.engine is not None else 0
             state = (self.model.flat_params.detach().cpu(), self.momentum.detach().cpu(), int(step))
         state = self.comm.bcast(state, root=donor)
-        if self.dropped:
+        if self.dropped and self.rank != donor:
             self.model.flat_params.copy_(state[0].to(self.device))
             self.momentum.copy_(state[1].to(self.device))
             if self.engine is not None:
                 self.engine.rejoin(state[2])
                 self._sync()
-            self.dropped = False
+        if self.dropped and self.rank == donor and self.engine is not None:
+            self.engine.rejoin(state[2])   # clears the donor's own leave marker; its step counter is the reference
+            self._sync()
+        self.dropped = False
         for r in came_back:
             self.membership.join(r)
         self.comm.barrier()  # nobody steps before every marker is cleared
@@ -441,7 +564,8 @@ class Trainer:
         for epoch in range(self.start_epoch, cfg.epochs):
             if self.rank == 0:
                 self._log("Starting epoch ", epoch)
-            self._epoch_boundary()
+            with nvtx_range(f"membership/epoch {epoch}"):
+                self._epoch_boundary()
             ev = self.failure.draw(steps_per_epoch) if cfg.failure_probability > 0 else None
             drop_at = None
             if ev is not None and cfg.failure_mode == "sleep":
@@ -464,7 +588,7 @@ class Trainer:
                 ev0 = ev1 = None
                 if self.device.type == "cuda":
                     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                with self.timers.add("training_time", self._sync):
+                with self.timers.add("training_time", self._sync), nvtx_range(f"train/epoch {epoch}"):
                     if ev0 is not None:
                         ev0.record()
                     total_loss, n_batches = self.train_epoch(shard, drop_at)
@@ -484,11 +608,12 @@ class Trainer:
                 if self.rank == 0:
                     self._log("* Averaging models...")
                 tname = "mpi_communication_time_parent" if self.rank == 0 else "mpi_communication_time_children"
-                with self.timers.add(tname, self._sync):
+                with self.timers.add(tname, self._sync), nvtx_range(f"average/epoch {epoch}"):
                     self.average_parameters()
 
             # loss bookkeeping: true mean over all batches of all trainers
-            stats = self.comm.allgather((total_loss, n_batches, t_dev, len(shard) if shard is not None else 0))
+            stats = self.comm.allgather((total_loss, n_batches, t_dev, len(shard) if shard is not None else 0,
+                                         self.last_exchange_us))
             sum_loss = sum(s[0] for s in stats)
             sum_batches = sum(s[1] for s in stats)
             mean_loss = sum_loss / max(1, sum_batches)
@@ -500,11 +625,20 @@ class Trainer:
                 imgs = sum(s[3] for s in stats)
                 rec.update(train_seconds_device_max=t_max, images_per_s=imgs / t_max if t_max > 0 else None,
                            step_us=1e6 * t_max / max(1, max(s[1] for s in stats)))
+            xus = [s[4] for s in stats if s[4] is not None]
+            if xus and cfg.sync_mode == "step-allreduce":
+                # exposed gradient exchange per step (max over ranks of the per-rank median) and what fraction of the
+                # NVLink roofline that is: bytes per direction at 900 GB/s over the measured time
+                variant = self._exchange_variant()
+                roof_us = exchange_bytes_per_direction(variant, len(self.membership.active)) / NVLINK_BYTES_PER_S * 1e6
+                rec.update(allreduce_us=max(xus), exchange_variant=[k for k, v in native.EXCHANGE_VARIANTS.items()
+                                                                    if v == variant][0],
+                           exchange_roofline_frac=roof_us / max(xus) if max(xus) > 0 else None)
             if self.rank == 0:
                 self._log(f"Global Average Training Loss: {mean_loss}")
                 self.run["train/loss"].append(mean_loss)
                 self._log("evaluating model")
-                with self.timers.add("evaluation_time", self._sync):
+                with self.timers.add("evaluation_time", self._sync), nvtx_range(f"eval/epoch {epoch}"):
                     val_loss, val_acc = self.evaluate(test)
                 self.run["val/loss"].append(val_loss)
                 self.run["val/acc"].append(val_acc)

@@ -47,7 +47,7 @@ def add_new_flags(p: argparse.ArgumentParser, sync_default: str) -> None:
     g.add_argument("--save", default=None, help="write the state_dict (reference format) here after every epoch")
     g.add_argument("--resume", default=None, help="load a state_dict (plus the .resume sidecar if present)")
     g.add_argument("--input-pipeline", default="device", choices=["device", "host"])
-    g.add_argument("--allreduce-variant", default="auto", choices=["auto", "one-shot", "two-shot", "nvls"],
+    g.add_argument("--allreduce-variant", default="auto", choices=["auto", "one-shot", "one-shot-128", "two-shot", "nvls"],
                    help="gradient exchange: one-shot push, two-shot (owner-reduce + broadcast), chosen by world size, or "
                         "(parameter averaging only) nvls = in-switch reduction over NVLink multicast")
     g.add_argument("--neptune", action="store_true", help="log to Neptune (needs NEPTUNE_API_TOKEN in the environment)")

@@ -120,7 +120,12 @@ int dnnb200_engine_set_membership(dnnb200_engine* e, unsigned int active_mask, u
                                   void* stream);
 /* variant of the exchange fused into the update kernel: 0 = one-shot (every rank pushes to every rank; tolerates
  * ranks leaving mid-epoch), 1 = two-shot (slice owners reduce and broadcast; static membership only),
- * 2 = NVLS (multimem.st flags + multimem.ld_reduce in the NVSwitch; static membership, needs attach_nvls) */
+ * 2 = NVLS (multimem.st flags + multimem.ld_reduce in the NVSwitch; static membership, needs attach_nvls),
+ * 3 = one-shot with 128-byte lines (31 values + 1 flag word per warp-wide store instead of 2 + 2 per 16-byte
+ * line: half the NVLink bytes, same single hop, same membership rules as 0).
+ * A peer that stays silent longer than timeout_ns: 0 and 3 leave it out and divide by the ranks present; 1 the
+ * owner leaves it out and rescales, a rank with a silent owner keeps its own gradient for that slice; 2 the
+ * slice falls back to this rank's own gradient. Always flagged in dnnb200_ctl::status. */
 int dnnb200_engine_set_exchange_variant(dnnb200_engine* e, int two_shot, void* stream);
 /* 0 = divide the exchanged sum by the number of ranks present (default); n = divide by n */
 int dnnb200_engine_set_divisor(dnnb200_engine* e, unsigned int divisor, void* stream);
@@ -155,8 +160,9 @@ int dnnb200_engine_step(dnnb200_engine* e, const float* x, const int64_t* y, int
 /* nsteps steps over device-resident batches x[nsteps][B][3][32][32], y[nsteps][B]: one native loop,
  * no per-step Python (the whole dataset fits in HBM many times over) */
 int dnnb200_engine_train_device(dnnb200_engine* e, const float* x, const int64_t* y, int B, int nsteps, void* stream);
-/* nsteps steps fed from PINNED host memory: per step an async H2D copy of that step's
- * inputs (32-slot device ring on a copy stream, events every 8 steps) and the two kernels; the update kernel writes
+/* nsteps steps fed from PINNED host memory: every step's inputs are copied host->device inside the call (32-slot
+ * device ring on a copy stream; the steps of a group -- 2 for the first group of a call, then 8 -- share one copy for
+ * their images and one for their labels and one pair of events) and run through the two kernels; the update kernel writes
  * the step's mean loss straight into h_losses[t] (pinned host memory, 4 bytes device->host per
  * step). Returns after everything is enqueued; the caller synchronises `stream` before reading
  * h_losses. */
@@ -194,7 +200,8 @@ int dnnb200_batch_grad_noalloc(const float* params, const float* x, const int64_
 /* peer-memory all-reduce of a flat vector (n % 4 == 0, n <= FLAT_NUMEL).
  * mode 0: out = mean(in); mode 1: fused SGD-momentum on the engine's params with g = mean(in)
  * (out may be NULL). variant (argument `two_shot`): 0 one-shot push, 1 two-shot (owner-reduce + broadcast),
- * 2 NVLS (in-switch reduction through a multicast mapping; needs dnnb200_engine_attach_nvls). */
+ * 2 NVLS (in-switch reduction through a multicast mapping; needs dnnb200_engine_attach_nvls),
+ * 3 one-shot push with 128-byte lines. */
 int dnnb200_engine_allreduce(dnnb200_engine* e, const float* in, float* out, int n, int mode, int two_shot,
                              void* stream);
 
@@ -207,6 +214,13 @@ int dnnb200_engine_attach_nvls(dnnb200_engine* e, float* local_buf, float* multi
 /* latency probe: `iters` round trips of one 16-byte LL line with rank `peer` (which must make the matching call);
  * returns the one-way store->visible latency over peer memory in microseconds. Synchronises. */
 int dnnb200_engine_pingpong(dnnb200_engine* e, int peer, int iters, double* h_one_way_us, void* stream);
+
+/* probe of the 128-byte-line assumption of exchange variant 3 with rank `peer` (which must make the matching
+ * call): n_ctas x 8 warps play ping-pong for `iters` rounds with one warp-wide 128-byte store per line and check
+ * every line that arrives. h_out3 = {words that did not belong to the flag they arrived with (must be 0), ns for
+ * all rounds, 1 if a wait was given up after 2 s}. Synchronises; allocates 24 bytes for the duration of the call. */
+int dnnb200_engine_ll128_probe(dnnb200_engine* e, int peer, int iters, int n_ctas, unsigned long long* h_out3,
+                               void* stream);
 
 /* membership epoch: announce that this rank stops taking part after the steps
  * already enqueued; peers divide by the survivors from then on */

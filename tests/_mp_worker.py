@@ -1,5 +1,6 @@
 """Worker for the multi-process CPU tests: trains a few epochs and dumps the final state."""
 import json
+import os
 import sys
 from pathlib import Path
 
@@ -16,9 +17,11 @@ def main():
     cfg = TrainConfig(device=kw.pop("device", "cpu"), synthetic=True, quiet=True, sync_mode=mode,
                       log_dir=out_dir + "/log", **kw)
     tr = Trainer(cfg)
+    if os.environ.get("DNNB200_PROVIDER_PROBE"):       # which control-plane provider did bootstrap.init() pick?
+        Path(os.environ["DNNB200_PROVIDER_PROBE"] + f".{tr.rank}").write_text(tr.comm.provider)
     hist = tr.fit()
     torch.save({"flat": tr.model.flat_params.detach().cpu(), "history": hist, "rank": tr.rank,
-                "timers": tr.timers.__dict__}, f"{out_dir}/rank{tr.rank}.pt")
+                "timers": tr.timers.__dict__, "exchange_table": tr.exchange_table}, f"{out_dir}/rank{tr.rank}.pt")
     tr.close()
     tr.comm.close()
 

@@ -46,13 +46,16 @@ def _rel(a, b):
     return ((a - b).abs().max() / b.abs().max().clamp_min(1e-9)).item()
 
 
-@pytest.mark.parametrize("two_shot", [False, True])
+VARIANTS = ["one-shot", "two-shot", "one-shot-128"]
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_vr_step_replicas_identical_and_match_oracle(world, two_shot):
+def test_vr_step_replicas_identical_and_match_oracle(world, variant):
     B = 16
     base, models, groups, engines = _make(world, B=B, seed=world)
     for e in engines:
-        e.set_exchange_variant(two_shot)
+        e.set_exchange_variant(variant)
     ref = copy.deepcopy(base)
     opt = torch.optim.SGD(ref.parameters(), lr=0.01, momentum=0.9)
     for step in range(4):
@@ -71,9 +74,12 @@ def test_vr_step_replicas_identical_and_match_oracle(world, two_shot):
     for g in groups: g.close()
 
 
-def test_membership_epoch_leave_and_rejoin():
+@pytest.mark.parametrize("variant", ["one-shot", "one-shot-128"])
+def test_membership_epoch_leave_and_rejoin(variant):
     world, B = 4, 8
     base, models, groups, engines = _make(world, B=B, seed=99)
+    for e in engines:
+        e.set_exchange_variant(variant)
     ref = copy.deepcopy(base)
     opt = torch.optim.SGD(ref.parameters(), lr=0.01, momentum=0.9)
 
@@ -110,7 +116,7 @@ def test_membership_epoch_leave_and_rejoin():
     for g in groups: g.close()
 
 
-@pytest.mark.parametrize("two_shot", [False, True])
+@pytest.mark.parametrize("two_shot", VARIANTS)
 @pytest.mark.parametrize("world", [2, 8])
 def test_vr_allreduce_mean(world, two_shot):
     base, models, groups, engines = _make(world, seed=5)
@@ -151,17 +157,44 @@ def test_vr_allreduce_fused_sgd_equals_unfused():
     for g in groups: g.close()
 
 
-def test_timeout_marks_status_instead_of_hanging():
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_timeout_marks_status_and_applies_a_clean_step(variant):
+    """A peer that neither steps nor announces that it left: the waiting rank must give up (not hang), say so in
+    its status word, and apply a step that is a true mean over the ranks that DID arrive -- here itself alone.
+    For two-shot that covers both halves: the slices rank 0 owns (missing contribution left out, sum rescaled)
+    and the slices the silent rank owns (rank 0 keeps its own gradient)."""
     world, B = 2, 4
     base, models, groups, engines = _make(world, B=B, seed=3)
     for e in engines:
         e.set_membership(0b11, timeout_ns=50_000_000)  # 50 ms
-    x, y = torch.randn(B, 3, 32, 32).cuda(), torch.randint(0, 10, (B,)).cuda()
-    # rank 1 neither steps nor announces that it left: rank 0 must give up, not hang
-    native.vr_step(engines, [x, None], [y, None], B)
+        e.set_exchange_variant(variant)
+    xc, yc = torch.randn(B, 3, 32, 32), torch.randint(0, 10, (B,))
+    ref = copy.deepcopy(base)
+    opt = torch.optim.SGD(ref.parameters(), lr=0.01, momentum=0.9)
+    _oracle_step(ref, opt, [xc], [yc])
+    native.vr_step(engines, [xc.cuda(), None], [yc.cuda(), None], B)
     torch.cuda.synchronize()
     c = engines[0].read_ctl()
     assert c.status & 1 and (c.status >> 8) & 0b10
     assert c.step == 1
+    assert _rel(models[0].flat_params, ref.flat_params) < 3e-5
+    for e in engines: e.close()
+    for g in groups: g.close()
+
+
+def test_vr_allreduce_short_vectors_with_128_byte_lines():
+    """Vector lengths that end inside a line, inside a slice, and exactly on their borders."""
+    world = 4
+    base, models, groups, engines = _make(world, seed=6)
+    torch.manual_seed(7)
+    for n in (4, 28, 32, 60, 64, 124, 508, 512, 516, 1024 + 36, L.FLAT_NUMEL - 4):
+        ins = [torch.randn(n, device="cuda") for _ in range(world)]
+        outs = [torch.full((n,), float("nan"), device="cuda") for _ in range(world)]
+        native.vr_allreduce(engines, ins, outs, n, mode=0, two_shot="one-shot-128")
+        torch.cuda.synchronize()
+        want = torch.stack([t.double() for t in ins]).mean(0)
+        for r in range(world):
+            assert torch.equal(outs[0], outs[r])
+        assert (outs[0].double() - want).abs().max().item() < 1e-6, n
     for e in engines: e.close()
     for g in groups: g.close()

@@ -92,3 +92,88 @@ def test_ipc_fused_step_with_nvls_exchange_matches_one_shot(tmp_path):
         assert torch.equal(b[0]["flat"], b[r]["flat"]), "NVLS replicas differ between ranks"
     rel = ((a[0]["flat"] - b[0]["flat"]).abs().max() / a[0]["flat"].abs().max()).item()
     assert rel < 1e-5, rel     # summation order inside the switch differs from rank order: last-bit differences only
+
+
+@needs2
+def test_ll128_lines_are_never_torn(tmp_path):
+    """The one-shot-128 exchange assumes that a warp-wide 128-byte store arrives in the peer's memory as one unit
+    (a load that returns this step's flag word also returns this step's 31 values). Hammer exactly that over
+    NVLink: 122 CTAs x 8 warps x 3000 rounds of ping-pong per pair of GPUs, every arriving line checked."""
+    from distributed_neural_network_b200.parallel import launch
+    n = min(torch.cuda.device_count(), 8) & ~1
+    rc = launch.spawn(n, [sys.executable, str(ROOT / "tests" / "_mp_probe_worker.py"), str(tmp_path), "3000", "122"])
+    assert rc == 0
+    res = [torch.load(f"{tmp_path}/rank{r}.pt", weights_only=False) for r in range(n)]
+    for r in res:
+        torn, us_round_trip, gave_up = r["probe"]
+        assert not gave_up, f"rank {r['rank']}: a line never arrived"
+        assert torn == 0, f"rank {r['rank']}: {torn} words arrived under the wrong flag"
+        assert 0.5 < us_round_trip < 200.0
+
+
+@needs2
+def test_ipc_one_shot_128_trains_the_same_bits_as_one_shot(tmp_path):
+    """Both one-shot forms add the contributions in rank order, so they must produce the SAME model bit for bit."""
+    n = min(torch.cuda.device_count(), 8)
+    kw = dict(train_size=64 * n, test_size=32, epochs=2, batch_size=8, lr=0.05, seed=11)
+    a = _launch(n, tmp_path / "ll16", "step-allreduce", allreduce_variant="one-shot", **kw)
+    b = _launch(n, tmp_path / "ll128", "step-allreduce", allreduce_variant="one-shot-128", **kw)
+    for r in range(n):
+        assert torch.equal(a[0]["flat"], b[r]["flat"])
+
+
+@needs2
+def test_exchange_variant_is_chosen_by_measurement(tmp_path):
+    n = min(torch.cuda.device_count(), 8)
+    res = _launch(n, tmp_path, "step-allreduce", train_size=64 * n, test_size=32, epochs=1, batch_size=16, lr=0.05,
+                  seed=5, calibrate_steps=100)
+    table = res[0]["exchange_table"]
+    assert table["world"] == n and set(table["us_per_step_max_over_ranks"]) >= {"one-shot", "one-shot-128", "two-shot"}
+    assert table["chosen"] == min(table["us_per_step_max_over_ranks"], key=table["us_per_step_max_over_ranks"].get)
+    assert all(r["exchange_table"]["chosen"] == table["chosen"] for r in res)
+    for r in range(1, n):
+        assert torch.equal(res[0]["flat"], res[r]["flat"])
+    assert res[0]["history"][-1].get("allreduce_us", 0) > 0
+
+
+@needs2
+def test_second_device_in_one_process():
+    """Function attributes and the no-allocation scratch are per DEVICE: everything that worked on cuda:0 must
+    work on cuda:1 afterwards in the same process (launches with > 48 KB of dynamic shared memory included)."""
+    import ctypes as C
+
+    from distributed_neural_network_b200 import Network
+    from distributed_neural_network_b200.ops import flat as L
+    from distributed_neural_network_b200.ops import native
+
+    lib = native.require()
+    fn = lib.dnnb200_batch_grad_noalloc
+    fn.restype = C.c_int
+    fn.argtypes = [C.c_void_p] * 3 + [C.c_int] + [C.c_void_p] * 3
+    torch.manual_seed(5)
+    base = Network()
+    x, y = torch.randn(16, 3, 32, 32), torch.randint(0, 10, (16,))
+    got = []
+    for d in (0, 1):
+        dev = torch.device("cuda", d)
+        with torch.cuda.device(dev):
+            import copy
+            m = copy.deepcopy(base).to(dev)
+            eng = native.Engine(m.flat_params, torch.zeros(L.FLAT_NUMEL, device=dev), None, 64, 0.01, 0.9)
+            xd, yd = x.to(dev), y.to(dev)
+            g_eng = torch.zeros(L.FLAT_NUMEL, device=dev)
+            eng.grad_only(xd, yd, g_eng)                           # clustered kernel (> 48 KB smem)
+            g_na = torch.full((L.FLAT_NUMEL,), float("nan"), device=dev)
+            loss = torch.zeros(1, device=dev)
+            rc = fn(m.flat_params.data_ptr(), xd.data_ptr(), yd.data_ptr(), 16, g_na.data_ptr(), loss.data_ptr(),
+                    torch.cuda.current_stream().cuda_stream)      # one-CTA kernel + the per-device scratch address
+            assert rc == 0, lib.dnnb200_last_error().decode()
+            ev_loss, hits = eng.evaluate(xd, yd, 8)                # eval kernel (> 48 KB smem)
+            eng.step(xd, yd)
+            torch.cuda.synchronize()
+            rel = ((g_na - g_eng).abs().max() / g_eng.abs().max()).item()
+            assert rel < 5e-5, (d, rel)
+            got.append((g_eng.cpu(), ev_loss, hits, m.flat_params.detach().cpu()))
+            eng.close()
+    assert torch.allclose(got[0][0], got[1][0], rtol=0, atol=0) and got[0][1:3] == got[1][1:3]
+    assert torch.equal(got[0][3], got[1][3])

@@ -120,3 +120,18 @@ def test_membership_invariants(world, ops):
         assert len(m.active) >= 1                             # the last member never leaves
         assert m.mask == sum(1 << q for q in m.active) and m.divisor == len(m.active)
         assert m.donor() == min(m.active)
+
+
+def test_donor_is_the_rank_that_kept_the_most_progress():
+    """Drop mode: a rank that stayed for the whole epoch donates its state; if every trainer dropped out at some
+    point, the one that trained longest does (not whoever has the lowest rank number)."""
+    from distributed_neural_network_b200.parallel.membership import Membership
+
+    m = Membership(4)
+    assert m.donor() == 0
+    # rank 0 dropped at step 3, rank 2 at step 40, ranks 1 and 3 stayed (100 steps)
+    assert m.donor({0: (True, 3), 1: (False, 100), 2: (True, 40), 3: (False, 100)}) == 1
+    # everybody dropped: rank 2 got furthest
+    assert m.donor({0: (True, 0), 1: (True, 17), 2: (True, 40), 3: (True, 5)}) == 2
+    # ties go to the lower rank
+    assert m.donor({0: (True, 9), 1: (True, 9)}) == 0

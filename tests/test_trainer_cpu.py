@@ -204,3 +204,31 @@ def test_run_training_sh_issues_the_reference_sweep(tmp_path):
     want = [f"-n {n} python data_parallelism_train.py --nb-proc {n} --batch-size {bs} --synthetic"
             for n in (4, 8) for bs in (1, 2, 4, 8, 16, 32, 64)]
     assert calls == want
+
+
+def test_mpi4py_control_plane_world2_equals_gloo(tmp_path):
+    """The mpi4py provider of the control plane (bootstrap._MpiComm: COMM_WORLD, Barrier, allgather, bcast,
+    Allreduce -- what the reference bootstraps with, data_parallelism_train.py:60-62). The image has no MPI, so a
+    socket-backed test double of mpi4py (baseline/shims) stands in; launched the way mpiexec would launch it
+    (OMPI_COMM_WORLD_* in the environment), the same run must give the same bits as over torch.distributed/gloo."""
+    import socket
+
+    from distributed_neural_network_b200.parallel import launch
+    kw = dict(train_size=128, test_size=32, epochs=1, batch_size=8, lr=0.05, seed=11)
+    gloo = _launch(2, tmp_path / "gloo", "step-allreduce", **kw)
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    out = tmp_path / "mpi"
+    out.mkdir()
+    probe = out / "provider"
+    env = {"OMP_NUM_THREADS": "1", "OMPI_COMM_WORLD_SIZE": "2", "REFSHIM_PORT": str(port),
+           "PYTHONPATH": str(ROOT / "baseline" / "shims") + os.pathsep + os.environ.get("PYTHONPATH", ""),
+           "DNNB200_PROVIDER_PROBE": str(probe)}
+    rc = launch.spawn(2, [sys.executable, str(ROOT / "tests" / "_mp_worker.py"), str(out), "step-allreduce",
+                          json.dumps(dict(kw, device="cpu"))], env_extra=env, gpus=0)
+    assert rc == 0
+    mpi = [torch.load(out / f"rank{r}.pt", weights_only=False) for r in range(2)]
+    assert (probe.parent / "provider.0").read_text() == "mpi4py" and (probe.parent / "provider.1").read_text() == "mpi4py"
+    assert torch.equal(mpi[0]["flat"], mpi[1]["flat"])
+    assert torch.equal(mpi[0]["flat"], gloo[0]["flat"]), "the control plane must not change the numbers"

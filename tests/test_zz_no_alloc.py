@@ -84,3 +84,29 @@ def test_no_alloc_entry_refuses_batches_beyond_its_scratch():
     torch.cuda.synchronize()
     assert (g == 7.0).all(), "a refused call must not launch anything"
     assert _call(fn, model.flat_params, x[:0], y[:0], g, loss) == 2   # empty batch is refused too
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_no_alloc_entry_on_a_second_device_of_the_same_process():
+    """Every GPU that loads the library holds its own copy of the built-in array, and the entry point looks the
+    array's address up per device: after cuda:0 has been served, cuda:1 must get its own address (and its own
+    kernel attributes), not a pointer into cuda:0's memory."""
+    lib, fn = _entry()
+    torch.manual_seed(77)
+    base = Network()
+    x, y = torch.randn(24, 3, 32, 32), torch.randint(0, 10, (24,))
+    results = []
+    for d in (0, 1, 0):
+        dev = torch.device("cuda", d)
+        with torch.cuda.device(dev):
+            params = base.flat_params.detach().to(dev)
+            xd, yd = x.to(dev), y.to(dev)
+            g = torch.full((L.FLAT_NUMEL,), float("nan"), device=dev)
+            loss = torch.zeros(1, device=dev)
+            rc = _call(fn, params, xd, yd, g, loss)
+            assert rc == 0, lib.dnnb200_last_error().decode()
+            torch.cuda.synchronize(dev)
+            assert torch.isfinite(g).all()
+            results.append((g.cpu(), loss.item()))
+    for g, loss in results[1:]:
+        assert torch.equal(g, results[0][0]) and loss == results[0][1]
