@@ -147,7 +147,8 @@ def run_ours(args) -> int:
                    "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 500), __file__,
                    "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup),
                    "--batch", str(args.batch), "--exchange", args.exchange, "--prep", str(args.prep),
-                   "--align", str(args.align), "--pool", str(args.pool)]
+                   "--align", str(args.align), "--pool", str(args.pool)] + \
+                  (["--precision", args.precision] if args.precision else [])
             return subprocess.call(cmd)
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     if not torch.cuda.is_available():
@@ -158,7 +159,7 @@ def run_ours(args) -> int:
 
     cfg = TrainConfig(batch_size=B, sync_mode="step-allreduce" if world > 1 else "none", synthetic=True, quiet=True,
                       seed=1234, lr=0.001, momentum=0.9, device="cuda", peer_timeout_s=60.0,
-                      allreduce_variant=args.exchange)
+                      allreduce_variant=args.exchange, precision=args.precision)
     trainer = Trainer(cfg)            # public API: model + engine + peer group + control plane
     eng, comm = trainer.engine, trainer.comm
     dev = trainer.device
@@ -291,7 +292,10 @@ def run_ours(args) -> int:
             "vs_baseline": round(value / BASELINE_IMG_S, 2),
             "baseline_ref": "3949 img/s: reference's best committed aggregate (3 procs = 2 children, bs16, 8-core CPU; "
                             "BASELINE.md section 2)",
-            "dtype": "fp32 (FFMA, fp32 accumulate, fp32 master weights; reference is fp32)",
+            "dtype": ("tf32 tensor-core operands for conv1/conv2 forward and the conv2 data gradient (tcgen05, fp32 "
+                      "accumulate); FC layers, weight gradients, softmax, SGD and master weights fp32"
+                      if eng.precision == "tf32" and cs > 1 else
+                      "fp32 (FFMA, fp32 accumulate, fp32 master weights; reference is fp32)"),
             "data": "synthetic CIFAR-10-shaped (3x32x32 in [-1,1], 10 classes), random-init weights",
             "config": {"model": "models/model.py Network (LeNet-5 style CNN, 62006 params)",
                        "global_batch": world * B, "per_gpu_batch": B, "seq_len": None,
@@ -428,6 +432,8 @@ def main() -> int:
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--exchange", choices=["auto", "one-shot", "one-shot-128", "two-shot", "nvls"], default="auto",
                     help="gradient exchange variant (auto: every usable variant is timed at start-up, the fastest runs)")
+    ap.add_argument("--precision", choices=["tf32", "fp32"], default=None,
+                    help="conv stages of the fused step: tf32 = tcgen05 tensor cores (default), fp32 = FFMA")
     ap.add_argument("--ref-max-steps", type=int, default=400)
     ap.add_argument("--ref-timeout", type=float, default=1500.0)
     a = ap.parse_args()

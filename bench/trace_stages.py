@@ -16,9 +16,10 @@ NAMES = ["start->arrive", "cluster_wait", "img+weights", "conv1", "wait p1", "co
 def main():
     B = int(sys.argv[1]) if len(sys.argv) > 1 else 16
     cs = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+    prec = sys.argv[3] if len(sys.argv) > 3 else native.default_precision()
     torch.manual_seed(0)
     m = Network().cuda()
-    eng = native.Engine(m.flat_params, torch.zeros(L.FLAT_NUMEL, device="cuda"), None, B, 0.001, 0.9)
+    eng = native.Engine(m.flat_params, torch.zeros(L.FLAT_NUMEL, device="cuda"), None, B, 0.001, 0.9, precision=prec)
     eng.set_cluster_size(cs)
     x = torch.randn(B, 3, 32, 32, device="cuda")
     y = torch.randint(0, 10, (B,), device="cuda")
@@ -32,7 +33,7 @@ def main():
     eng.set_trace(None)
     t = tr.view(n_cta, 32).cpu()
     d = (t[:, 1:14] - t[:, 0:13]).float()
-    print(f"B={B} cs={cs}: per-stage cycles (mean / max over {n_cta} CTAs); total {(t[:,13]-t[:,0]).float().mean():.0f} cycles")
+    print(f"B={B} cs={cs} {prec}: per-stage cycles (mean / max over {n_cta} CTAs); total {(t[:,13]-t[:,0]).float().mean():.0f} cycles")
     for k in range(13):
         print(f"  {NAMES[k+1]:28s} {d[:,k].mean():8.0f} {d[:,k].max():8.0f}")
     ent, ext = t[:, 14].double(), t[:, 15].double()
@@ -48,6 +49,10 @@ def main():
         (fc[:,1]-fc[:,0]).mean(), (fc[:,2]-fc[:,1]).mean(), (fc[:,3]-fc[:,2]).mean(), (fc[:,4]-fc[:,3]).mean(),
         (fc[:,5]-fc[:,4]).mean(), (fc[:,6]-fc[:,5]).mean(), (fc[:,7]-fc[:,6]).mean()))
     print(f"    fc1 stage start (trace6) -> first row start {(fc[:,0]-t[:,6].double()).mean():.0f} cycles")
+    if prec == "tf32":   # thread 0's MMA issue loops (stamps 30 / 31 / 21 sit just before the commits)
+        print(f"    tcgen05: conv1 stage start -> its MMAs issued {(t[:,30]-t[:,2]).double().mean():.0f} cycles; "
+              f"conv2: p1 complete (trace4) -> MMAs issued {(t[:,31]-t[:,4]).double().mean():.0f}; "
+              f"dgrad: dx1 done (trace10) -> MMAs issued {(t[:,21]-t[:,10]).double().mean():.0f}")
     loop_ns = (t[:, 13] - t[:, 0]).double().mean() / 1.965
     print(f"  image loop {loop_ns:.0f} ns  => prologue (entry -> cluster barrier) ~ {(ext-ent).mean() - loop_ns:.0f} ns")
 

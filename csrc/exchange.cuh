@@ -37,10 +37,12 @@ constexpr int kLineData = 31;
 constexpr int kLines128 = (kSlice + kLineData - 1) / kLineData;   // 17
 constexpr int kSlice128 = kLines128 * 32;                         // 544 words per (slice, source) in the receive area
 
+constexpr int kMaxPeers128 = 7;                                   // one NVSwitch domain: 8 GPUs
+
 struct ExchangeShared {
   unsigned int present;  // bitmask of ranks whose contribution enters the sum
-  alignas(16) float in[kLines128 * kLineData + 1];   // 128-byte-line variant: my slice, re-laid out line by line
-  alignas(16) float out[kLines128 * kLineData + 1];  //   and the sum over the ranks
+  alignas(16) float in[kLines128 * kLineData + 1];                 // 128-byte-line variant: my slice, and ...
+  alignas(16) float rx[kMaxPeers128][kLines128 * kLineData + 1];   //   ... the lines of every peer as they arrive
 };
 
 // The two StepCtl fields every exchange needs, read by the caller (the update kernel reads them BEFORE it waits for
@@ -219,7 +221,7 @@ __device__ __forceinline__ void exchange_slice(const RankCtx& cx, const Exchange
 // of this step also holds the 31 values of this step. 1/32 of the bytes is overhead instead of 1/2:
 // 7 x 265 KB per GPU at 8 GPUs, still ONE latency hop, and membership-safe like the 16-byte one-shot
 // (leave markers, timeout, the CTA agrees on one set of contributors, rank-ordered sum => identical bits).
-// The thread-owned values are re-laid out line by line through shared memory (sh->in / sh->out).
+// The thread-owned values are picked up line by line from shared memory (sh->in); arriving lines are parked there (sh->rx).
 // tests/test_gpu_multiproc.py::test_ll128_lines_are_never_torn hammers the atomicity assumption over NVLink.
 __device__ __forceinline__ void st_line_word(float* p, unsigned int w) {
   asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(w) : "memory");
@@ -230,14 +232,22 @@ __device__ __forceinline__ unsigned int ld_line_word(const float* p) {
   return w;
 }
 
-// kThreads = threads of the CTA (kSlice / kVec). n_valid = how many of the slice's kSlice values exist (the last
-// slice of a vector is short): only the lines that carry one of them travel.
+// n_valid = how many of the slice's kSlice values exist (the last slice of a vector is short): only the lines
+// that carry one of them travel. At most kMaxPeers128 peers (one NVSwitch domain).
+//
+// Gather = independent jobs. Every (line, peer) pair is one job; the jobs are dealt round-robin to the warps and
+// a warp keeps all of its pending jobs in flight at once (one batch of loads per polling round), parks each line
+// that has arrived in shared memory (sh->rx[peer slot]) and drops it from its pending mask. Nothing waits for a
+// particular line, so a late peer costs one latency, not one per line. After one block barrier every thread adds,
+// in rank order, its own values and the parked values of the ranks the CTA agreed on.
 template <int kVec>
 __device__ __forceinline__ void exchange_slice_ll128(const RankCtx& cx, const ExchangeCfg cfg, ExchangeShared* sh,
                                                      int slice, unsigned int seq, int n_valid, float (&v)[kVec],
                                                      int* n_present) {
   static_assert(kVec == 2 || kVec == 4, "vector width");
   constexpr int kWarps = kSlice / kVec / 32;
+  constexpr int kMaxJobs = (kLines128 * kMaxPeers128 + kWarps - 1) / kWarps;   // 15 (8 warps) / 30 (4 warps)
+  static_assert(kMaxJobs <= 32, "a warp tracks its jobs in one 32-bit mask");
   const int world = cx.world, rank = cx.rank;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const unsigned int parity = seq & 1u;
@@ -247,106 +257,124 @@ __device__ __forceinline__ void exchange_slice_ll128(const RankCtx& cx, const Ex
   const int n_lines = (n_valid + kLineData - 1) / kLineData;
   const size_t area = (size_t)slice * kSlice128;   // word offset of this slice inside a (parity, source) block
 
-  // 1. my values, line layout: word w of the slice sits at in[w] (lines are consecutive runs of 31)
+  // 1. my values where a warp can pick them up line by line (word w of the slice at in[w])
 #pragma unroll
   for (int k = 0; k < kVec; ++k) sh->in[kVec * tid + k] = v[k];
   if (tid == 0) sh->present = configured;
+  // the configured peers, compacted: slot q <-> rank (same on every thread: `configured` is uniform)
+  int n_peers = 0;
+  unsigned int peer_of = 0u;   // 4 bits per slot
+  for (int p = 0; p < world; ++p)
+    if (p != rank && ((configured >> p) & 1u) && n_peers < kMaxPeers128) peer_of |= (unsigned int)p << (4 * n_peers++);
   __syncthreads();
 
   // 2. push: one warp-wide store per (line, peer)
   for (int L = warp; L < n_lines; L += kWarps) {
     const int w = L * kLineData + lane;
     const unsigned int word = lane == kLineData ? seq : (w < kSlice ? __float_as_uint(sh->in[w]) : 0u);
-    for (int p = 0; p < world; ++p) {
-      if (p == rank || !((configured >> p) & 1u)) continue;
+    for (int q = 0; q < n_peers; ++q) {
+      const int p = (int)((peer_of >> (4 * q)) & 15u);
       st_line_word(cx.recv[p] + ((size_t)(parity * world + rank) * kLLStride + area + (size_t)L * 32 + lane), word);
     }
   }
 
-  // 3. gather my lines from my own receive area; all pending peers of a line are polled as one batch of loads
+  // 3. gather: job j = line * kMaxPeers128 + peer slot; warp w owns the jobs j = w + kWarps * i
   const float* my_recv = cx.recv[rank];
-  unsigned int absent_warp = 0u;   // warp-uniform
-  unsigned int used_any = 0u;      // union over my lines of the sets that entered their sums
-  for (int L = warp; L < n_lines; L += kWarps) {
-    const int w = L * kLineData + lane;
-    const float mine = (lane < kLineData && w < kSlice) ? sh->in[w] : 0.f;
-    float acc = 0.f;
-    unsigned int absent = absent_warp;
-    for (int g0 = 0; g0 < world; g0 += 8) {
-      unsigned int t[8];
-      unsigned int pending = (configured >> g0) & 0xffu & ~(absent >> g0);
-      if (rank >= g0 && rank < g0 + 8) pending &= ~(1u << (rank - g0));
-      if (world - g0 < 8) pending &= (1u << (world - g0)) - 1u;
-      unsigned int spins = 0;
-      unsigned long long t0 = 0;
-      while (pending) {
-        unsigned int arrived = 0u;
+  unsigned int pending = 0u;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          if ((pending >> j) & 1u) {
-            t[j] = ld_line_word(my_recv + ((size_t)(parity * world + g0 + j) * kLLStride + area + (size_t)L * 32 + lane));
-            if (__shfl_sync(0xffffffffu, t[j], kLineData) == seq) arrived |= 1u << j;
-          }
-        }
-        pending &= ~arrived;
-        if (!pending) break;
-        if ((++spins & 0x3fu) != 0u) continue;
-        // something is late: has it left (announced), or is it time to give up? (all lanes take the same path)
+  for (int i = 0; i < kMaxJobs; ++i) {
+    const int j = warp + kWarps * i, L = j / kMaxPeers128, q = j - L * kMaxPeers128;
+    if (L < n_lines && q < n_peers) pending |= 1u << i;
+  }
+  unsigned int absent = 0u;    // ranks this warp gave up on (warp-uniform)
+  unsigned int spins = 0;
+  unsigned long long t0 = 0;
+  while (pending) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          if (!((pending >> j) & 1u)) continue;
-          const unsigned int l = ld_acquire_sys(my_flags + (g0 + j) * kFlagRow + kLeaveSlot);
-          if (l != 0u && (int)(seq - l) >= 0) {
-            // a peer that left pushed every line of its last step BEFORE it wrote the marker: one more look settles it
-            t[j] = ld_line_word(my_recv + ((size_t)(parity * world + g0 + j) * kLLStride + area + (size_t)L * 32 + lane));
-            if (__shfl_sync(0xffffffffu, t[j], kLineData) != seq) absent |= 1u << (g0 + j);
-            pending &= ~(1u << j);
-          }
-        }
-        if (pending && tmo != 0ull) {
-          const unsigned long long now = globaltimer_ns();
-          if (t0 == 0ull) t0 = now;
-          else if (__shfl_sync(0xffffffffu, (now - t0 > tmo) ? 1 : 0, 0)) {
-            if (lane == 0) atomicOr(&cx.ctl->status, kStatusTimeout | (pending << (8 + g0)));
-            absent |= pending << g0;
-            pending = 0u;
-          }
+    for (int i0 = 0; i0 < kMaxJobs; i0 += 8) {   // up to 8 independent loads in flight, THEN the checks
+      unsigned int got[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u;
+        if (i < kMaxJobs && ((pending >> i) & 1u)) {
+          const int j = warp + kWarps * i, L = j / kMaxPeers128, q = j - L * kMaxPeers128;
+          const int p = (int)((peer_of >> (4 * q)) & 15u);
+          got[u] = ld_line_word(my_recv + ((size_t)(parity * world + p) * kLLStride + area + (size_t)L * 32 + lane));
         }
       }
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {   // rank-ordered sum, my own contribution at its rank position
-        const int pr = g0 + j;
-        if (pr >= world || !((configured >> pr) & 1u)) continue;
-        if (pr == rank) acc += mine;
-        else if (!((absent >> pr) & 1u)) acc += __uint_as_float(t[j]);
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u;
+        if (i < kMaxJobs && ((pending >> i) & 1u)) {
+          const int j = warp + kWarps * i, L = j / kMaxPeers128, q = j - L * kMaxPeers128;
+          if (__shfl_sync(0xffffffffu, got[u], kLineData) == seq) {
+            if (lane < kLineData) sh->rx[q][L * kLineData + lane] = __uint_as_float(got[u]);
+            pending &= ~(1u << i);
+          }
+        }
       }
     }
-    if (lane < kLineData) sh->out[w] = acc;
-    used_any |= configured & ~absent;
-    absent_warp |= absent;   // a rank that is gone for one line of this step is gone for all of them
+    if (!pending) break;
+    if ((++spins & 0x3fu) != 0u) continue;
+    // something is late: has its sender left (announced), or is it time to give up? (all lanes take the same path)
+    bool expired = false;
+    if (tmo != 0ull) {
+      const unsigned long long now = globaltimer_ns();
+      if (t0 == 0ull) t0 = now;
+      expired = __shfl_sync(0xffffffffu, (now - t0 > tmo) ? 1 : 0, 0) != 0;
+    }
+    for (int i = 0; i < kMaxJobs; ++i) {
+      if (!((pending >> i) & 1u)) continue;
+      const int j = warp + kWarps * i, L = j / kMaxPeers128, q = j - L * kMaxPeers128;
+      const int p = (int)((peer_of >> (4 * q)) & 15u);
+      const unsigned int l = ld_acquire_sys(my_flags + p * kFlagRow + kLeaveSlot);
+      const bool left = l != 0u && (int)(seq - l) >= 0;
+      if (!left && !expired) continue;
+      if (left) {
+        // a peer that left pushed every line of its last step BEFORE it wrote the marker: one more look settles it
+        const unsigned int got = ld_line_word(my_recv + ((size_t)(parity * world + p) * kLLStride + area + (size_t)L * 32 + lane));
+        if (__shfl_sync(0xffffffffu, got, kLineData) == seq) {
+          if (lane < kLineData) sh->rx[q][L * kLineData + lane] = __uint_as_float(got);
+          pending &= ~(1u << i);
+          continue;
+        }
+      } else if (lane == 0) {
+        atomicOr(&cx.ctl->status, kStatusTimeout | (1u << (8 + p)));
+      }
+      absent |= 1u << p;
+      pending &= ~(1u << i);
+    }
   }
   // 4. the CTA agrees on ONE set of contributors (a rank pushes all lines of a step or none, so views only differ
-  //    when a timeout races with late data): union of everybody's "absent"; a warp that summed a larger set for
-  //    any of its lines redoes them from the receive area (the lines of the ranks that stay in have all arrived)
-  if (absent_warp && lane == 0) atomicAnd(&sh->present, ~absent_warp);
+  //    when a timeout races with late data): everybody's "absent" is taken out
+  if (absent && lane == 0) atomicAnd(&sh->present, ~absent);
   __syncthreads();
   const unsigned int present = sh->present;
-  if (used_any & ~present) {   // warp-uniform
-    for (int L = warp; L < n_lines; L += kWarps) {
-      const int w = L * kLineData + lane;
-      float acc = 0.f;
-      for (int p = 0; p < world; ++p) {
-        if (!((present >> p) & 1u)) continue;
-        if (p == rank) acc += (lane < kLineData && w < kSlice) ? sh->in[w] : 0.f;
-        else acc += __uint_as_float(ld_line_word(my_recv + ((size_t)(parity * world + p) * kLLStride + area + (size_t)L * 32 + lane)));
+  // 5. rank-ordered sum, my own contribution (registers) at its rank position
+  float acc[kVec];
+#pragma unroll
+  for (int k = 0; k < kVec; ++k) acc[k] = 0.f;
+  {
+    int q = 0;
+    for (int p = 0; p < world; ++p) {
+      if (p == rank) {
+        if ((configured >> p) & 1u) {
+#pragma unroll
+          for (int k = 0; k < kVec; ++k) acc[k] += v[k];
+        }
+        continue;
       }
-      if (lane < kLineData) sh->out[w] = acc;
+      if (!((configured >> p) & 1u) || q >= n_peers) continue;
+      if ((present >> p) & 1u) {
+#pragma unroll
+        for (int k = 0; k < kVec; ++k) acc[k] += sh->rx[q][kVec * tid + k];
+      }
+      ++q;
     }
   }
-  __syncthreads();
   if (kVec * tid < n_valid) {
 #pragma unroll
-    for (int k = 0; k < kVec; ++k) v[k] = sh->out[kVec * tid + k];
+    for (int k = 0; k < kVec; ++k) v[k] = acc[k];
   }
   *n_present = __popc(present);
 }

@@ -28,6 +28,7 @@
 
 #include "common.cuh"
 #include "layout.h"
+#include "tc_common.cuh"
 
 namespace cg = cooperative_groups;
 
@@ -41,7 +42,11 @@ constexpr int kXCh = 32 * kXRow + 8;       //   kernel rows of a wgrad gather fa
 // stage barriers: one mbarrier per all-gather, completed by the st.async traffic itself
 enum { kBarP1 = 0, kBarP2, kBarH1, kBarH2, kBarD1, kBarG2, kBarW1, kNumStageBars };
 
-struct __align__(16) CLSmem {
+template <bool kTC>
+struct CLSmemT;
+
+template <>
+struct __align__(16) CLSmemT<false> {
   alignas(16) float xd[kImgNumel];    // image as it is in global memory (ONE 12 KB TMA bulk copy)
   alignas(16) float x[3 * kXCh];      // image, CHW with padded rows (re-laid out by the threads)
   alignas(16) float cw[kConvPrefix];  // conv1.weight | conv1.bias | conv2.weight | conv2.bias exactly as in the flat
@@ -64,6 +69,56 @@ struct __align__(16) CLSmem {
   alignas(8) unsigned long long mbar;                  // image bulk copies
   alignas(8) unsigned long long cbar;                  // conv weights bulk copy (once per launch)
   alignas(8) unsigned long long sbar[kNumStageBars];   // all-gather completion
+};
+
+// ---- tensor-core instantiation (kTC): geometry of the three implicit GEMMs ------------------------------------
+// conv1 forward, conv2 forward and the conv2 data gradient run on tcgen05 (kind::tf32, fp32 accumulators in
+// TMEM); everything else (FC chain, both weight gradients, softmax) stays fp32 FFMA. All three GEMMs use the
+// trick of tc_conv.cu: the activation plane is NHWC with 4 floats per pixel, so one pixel of one channel group is
+// one 16-byte K-chunk of a no-swizzle K-major operand and a filter tap is just a different START ADDRESS into the
+// same plane. New here: the 8-row groups of a tile are laid along image ROWS (SBO = one plane row), so a 128-row
+// tile is 16 conv rows x 8 columns and the four pixels of every 2x2 pooling window sit in ONE warp's TMEM lanes
+// (lanes l, l^1, l^8, l^9): bias + ReLU + max-pool + argmax are register shuffles, no shared-memory round trip.
+constexpr int kXPitch = 33;                            // conv1 plane: pixels per row (33, not 32: the five kernel
+                                                       //   rows of a wgrad gather then fall into different banks)
+constexpr int kXPlanePix = 36 * kXPitch + 12;          // rows 0..35 are reachable (tile rows 16..31 + 4) + tap reach
+constexpr int kP1Pitch = 14;
+constexpr int kP1PlanePix = 20 * kP1Pitch + 24;        // conv2 tiles reach rows 0..19, columns up to 19
+constexpr int kDPitch = 18;                            // conv2 output gradient, zero border of 4
+constexpr int kDPlanePix = 2 * 128 + 4 * kDPitch + 4 + 12;   // two tiles + reach of the last tap (344)
+constexpr int kB1Chunks = 26, kB2Chunks = 50, kBdChunks = 100;   // K-chunks (4 floats) of the three B operands
+constexpr int kTmemCols = 128;                         // [0,64) conv1 tiles, [64,96) conv2 tiles, [96,128) dgrad tiles
+constexpr uint32_t kTmemC2 = 64, kTmemDg = 96;
+enum { kTBarC1 = 0, kTBarC2, kTBarDg, kNumTcBars };
+
+template <>
+struct __align__(128) CLSmemT<true> {
+  alignas(128) float xpl[kXPlanePix * 4];        // image, NHWC4 (x, y, z, 0) per pixel, row pitch kXPitch: conv1 A operand
+                                                 //   and the conv1 weight gradient's gather
+  alignas(128) float dpl[4 * kDPlanePix * 4];    // dL/d(conv2 output), 4 planes of 4 channels, zero-padded 18x18: dgrad A
+  alignas(128) float p1n[2 * kP1PlanePix * 4];   // pooled conv1 output, 2 planes of 4 channels (6, 7 stay zero): conv2 A.
+                                                 //   The two low mantissa bits of every value carry the pooling argmax
+  alignas(128) float sb1[2 * kB1Chunks * 32];    // conv1.weight as canonical K-major B operand [n-group][chunk][8][4]
+  alignas(128) float sb2[2 * kB2Chunks * 32];    // conv2.weight, K = (tap, channel group)
+  alignas(128) float sbd[2 * kBdChunks * 32];    // conv2.weight flipped and transposed for the data gradient, K = (tap, o)
+  alignas(16) float xd[kImgNumel];               // image as it is in global memory (ONE 12 KB TMA bulk copy)
+  alignas(16) float cw[kConvPrefix];
+  alignas(16) float p2[400];
+  alignas(16) float h1[120];
+  alignas(16) float h2[88];
+  alignas(16) float logits[16];
+  alignas(16) float d3[16];
+  alignas(16) float d2[88];
+  alignas(16) float d1[120];
+  alignas(16) float g2[400];
+  alignas(16) float g1[1176 + 8];
+  alignas(16) int idx2[400];
+  alignas(16) int poff[196];          // (2*ph)*kXPitch + 2*pw of pooled pixel q
+  alignas(8) unsigned long long mbar;
+  alignas(8) unsigned long long cbar;
+  alignas(8) unsigned long long sbar[kNumStageBars];
+  alignas(8) unsigned long long tbar[kNumTcBars];      // tcgen05.commit targets
+  uint32_t tmem_slot;
 };
 
 __device__ __forceinline__ uint32_t cl_smem_u32(const void* p) {
@@ -109,6 +164,20 @@ __device__ __forceinline__ void cl_st_async(uint32_t remote_addr, uint32_t v, ui
                "r"(v), "r"(remote_bar)
                : "memory");
 }
+// 16 / 8 bytes at once (one pixel of an NHWC4 plane): same crediting of the destination's mbarrier
+__device__ __forceinline__ void cl_st_async_v4(uint32_t remote_addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d,
+                                               uint32_t remote_bar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(
+                   remote_addr),
+               "r"(a), "r"(b), "r"(c), "r"(d), "r"(remote_bar)
+               : "memory");
+}
+__device__ __forceinline__ void cl_st_async_v2(uint32_t remote_addr, uint32_t a, uint32_t b, uint32_t remote_bar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.b32 [%0], {%1, %2}, [%3];" ::"r"(
+                   remote_addr),
+               "r"(a), "r"(b), "r"(remote_bar)
+               : "memory");
+}
 __device__ __forceinline__ void cl_cluster_arrive() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
 }
@@ -125,8 +194,9 @@ template <int CS>
 struct Remote {
   uint32_t base[CS];
 };
-#define CL_OFF(field) ((uint32_t)offsetof(CLSmem, field))
-#define CL_BAR(i) ((uint32_t)(offsetof(CLSmem, sbar) + 8 * (i)))
+// (used inside the kernel, where SM names the instantiation's CLSmemT)
+#define CL_OFF(field) ((uint32_t)offsetof(SM, field))
+#define CL_BAR(i) ((uint32_t)(offsetof(SM, sbar) + 8 * (i)))
 
 template <int CS>
 __device__ __forceinline__ void push_all(const Remote<CS>& R, uint32_t field_off, uint32_t bar_off, uint32_t v) {
@@ -268,29 +338,39 @@ struct FCSmem {
   alignas(16) float rx_g2[CS * kFlat];  // partial dL/dp2
   alignas(8) unsigned long long wbar;   // weight prefetch
 };
-constexpr size_t kFcOff = (sizeof(CLSmem) + 127) & ~(size_t)127;
+template <bool kTC>
+__host__ __device__ constexpr size_t fc_off() {
+  return (sizeof(CLSmemT<kTC>) + 127) & ~(size_t)127;
+}
 // conv1 weight-gradient partials of the CTAs of a cluster, collected by CTA 0 (row d = CTA d: 450 weights + 6 biases)
 constexpr int kW1Row = 456;
 // scratch for split reductions, sized for the cluster size: conv2 dgrad partials 16*6*nq + conv2 wgrad partials
 // 5*no*150 live together; every other use (conv2 forward partials, conv1 wgrad partials, CS<4 FC splits) is smaller
-template <int CS>
+// (tensor-core instantiation: the data gradient and the conv2 forward need no partials, only the two weight
+// gradients do -- 5*no*150 and 5*450+30 floats; clusters below 4 still split the FC data gradients through it)
+template <int CS, bool kTC = false>
 struct W1Rx {
   static constexpr int kNq = (196 + CS - 1) / CS, kNo = (16 + CS - 1) / CS;
-  static constexpr int kRed0 = 96 * kNq + 5 * kNo * 150;
-  static constexpr int kRed = kRed0 > 6400 ? kRed0 : 6400;
+  static constexpr int kRed0 = kTC ? (5 * kNo * 150 > 2304 ? 5 * kNo * 150 : 2304) : 96 * kNq + 5 * kNo * 150;
+  static constexpr int kRedMin = (kTC && CS >= 4) ? 0 : 6400;
+  static constexpr int kRed = kRed0 > kRedMin ? kRed0 : kRedMin;
   alignas(16) float red[kRed];
   alignas(16) float rx[CS * kW1Row];
 };
-template <int CS>
+template <int CS, bool kTC = false>
 __host__ __device__ constexpr size_t w1rx_offset() {
-  return CS >= 4 ? ((kFcOff + sizeof(FCSmem<CS>) + 127) & ~(size_t)127) : kFcOff;
+  return CS >= 4 ? ((fc_off<kTC>() + sizeof(FCSmem<CS>) + 127) & ~(size_t)127) : fc_off<kTC>();
 }
-template <int CS>
+template <int CS, bool kTC = false>
 __host__ __device__ constexpr size_t cluster_smem_bytes() {
-  return w1rx_offset<CS>() + sizeof(W1Rx<CS>);
+  return w1rx_offset<CS, kTC>() + sizeof(W1Rx<CS, kTC>);
 }
 static_assert(cluster_smem_bytes<4>() <= 227 * 1024 && cluster_smem_bytes<2>() <= 227 * 1024 &&
               cluster_smem_bytes<8>() <= 227 * 1024, "shared memory budget");
+static_assert(cluster_smem_bytes<2, true>() <= 227 * 1024 && cluster_smem_bytes<3, true>() <= 227 * 1024 &&
+              cluster_smem_bytes<4, true>() <= 227 * 1024 && cluster_smem_bytes<5, true>() <= 227 * 1024 &&
+              cluster_smem_bytes<6, true>() <= 227 * 1024 && cluster_smem_bytes<7, true>() <= 227 * 1024 &&
+              cluster_smem_bytes<8, true>() <= 227 * 1024, "shared memory budget (tensor-core instantiation)");
 
 // rows [m0, m1) of y = act(b + W . in) with the rows in shared memory (wsm[0] is row m0)
 template <int CS, int K, bool kRelu>
@@ -352,7 +432,7 @@ __device__ __forceinline__ void fc_dx_partial_push(const float* wsm, const float
 #ifndef DNN_F_MAXNREG
 #define DNN_F_MAXNREG 0
 #endif
-template <int CS>
+template <int CS, bool kTC>
 #if DNN_F_MAXNREG > 0
 __global__ void __maxnreg__(DNN_F_MAXNREG)
 #else
@@ -365,7 +445,9 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
                        const unsigned int* __restrict__ ready_ctr, unsigned int ready_expect) {
   static_assert(CS >= 2 && CS <= 8, "the one-CTA case is fused_step.cu's fwd_bwd_kernel");
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  CLSmem& s = *reinterpret_cast<CLSmem*>(smem_raw);
+  using SM = CLSmemT<kTC>;
+  SM& s = *reinterpret_cast<SM*>(smem_raw);
+  constexpr size_t kFcOff = fc_off<kTC>();
   cg::cluster_group cluster = cg::this_cluster();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (trace != nullptr && tid == 0) trace[blockIdx.x * 32 + 14] = (long long)globaltimer_ns();
@@ -378,8 +460,9 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
   FCSmem<kPre ? CS : 4>& f = *reinterpret_cast<FCSmem<kPre ? CS : 4>*>(smem_raw + kFcOff);
   constexpr uint32_t kRxD1 = (uint32_t)(kFcOff + offsetof(FCSmem<kPre ? CS : 4>, rx_d1));
   constexpr uint32_t kRxG2 = (uint32_t)(kFcOff + offsetof(FCSmem<kPre ? CS : 4>, rx_g2));
-  W1Rx<CS>& tail = *reinterpret_cast<W1Rx<CS>*>(smem_raw + w1rx_offset<CS>());
-  constexpr uint32_t kRxW1 = (uint32_t)(w1rx_offset<CS>() + offsetof(W1Rx<CS>, rx));
+  using Tail = W1Rx<CS, kTC>;
+  Tail& tail = *reinterpret_cast<Tail*>(smem_raw + w1rx_offset<CS, kTC>());
+  constexpr uint32_t kRxW1 = (uint32_t)(w1rx_offset<CS, kTC>() + offsetof(Tail, rx));
   const float* rx_w1 = tail.rx;
   float* const sred = tail.red;
 
@@ -393,9 +476,34 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
 #pragma unroll
     for (int i = 0; i < kNumStageBars; ++i) cl_mbar_init(&s.sbar[i], 1);
     if (kPre) cl_mbar_init(&f.wbar, 1);
+    if constexpr (kTC) {   // one arrival per issuing thread: conv1 one per tile of mine, conv2 and the data gradient two
+      cl_mbar_init(&s.tbar[kTBarC1], (8 - r + CS - 1) / CS);
+      cl_mbar_init(&s.tbar[kTBarC2], 2);
+      cl_mbar_init(&s.tbar[kTBarDg], 2);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  uint32_t tmem = 0;
+  if constexpr (kTC) {
+    // tensor memory for the accumulators of the three GEMMs (one warp allocates, the same warp frees at the end);
+    // and everything in the operand buffers that is padding is zeroed ONCE, long before any weight or image arrives:
+    // B-operand rows/chunks without a weight, the pad column/rows of the image plane, channels 6..7 of p1
+    if (warp == 1) tc::tmem_alloc<kTmemCols>(&s.tmem_slot);
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = tid; i < (int)(sizeof(s.sb1) + sizeof(s.sb2) + sizeof(s.sbd)) / 16; i += kCLThreads)
+      reinterpret_cast<float4*>(s.sb1)[i] = z;   // sb1 | sb2 | sbd are contiguous (static_assert below)
+    for (int i = tid; i < kXPlanePix; i += kCLThreads) reinterpret_cast<float4*>(s.xpl)[i] = z;
+    for (int i = tid; i < 2 * kP1PlanePix; i += kCLThreads) reinterpret_cast<float4*>(s.p1n)[i] = z;
+    for (int i = tid; i < 4 * kDPlanePix; i += kCLThreads) reinterpret_cast<float4*>(s.dpl)[i] = z;
+    static_assert(offsetof(SM, sb2) == offsetof(SM, sb1) + sizeof(s.sb1) &&
+                  offsetof(SM, sbd) == offsetof(SM, sb2) + sizeof(s.sb2), "B operands are zeroed as one block");
+    tc::tc_fence_before();
+  }
   __syncthreads();
+  if constexpr (kTC) {
+    tc::tc_fence_after();
+    tmem = s.tmem_slot;
+  }
   // tell the cluster "my barriers exist"; the matching wait sits just before the first remote store
   CL_TRACE(17);
   cl_cluster_arrive_relaxed();
@@ -413,10 +521,27 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
   };
   // dense CHW image -> padded rows (36 floats, 16-byte aligned) for the conv1 patch loads
   auto relayout_image = [&]() {
-    for (int i = tid; i < kImgNumel / 4; i += kCLThreads) {
-      const float4 v = reinterpret_cast<const float4*>(s.xd)[i];
-      const int e = i * 4, c = e >> 10, h = (e >> 5) & 31, w = e & 31;
-      *reinterpret_cast<float4*>(s.x + c * kXCh + h * kXRow + w) = v;
+    if constexpr (kTC) {   // dense CHW -> NHWC4 pixels (x, y, z, 0) at row pitch kXPitch: the conv1 A operand
+      for (int px = tid; px < 1024; px += kCLThreads) {
+        const float4 v = make_float4(s.xd[px], s.xd[1024 + px], s.xd[2048 + px], 0.f);
+        *reinterpret_cast<float4*>(s.xpl + ((px >> 5) * kXPitch + (px & 31)) * 4) = v;
+      }
+    } else {
+      for (int i = tid; i < kImgNumel / 4; i += kCLThreads) {
+        const float4 v = reinterpret_cast<const float4*>(s.xd)[i];
+        const int e = i * 4, c = e >> 10, h = (e >> 5) & 31, w = e & 31;
+        *reinterpret_cast<float4*>(s.x + c * kXCh + h * kXRow + w) = v;
+      }
+    }
+  };
+  // dense dL/d(conv2 output), zero-padded: rewritten (scattered into) for every image, so zeroed for every image
+  auto zero_grad_plane = [&]() {
+    if constexpr (kTC) {
+      if (first_img) return;   // zeroed with the other operand buffers at kernel start
+      const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int i = tid; i < 4 * kDPlanePix; i += kCLThreads) reinterpret_cast<float4*>(s.dpl)[i] = z;
+    } else {
+      for (int i = tid; i < 16 * 18 * 18; i += kCLThreads) s.dc2p[i] = 0.f;
     }
   };
   load_image(img);   // the input batch does not depend on the previous kernel of the stream,
@@ -460,7 +585,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     }
   }
 
-  if (tid < 196) s.poff[tid] = (2 * (tid / 14)) * kXRow + 2 * (tid % 14);
+  if (tid < 196) s.poff[tid] = (2 * (tid / 14)) * (kTC ? kXPitch : kXRow) + 2 * (tid % 14);
   CL_TRACE(19);
   CL_TRACE(20);
 
@@ -481,8 +606,10 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     // the label is only needed by the softmax, six stages from here: fetch it now, off that stage's critical path
     const int label = (int)__ldg(labels + img);
     if (tid == 0) {  // arm this image's all-gathers: bytes each one will deliver into THIS CTA
-      cl_mbar_expect_tx(&s.sbar[kBarP1], 1176 * 8);
-      cl_mbar_expect_tx(&s.sbar[kBarP2], 400 * 8);
+      cl_mbar_expect_tx(&s.sbar[kBarP1], kTC ? 1176 * 4 : 1176 * 8);   // (kTC: the argmax rides in the value's low bits)
+      if (!kTC) cl_mbar_expect_tx(&s.sbar[kBarP2], 400 * 8);
+      else if ((r ^ 1) < CS)   // kTC: paired CTAs compute one conv2 tile each; I receive the OTHER tile's pooled outputs:
+        cl_mbar_expect_tx(&s.sbar[kBarP2], ((r & 1) ? 16 * 5 * 4 : 16 * 5 * 1) * 8);   // columns 0..3 (tile 0) or 4 (tile 1)
       cl_mbar_expect_tx(&s.sbar[kBarH1], kF1 * 4);
       cl_mbar_expect_tx(&s.sbar[kBarH2], kF2 * 4);
       cl_mbar_expect_tx(&s.sbar[kBarD1], (kPre ? CS : 1) * kF1 * 4);
@@ -497,30 +624,267 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     __syncthreads();
     CL_TRACE(2);
 
-    // ================= conv1 + bias + ReLU + maxpool, my pooled pixels =================
-    // (split by pooled PIXEL range, not by row: 196 pixels divide evenly over any cluster size)
-    {
-      const int npx = nq;
-      for (int item = tid; item < npx * 6; item += kCLThreads) {
-        const int ch = item / npx, px = item - ch * npx;
-        const int ph = (q0 + px) / 14, pw = (q0 + px) % 14;
-        float a00 = 0.f, a01 = 0.f, a10 = 0.f, a11 = 0.f;
-#pragma unroll 1
-        for (int c = 0; c < 3; ++c) {
-          const float* xb = s.x + c * kXCh + (2 * ph) * kXRow + 2 * pw;
+    if constexpr (kTC) {
+      // ================= conv1 and conv2 on the tensor cores =================
+      // What a tiny MMA costs (bench/tc_mma_rate.py): M=128, N=16, K=8 takes ~64 cycles from one issuing thread and
+      // ~47 from two or more (the tensor pipe re-reads 4 KB of A for 16k MACs), whatever N or the layout. So the
+      // stages are sized in MMAs: each issuing thread does as little else as possible (a 64-bit add per descriptor,
+      // the offsets are compile-time constants), and two threads issue wherever there are two independent tiles.
+      constexpr uint32_t kIdesc = tc::idesc_tf32(128, 16);
+      const int n_tile1 = (8 - r + CS - 1) / CS;   // conv1: 8 tiles per image (2 row blocks x 4 column blocks), dealt round-robin
+      // conv2: two tiles (columns 0..7 / 8..15). Paired CTAs (r, r^1) compute one each and hand the result to the
+      // partner; a CTA without partner (last one of an odd cluster) computes both.
+      const bool paired = (r ^ 1) < CS;
+      if (first_img) {
+        // conv1.weight -> B operand (450 real entries, the rest stays zero): element (n, chunk = tap, c)
+        for (int i = tid; i < 450; i += kCLThreads) {
+          const int n = i / 75, rem = i - n * 75, c = rem / 25, tap = rem - c * 25;
+          s.sb1[((n >> 3) * kB1Chunks + tap) * 32 + (n & 7) * 4 + c] = s.cw[kOffW1 + i];
+        }
+      }
+      tc::fence_proxy_async();   // plane and weights were written with st.shared; the tensor core reads through the async proxy
+      __syncthreads();
+      if (lane == 0 && warp < n_tile1) {           // one issuing thread per tile of mine
+        tc::tc_fence_after();
+        const int t = r + warp * CS;
+        const uint32_t a_addr = tc::smem_u32(s.xpl) + (uint32_t)((16 * (t >> 2)) * kXPitch + 8 * (t & 3)) * 16;
+        // K-chunks of MMA j = taps 2j and 2j+1: 16 bytes apart inside a kernel row, (pitch - 4) pixels across rows
+        const uint64_t a_in = tc::smem_desc_nosw(a_addr, 16, kXPitch * 16);
+        const uint64_t a_x = tc::smem_desc_nosw(a_addr, (kXPitch - 4) * 16, kXPitch * 16);
+        const uint64_t b0 = tc::smem_desc_nosw(tc::smem_u32(s.sb1), 128, kB1Chunks * 128);
+        const uint32_t d = tmem + (uint32_t)warp * 16;
+#pragma unroll
+        for (int j = 0; j < kB1Chunks / 2; ++j) {
+          const int t0 = 2 * j;
+          const int off0 = (t0 / 5) * kXPitch + (t0 % 5);                // compile-time after unrolling
+          const bool cross = (t0 % 5) == 4;                              // tap 2j+1 starts the next kernel row
+          tc::mma_tf32(d, (cross ? a_x : a_in) + (uint64_t)off0, b0 + (uint64_t)(16 * j), kIdesc, j > 0);
+        }                                                                // (tap 25 does not exist: its B chunk is zero)
+        tc::mma_commit(reinterpret_cast<uint64_t*>(&s.tbar[kTBarC1]));
+        if (warp == 0) CL_TRACE(30);
+      }
+      if (first_img) {
+        // While the tensor core works: the other two B operands (needed from conv2 on). A warp writes 32 consecutive
+        // floats of an operand per step -- (row n%8, component) of one K-chunk -- so the stores are conflict-free.
+        //   sb2: conv2.weight, chunk = 2*tap + ch/4, element (n = o, c = ch%4)
+        //   sbd: the same weights for the data gradient dX[ch] = sum_{tap,o} dCp[o](shifted by tap) W[o][ch][24 - tap]:
+        //        n = ch, chunk = 4*tap' + o/4 with tap' = 24 - tap, component o%4
+        for (int it = warp; it < 200; it += kCLThreads / 32) {
+          if (it < 100) {
+            const int og = it / 50, rem = it - og * 50, tap = rem >> 1, cg = rem & 1;
+            const int o = og * 8 + (lane >> 2), ch = cg * 4 + (lane & 3);
+            if (ch < 6) s.sb2[(og * kB2Chunks + rem) * 32 + lane] = s.cw[kOffW2 + (o * 6 + ch) * 25 + tap];
+          } else {
+            const int u = it - 100, tp = u >> 2, og = u & 3;       // tp = flipped tap, og = group of 4 output channels
+            const int ch = lane >> 2, o = og * 4 + (lane & 3);
+            if (ch < 6) s.sbd[(4 * tp + og) * 32 + lane] = s.cw[kOffW2 + (o * 6 + ch) * 25 + (24 - tp)];
+          }
+        }
+        tc::fence_proxy_async();
+      }
+      CL_TRACE(3);
+      cl_mbar_wait(&s.tbar[kTBarC1], phase);
+      tc::tc_fence_after();
+      {
+        // epilogue: lane = (conv row 4*(warp%4) + lane/8 of the tile, column lane%8); 2x2 windows by shuffles. The
+        // top-left lane of a window sends the pooled pixel of one NHWC4 plane with ONE vector st.async per CTA.
+        // With at most two tiles the 16 warps split the planes (channels 0-3 / 4-5); with more, a warp does both.
+        int slot, c0, nc;
+        if (n_tile1 <= 2) { slot = (warp >> 2) & 1; c0 = (warp >> 3) * 4; nc = (warp >> 3) ? 2 : 4; }
+        else { slot = warp >> 2; c0 = 0; nc = 6; }
+        if (slot < n_tile1) {
+          const int t = r + slot * CS;
+          float v[8];
+          tc::tmem_ld8(tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)slot * 16, v);
+          const int row = 16 * (t >> 2) + 4 * (warp & 3) + (lane >> 3), col = 8 * (t & 3) + (lane & 7);
+          const int ph = row >> 1, pw = col >> 1;
+          const bool mine = !(lane & 1) && !((lane >> 3) & 1) && ph < 14 && pw < 14;   // top-left lane of a valid window
+          uint32_t word[6];
+#pragma unroll
+          for (int c = 0; c < 6; ++c) {
+            word[c] = 0u;
+            if (c < c0 || c >= c0 + nc) continue;   // warp-uniform
+            const float a00 = fmaxf(v[c] + s.cw[kOffB1 + c], 0.f);
+            const float a01 = __shfl_xor_sync(0xffffffffu, a00, 1);
+            const float a10 = __shfl_xor_sync(0xffffffffu, a00, 8);
+            const float a11 = __shfl_xor_sync(0xffffffffu, a00, 9);
+            float best = a00;
+            uint32_t bi = 0;
+            if (a01 > best) { best = a01; bi = 1; }
+            if (a10 > best) { best = a10; bi = 2; }
+            if (a11 > best) { best = a11; bi = 3; }
+            // the argmax rides in the two low mantissa bits (far below the TF32 rounding of the value's inputs)
+            word[c] = (__float_as_uint(best) & ~3u) | bi;
+          }
+          if (mine) {
+            const uint32_t px = (uint32_t)(ph * 14 + pw) * 16;
+            if (c0 == 0) {
+#pragma unroll
+              for (int d = 0; d < CS; ++d)
+                cl_st_async_v4(R.base[d] + CL_OFF(p1n) + px, word[0], word[1], word[2], word[3], R.base[d] + CL_BAR(kBarP1));
+            }
+            if (c0 + nc == 6) {
+#pragma unroll
+              for (int d = 0; d < CS; ++d)
+                cl_st_async_v2(R.base[d] + CL_OFF(p1n) + (uint32_t)kP1PlanePix * 16 + px, word[4], word[5],
+                               R.base[d] + CL_BAR(kBarP1));
+            }
+          }
+        }
+      }
+      tc::tc_fence_before();
+      if (first_img) __syncthreads();   // sb2 / sbd are complete (and fenced) before anybody issues conv2
+      CL_TRACE(4);
+      if (lane == 0 && warp < 2) {
+        cl_mbar_wait(&s.sbar[kBarP1], phase);      // every CTA's part of p1 has landed (st.async from the whole cluster)
+        tc::fence_proxy_async();
+        tc::tc_fence_after();
+        // paired: my tile (columns 8*(r&1)..), its 25 taps split over the two issuing threads and two accumulators
+        // (added in the epilogue); alone: issuing thread w computes tile w
+        const int cb = paired ? (r & 1) : warp;
+        const int j0 = paired ? (warp ? 13 : 0) : 0, j1 = paired ? (warp ? 25 : 13) : 25;
+        const uint64_t a0 = tc::smem_desc_nosw(tc::smem_u32(s.p1n) + (uint32_t)(8 * cb) * 16, kP1PlanePix * 16, kP1Pitch * 16);
+        const uint64_t b0 = tc::smem_desc_nosw(tc::smem_u32(s.sb2), 128, kB2Chunks * 128);
+        const uint32_t d = tmem + kTmemC2 + (uint32_t)warp * 16;
+        int kh = j0 / 5, kw = j0 - kh * 5;
+#pragma unroll 5
+        for (int j = j0; j < j1; ++j) {            // K-chunks of MMA j = the two channel groups of tap j
+          tc::mma_tf32(d, a0 + (uint64_t)(kh * kP1Pitch + kw), b0 + (uint64_t)(16 * j), kIdesc, j > j0);
+          if (++kw == 5) { kw = 0; ++kh; }
+        }
+        tc::mma_commit(reinterpret_cast<uint64_t*>(&s.tbar[kTBarC2]));
+        if (warp == 0) CL_TRACE(31);
+      }
+      cl_mbar_wait(&s.tbar[kTBarC2], phase);
+      tc::tc_fence_after();
+      cl_mbar_wait(&s.sbar[kBarP1], phase);        // (complete by now) acquire: later stages read p1 with ordinary loads
+      CL_TRACE(5);
+      {
+        // 16 warps = 4 lane quarters x 2 halves of the channels x (paired: nothing more / alone: the 2 tiles)
+        const int half = (warp >> 2) & 1, cb = paired ? (r & 1) : (warp >> 3);
+        if (paired ? warp < 8 : true) {
+          float v[8];
+          const uint32_t lanes = (uint32_t)((warp & 3) * 32) << 16;
+          if (paired) {
+            float u[8];
+            tc::tmem_ld8(tmem + lanes + kTmemC2 + (uint32_t)(half * 8), v);
+            tc::tmem_ld8(tmem + lanes + kTmemC2 + 16 + (uint32_t)(half * 8), u);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) v[c] += u[c];
+          } else {
+            tc::tmem_ld8(tmem + lanes + kTmemC2 + (uint32_t)(cb * 16 + half * 8), v);
+          }
+          const int row = 4 * (warp & 3) + (lane >> 3), col = 8 * cb + (lane & 7);
+          const int ph = row >> 1, pw = col >> 1;
+          const bool mine = !(lane & 1) && !((lane >> 3) & 1) && ph < 5 && pw < 5;
+          const uint32_t partner = R.base[paired ? (r ^ 1) : r];
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const int o = half * 8 + c;
+            const float a00 = fmaxf(v[c] + s.cw[kOffB2 + o], 0.f);
+            const float a01 = __shfl_xor_sync(0xffffffffu, a00, 1);
+            const float a10 = __shfl_xor_sync(0xffffffffu, a00, 8);
+            const float a11 = __shfl_xor_sync(0xffffffffu, a00, 9);
+            float best = a00;
+            int bi = 0;
+            if (a01 > best) { best = a01; bi = 1; }
+            if (a10 > best) { best = a10; bi = 2; }
+            if (a11 > best) { best = a11; bi = 3; }
+            if (mine) {
+              const int oi = o * 25 + ph * 5 + pw;
+              s.p2[oi] = best;
+              s.idx2[oi] = bi;
+              if (paired) {   // my tile's share of p2 for the partner, which computed the other tile
+                cl_st_async(partner + CL_OFF(p2) + 4u * (uint32_t)oi, __float_as_uint(best), partner + CL_BAR(kBarP2));
+                cl_st_async(partner + CL_OFF(idx2) + 4u * (uint32_t)oi, (uint32_t)bi, partner + CL_BAR(kBarP2));
+              }
+            }
+          }
+        }
+      }
+      tc::tc_fence_before();
+      if (paired) cl_mbar_wait(&s.sbar[kBarP2], phase);   // the partner's tile has landed
+      __syncthreads();   // p2 / idx2 complete in this CTA
+    } else {
+      // ================= conv1 + bias + ReLU + maxpool, my pooled pixels =================
+      // (split by pooled PIXEL range, not by row: 196 pixels divide evenly over any cluster size)
+      {
+        const int npx = nq;
+        for (int item = tid; item < npx * 6; item += kCLThreads) {
+          const int ch = item / npx, px = item - ch * npx;
+          const int ph = (q0 + px) / 14, pw = (q0 + px) % 14;
+          float a00 = 0.f, a01 = 0.f, a10 = 0.f, a11 = 0.f;
+  #pragma unroll 1
+          for (int c = 0; c < 3; ++c) {
+            const float* xb = s.x + c * kXCh + (2 * ph) * kXRow + 2 * pw;
+            float patch[6][6];
+  #pragma unroll
+            for (int rr = 0; rr < 6; ++rr)
+  #pragma unroll
+              for (int q = 0; q < 3; ++q) {
+                const float2 v = *reinterpret_cast<const float2*>(xb + rr * kXRow + 2 * q);
+                patch[rr][2 * q] = v.x;
+                patch[rr][2 * q + 1] = v.y;
+              }
+            const float* wb = s.cw + kOffW1 + (ch * 3 + c) * 25;
+  #pragma unroll
+            for (int kh = 0; kh < 5; ++kh)
+  #pragma unroll
+              for (int kw = 0; kw < 5; ++kw) {
+                const float w = wb[kh * 5 + kw];
+                a00 += w * patch[kh][kw];
+                a01 += w * patch[kh][kw + 1];
+                a10 += w * patch[kh + 1][kw];
+                a11 += w * patch[kh + 1][kw + 1];
+              }
+          }
+          const float bias = s.cw[kOffB1 + ch];
+          float best = fmaxf(a00 + bias, 0.f);
+          int bi = 0;
+          float v = fmaxf(a01 + bias, 0.f);
+          if (v > best) { best = v; bi = 1; }
+          v = fmaxf(a10 + bias, 0.f);
+          if (v > best) { best = v; bi = 2; }
+          v = fmaxf(a11 + bias, 0.f);
+          if (v > best) { best = v; bi = 3; }
+          const uint32_t oi = (uint32_t)(ch * 196 + ph * 14 + pw);
+          push_all<CS>(R, CL_OFF(p1) + 4u * oi, CL_BAR(kBarP1), __float_as_uint(best));
+          push_all<CS>(R, CL_OFF(idx1) + 4u * oi, CL_BAR(kBarP1), (uint32_t)bi);
+        }
+      }
+      if (first_img) {  // conv2 weights in data-gradient layout [(o,tap)][c8]: built once, off the critical path
+        for (int ot = tid; ot < 400; ot += kCLThreads) {
+          const int o = ot / 25, t = ot - o * 25;
+          const float* src = s.cw + kOffW2 + o * 150 + t;
+          reinterpret_cast<float4*>(s.w2d)[ot * 2] = make_float4(src[0], src[25], src[50], src[75]);
+          reinterpret_cast<float4*>(s.w2d)[ot * 2 + 1] = make_float4(src[100], src[125], 0.f, 0.f);
+        }
+      }
+      CL_TRACE(3);
+      cl_mbar_wait(&s.sbar[kBarP1], phase);
+      CL_TRACE(4);
+
+      // ================= conv2 + bias + ReLU + maxpool, my output channels =================
+      {
+        const int no = o1 - o0;
+        for (int item = tid; item < no * 150; item += kCLThreads) {
+          const int pp = item % 25, oc = item / 25, c = oc % 6, ol = oc / 6;
+          const int ph = pp / 5, pw = pp - ph * 5;
+          const float* xb = s.p1 + c * 196 + (2 * ph) * 14 + 2 * pw;
           float patch[6][6];
-#pragma unroll
+  #pragma unroll
           for (int rr = 0; rr < 6; ++rr)
-#pragma unroll
+  #pragma unroll
             for (int q = 0; q < 3; ++q) {
-              const float2 v = *reinterpret_cast<const float2*>(xb + rr * kXRow + 2 * q);
+              const float2 v = *reinterpret_cast<const float2*>(xb + rr * 14 + 2 * q);
               patch[rr][2 * q] = v.x;
               patch[rr][2 * q + 1] = v.y;
             }
-          const float* wb = s.cw + kOffW1 + (ch * 3 + c) * 25;
-#pragma unroll
+          const float* wb = s.cw + kOffW2 + ((o0 + ol) * 6 + c) * 25;
+          float a00 = 0.f, a01 = 0.f, a10 = 0.f, a11 = 0.f;
+  #pragma unroll
           for (int kh = 0; kh < 5; ++kh)
-#pragma unroll
+  #pragma unroll
             for (int kw = 0; kw < 5; ++kw) {
               const float w = wb[kh * 5 + kw];
               a00 += w * patch[kh][kw];
@@ -528,88 +892,34 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
               a10 += w * patch[kh + 1][kw];
               a11 += w * patch[kh + 1][kw + 1];
             }
+          *reinterpret_cast<float4*>(sred + item * 4) = make_float4(a00, a01, a10, a11);
         }
-        const float bias = s.cw[kOffB1 + ch];
-        float best = fmaxf(a00 + bias, 0.f);
-        int bi = 0;
-        float v = fmaxf(a01 + bias, 0.f);
-        if (v > best) { best = v; bi = 1; }
-        v = fmaxf(a10 + bias, 0.f);
-        if (v > best) { best = v; bi = 2; }
-        v = fmaxf(a11 + bias, 0.f);
-        if (v > best) { best = v; bi = 3; }
-        const uint32_t oi = (uint32_t)(ch * 196 + ph * 14 + pw);
-        push_all<CS>(R, CL_OFF(p1) + 4u * oi, CL_BAR(kBarP1), __float_as_uint(best));
-        push_all<CS>(R, CL_OFF(idx1) + 4u * oi, CL_BAR(kBarP1), (uint32_t)bi);
-      }
-    }
-    if (first_img) {  // conv2 weights in data-gradient layout [(o,tap)][c8]: built once, off the critical path
-      for (int ot = tid; ot < 400; ot += kCLThreads) {
-        const int o = ot / 25, t = ot - o * 25;
-        const float* src = s.cw + kOffW2 + o * 150 + t;
-        reinterpret_cast<float4*>(s.w2d)[ot * 2] = make_float4(src[0], src[25], src[50], src[75]);
-        reinterpret_cast<float4*>(s.w2d)[ot * 2 + 1] = make_float4(src[100], src[125], 0.f, 0.f);
-      }
-    }
-    CL_TRACE(3);
-    cl_mbar_wait(&s.sbar[kBarP1], phase);
-    CL_TRACE(4);
-
-    // ================= conv2 + bias + ReLU + maxpool, my output channels =================
-    {
-      const int no = o1 - o0;
-      for (int item = tid; item < no * 150; item += kCLThreads) {
-        const int pp = item % 25, oc = item / 25, c = oc % 6, ol = oc / 6;
-        const int ph = pp / 5, pw = pp - ph * 5;
-        const float* xb = s.p1 + c * 196 + (2 * ph) * 14 + 2 * pw;
-        float patch[6][6];
-#pragma unroll
-        for (int rr = 0; rr < 6; ++rr)
-#pragma unroll
-          for (int q = 0; q < 3; ++q) {
-            const float2 v = *reinterpret_cast<const float2*>(xb + rr * 14 + 2 * q);
-            patch[rr][2 * q] = v.x;
-            patch[rr][2 * q + 1] = v.y;
+        __syncthreads();
+        for (int t = tid; t < no * 25; t += kCLThreads) {
+          const int ol = t / 25, pp = t - ol * 25, o = o0 + ol;
+          float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  #pragma unroll
+          for (int c = 0; c < 6; ++c) {
+            const float4 q = *reinterpret_cast<const float4*>(sred + ((ol * 6 + c) * 25 + pp) * 4);
+            v.x += q.x; v.y += q.y; v.z += q.z; v.w += q.w;
           }
-        const float* wb = s.cw + kOffW2 + ((o0 + ol) * 6 + c) * 25;
-        float a00 = 0.f, a01 = 0.f, a10 = 0.f, a11 = 0.f;
-#pragma unroll
-        for (int kh = 0; kh < 5; ++kh)
-#pragma unroll
-          for (int kw = 0; kw < 5; ++kw) {
-            const float w = wb[kh * 5 + kw];
-            a00 += w * patch[kh][kw];
-            a01 += w * patch[kh][kw + 1];
-            a10 += w * patch[kh + 1][kw];
-            a11 += w * patch[kh + 1][kw + 1];
-          }
-        *reinterpret_cast<float4*>(sred + item * 4) = make_float4(a00, a01, a10, a11);
-      }
-      __syncthreads();
-      for (int t = tid; t < no * 25; t += kCLThreads) {
-        const int ol = t / 25, pp = t - ol * 25, o = o0 + ol;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-        for (int c = 0; c < 6; ++c) {
-          const float4 q = *reinterpret_cast<const float4*>(sred + ((ol * 6 + c) * 25 + pp) * 4);
-          v.x += q.x; v.y += q.y; v.z += q.z; v.w += q.w;
+          const float bias = s.cw[kOffB2 + o];
+          float best = fmaxf(v.x + bias, 0.f);
+          int bi = 0;
+          float u = fmaxf(v.y + bias, 0.f);
+          if (u > best) { best = u; bi = 1; }
+          u = fmaxf(v.z + bias, 0.f);
+          if (u > best) { best = u; bi = 2; }
+          u = fmaxf(v.w + bias, 0.f);
+          if (u > best) { best = u; bi = 3; }
+          const uint32_t oi = (uint32_t)(o * 25 + pp);
+          push_all<CS>(R, CL_OFF(p2) + 4u * oi, CL_BAR(kBarP2), __float_as_uint(best));
+          push_all<CS>(R, CL_OFF(idx2) + 4u * oi, CL_BAR(kBarP2), (uint32_t)bi);
         }
-        const float bias = s.cw[kOffB2 + o];
-        float best = fmaxf(v.x + bias, 0.f);
-        int bi = 0;
-        float u = fmaxf(v.y + bias, 0.f);
-        if (u > best) { best = u; bi = 1; }
-        u = fmaxf(v.z + bias, 0.f);
-        if (u > best) { best = u; bi = 2; }
-        u = fmaxf(v.w + bias, 0.f);
-        if (u > best) { best = u; bi = 3; }
-        const uint32_t oi = (uint32_t)(o * 25 + pp);
-        push_all<CS>(R, CL_OFF(p2) + 4u * oi, CL_BAR(kBarP2), __float_as_uint(best));
-        push_all<CS>(R, CL_OFF(idx2) + 4u * oi, CL_BAR(kBarP2), (uint32_t)bi);
       }
-    }
     CL_TRACE(5);
-    cl_mbar_wait(&s.sbar[kBarP2], phase);
+      cl_mbar_wait(&s.sbar[kBarP2], phase);
+    }
     CL_TRACE(6);
 
     // ================= fc1, fc2 (rows split), fc3 + softmax-CE (redundant) =================
@@ -682,7 +992,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       __syncthreads();
       CL_TRACE(9);
       fc_dx_partial_push<CS, kFlat>(f.wf1, s.d1, f1m0, f1m1, r, R, kRxG2, CL_BAR(kBarG2));
-      for (int i = tid; i < 16 * 18 * 18; i += kCLThreads) s.dc2p[i] = 0.f;  // while the partials are in flight
+      zero_grad_plane();  // while the partials are in flight
       cl_mbar_wait(&s.sbar[kBarG2], phase);
       if (tid < kFlat) {
         float a = 0.f;
@@ -700,8 +1010,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       CL_TRACE(9);
       __syncthreads();  // `red` is reused by the next split
       fc_dx_split_push<CS, kF1, kFlat>(params + kOffF1W, s.d1, s.p2, g2k0, g2k1, sred, R, CL_OFF(g2), CL_BAR(kBarG2));
-      // zero the dense gradient plane while the g2 traffic is in flight
-      for (int i = tid; i < 16 * 18 * 18; i += kCLThreads) s.dc2p[i] = 0.f;
+      zero_grad_plane();  // while the g2 traffic is in flight
       cl_mbar_wait(&s.sbar[kBarG2], phase);
       __syncthreads();
       CL_TRACE(10);
@@ -718,7 +1027,12 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     if (tid < 400) {  // scatter the pooled gradient to its argmax position (maxpool backward)
       const int o = tid / 25, pp = tid - o * 25, ph = pp / 5, pw = pp - ph * 5;
       const int id = s.idx2[tid];
-      s.dc2p[o * 324 + (2 * ph + (id >> 1) + 4) * 18 + (2 * pw + (id & 1) + 4)] = s.g2[tid];
+      if constexpr (kTC) {
+        s.dpl[(((o >> 2) * kDPlanePix) + (2 * ph + (id >> 1) + 4) * kDPitch + (2 * pw + (id & 1) + 4)) * 4 + (o & 3)] = s.g2[tid];
+        tc::fence_proxy_async();
+      } else {
+        s.dc2p[o * 324 + (2 * ph + (id >> 1) + 4) * 18 + (2 * pw + (id & 1) + 4)] = s.g2[tid];
+      }
     }
     __syncthreads();  // the data-gradient items below read the plane just scattered
 
@@ -727,12 +1041,37 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     // first, the weight-gradient items fill the remaining threads, and only two block barriers are needed.
     {
       const int no = o1 - o0;
-      const int n_dg = nq * 16;           // data gradient: (o, pixel) -> 6 channel sums
-      const int n_wg = no * 30 * 5;       // weight gradient: (pixel row, o, c, kh) -> 5 taps
-      float* red_dg = sred;              // [16*6][nq]
-      float* red_wg = sred + 96 * nq;    // [5][no*150]
+      const int n_dg = kTC ? 0 : nq * 16;   // data gradient: (o, pixel) -> 6 channel sums (kTC: on the tensor core instead)
+      const int n_wg = no * 30 * 5;         // weight gradient: (pixel row, o, c, kh) -> 5 taps
+      float* red_dg = sred;                            // [16*6][nq]
+      float* red_wg = kTC ? sred : sred + 96 * nq;     // [5][no*150]
+      // kTC: dX[c][ih][iw] = sum_{o,a,b} dCp[o][ih+a][iw+b] W[o][c][4-a][4-b] as ONE 128-row tile of the implicit GEMM
+      // over the zero-padded gradient planes: GEMM row m = ih*18 + iw, my pixel rows start at row dg_m0 of the plane
+      // (clamped so that the tile ends inside the plane; any cluster size's pixel range spans fewer than 128 rows).
+      const int dg_m0 = min((q0 / 14) * kDPitch, 128);
+      if constexpr (kTC) {
+        if (lane == 0 && warp < 2) {   // two issuing threads, 25 MMAs each, into two accumulators (added in the epilogue)
+          tc::tc_fence_after();
+          constexpr uint32_t kIdesc = tc::idesc_tf32(128, 16);
+          // K-chunks of MMA j = two of the four channel planes of tap j/2: planes 0,1 for even j, 2,3 for odd j
+          const uint64_t a0 = tc::smem_desc_nosw(tc::smem_u32(s.dpl) + (uint32_t)dg_m0 * 16, kDPlanePix * 16, 128);
+          const uint64_t b0 = tc::smem_desc_nosw(tc::smem_u32(s.sbd), 128, kBdChunks * 128);
+          const uint32_t d = tmem + kTmemDg + (uint32_t)warp * 16;
+          const int j0 = 25 * warp;
+          int tap = j0 >> 1, kh = tap / 5, kw = tap - kh * 5;
+#pragma unroll 5
+          for (int j = j0; j < j0 + 25; ++j) {
+            tc::mma_tf32(d, a0 + (uint64_t)(kh * kDPitch + kw + (j & 1) * (2 * kDPlanePix)), b0 + (uint64_t)(16 * j), kIdesc,
+                         j > j0);
+            if (j & 1) { if (++kw == 5) { kw = 0; ++kh; } }
+          }
+          tc::mma_commit(reinterpret_cast<uint64_t*>(&s.tbar[kTBarDg]));
+          if (warp == 0) CL_TRACE(21);
+        }
+      }
       for (int item = tid; item < n_dg + n_wg; item += kCLThreads) {
         if (item < n_dg) {
+         if constexpr (!kTC) {
           const int o = item / nq, ql = item - o * nq, q = q0 + ql;
           const int ih = q / 14, iw = q - ih * 14;
           float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -753,6 +1092,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
           }
 #pragma unroll
           for (int c = 0; c < 6; ++c) red_dg[(o * 6 + c) * nq + ql] = acc[c];
+         }
         } else {
           const int t = item - n_dg, nitem = no * 30;
           const int pg = t / nitem, rem = t - pg * nitem;
@@ -763,8 +1103,13 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
             const int pp = pg * 5 + k;  // pooled row pg, column k
             const float g = s.g2[o * 25 + pp];
             const int id = s.idx2[o * 25 + pp];
-            const float* row = s.p1 + c * 196 + (2 * pg + (id >> 1) + kh) * 14 + 2 * k + (id & 1);
-            a0 += g * row[0]; a1 += g * row[1]; a2 += g * row[2]; a3 += g * row[3]; a4 += g * row[4];
+            if constexpr (kTC) {   // p1 is NHWC4 here: consecutive pixels are 4 floats apart
+              const float* row = s.p1n + (((c >> 2) * kP1PlanePix) + (2 * pg + (id >> 1) + kh) * 14 + 2 * k + (id & 1)) * 4 + (c & 3);
+              a0 += g * row[0]; a1 += g * row[4]; a2 += g * row[8]; a3 += g * row[12]; a4 += g * row[16];
+            } else {
+              const float* row = s.p1 + c * 196 + (2 * pg + (id >> 1) + kh) * 14 + 2 * k + (id & 1);
+              a0 += g * row[0]; a1 += g * row[1]; a2 += g * row[2]; a3 += g * row[3]; a4 += g * row[4];
+            }
           }
           float* dst = red_wg + pg * (no * 150) + ol * 150 + c * 25 + kh * 5;
           dst[0] = a0; dst[1] = a1; dst[2] = a2; dst[3] = a3; dst[4] = a4;
@@ -772,16 +1117,38 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       }
       __syncthreads();
       CL_TRACE(11);
+      if constexpr (kTC) {
+        cl_mbar_wait(&s.tbar[kTBarDg], phase);
+        tc::tc_fence_after();
+        if (warp < 4) {   // TMEM lane = GEMM row: dL/dp1 for my pixels, masked by ReLU (stays in this CTA)
+          float v[8], u[8];
+          tc::tmem_ld8(tmem + ((uint32_t)(warp * 32) << 16) + kTmemDg, v);
+          tc::tmem_ld8(tmem + ((uint32_t)(warp * 32) << 16) + kTmemDg + 16, u);
+#pragma unroll
+          for (int c = 0; c < 6; ++c) v[c] += u[c];
+          const int m = dg_m0 + warp * 32 + lane, ih = m / kDPitch, iw = m - ih * kDPitch, q = ih * 14 + iw;
+          if (iw < 14 && q >= q0 && q < q1) {
+#pragma unroll
+            for (int c = 0; c < 6; ++c) {
+              const uint32_t pbits = __float_as_uint(s.p1n[(((c >> 2) * kP1PlanePix) + q) * 4 + (c & 3)]);
+              s.g1[c * 196 + q] = (pbits & ~3u) != 0u ? v[c] : 0.f;   // p1 > 0, ignoring the argmax bits
+            }
+          }
+        }
+        tc::tc_fence_before();
+      }
       float* dst = part2 + (size_t)img * (kConvPrefix - kOffW2);
-      const int n_g1 = nq * 6, n_w2 = no * 150;
+      const int n_g1 = kTC ? 0 : nq * 6, n_w2 = no * 150;
       for (int t = tid; t < n_g1 + n_w2 + no; t += kCLThreads) {
         if (t < n_g1) {                    // dL/dp1 for my pixels, masked by ReLU (stays in this CTA)
+         if constexpr (!kTC) {
           const int c = t / nq, ql = t - c * nq;
           float v = 0.f;
 #pragma unroll
           for (int o = 0; o < 16; ++o) v += red_dg[(o * 6 + c) * nq + ql];
           const int gi = c * 196 + q0 + ql;
           s.g1[gi] = s.p1[gi] > 0.f ? v : 0.f;
+         }
         } else if (t < n_g1 + n_w2) {      // conv2.weight gradient of this image, my channels
           const int u = t - n_g1;
           float a = 0.f;
@@ -806,15 +1173,27 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
         const int pg = tid / 90, rem = tid - pg * 90;
         const int o = rem / 15, r2 = rem - o * 15, c = r2 / 5, kh = r2 - c * 5;
         const float* gp = s.g1 + o * 196;
-        const int* ip = s.idx1 + o * 196;
-        const float* xb = s.x + c * kXCh + kh * kXRow;
         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+        if constexpr (kTC) {   // argmax from the low bits of p1, image from the NHWC4 plane (pixels 4 floats apart)
+          const float* pv = s.p1n + ((o >> 2) * kP1PlanePix) * 4 + (o & 3);
+          const float* xb = s.xpl + (kh * kXPitch) * 4 + c;
 #pragma unroll 4
-        for (int q = q0 + pg; q < q1; q += 5) {
-          const float g = gp[q];
-          const int id = ip[q];
-          const float* row = xb + s.poff[q] + (id >> 1) * kXRow + (id & 1);
-          a0 += g * row[0]; a1 += g * row[1]; a2 += g * row[2]; a3 += g * row[3]; a4 += g * row[4];
+          for (int q = q0 + pg; q < q1; q += 5) {
+            const float g = gp[q];
+            const int id = (int)(__float_as_uint(pv[q * 4]) & 3u);
+            const float* row = xb + (s.poff[q] + (id >> 1) * kXPitch + (id & 1)) * 4;
+            a0 += g * row[0]; a1 += g * row[4]; a2 += g * row[8]; a3 += g * row[12]; a4 += g * row[16];
+          }
+        } else {
+          const int* ip = s.idx1 + o * 196;
+          const float* xb = s.x + c * kXCh + kh * kXRow;
+#pragma unroll 4
+          for (int q = q0 + pg; q < q1; q += 5) {
+            const float g = gp[q];
+            const int id = ip[q];
+            const float* row = xb + s.poff[q] + (id >> 1) * kXRow + (id & 1);
+            a0 += g * row[0]; a1 += g * row[1]; a2 += g * row[2]; a3 += g * row[3]; a4 += g * row[4];
+          }
         }
         float* dst = sred + pg * 450 + o * 75 + c * 25 + kh * 5;
         dst[0] = a0; dst[1] = a1; dst[2] = a2; dst[3] = a3; dst[4] = a4;
@@ -864,16 +1243,21 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       load_image(img + n_clusters);
     }
   }
+  if constexpr (kTC) {
+    tc::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tc::tmem_free<kTmemCols>(tmem);
+  }
 }
 
-template <int CS>
+template <int CS, bool kTC>
 static int launch_cluster_t(const float* params, const float* x, const long long* labels, float* saved, float* part1,
                             float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
                             long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
                             cudaStream_t stream) {
   static PerDeviceOnce attr_set;
-  auto kern = fwd_bwd_cluster_kernel<CS>;
-  const size_t smem = cluster_smem_bytes<CS>();
+  auto kern = fwd_bwd_cluster_kernel<CS, kTC>;
+  const size_t smem = cluster_smem_bytes<CS, kTC>();
   if (int rc = ensure_max_dynamic_smem(attr_set, kern, smem)) return rc;
   const int n_clusters = B < max_clusters ? B : max_clusters;
   cudaLaunchConfig_t cfg = {};
@@ -908,12 +1292,12 @@ int pick_cluster_size(int B, int num_sms) {
 }
 
 // how many clusters of CS CTAs of this kernel the device can hold at once
-template <int CS>
+template <int CS, bool kTC>
 static int max_active_clusters_t() {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(CS * 64);
   cfg.blockDim = dim3(kCLThreads);
-  cfg.dynamicSmemBytes = cluster_smem_bytes<CS>();
+  cfg.dynamicSmemBytes = cluster_smem_bytes<CS, kTC>();
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CS;
@@ -922,41 +1306,57 @@ static int max_active_clusters_t() {
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   int n = 0;
-  cudaFuncSetAttribute(fwd_bwd_cluster_kernel<CS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                       (int)cluster_smem_bytes<CS>());
-  if (cudaOccupancyMaxActiveClusters(&n, fwd_bwd_cluster_kernel<CS>, &cfg) != cudaSuccess) {
+  cudaFuncSetAttribute(fwd_bwd_cluster_kernel<CS, kTC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                       (int)cluster_smem_bytes<CS, kTC>());
+  if (cudaOccupancyMaxActiveClusters(&n, fwd_bwd_cluster_kernel<CS, kTC>, &cfg) != cudaSuccess) {
     cudaGetLastError();
     return 0;
   }
   return n;
 }
-int max_active_clusters(int cs) {
+template <bool kTC>
+static int max_active_clusters_p(int cs) {
   switch (cs) {
-    case 2: return max_active_clusters_t<2>();
-    case 3: return max_active_clusters_t<3>();
-    case 4: return max_active_clusters_t<4>();
-    case 5: return max_active_clusters_t<5>();
-    case 6: return max_active_clusters_t<6>();
-    case 7: return max_active_clusters_t<7>();
-    case 8: return max_active_clusters_t<8>();
+    case 2: return max_active_clusters_t<2, kTC>();
+    case 3: return max_active_clusters_t<3, kTC>();
+    case 4: return max_active_clusters_t<4, kTC>();
+    case 5: return max_active_clusters_t<5, kTC>();
+    case 6: return max_active_clusters_t<6, kTC>();
+    case 7: return max_active_clusters_t<7, kTC>();
+    case 8: return max_active_clusters_t<8, kTC>();
     default: return 0;
   }
 }
+int max_active_clusters(int cs, bool tensor_cores) {
+  return tensor_cores ? max_active_clusters_p<true>(cs) : max_active_clusters_p<false>(cs);
+}
 
-int launch_fwd_bwd_cluster(int cs, const float* params, const float* x, const long long* labels, float* saved,
-                           float* part1, float* part2, float* img_loss, int* img_correct, int B, int num_sms /* = max resident clusters */,
-                           long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
-                           cudaStream_t stream) {
+template <bool kTC>
+static int launch_cluster_p(int cs, const float* params, const float* x, const long long* labels, float* saved,
+                            float* part1, float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
+                            long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
+                            cudaStream_t stream) {
+#define DNN_CL_CASE(N)                                                                                              \
+  case N:                                                                                                           \
+    return launch_cluster_t<N, kTC>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, max_clusters, \
+                                    trace, ready_ctr, ready_expect, stream);
   switch (cs) {
-    case 8: return launch_cluster_t<8>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, ready_ctr, ready_expect, stream);
-    case 7: return launch_cluster_t<7>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, ready_ctr, ready_expect, stream);
-    case 6: return launch_cluster_t<6>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, ready_ctr, ready_expect, stream);
-    case 5: return launch_cluster_t<5>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, ready_ctr, ready_expect, stream);
-    case 4: return launch_cluster_t<4>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, ready_ctr, ready_expect, stream);
-    case 3: return launch_cluster_t<3>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, ready_ctr, ready_expect, stream);
-    case 2: return launch_cluster_t<2>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, num_sms, trace, ready_ctr, ready_expect, stream);
+    DNN_CL_CASE(8) DNN_CL_CASE(7) DNN_CL_CASE(6) DNN_CL_CASE(5) DNN_CL_CASE(4) DNN_CL_CASE(3) DNN_CL_CASE(2)
     default: set_last_error("cluster size %d not supported", cs); return kErrArg;
   }
+#undef DNN_CL_CASE
+}
+
+// tensor_cores: conv1/conv2 forward and the conv2 data gradient on tcgen05 (TF32 operands, fp32 accumulate);
+// false: everything fp32 FFMA (the parity path, bit-comparable in structure with the one-CTA kernel)
+int launch_fwd_bwd_cluster(int cs, bool tensor_cores, const float* params, const float* x, const long long* labels,
+                           float* saved, float* part1, float* part2, float* img_loss, int* img_correct, int B,
+                           int max_clusters, long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
+                           cudaStream_t stream) {
+  return tensor_cores ? launch_cluster_p<true>(cs, params, x, labels, saved, part1, part2, img_loss, img_correct, B,
+                                               max_clusters, trace, ready_ctr, ready_expect, stream)
+                      : launch_cluster_p<false>(cs, params, x, labels, saved, part1, part2, img_loss, img_correct, B,
+                                                max_clusters, trace, ready_ctr, ready_expect, stream);
 }
 
 }  // namespace dnnb200

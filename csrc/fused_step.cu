@@ -18,6 +18,7 @@
 // with the 2-bit argmax as an address offset (4x fewer MACs than the dense form),
 // and ReLU'/pool' cost nothing (K14/K15 fused away).
 #include <cuda_runtime.h>
+#include <type_traits>
 #include <stdint.h>
 
 #include "common.cuh"
@@ -585,11 +586,13 @@ __device__ __forceinline__ float2 local_grad2(const RankCtx& cx, int i, int B, i
 //      and the NEXT step's clusters cannot be placed there until those CTAs have exited -- which, after NVLink
 //      stores, takes ~3 us longer than their last instruction (the stores drain first). Measured at 2 GPUs:
 //      25.3 -> 22.4 us per step; on one GPU the same budget costs 0.7 us, hence two instantiations.
-template <bool kEmulated, int kMinBlocks>
+// kExchange = false: the instantiation for a rank without peers carries no exchange code at all (and no register
+// pressure from it).
+template <bool kEmulated, int kMinBlocks, bool kExchange>
 __global__ void __launch_bounds__(kUpdThreads, kMinBlocks)
 update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slot, int flags,
               float* __restrict__ host_loss) {
-  __shared__ ExchangeShared xsh;
+  __shared__ typename std::conditional<kExchange, ExchangeShared, int>::type xsh;
   __shared__ RankCtx cx;        // this rank's context and ...
   __shared__ StepCtl ctl_snap;  // ... the host-set fields of its control block, staged BEFORE the dependency wait
   const int slice = blockIdx.x, tid = threadIdx.x;
@@ -678,8 +681,8 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
   }
   int n = 1;
   if (tr && tid == 0) tr[slice * 8 + 2] = (long long)globaltimer_ns();
-  if (cx.world > 1 && !grad_only) {
-    const unsigned int variant = ctl_snap.two_shot;   // 0 one-shot, 1 two-shot, 2 NVLS
+  if constexpr (kExchange) if (cx.world > 1 && !grad_only) {
+    const unsigned int variant = ctl_snap.two_shot;   // 0 one-shot, 1 two-shot, 2 NVLS, 3 one-shot with 128-byte lines
     ExchangeCfg cfg;
     cfg.configured = ctl_snap.active_mask;
     cfg.timeout_ns = ctl_snap.timeout_ns;
@@ -691,7 +694,10 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
     }
     else exchange_slice<kUVec>(cx, cfg, &xsh, slice, seq, i, in_range, v, &n);
   }
-  if (tr && tid == 0) tr[slice * 8 + 3] = (long long)globaltimer_ns();
+  if (tr && tid == 0) {
+    tr[slice * 8 + 3] = (long long)globaltimer_ns();
+    tr[slice * 8 + 7] = n;   // how many ranks entered this slice's sum (the divisor unless the host overrides it)
+  }
 
   if (in_range && grad_only) {
     if (cx.grads) {
@@ -789,7 +795,7 @@ int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int n_part1
   if (n_virtual_ranks > 1) {
     // ranks emulated on ONE device wait on each other: every CTA must be resident
     void* args[] = {(void*)&d_ctxs, (void*)&B, (void*)&n_part1, (void*)&loss_slot, (void*)&flags, (void*)&host_loss};
-    DNN_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)update_kernel<true, 7>, grid, dim3(kUpdThreads), args, 0, stream));
+    DNN_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)update_kernel<true, 7, true>, grid, dim3(kUpdThreads), args, 0, stream));
   } else {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
@@ -802,9 +808,11 @@ int launch_update(const RankCtx* d_ctxs, int n_virtual_ranks, int B, int n_part1
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     if (flags & kUpdFlagPeers)
-      DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, update_kernel<false, 3>, d_ctxs, B, n_part1, loss_slot, flags, host_loss));
+      DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, update_kernel<false, 3, true>, d_ctxs, B, n_part1, loss_slot, flags, host_loss));
+    else if (flags & kUpdFlagHasGroup)   // peers, but the A/B switch asked for the unconstrained register budget
+      DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, update_kernel<false, 1, true>, d_ctxs, B, n_part1, loss_slot, flags, host_loss));
     else
-      DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, update_kernel<false, 1>, d_ctxs, B, n_part1, loss_slot, flags, host_loss));
+      DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, update_kernel<false, 1, false>, d_ctxs, B, n_part1, loss_slot, flags, host_loss));
   }
   return kOk;
 }

@@ -35,11 +35,11 @@ void set_last_error(const char* fmt, ...) {
 int launch_fwd_bwd(bool train, const float* params, const float* x, const long long* labels, float* saved,
                    float* part1, float* part2, float* img_loss, int* img_correct, float* logits_out, int B,
                    int max_ctas, cudaStream_t stream);
-int launch_fwd_bwd_cluster(int cs, const float* params, const float* x, const long long* labels, float* saved,
-                           float* part1, float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
-                           long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
+int launch_fwd_bwd_cluster(int cs, bool tensor_cores, const float* params, const float* x, const long long* labels,
+                           float* saved, float* part1, float* part2, float* img_loss, int* img_correct, int B,
+                           int max_clusters, long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
                            cudaStream_t stream);
-int max_active_clusters(int cs);
+int max_active_clusters(int cs, bool tensor_cores);
 int launch_pingpong(const RankCtx* d_ctx, int peer, int iters, unsigned int base_seq, long long* d_out_ns,
                     cudaStream_t stream);
 int launch_ll128_probe(const RankCtx* d_ctx, int peer, int iters, int n_ctas, unsigned int base_seq,
@@ -64,6 +64,8 @@ int launch_tc_gemm_probe(const float*, const float*, float*, int, cudaStream_t);
 int launch_tc_linear_fwd(const float*, const float*, const float*, float*, int, int, int, int, cudaStream_t);
 int launch_tc_lab(const float*, int, const float*, int, unsigned long long, unsigned long long, unsigned int, int, int,
                   int, float*, int, cudaStream_t);
+int launch_tc_lab_time(int, int, unsigned long long, unsigned long long, unsigned int, int, int, int, int, int, long long*,
+                       cudaStream_t);
 int launch_tc_linear_bwd(const float*, const float*, const float*, const float*, float*, float*, float*, float*, int,
                          int, int, int, cudaStream_t);
 
@@ -111,7 +113,9 @@ struct dnnb200_engine {
   unsigned int updates_launched = 0;   // update kernels launched on d_ctx == StepCtl::updates_done once they finish
   int debug_flags = 0;             // OR-ed into the update kernel's flags (bit 1: no early launch of the successor)
   int forced_cluster = 0;          // 0 = pick per batch size
-  int max_clusters[9] = {};        // resident clusters of the fwd/bwd kernel per cluster size (index = CS)
+  int max_clusters[9] = {};        // resident clusters of the fwd/bwd kernel per cluster size (index = CS), for `tf32`
+  int max_clusters_p[2][9] = {};   // the same for both precisions ([0] fp32 FFMA, [1] TF32 tensor cores)
+  int tf32 = 1;                    // conv stages of the clustered kernel on tcgen05 (default) or fp32 FFMA
   int* img_correct = nullptr;
   float* eval_loss = nullptr;
   int* eval_correct = nullptr;
@@ -266,7 +270,7 @@ static int fwd_bwd_any(dnnb200_engine* e, const float* x, const long long* y, in
   if (cs == 1)
     return launch_fwd_bwd(true, e->params, x, y, e->saved, e->part1, e->part2, e->img_loss, e->img_correct, nullptr,
                           B, e->num_sms, s);
-  return launch_fwd_bwd_cluster(cs, e->params, x, y, e->saved, e->part1, e->part2, e->img_loss, e->img_correct, B,
+  return launch_fwd_bwd_cluster(cs, e->tf32 != 0, e->params, x, y, e->saved, e->part1, e->part2, e->img_loss, e->img_correct, B,
                                 e->max_clusters[cs] > 0 ? e->max_clusters[cs] : 1, e->trace,
                                 chained && !(e->debug_flags & 8) ? &e->ctl->updates_done : nullptr, e->updates_launched, s);
 }
@@ -279,7 +283,8 @@ static inline bool stream_capturing(cudaStream_t s) {
 }
 
 static inline int peers_flag(const dnnb200_engine* e) {
-  return (e->h_ctx.world > 1 && !(e->debug_flags & 32)) ? (int)kUpdFlagPeers : 0;   // debug bit 32: A/B switch
+  if (e->h_ctx.world <= 1) return 0;
+  return (int)kUpdFlagHasGroup | ((e->debug_flags & 32) ? 0 : (int)kUpdFlagPeers);   // debug bit 32: A/B switch
 }
 
 static int step_kernels(dnnb200_engine* e, const float* x, const long long* y, int B, int flags, cudaStream_t s,
@@ -349,6 +354,11 @@ int dnnb200_tc_lab(const float* a_img, int a_floats, const float* b_img, int b_f
                    void* stream) {
   return launch_tc_lab(a_img, a_floats, b_img, b_floats, adesc, bdesc, idesc, nmma, a_step, b_step, D, ncols,
                        (cudaStream_t)stream);
+}
+int dnnb200_tc_lab_time(int a_bytes, int b_bytes, unsigned long long adesc, unsigned long long bdesc, unsigned int idesc,
+                        int nmma, int a_step, int b_step, int n_acc, int acc_cols, long long* d_out2, void* stream) {
+  return launch_tc_lab_time(a_bytes, b_bytes, adesc, bdesc, idesc, nmma, a_step, b_step, n_acc, acc_cols, d_out2,
+                            (cudaStream_t)stream);
 }
 int dnnb200_tc_gemm_probe(const float* A, const float* B, float* D, int K, void* stream) {
   return launch_tc_gemm_probe(A, B, D, K, (cudaStream_t)stream);
@@ -440,7 +450,11 @@ static int engine_fill(dnnb200_engine* e, float* params, float* momentum, float*
   DNN_CUDA_CHECK(cudaMemset(e->part1, 0, (size_t)max_batch * 8 * kOffW2 * sizeof(float)));
   DNN_CUDA_CHECK(cudaMalloc(&e->part2, (size_t)max_batch * (kConvPrefix - kOffW2) * sizeof(float)));
   DNN_CUDA_CHECK(cudaMemset(e->part2, 0, (size_t)max_batch * (kConvPrefix - kOffW2) * sizeof(float)));
-  for (int cs = 2; cs <= 8; ++cs) e->max_clusters[cs] = max_active_clusters(cs);
+  for (int cs = 2; cs <= 8; ++cs) {
+    e->max_clusters_p[0][cs] = max_active_clusters(cs, false);
+    e->max_clusters_p[1][cs] = max_active_clusters(cs, true);
+    e->max_clusters[cs] = e->max_clusters_p[e->tf32][cs];
+  }
   DNN_CUDA_CHECK(cudaMemset(e->saved, 0, (size_t)max_batch * kSavStride * sizeof(float)));
   DNN_CUDA_CHECK(cudaMalloc(&e->img_loss, (size_t)max_batch * sizeof(float)));
   DNN_CUDA_CHECK(cudaMalloc(&e->img_correct, (size_t)max_batch * sizeof(int)));
@@ -539,6 +553,8 @@ int dnnb200_engine_set_exchange_variant(dnnb200_engine* e, int two_shot, void* s
   DNN_ARG_CHECK(two_shot >= 0 && two_shot <= 3,
                 "exchange variant must be 0 (one-shot), 1 (two-shot), 2 (NVLS) or 3 (one-shot, 128-byte lines)");
   DNN_ARG_CHECK(two_shot != 2 || e->h_ctx.nvls_mc != nullptr, "the NVLS variant needs dnnb200_engine_attach_nvls first");
+  DNN_ARG_CHECK(two_shot != 3 || e->h_ctx.world <= 8, "the 128-byte-line variant handles at most 8 ranks, this group has %d",
+                e->h_ctx.world);
   ctl_set_variant_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(e->ctl, (unsigned int)two_shot);
   DNN_CUDA_CHECK(cudaGetLastError());
   return kOk;
@@ -579,6 +595,15 @@ int dnnb200_engine_set_cluster_size(dnnb200_engine* e, int cs) {
   DNN_ARG_CHECK(cs >= 0 && cs <= 8, "cluster size must be 0 (auto) or 1..8");
   DNN_ARG_CHECK(cs <= 1 || e->max_clusters[cs] > 0, "clusters of %d CTAs cannot be scheduled on this device", cs);
   e->forced_cluster = cs;
+  return kOk;
+}
+
+int dnnb200_engine_set_precision(dnnb200_engine* e, int tf32) {
+  DNN_ARG_CHECK(e, "null engine");
+  DNN_ARG_CHECK(tf32 == 0 || tf32 == 1, "precision must be 0 (fp32 FFMA) or 1 (TF32 tensor cores)");
+  e->tf32 = tf32;
+  for (int cs = 2; cs <= 8; ++cs) e->max_clusters[cs] = e->max_clusters_p[tf32][cs];
+  if (e->forced_cluster > 1 && e->max_clusters[e->forced_cluster] <= 0) e->forced_cluster = 0;
   return kOk;
 }
 
@@ -774,6 +799,7 @@ int dnnb200_engine_allreduce(dnnb200_engine* e, const float* in, float* out, int
   DNN_ARG_CHECK(e && in, "engine_allreduce: null argument");
   DNN_ARG_CHECK(two_shot != 2 || (e->h_ctx.nvls_mc != nullptr && e->h_ctx.nvls_local != nullptr),
                 "engine_allreduce: the NVLS variant needs dnnb200_engine_attach_nvls first");
+  DNN_ARG_CHECK(two_shot != 3 || e->h_ctx.world <= 8, "engine_allreduce: the 128-byte-line variant handles at most 8 ranks");
   const float* ins[1] = {in};
   float* outs[1] = {out};
   int rc = launch_allreduce(e->d_ctx, 1, ins, outs, n, mode, two_shot, (cudaStream_t)stream);

@@ -24,6 +24,7 @@ enum UpdateFlags : int {
   kUpdFlagTraceRing = 4,   // trace buffer keeps the last 1024 steps
   kUpdFlagPeers = 16,      // this rank exchanges with real peers: use the instantiation that fits beside the
                            // forward/backward kernel (see update_kernel)
+  kUpdFlagHasGroup = 64,   // a group of more than one rank is attached (set even when the A/B switch clears bit 16)
 };
 
 enum StepStatus : unsigned int {

@@ -53,6 +53,22 @@ class Ctl(C.Structure):
     ]
 
 
+# Arithmetic of the conv stages of the clustered step kernel: "tf32" = tcgen05 implicit GEMMs (TF32 operands, fp32
+# accumulate; the product default), "fp32" = FFMA throughout (matches PyTorch fp32 to 2e-5; what the parity tests use).
+_default_precision = os.environ.get("DNNB200_PRECISION", "tf32")
+
+
+def set_default_precision(p: str) -> None:
+    global _default_precision
+    if p not in ("tf32", "fp32"):
+        raise ValueError("precision must be 'tf32' or 'fp32'")
+    _default_precision = p
+
+
+def default_precision() -> str:
+    return _default_precision
+
+
 EXCHANGE_VARIANTS = {"one-shot": 0, "two-shot": 1, "nvls": 2, "one-shot-128": 3}
 
 
@@ -270,7 +286,7 @@ class Engine:
     """Owns the step buffers; updates ``params``/``momentum`` (flat CUDA tensors) in place."""
 
     def __init__(self, params: torch.Tensor, momentum: torch.Tensor, grads: Optional[torch.Tensor],
-                 max_batch: int, lr: float, mu: float):
+                 max_batch: int, lr: float, mu: float, precision: Optional[str] = None):
         lib = require()
         for name, t in (("params", params), ("momentum", momentum)):
             _f32(t, name)
@@ -283,6 +299,8 @@ class Engine:
         with torch.cuda.device(params.device):
             _check(lib.dnnb200_engine_create(_p(params), _p(momentum), _p(grads), max_batch, C.c_float(lr),
                                              C.c_float(mu), C.byref(self._h)))
+        self.precision = ""
+        self.set_precision(precision or _default_precision)
 
     # -- configuration
     def attach_group(self, group: Optional[Group]) -> None:
@@ -304,6 +322,14 @@ class Engine:
     def set_divisor(self, divisor: int) -> None:
         """0 = divide exchanged sums by the ranks present; n = divide by n."""
         _check(require().dnnb200_engine_set_divisor(self._h, C.c_uint(divisor), _stream()))
+
+    def set_precision(self, precision: str) -> None:
+        """"tf32": conv1/conv2 forward and the conv2 data gradient of the clustered step kernel run as implicit GEMMs
+        on the tensor cores (tcgen05, TF32 operands, fp32 accumulation); "fp32": FFMA throughout."""
+        if precision not in ("tf32", "fp32"):
+            raise ValueError("precision must be 'tf32' or 'fp32'")
+        _check(require().dnnb200_engine_set_precision(self._h, 1 if precision == "tf32" else 0))
+        self.precision = precision
 
     def zero_momentum(self) -> None:
         _check(require().dnnb200_engine_zero_momentum(self._h, _stream()))

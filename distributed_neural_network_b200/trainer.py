@@ -72,6 +72,8 @@ class TrainConfig:
     allreduce_variant: str = "auto"        # auto (measured at start-up) | one-shot | one-shot-128 | two-shot | nvls
     calibrate_exchange: bool = True        # auto: time every usable variant on this world size and take the fastest
     calibrate_steps: int = 300
+    precision: Optional[str] = None        # conv stages of the fused step: tf32 (tensor cores, the default) | fp32 (FFMA,
+                                           # parity with PyTorch fp32); None = native.default_precision()
     exchange_timing: bool = True           # per-epoch "allreduce_us" in the JSONL (the reference books its
                                            # mpi_communication_time_children, data_parallelism_train.py:209-213)
     peer_timeout_s: float = 30.0
@@ -144,13 +146,14 @@ class Trainer:
         self.group: Optional[native.Group] = None
         self.first_step = True
         self.nvls_ok = False
+        self._nvls_probed = False
         self._utrace: Optional[torch.Tensor] = None
         self.last_exchange_us: Optional[float] = None  # median exposed exchange per step over the epoch's last steps
         self.exchange_choice: Optional[str] = None     # measured winner (calibrate_exchange)
         self.exchange_table: Dict = {}
         if self.device.type == "cuda":
             self.engine = native.Engine(self.model.flat_params, self.momentum, None, max(cfg.batch_size, 1),
-                                        cfg.lr, cfg.momentum)
+                                        cfg.lr, cfg.momentum, precision=cfg.precision)
             if self.world > 1:
                 self.group = native.Group(self.rank, self.world)
                 handles = self.comm.allgather(self.group.handle)
@@ -163,7 +166,8 @@ class Trainer:
                     self.nvls_buf, self.nvls_mc = made
                     self.engine.attach_nvls(self.nvls_buf, self.nvls_mc)
                     self.nvls_ok = True
-                    self._apply_membership()
+                self._nvls_probed = True
+                self._apply_membership()
         self.failure = FailureSimulator(cfg.failure_probability, cfg.failure_duration, cfg.failure_mode, cfg.seed,
                                         self.rank)
         self.dropped = False
@@ -216,7 +220,7 @@ class Trainer:
         v = self.cfg.allreduce_variant
         usable = self._usable_variants()
         if v != "auto":
-            if v == "nvls" and not self.nvls_ok:
+            if v == "nvls" and not self.nvls_ok and self._nvls_probed:
                 raise RuntimeError("--allreduce-variant nvls: NVLink multicast is not available to this job")
             return native.variant_id(v if v in usable else "one-shot")
         if self.exchange_choice in usable:

@@ -50,6 +50,9 @@ def add_new_flags(p: argparse.ArgumentParser, sync_default: str) -> None:
     g.add_argument("--allreduce-variant", default="auto", choices=["auto", "one-shot", "one-shot-128", "two-shot", "nvls"],
                    help="gradient exchange: one-shot push, two-shot (owner-reduce + broadcast), chosen by world size, or "
                         "(parameter averaging only) nvls = in-switch reduction over NVLink multicast")
+    g.add_argument("--precision", default=None, choices=["tf32", "fp32"],
+                   help="convolution stages of the fused GPU step: tf32 = tcgen05 tensor cores (default), "
+                        "fp32 = FFMA throughout (bit-level parity runs against PyTorch fp32)")
     g.add_argument("--neptune", action="store_true", help="log to Neptune (needs NEPTUNE_API_TOKEN in the environment)")
     g.add_argument("--quiet", action="store_true")
 
@@ -64,4 +67,4 @@ def config_from_args(a: argparse.Namespace) -> TrainConfig:
         device=a.device, data_root=a.data_root, synthetic=True if a.synthetic else None,
         train_size=a.train_size, test_size=a.test_size, seed=a.seed, log_dir=a.log_dir, jsonl=a.jsonl,
         save=a.save, resume=a.resume, input_pipeline=a.input_pipeline, allreduce_variant=a.allreduce_variant,
-        neptune=a.neptune, quiet=a.quiet)
+        neptune=a.neptune, quiet=a.quiet, precision=a.precision)

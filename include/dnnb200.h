@@ -55,6 +55,10 @@ int dnnb200_tc_conv_relu_pool_fwd(const float* x, const float* w, const float* b
 int dnnb200_tc_lab(const float* a_img, int a_floats, const float* b_img, int b_floats, unsigned long long adesc,
                    unsigned long long bdesc, unsigned int idesc, int nmma, int a_step, int b_step, float* D,
                    int ncols, void* stream);
+/* timing twin: nmma MMAs over zeroed operands of a_bytes / b_bytes, accumulating round-robin into n_acc tiles of
+ * acc_cols tensor-memory columns; d_out2 (device) = {cycles spent issuing, cycles until the commit barrier fired} */
+int dnnb200_tc_lab_time(int a_bytes, int b_bytes, unsigned long long adesc, unsigned long long bdesc, unsigned int idesc,
+                        int nmma, int a_step, int b_step, int n_acc, int acc_cols, long long* d_out2, void* stream);
 /* D[128,16] = A[128,K] B[16,K]^T through the same descriptors (unit test of the encodings) */
 int dnnb200_tc_gemm_probe(const float* A, const float* B, float* D, int K, void* stream);
 /* y[N,M] = act(x[N,K] w[M,K]^T + b[M]) (K8-K10) */
@@ -141,12 +145,18 @@ unsigned long long dnnb200_engine_launches(const dnnb200_engine* e);
  * (distributed shared memory between them). 0 = choose per batch size so the batch is one wave. */
 int dnnb200_engine_set_cluster_size(dnnb200_engine* e, int cs);
 int dnnb200_engine_cluster_info(const dnnb200_engine* e, int B, int* chosen, int* max_clusters9);
+/* arithmetic of the convolution stages of the clustered forward/backward kernel (conv1 and conv2 forward, conv2
+ * data gradient): 1 (default) = implicit GEMMs on the tensor cores (tcgen05.mma kind::tf32: operands rounded to
+ * TF32, fp32 accumulation in tensor memory); 0 = fp32 FFMA throughout, the path that matches PyTorch fp32 to 2e-5.
+ * Everything else (FC layers, weight gradients, softmax, SGD, master weights) is fp32 either way. Batches that
+ * run the one-CTA-per-image kernel (cluster size 1) are always fp32. */
+int dnnb200_engine_set_precision(dnnb200_engine* e, int tf32);
 /* development aid: d_trace[cta*16 + k] receives the SM clock at stage boundary k of the clustered
  * forward/backward kernel (NULL switches it off) */
 int dnnb200_engine_set_trace(dnnb200_engine* e, long long* d_trace);
 /* same for the update kernel: d_trace[slice*8 + k] = globaltimer (ns) at k = 0 entry, 1 after the dependency wait,
  * 2 after the local gradient, 3 after the exchange, 4 after the SGD stores, 5 after the fence, 6 after the
- * last-CTA counter; [122*8] words, or [1024*122*8] with debug flag 4 (ring over the last 1024 steps) */
+ * last-CTA counter, and k = 7 the number of ranks that entered the slice's sum; [122*8] words, or [1024*122*8] with debug flag 4 (ring over the last 1024 steps) */
 int dnnb200_engine_set_update_trace(dnnb200_engine* e, long long* d_trace);
 /* development aid / A-B switches, OR-ed: 2 = the update kernel does not trigger the early launch of the next
  * kernel; 4 = the update trace is a ring over the last 1024 steps; 8 = chained steps wait for the completion of

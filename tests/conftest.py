@@ -9,6 +9,10 @@ if str(ROOT) not in sys.path:
     sys.path.insert(0, str(ROOT))
 
 os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+# The parity tests compare the fused step with PyTorch fp32 at 2e-5: they run the fp32 FFMA instantiation. The
+# tensor-core (TF32) instantiation -- the product default -- is tested against it in tests/test_gpu_tc_step.py,
+# which asks for it explicitly. (An environment variable, so that worker processes inherit it.)
+os.environ.setdefault("DNNB200_PRECISION", "fp32")
 
 
 def pytest_configure(config):
