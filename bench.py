@@ -344,6 +344,14 @@ def run_reference(args) -> int:
         return 0  # the reference's ranks are spawned by rank 0 below (it is a CPU program)
     ref = ROOT / "baseline" / "_ref" / "data_parallelism_train.py"
     if not ref.exists():
+        try:
+            sys.path.insert(0, str(ROOT / "baseline"))
+            import install_reference
+
+            install_reference.ensure()
+        except Exception:
+            pass
+    if not ref.exists():
         print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is empty: the reference has no "
                           "setup.py/pyproject.toml (pip install fails) and its sources were not copied in"}))
         return 0
