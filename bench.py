@@ -441,7 +441,7 @@ def main() -> int:
     ap.add_argument("--exchange", choices=["auto", "one-shot", "one-shot-128", "two-shot", "nvls"], default="auto",
                     help="gradient exchange variant (auto: every usable variant is timed at start-up, the fastest runs)")
     ap.add_argument("--precision", choices=["tf32", "fp32"], default=None,
-                    help="conv stages of the fused step: tf32 = tcgen05 tensor cores (default), fp32 = FFMA")
+                    help="conv stages of the fused step: fp32 = FFMA (default, measured faster), tf32 = tcgen05 tensor cores")
     ap.add_argument("--ref-max-steps", type=int, default=400)
     ap.add_argument("--ref-timeout", type=float, default=1500.0)
     a = ap.parse_args()

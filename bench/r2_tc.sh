@@ -1,9 +1,10 @@
 #!/bin/sh
 # tensor-core step kernel: its tests first (they fail fast if the kernel is wrong), then the A/B against fp32
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_tc_step.py -x -q > gpurun_out/pytest_tc_step.log 2>&1; echo "pytest tc exit $?"; tail -15 gpurun_out/pytest_tc_step.log
-for P in fp32 tf32; do
-  DNNB200_PRECISION=$P timeout 300 python bench.py --steps 2000 --warmup 5 > gpurun_out/r2_bench_n1_$P.json 2> gpurun_out/r2_bench_n1_$P.err; echo "bench $P exit $?"
+timeout 600 python -m pytest tests/test_gpu_tc_step.py tests/test_gpu_exchange.py -x -q > gpurun_out/pytest_tc_step.log 2>&1; echo "pytest tc exit $?"; tail -4 gpurun_out/pytest_tc_step.log
+for P in ${PRECS:-tf32}; do
+  timeout 300 python bench.py --steps 2000 --warmup 5 --precision $P > gpurun_out/r2_bench_n1_$P.json 2> gpurun_out/r2_bench_n1_$P.err; echo "bench $P exit $?"
   python -c "
 import json; d=json.load(open('gpurun_out/r2_bench_n1_$P.json')); print('$P', d['value'], round(d['ms_per_step']*1e3,2), 'us/step | e2e', d['e2e']['value'], d['dtype'][:40])" || tail -5 gpurun_out/r2_bench_n1_$P.err
 done
+python bench/trace_stages.py 16 6 tf32 | head -24

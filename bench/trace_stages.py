@@ -28,7 +28,9 @@ def main():
     n_cta = B * cs
     tr = torch.zeros(n_cta * 32, dtype=torch.int64, device="cuda")
     eng.set_trace(tr)
-    eng.step(x, y)
+    # four steps chained inside one engine call: the stamps of the LAST one stay in the buffer (a chained step waits on
+    # the update counter and, in tf32 mode, fetches its B operands ready-made -- the path a training run takes)
+    eng.train_device(x.unsqueeze(0).repeat(4, 1, 1, 1, 1), y.unsqueeze(0).repeat(4, 1))
     torch.cuda.synchronize()
     eng.set_trace(None)
     t = tr.view(n_cta, 32).cpu()

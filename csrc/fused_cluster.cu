@@ -86,7 +86,6 @@ constexpr int kP1Pitch = 14;
 constexpr int kP1PlanePix = 20 * kP1Pitch + 24;        // conv2 tiles reach rows 0..19, columns up to 19
 constexpr int kDPitch = 18;                            // conv2 output gradient, zero border of 4
 constexpr int kDPlanePix = 2 * 128 + 4 * kDPitch + 4 + 12;   // two tiles + reach of the last tap (344)
-constexpr int kB1Chunks = 26, kB2Chunks = 50, kBdChunks = 100;   // K-chunks (4 floats) of the three B operands
 constexpr int kTmemCols = 128;                         // [0,64) conv1 tiles, [64,96) conv2 tiles, [96,128) dgrad tiles
 constexpr uint32_t kTmemC2 = 64, kTmemDg = 96;
 enum { kTBarC1 = 0, kTBarC2, kTBarDg, kNumTcBars };
@@ -118,6 +117,7 @@ struct __align__(128) CLSmemT<true> {
   alignas(8) unsigned long long cbar;
   alignas(8) unsigned long long sbar[kNumStageBars];
   alignas(8) unsigned long long tbar[kNumTcBars];      // tcgen05.commit targets
+  alignas(8) unsigned long long pbar;                  // bulk copy of sb2 | sbd (packed operands from global memory)
   uint32_t tmem_slot;
 };
 
@@ -423,6 +423,20 @@ __device__ __forceinline__ void fc_dx_partial_push(const float* wsm, const float
   }
 }
 
+// MMAs J0..J1-1 of an implicit-GEMM tile, everything but the two descriptor bases a compile-time constant: per MMA
+// the issuing thread executes two 64-bit adds and the instruction. A operand: tap (kh, kw) = the plane shifted by
+// kh*PITCH + kw pixels (16 bytes each). PLANE2 == 0: MMA j is tap j (its two K-chunks are the descriptor's LBO apart);
+// PLANE2 != 0: MMA j is tap j/2 and odd j reads the second pair of planes, PLANE2 pixels further on.
+template <int J0, int J1, int PITCH, int PLANE2>
+__device__ __forceinline__ void tc_issue_taps(uint32_t d_tmem, uint64_t a0, uint64_t b0, uint32_t idesc) {
+#pragma unroll
+  for (int j = J0; j < J1; ++j) {
+    const int tap = PLANE2 ? (j >> 1) : j;
+    const int off = (tap / 5) * PITCH + (tap % 5) + (PLANE2 ? (j & 1) * PLANE2 : 0);
+    tc::mma_tf32(d_tmem, a0 + (uint64_t)off, b0 + (uint64_t)(16 * j), idesc, j > J0);
+  }
+}
+
 // development aid: thread 0 of every CTA stamps the SM clock at stage boundaries (trace == nullptr in production)
 #define CL_TRACE(k) do { if (trace != nullptr && tid == 0) trace[blockIdx.x * 32 + (k)] = clock64(); } while (0)
 
@@ -442,7 +456,8 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
                        const long long* __restrict__ labels, float* __restrict__ saved,
                        float* __restrict__ part1, float* __restrict__ part2, float* __restrict__ img_loss,
                        int* __restrict__ img_correct, int B, float inv_batch, long long* __restrict__ trace,
-                       const unsigned int* __restrict__ ready_ctr, unsigned int ready_expect) {
+                       const unsigned int* __restrict__ ready_ctr, unsigned int ready_expect,
+                       const float* __restrict__ packed) {
   static_assert(CS >= 2 && CS <= 8, "the one-CTA case is fused_step.cu's fwd_bwd_kernel");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   using SM = CLSmemT<kTC>;
@@ -480,6 +495,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       cl_mbar_init(&s.tbar[kTBarC1], (8 - r + CS - 1) / CS);
       cl_mbar_init(&s.tbar[kTBarC2], 2);
       cl_mbar_init(&s.tbar[kTBarDg], 2);
+      cl_mbar_init(&s.pbar, 1);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -488,21 +504,29 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     // tensor memory for the accumulators of the three GEMMs (one warp allocates, the same warp frees at the end);
     // and everything in the operand buffers that is padding is zeroed ONCE, long before any weight or image arrives:
     // B-operand rows/chunks without a weight, the pad column/rows of the image plane, channels 6..7 of p1
-    if (warp == 1) tc::tmem_alloc<kTmemCols>(&s.tmem_slot);
+    // (shared-memory stores run at 128 bytes per cycle: zeroing all 96 KB of operand buffers cost 800 cycles of
+    // every launch. Zeroed now is only what a VALID output row can read and nothing else writes.)
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int i = tid; i < (int)(sizeof(s.sb1) + sizeof(s.sb2) + sizeof(s.sbd)) / 16; i += kCLThreads)
-      reinterpret_cast<float4*>(s.sb1)[i] = z;   // sb1 | sb2 | sbd are contiguous (static_assert below)
-    for (int i = tid; i < kXPlanePix; i += kCLThreads) reinterpret_cast<float4*>(s.xpl)[i] = z;
+    if (packed == nullptr) {   // B operands are packed in this kernel: their padding must be zero beforehand
+      for (int i = tid; i < (int)(sizeof(s.sb1) + sizeof(s.sb2) + sizeof(s.sbd)) / 16; i += kCLThreads)
+        reinterpret_cast<float4*>(s.sb1)[i] = z;   // sb1 | sb2 | sbd are contiguous (static_assert below)
+    }
+    // image plane: the pad column (the 26th, weightless K-chunk of conv1 reads one pixel past tap 24) and the rows
+    // below the image (only rows of the tile that are thrown away read them, but NaN patterns are best kept out)
+    for (int i = tid; i < 32; i += kCLThreads) reinterpret_cast<float4*>(s.xpl)[i * kXPitch + 32] = z;
+    for (int i = 32 * kXPitch + tid; i < kXPlanePix; i += kCLThreads) reinterpret_cast<float4*>(s.xpl)[i] = z;
     for (int i = tid; i < 2 * kP1PlanePix; i += kCLThreads) reinterpret_cast<float4*>(s.p1n)[i] = z;
-    for (int i = tid; i < 4 * kDPlanePix; i += kCLThreads) reinterpret_cast<float4*>(s.dpl)[i] = z;
     static_assert(offsetof(SM, sb2) == offsetof(SM, sb1) + sizeof(s.sb1) &&
                   offsetof(SM, sbd) == offsetof(SM, sb2) + sizeof(s.sb2), "B operands are zeroed as one block");
-    tc::tc_fence_before();
   }
   __syncthreads();
   if constexpr (kTC) {
-    tc::tc_fence_after();
-    tmem = s.tmem_slot;
+    // (allocation takes a few hundred cycles: warp 1 does it while the others go on to the image and the dependency
+    // wait; the address is picked up after the block barrier at the top of the image loop)
+    if (warp == 1) {
+      tc::tmem_alloc<kTmemCols>(&s.tmem_slot);
+      tc::tc_fence_before();
+    }
   }
   // tell the cluster "my barriers exist"; the matching wait sits just before the first remote store
   CL_TRACE(17);
@@ -537,7 +561,6 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
   // dense dL/d(conv2 output), zero-padded: rewritten (scattered into) for every image, so zeroed for every image
   auto zero_grad_plane = [&]() {
     if constexpr (kTC) {
-      if (first_img) return;   // zeroed with the other operand buffers at kernel start
       const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
       for (int i = tid; i < 4 * kDPlanePix; i += kCLThreads) reinterpret_cast<float4*>(s.dpl)[i] = z;
     } else {
@@ -570,8 +593,21 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
   if (tid == 0) {
     // every weight this CTA needs arrives by TMA bulk copy, issued before anything else: the conv block now,
     // (clusters >= 4) my FC row slices + the FC biases, which land while the conv layers run
-    cl_mbar_expect_tx(&s.cbar, kConvPrefix * 4);
-    cl_bulk_g2s(s.cw, params, kConvPrefix * 4, &s.cbar);
+    if constexpr (kTC) {
+      if (packed != nullptr) {   // conv weights as ready-made B operands: conv1's with the first barrier, the rest later
+        cl_mbar_expect_tx(&s.cbar, kConvPrefix * 4 + (uint32_t)sizeof(s.sb1));
+        cl_bulk_g2s(s.sb1, packed + kPackB1, (uint32_t)sizeof(s.sb1), &s.cbar);
+        cl_bulk_g2s(s.cw, params, kConvPrefix * 4, &s.cbar);   // (biases)
+        cl_mbar_expect_tx(&s.pbar, (uint32_t)(sizeof(s.sb2) + sizeof(s.sbd)));
+        cl_bulk_g2s(s.sb2, packed + kPackB2, (uint32_t)(sizeof(s.sb2) + sizeof(s.sbd)), &s.pbar);
+      } else {
+        cl_mbar_expect_tx(&s.cbar, kConvPrefix * 4);
+        cl_bulk_g2s(s.cw, params, kConvPrefix * 4, &s.cbar);
+      }
+    } else {
+      cl_mbar_expect_tx(&s.cbar, kConvPrefix * 4);
+      cl_bulk_g2s(s.cw, params, kConvPrefix * 4, &s.cbar);
+    }
     if (kPre) {
       const int a0 = r * kF1 / CS, a1 = (r + 1) * kF1 / CS, c0 = r * kF2 / CS, c1 = (r + 1) * kF2 / CS;
       const uint32_t n1 = (uint32_t)(a1 - a0) * kFlat * 4, n2 = (uint32_t)(c1 - c0) * kF1 * 4, n3 = kF3 * kF2 * 4;
@@ -622,6 +658,10 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     }
     cl_mbar_wait(&s.cbar, 0);      // conv weights landed (first image; complete ever after)
     __syncthreads();
+    if constexpr (kTC) {
+      tc::tc_fence_after();
+      tmem = s.tmem_slot;
+    }
     CL_TRACE(2);
 
     if constexpr (kTC) {
@@ -635,7 +675,8 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       // conv2: two tiles (columns 0..7 / 8..15). Paired CTAs (r, r^1) compute one each and hand the result to the
       // partner; a CTA without partner (last one of an odd cluster) computes both.
       const bool paired = (r ^ 1) < CS;
-      if (first_img) {
+      const bool pack_here = first_img && packed == nullptr;   // no ready-made operands: pack the weights in here
+      if (pack_here) {
         // conv1.weight -> B operand (450 real entries, the rest stays zero): element (n, chunk = tap, c)
         for (int i = tid; i < 450; i += kCLThreads) {
           const int n = i / 75, rem = i - n * 75, c = rem / 25, tap = rem - c * 25;
@@ -663,21 +704,38 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
         tc::mma_commit(reinterpret_cast<uint64_t*>(&s.tbar[kTBarC1]));
         if (warp == 0) CL_TRACE(30);
       }
-      if (first_img) {
+      if (pack_here) {
         // While the tensor core works: the other two B operands (needed from conv2 on). A warp writes 32 consecutive
         // floats of an operand per step -- (row n%8, component) of one K-chunk -- so the stores are conflict-free.
         //   sb2: conv2.weight, chunk = 2*tap + ch/4, element (n = o, c = ch%4)
         //   sbd: the same weights for the data gradient dX[ch] = sum_{tap,o} dCp[o](shifted by tap) W[o][ch][24 - tap]:
         //        n = ch, chunk = 4*tap' + o/4 with tap' = 24 - tap, component o%4
-        for (int it = warp; it < 200; it += kCLThreads / 32) {
-          if (it < 100) {
-            const int og = it / 50, rem = it - og * 50, tap = rem >> 1, cg = rem & 1;
-            const int o = og * 8 + (lane >> 2), ch = cg * 4 + (lane & 3);
-            if (ch < 6) s.sb2[(og * kB2Chunks + rem) * 32 + lane] = s.cw[kOffW2 + (o * 6 + ch) * 25 + tap];
-          } else {
-            const int u = it - 100, tp = u >> 2, og = u & 3;       // tp = flipped tap, og = group of 4 output channels
-            const int ch = lane >> 2, o = og * 4 + (lane & 3);
-            if (ch < 6) s.sbd[(4 * tp + og) * 32 + lane] = s.cw[kOffW2 + (o * 6 + ch) * 25 + (24 - tp)];
+        // (warps 4..15: the first four may be issuing conv1; four items at a time, loads ahead of the stores)
+        if (warp >= 4) {
+          for (int it0 = warp - 4; it0 < 200; it0 += 4 * 12) {
+            float w[4];
+            int dst[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int it = it0 + 12 * u;
+              dst[u] = -1;
+              w[u] = 0.f;
+              if (it < 100) {
+                const int og = it / 50, rem = it - og * 50, tap = rem >> 1, cg = rem & 1;
+                const int o = og * 8 + (lane >> 2), ch = cg * 4 + (lane & 3);
+                if (ch < 6) { dst[u] = (og * kB2Chunks + rem) * 32 + lane; w[u] = s.cw[kOffW2 + (o * 6 + ch) * 25 + tap]; }
+              } else if (it < 200) {
+                const int v = it - 100, tp = v >> 2, og = v & 3;     // tp = flipped tap, og = group of 4 output channels
+                const int ch = lane >> 2, o = og * 4 + (lane & 3);
+                if (ch < 6) {
+                  dst[u] = (int)(sizeof(s.sb2) / 4) + (4 * tp + og) * 32 + lane;   // sbd follows sb2
+                  w[u] = s.cw[kOffW2 + (o * 6 + ch) * 25 + (24 - tp)];
+                }
+              }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+              if (dst[u] >= 0) s.sb2[dst[u]] = w[u];
           }
         }
         tc::fence_proxy_async();
@@ -733,25 +791,23 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
         }
       }
       tc::tc_fence_before();
-      if (first_img) __syncthreads();   // sb2 / sbd are complete (and fenced) before anybody issues conv2
+      if (pack_here) __syncthreads();   // sb2 / sbd are complete (and fenced) before anybody issues conv2
       CL_TRACE(4);
       if (lane == 0 && warp < 2) {
+        if (packed != nullptr) cl_mbar_wait(&s.pbar, 0);   // sb2 | sbd have landed (long ago; stays complete)
         cl_mbar_wait(&s.sbar[kBarP1], phase);      // every CTA's part of p1 has landed (st.async from the whole cluster)
         tc::fence_proxy_async();
         tc::tc_fence_after();
         // paired: my tile (columns 8*(r&1)..), its 25 taps split over the two issuing threads and two accumulators
         // (added in the epilogue); alone: issuing thread w computes tile w
         const int cb = paired ? (r & 1) : warp;
-        const int j0 = paired ? (warp ? 13 : 0) : 0, j1 = paired ? (warp ? 25 : 13) : 25;
         const uint64_t a0 = tc::smem_desc_nosw(tc::smem_u32(s.p1n) + (uint32_t)(8 * cb) * 16, kP1PlanePix * 16, kP1Pitch * 16);
         const uint64_t b0 = tc::smem_desc_nosw(tc::smem_u32(s.sb2), 128, kB2Chunks * 128);
         const uint32_t d = tmem + kTmemC2 + (uint32_t)warp * 16;
-        int kh = j0 / 5, kw = j0 - kh * 5;
-#pragma unroll 5
-        for (int j = j0; j < j1; ++j) {            // K-chunks of MMA j = the two channel groups of tap j
-          tc::mma_tf32(d, a0 + (uint64_t)(kh * kP1Pitch + kw), b0 + (uint64_t)(16 * j), kIdesc, j > j0);
-          if (++kw == 5) { kw = 0; ++kh; }
-        }
+        // K-chunks of MMA j = the two channel groups of tap j
+        if (!paired) tc_issue_taps<0, 25, kP1Pitch, 0>(d, a0, b0, kIdesc);
+        else if (warp == 0) tc_issue_taps<0, 13, kP1Pitch, 0>(d, a0, b0, kIdesc);
+        else tc_issue_taps<13, 25, kP1Pitch, 0>(d, a0, b0, kIdesc);
         tc::mma_commit(reinterpret_cast<uint64_t*>(&s.tbar[kTBarC2]));
         if (warp == 0) CL_TRACE(31);
       }
@@ -1057,19 +1113,16 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
           const uint64_t a0 = tc::smem_desc_nosw(tc::smem_u32(s.dpl) + (uint32_t)dg_m0 * 16, kDPlanePix * 16, 128);
           const uint64_t b0 = tc::smem_desc_nosw(tc::smem_u32(s.sbd), 128, kBdChunks * 128);
           const uint32_t d = tmem + kTmemDg + (uint32_t)warp * 16;
-          const int j0 = 25 * warp;
-          int tap = j0 >> 1, kh = tap / 5, kw = tap - kh * 5;
-#pragma unroll 5
-          for (int j = j0; j < j0 + 25; ++j) {
-            tc::mma_tf32(d, a0 + (uint64_t)(kh * kDPitch + kw + (j & 1) * (2 * kDPlanePix)), b0 + (uint64_t)(16 * j), kIdesc,
-                         j > j0);
-            if (j & 1) { if (++kw == 5) { kw = 0; ++kh; } }
-          }
+          if (warp == 0) tc_issue_taps<0, 25, kDPitch, 2 * kDPlanePix>(d, a0, b0, kIdesc);
+          else tc_issue_taps<25, 50, kDPitch, 2 * kDPlanePix>(d, a0, b0, kIdesc);
           tc::mma_commit(reinterpret_cast<uint64_t*>(&s.tbar[kTBarDg]));
           if (warp == 0) CL_TRACE(21);
         }
       }
-      for (int item = tid; item < n_dg + n_wg; item += kCLThreads) {
+      // (kTC: warps 0 and 1 hold the two issuing threads; their other lanes would only start on weight-gradient
+      // items once the issue loop is through, so the items go to warps 2..15)
+      for (int item = kTC ? tid - 64 : tid; item < n_dg + n_wg; item += kTC ? kCLThreads - 64 : kCLThreads) {
+        if (item < 0) break;
         if (item < n_dg) {
          if constexpr (!kTC) {
           const int o = item / nq, ql = item - o * nq, q = q0 + ql;
@@ -1254,7 +1307,7 @@ template <int CS, bool kTC>
 static int launch_cluster_t(const float* params, const float* x, const long long* labels, float* saved, float* part1,
                             float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
                             long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
-                            cudaStream_t stream) {
+                            const float* packed, cudaStream_t stream) {
   static PerDeviceOnce attr_set;
   auto kern = fwd_bwd_cluster_kernel<CS, kTC>;
   const size_t smem = cluster_smem_bytes<CS, kTC>();
@@ -1278,7 +1331,8 @@ static int launch_cluster_t(const float* params, const float* x, const long long
   cfg.numAttrs = 2;
   const float inv_batch = 1.f / (float)B;
   DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, params, x, labels, saved, part1, part2, img_loss, img_correct, B,
-                                    inv_batch, trace, CS >= 4 ? ready_ctr : nullptr, ready_expect));
+                                    inv_batch, trace, CS >= 4 ? ready_ctr : nullptr, ready_expect,
+                                    kTC ? packed : nullptr));
   return kOk;
 }
 
@@ -1335,11 +1389,11 @@ template <bool kTC>
 static int launch_cluster_p(int cs, const float* params, const float* x, const long long* labels, float* saved,
                             float* part1, float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
                             long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
-                            cudaStream_t stream) {
+                            const float* packed, cudaStream_t stream) {
 #define DNN_CL_CASE(N)                                                                                              \
   case N:                                                                                                           \
     return launch_cluster_t<N, kTC>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, max_clusters, \
-                                    trace, ready_ctr, ready_expect, stream);
+                                    trace, ready_ctr, ready_expect, packed, stream);
   switch (cs) {
     DNN_CL_CASE(8) DNN_CL_CASE(7) DNN_CL_CASE(6) DNN_CL_CASE(5) DNN_CL_CASE(4) DNN_CL_CASE(3) DNN_CL_CASE(2)
     default: set_last_error("cluster size %d not supported", cs); return kErrArg;
@@ -1352,11 +1406,11 @@ static int launch_cluster_p(int cs, const float* params, const float* x, const l
 int launch_fwd_bwd_cluster(int cs, bool tensor_cores, const float* params, const float* x, const long long* labels,
                            float* saved, float* part1, float* part2, float* img_loss, int* img_correct, int B,
                            int max_clusters, long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
-                           cudaStream_t stream) {
+                           const float* packed, cudaStream_t stream) {
   return tensor_cores ? launch_cluster_p<true>(cs, params, x, labels, saved, part1, part2, img_loss, img_correct, B,
-                                               max_clusters, trace, ready_ctr, ready_expect, stream)
+                                               max_clusters, trace, ready_ctr, ready_expect, packed, stream)
                       : launch_cluster_p<false>(cs, params, x, labels, saved, part1, part2, img_loss, img_correct, B,
-                                                max_clusters, trace, ready_ctr, ready_expect, stream);
+                                                max_clusters, trace, ready_ctr, ready_expect, nullptr, stream);
 }
 
 }  // namespace dnnb200

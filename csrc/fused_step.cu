@@ -586,6 +586,18 @@ __device__ __forceinline__ float2 local_grad2(const RankCtx& cx, int i, int B, i
 //      and the NEXT step's clusters cannot be placed there until those CTAs have exited -- which, after NVLink
 //      stores, takes ~3 us longer than their last instruction (the stores drain first). Measured at 2 GPUs:
 //      25.3 -> 22.4 us per step; on one GPU the same budget costs 0.7 us, hence two instantiations.
+// flat index i of a conv weight -> its places in the packed B operands (layout.h); biases and gaps have none
+__device__ __forceinline__ void pack_conv_weight(float* __restrict__ packed, int i, float w) {
+  if (i < kOffW1 + 450) {
+    const int n = i / 75, rem = i - n * 75, c = rem / 25, tap = rem - c * 25;
+    packed[kPackB1 + ((n >> 3) * kB1Chunks + tap) * 32 + (n & 7) * 4 + c] = w;
+  } else if (i >= kOffW2 && i < kOffW2 + 2400) {
+    const int e = i - kOffW2, o = e / 150, rem = e - o * 150, ch = rem / 25, tap = rem - ch * 25;
+    packed[kPackB2 + ((o >> 3) * kB2Chunks + 2 * tap + (ch >> 2)) * 32 + (o & 7) * 4 + (ch & 3)] = w;
+    packed[kPackBd + (4 * (24 - tap) + (o >> 2)) * 32 + ch * 4 + (o & 3)] = w;
+  }
+}
+
 // kExchange = false: the instantiation for a rank without peers carries no exchange code at all (and no register
 // pressure from it).
 template <bool kEmulated, int kMinBlocks, bool kExchange>
@@ -718,6 +730,10 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
       pp.y -= lr * mm.y;
       *reinterpret_cast<float2*>(cx.momentum + i + k) = mm;
       *reinterpret_cast<float2*>(cx.params + i + k) = pp;
+      if (cx.packed != nullptr && i + k < kConvPrefix) {   // (slices 0..5 only) the tensor-core view of the conv weights
+        pack_conv_weight(cx.packed, i + k, pp.x);
+        pack_conv_weight(cx.packed, i + k + 1, pp.y);
+      }
       if (cx.grads) *reinterpret_cast<float2*>(cx.grads + i + k) = make_float2(g0, g1);
     }
   }

@@ -42,6 +42,17 @@ constexpr int kC1 = 6, kC1H = 28, kP1H = 14;   // conv1 out 6x28x28, pooled 6x14
 constexpr int kC2 = 16, kC2H = 10, kP2H = 5;   // conv2 out 16x10x10, pooled 16x5x5
 constexpr int kF1 = 120, kF2 = 84, kF3 = 10, kFlat = 400;
 
+// Tensor-core instantiation of the step kernel: the conv weights as the three canonical K-major B operands of its
+// implicit GEMMs (fused_cluster.cu), kept in global memory next to the flat parameters and refreshed by the update
+// kernel with every step, so that the step kernel fetches them with bulk copies instead of re-packing 5 250 weights
+// in shared memory at every launch. Element (row n, K-chunk q, component c) of an operand with NCH chunks sits at
+// ((n / 8) * NCH + q) * 32 + (n % 8) * 4 + c; everything that is not a weight is zero and stays zero.
+constexpr int kB1Chunks = 26, kB2Chunks = 50, kBdChunks = 100;
+constexpr int kPackB1 = 0;                              // conv1.weight: n = o, chunk = tap, c = input channel
+constexpr int kPackB2 = kPackB1 + 2 * kB1Chunks * 32;   // conv2.weight: n = o, chunk = 2*tap + ch/4, c = ch%4
+constexpr int kPackBd = kPackB2 + 2 * kB2Chunks * 32;   // conv2.weight for the data gradient: n = ch, chunk = 4*(24-tap) + o/4, c = o%4
+constexpr int kPackNumel = kPackBd + 2 * kBdChunks * 32;   // 11 264 floats
+
 // Gradient exchange: the flat vector is cut into slices of kSlice floats; one
 // CTA of the update kernel owns one slice end to end (wgrad -> push to peers ->
 // reduce -> SGD), so the NVLink transfer of early slices overlaps the math of

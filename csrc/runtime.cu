@@ -38,7 +38,7 @@ int launch_fwd_bwd(bool train, const float* params, const float* x, const long l
 int launch_fwd_bwd_cluster(int cs, bool tensor_cores, const float* params, const float* x, const long long* labels,
                            float* saved, float* part1, float* part2, float* img_loss, int* img_correct, int B,
                            int max_clusters, long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
-                           cudaStream_t stream);
+                           const float* packed, cudaStream_t stream);
 int max_active_clusters(int cs, bool tensor_cores);
 int launch_pingpong(const RankCtx* d_ctx, int peer, int iters, unsigned int base_seq, long long* d_out_ns,
                     cudaStream_t stream);
@@ -109,13 +109,14 @@ struct dnnb200_engine {
   int device = 0, max_batch = 0;
   float *params = nullptr, *momentum = nullptr, *grads = nullptr;
   float *saved = nullptr, *part1 = nullptr, *part2 = nullptr, *img_loss = nullptr;
+  float* packed = nullptr;         // conv weights as tensor-core B operands (layout.h), refreshed by every update kernel
   long long* trace = nullptr;      // development aid: per-CTA stage timestamps of the cluster kernel
   unsigned int updates_launched = 0;   // update kernels launched on d_ctx == StepCtl::updates_done once they finish
   int debug_flags = 0;             // OR-ed into the update kernel's flags (bit 1: no early launch of the successor)
   int forced_cluster = 0;          // 0 = pick per batch size
   int max_clusters[9] = {};        // resident clusters of the fwd/bwd kernel per cluster size (index = CS), for `tf32`
   int max_clusters_p[2][9] = {};   // the same for both precisions ([0] fp32 FFMA, [1] TF32 tensor cores)
-  int tf32 = 1;                    // conv stages of the clustered kernel on tcgen05 (default) or fp32 FFMA
+  int tf32 = 0;                    // conv stages of the clustered kernel: 0 fp32 FFMA (default), 1 tcgen05 (TF32 operands)
   int* img_correct = nullptr;
   float* eval_loss = nullptr;
   int* eval_correct = nullptr;
@@ -272,7 +273,11 @@ static int fwd_bwd_any(dnnb200_engine* e, const float* x, const long long* y, in
                           B, e->num_sms, s);
   return launch_fwd_bwd_cluster(cs, e->tf32 != 0, e->params, x, y, e->saved, e->part1, e->part2, e->img_loss, e->img_correct, B,
                                 e->max_clusters[cs] > 0 ? e->max_clusters[cs] : 1, e->trace,
-                                chained && !(e->debug_flags & 8) ? &e->ctl->updates_done : nullptr, e->updates_launched, s);
+                                chained && !(e->debug_flags & 8) ? &e->ctl->updates_done : nullptr, e->updates_launched,
+                                // ready-made operands are only trusted when the previous operation on the stream was this
+                                // engine's own update kernel (which wrote them together with the parameters): the host
+                                // may change the parameters between calls
+                                chained && !(e->debug_flags & 128) ? e->packed : nullptr, s);
 }
 
 // The counter value a chained step waits for is a kernel ARGUMENT: baked into a CUDA graph it would be stale on
@@ -457,6 +462,8 @@ static int engine_fill(dnnb200_engine* e, float* params, float* momentum, float*
   }
   DNN_CUDA_CHECK(cudaMemset(e->saved, 0, (size_t)max_batch * kSavStride * sizeof(float)));
   DNN_CUDA_CHECK(cudaMalloc(&e->img_loss, (size_t)max_batch * sizeof(float)));
+  DNN_CUDA_CHECK(cudaMalloc(&e->packed, (size_t)kPackNumel * sizeof(float)));
+  DNN_CUDA_CHECK(cudaMemset(e->packed, 0, (size_t)kPackNumel * sizeof(float)));   // everything that is not a weight stays zero
   DNN_CUDA_CHECK(cudaMalloc(&e->img_correct, (size_t)max_batch * sizeof(int)));
   DNN_CUDA_CHECK(cudaMalloc(&e->ctl, sizeof(StepCtl)));
   DNN_CUDA_CHECK(cudaMalloc(&e->loss_ring, (size_t)(e->loss_ring_mask + 1) * sizeof(float)));
@@ -479,6 +486,7 @@ static int engine_fill(dnnb200_engine* e, float* params, float* momentum, float*
   e->h_ctx.part1 = e->part1;
   e->h_ctx.part2 = e->part2;
   e->h_ctx.img_loss = e->img_loss;
+  e->h_ctx.packed = e->packed;
   e->h_ctx.loss_ring = e->loss_ring;
   e->h_ctx.loss_ring_mask = e->loss_ring_mask;
   e->h_ctx.ctl = e->ctl;
@@ -509,6 +517,7 @@ int dnnb200_engine_create(float* params, float* momentum, float* grads, int max_
 int dnnb200_engine_destroy(dnnb200_engine* e) {
   if (!e) return kOk;
   cudaDeviceSynchronize();
+  cudaFree(e->packed);
   cudaFree(e->saved); cudaFree(e->part1); cudaFree(e->part2); cudaFree(e->img_loss); cudaFree(e->img_correct);
   cudaFree(e->eval_loss); cudaFree(e->eval_correct); cudaFree(e->d_eval_out);
   cudaFree(e->ctl); cudaFree(e->loss_ring); cudaFree(e->d_ctx);
@@ -864,7 +873,8 @@ int dnnb200_vr_step(dnnb200_engine** engines, int n, const float* const* xs, con
   int rc = gather_ctxs(live.data(), (int)live.size(), &d);
   if (rc) return rc;
   const int lslot = (int)(live[0]->steps_launched & (unsigned long long)live[0]->loss_ring_mask);
-  rc = launch_update(d, (int)live.size(), B, n_part1, lslot, 0, nullptr, s);
+  // (a single live rank of a larger group still runs the exchange code: it waits for, and gives up on, the others)
+  rc = launch_update(d, (int)live.size(), B, n_part1, lslot, live[0]->h_ctx.world > 1 ? (int)kUpdFlagHasGroup : 0, nullptr, s);
   cudaStreamSynchronize(s);
   cudaFree(d);
   if (rc) return rc;

@@ -68,6 +68,7 @@ struct RankCtx {
   float* nvls_local;      // NVLS variant: this rank's symmetric buffer [2][kFlatNumel] floats + [2][kMaxWorld][kFlagRow] flags
   float* nvls_mc;         //   and the MULTICAST address of the same buffer on all ranks (nullptr: not available)
   long long* trace;       // development aid: update-kernel timestamps (globaltimer ns), nullptr in production
+  float* packed;          // [kPackNumel] conv weights as tensor-core B operands (layout.h), refreshed with every update
   float* recv[kMaxWorld];          // recv[p]  = rank p's receive area as mapped in THIS process
   unsigned int* flags[kMaxWorld];  // flags[p] = rank p's flag area as mapped in THIS process
 };

@@ -53,9 +53,12 @@ class Ctl(C.Structure):
     ]
 
 
-# Arithmetic of the conv stages of the clustered step kernel: "tf32" = tcgen05 implicit GEMMs (TF32 operands, fp32
-# accumulate; the product default), "fp32" = FFMA throughout (matches PyTorch fp32 to 2e-5; what the parity tests use).
-_default_precision = os.environ.get("DNNB200_PRECISION", "tf32")
+# Arithmetic of the conv stages of the clustered step kernel: "fp32" = FFMA throughout (matches PyTorch fp32 to 2e-5),
+# "tf32" = tcgen05 implicit GEMMs (TF32 operands, fp32 accumulate). Both are built and tested; the default is the one
+# that MEASURES faster at the benchmark's batch size -- fp32, by 1.3 us per step (profiles/step_tc_ab_v1.md: the
+# model's GEMMs are so small that a step needs ~50 dependent tcgen05.mma of M=128 N=16 K=8, each of which costs the
+# issuing thread 64 cycles whatever its size).
+_default_precision = os.environ.get("DNNB200_PRECISION", "fp32")
 
 
 def set_default_precision(p: str) -> None:

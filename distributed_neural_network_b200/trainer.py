@@ -72,8 +72,9 @@ class TrainConfig:
     allreduce_variant: str = "auto"        # auto (measured at start-up) | one-shot | one-shot-128 | two-shot | nvls
     calibrate_exchange: bool = True        # auto: time every usable variant on this world size and take the fastest
     calibrate_steps: int = 300
-    precision: Optional[str] = None        # conv stages of the fused step: tf32 (tensor cores, the default) | fp32 (FFMA,
-                                           # parity with PyTorch fp32); None = native.default_precision()
+    precision: Optional[str] = None        # conv stages of the fused step: fp32 (FFMA; parity with PyTorch fp32 and, at
+                                           # these GEMM sizes, the faster one) | tf32 (tcgen05 tensor cores);
+                                           # None = native.default_precision()
     exchange_timing: bool = True           # per-epoch "allreduce_us" in the JSONL (the reference books its
                                            # mpi_communication_time_children, data_parallelism_train.py:209-213)
     peer_timeout_s: float = 30.0

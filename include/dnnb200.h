@@ -146,8 +146,9 @@ unsigned long long dnnb200_engine_launches(const dnnb200_engine* e);
 int dnnb200_engine_set_cluster_size(dnnb200_engine* e, int cs);
 int dnnb200_engine_cluster_info(const dnnb200_engine* e, int B, int* chosen, int* max_clusters9);
 /* arithmetic of the convolution stages of the clustered forward/backward kernel (conv1 and conv2 forward, conv2
- * data gradient): 1 (default) = implicit GEMMs on the tensor cores (tcgen05.mma kind::tf32: operands rounded to
- * TF32, fp32 accumulation in tensor memory); 0 = fp32 FFMA throughout, the path that matches PyTorch fp32 to 2e-5.
+ * data gradient): 1 = implicit GEMMs on the tensor cores (tcgen05.mma kind::tf32: operands rounded to TF32, fp32
+ * accumulation in tensor memory); 0 (default of a new engine) = fp32 FFMA throughout, the path that matches PyTorch
+ * fp32 to 2e-5 and that measures faster at batch 16 (profiles/step_tc_ab_v1.md).
  * Everything else (FC layers, weight gradients, softmax, SGD, master weights) is fp32 either way. Batches that
  * run the one-CTA-per-image kernel (cluster size 1) are always fp32. */
 int dnnb200_engine_set_precision(dnnb200_engine* e, int tf32);
