@@ -15,3 +15,4 @@ for N in 2 4 8; do
   run $N 5000 auto
   for V in one-shot one-shot-128 two-shot nvls; do run $N 2000 $V; done
 done
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $NG --master-addr 127.0.0.1 --master-port 29655 bench/fault_drill.py 2>&1 | tail -6

@@ -81,7 +81,7 @@ allreduce_kernel(const RankCtx* __restrict__ ctxs, const ArParams prm) {
     v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
   }
   int n = 1;
-  const ExchangeCfg cfg = exchange_cfg(ctl);
+  const ExchangeCfg cfg = exchange_cfg(cx, ctl, seq);
   if (world > 1 && !prm.two_shot) {
     exchange_slice<4>(cx, cfg, &xsh, slice, seq, i, in_range, v, &n);
     if (in_range) finish(cx, prm, vr, i, v, n);

@@ -50,11 +50,26 @@ struct ExchangeShared {
 struct ExchangeCfg {
   unsigned int configured;        // StepCtl::active_mask
   unsigned long long timeout_ns;  // StepCtl::timeout_ns
+  unsigned int left;              // ranks whose leave marker already covers this step (leave_mask below): known to be
+                                  // absent before the exchange starts, so nobody spins on them step after step
 };
-__device__ __forceinline__ ExchangeCfg exchange_cfg(const StepCtl* ctl) {
+// Which configured ranks have announced that they take no part in sequence number `seq` any more? Their markers sit
+// in MY flag rows. Read early (the update kernel does it before its dependency wait): a marker that appears later is
+// still found by the waiters themselves, once, the slow way.
+__device__ __forceinline__ unsigned int leave_mask(const RankCtx& cx, unsigned int configured, unsigned int seq) {
+  unsigned int m = 0u;
+  for (int p = 0; p < cx.world; ++p) {
+    if (p == cx.rank || !((configured >> p) & 1u)) continue;
+    const unsigned int l = ld_relaxed_sys(cx.flags[cx.rank] + p * kFlagRow + kLeaveSlot);
+    if (l != 0u && (int)(seq - l) >= 0) m |= 1u << p;
+  }
+  return m;
+}
+__device__ __forceinline__ ExchangeCfg exchange_cfg(const RankCtx& cx, const StepCtl* ctl, unsigned int seq) {
   ExchangeCfg c;
   c.configured = ctl->active_mask;
   c.timeout_ns = ctl->timeout_ns;
+  c.left = cx.world > 1 ? leave_mask(cx, c.configured, seq) : 0u;
   return c;
 }
 
@@ -94,7 +109,7 @@ __device__ __forceinline__ void exchange_slice(const RankCtx& cx, const Exchange
   const int world = cx.world, rank = cx.rank;
   const int tid = threadIdx.x;
   const unsigned int parity = seq & 1u;
-  const unsigned int configured = cfg.configured;
+  const unsigned int configured = cfg.configured & ~(cfg.left & ~(1u << rank));   // (ranks already known to be gone)
   const unsigned int* my_flags = cx.flags[rank];
 
   // 1. push my values to every configured peer: one 16-byte LL line per pair of floats.
@@ -251,7 +266,7 @@ __device__ __forceinline__ void exchange_slice_ll128(const RankCtx& cx, const Ex
   const int world = cx.world, rank = cx.rank;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const unsigned int parity = seq & 1u;
-  const unsigned int configured = cfg.configured;
+  const unsigned int configured = cfg.configured & ~(cfg.left & ~(1u << rank));   // (ranks already known to be gone)
   const unsigned long long tmo = cfg.timeout_ns;
   const unsigned int* my_flags = cx.flags[rank];
   const int n_lines = (n_valid + kLineData - 1) / kLineData;

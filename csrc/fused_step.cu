@@ -630,6 +630,11 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
   if (tid < (int)(sizeof(StepCtl) / 4))
     reinterpret_cast<unsigned int*>(&ctl_snap)[tid] = reinterpret_cast<const volatile unsigned int*>(ctl)[tid];
   __syncthreads();
+  // ranks that have announced their departure (leave markers in my flag rows): looked up now, off the critical path
+  unsigned int left_now = 0u;
+  if constexpr (kExchange) {
+    if (cx.world > 1) left_now = leave_mask(cx, ctl_snap.active_mask, (unsigned int)(ctl_snap.step + 1ull));
+  }
   // parameters and momentum of my elements were written by the PREVIOUS update kernel, which had completed (and
   // fenced) before this step's forward/backward kernel let us start: fetch them now (from L2, the coherence
   // point), so that the SGD update after the exchange has no load left in front of its stores
@@ -698,6 +703,7 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
     ExchangeCfg cfg;
     cfg.configured = ctl_snap.active_mask;
     cfg.timeout_ns = ctl_snap.timeout_ns;
+    cfg.left = left_now;
     if (variant == 2u && cx.nvls_mc != nullptr) exchange_slice_nvls<kUVec>(cx, cfg, &xsh, slice, seq, i, in_range, v, &n);
     else if (variant == 1u) exchange_slice_two_shot<kUVec>(cx, cfg, &xsh, slice, seq, i, in_range, v, &n);
     else if (variant == 3u) {
