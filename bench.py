@@ -108,6 +108,23 @@ class ClockSampler:
         if self._t:
             self._t.join()
 
+    def nvlink_kib(self):
+        """(transmitted, received) KiB over all NVLinks of this GPU since the driver loaded (payload counters), or None."""
+        if not self.ok:
+            return None
+        try:
+            nv = self._nv
+            vals = nv.nvmlDeviceGetFieldValues(self._h, [(nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, 0xffffffff),
+                                                         (nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, 0xffffffff)])
+            out = []
+            for v in vals:
+                if v.nvmlReturn != 0:
+                    return None
+                out.append(int(v.value.ullVal))
+            return tuple(out)
+        except Exception:
+            return None
+
     def window(self, t_lo: float, t_hi: float):
         self.t_lo, self.t_hi = t_lo, t_hi
 
@@ -245,8 +262,10 @@ def run_ours(args) -> int:
         eng.set_update_trace(utrace)
         eng.set_debug_flags(4)                  # ring mode: keep the stamps of the last 1024 steps
         comm.barrier()
+        nvl0 = clk.nvlink_kib()
         run_device(A + n_tr)
         torch.cuda.synchronize()
+        nvl1 = clk.nvlink_kib()
         eng.set_debug_flags(0)
         eng.set_update_trace(None)
         end = int(eng.read_ctl().step)
@@ -256,7 +275,10 @@ def run_ours(args) -> int:
         xch_done = u[idx, :, 3].max(axis=1)     # last slice has the sum of all ranks
         wait = np.sort((xch_done - grad_done) / 1e3)
         xch = {"median_us": float(wait[len(wait) // 2]), "p90_us": float(wait[int(len(wait) * 0.9)]),
-               "mean_us": float(wait.mean()), "steps": n_tr}
+               "mean_us": float(wait.mean()), "steps": n_tr,
+               # what the NVLink counters of this GPU saw per step during the traced pass (payload bytes, all links)
+               "nvlink_tx_bytes_per_step": (nvl1[0] - nvl0[0]) * 1024 / (A + n_tr) if nvl0 and nvl1 else None,
+               "nvlink_rx_bytes_per_step": (nvl1[1] - nvl0[1]) * 1024 / (A + n_tr) if nvl0 and nvl1 else None}
         comm.barrier()
 
     stats = comm.allgather({"ms": ms, "e2e_s": e2e_s, "launches": launches, "clk": clk.summary(),
@@ -282,7 +304,11 @@ def run_ours(args) -> int:
                                                "local batch gradient), globaltimer stamps of the update kernel; median over "
                                                f"{xs[0]['steps']} traced steps run after the timed region, max over ranks; "
                                                "compute at peak is negligible, so the roofline is the NVLink time",
-                                 "per_rank_median_us": [round(x["median_us"], 3) for x in xs]}}
+                                 "per_rank_median_us": [round(x["median_us"], 3) for x in xs],
+                                 "nvlink_counters_bytes_per_step_per_gpu": {
+                                     "tx": xs[0]["nvlink_tx_bytes_per_step"], "rx": xs[0]["nvlink_rx_bytes_per_step"],
+                                     "note": "NVML NVLINK_THROUGHPUT_DATA_TX/RX of rank 0's GPU over the traced pass "
+                                             "(KiB granularity), to set against bytes_per_direction_per_gpu"}}}
         out = {
             "metric": METRIC, "value": round(value, 1), "unit": "images/s", "n_gpus": world, "steps": K,
             "warmup": prep + A, "warmup_requested": args.warmup,

@@ -40,6 +40,16 @@ def main():
             out[f"{name}_fwd_N{N}_tcgen05_us"] = round(t_us(lambda: native.tc_conv_relu_pool_fwd(x, w, b, y, idx)), 2)
             out[f"{name}_fwd_N{N}_ffma_us"] = round(t_us(lambda: native.conv_relu_pool_fwd(x, w, b, y, idx)), 2)
             out[f"{name}_fwd_N{N}_torch_cudnn_us"] = round(t_us(lambda: F.max_pool2d(F.relu(F.conv2d(x, w, b)), 2, 2)), 2)
+            # weight + bias gradient (K16 / K17): pooled-grid FFMA kernel, tensor-core kernel, cuDNN (dense gradient given)
+            native.conv_relu_pool_fwd(x, w, b, y, idx)
+            dyp = torch.randn_like(y)
+            dw, db = torch.empty_like(w), torch.empty_like(b)
+            out[f"{name}_wgrad_N{N}_ffma_pooled_grid_us"] = round(
+                t_us(lambda: native.conv_relu_pool_bwd(x, w, y, idx, dyp, None, dw, db)), 2)
+            out[f"{name}_wgrad_N{N}_tcgen05_us"] = round(t_us(lambda: native.tc_conv_wgrad(x, y, idx, dyp, dw, db)), 2)
+            dense = torch.zeros(N, Co, H - 4, H - 4, device="cuda")
+            out[f"{name}_wgrad_N{N}_torch_cudnn_dense_us"] = round(
+                t_us(lambda: torch.nn.grad.conv2d_weight(x, w.shape, dense)), 2)
         for name, (K, M) in (("fc1", (400, 120)), ("fc2", (120, 84))):
             x = torch.randn(N, K, device="cuda")
             w = torch.randn(M, K, device="cuda") * 0.1

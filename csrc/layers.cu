@@ -295,10 +295,18 @@ int launch_conv_relu_pool_fwd(const float* x, const float* w, const float* b, fl
 int launch_tc_conv2_dgrad(const float* w, const float* y, const unsigned char* idx, const float* dy, float* dx, int N,
                           cudaStream_t s);
 
+int launch_tc_conv_wgrad(const float* x, const float* y, const unsigned char* idx, const float* dy, float* dw,
+                         float* db, int N, int Ci, int H, int W, int Co, cudaStream_t s);
+
 int launch_conv_relu_pool_bwd(const float* x, const float* w, const float* y, const unsigned char* idx,
                               const float* dy, float* dx, float* dw, float* db, int N, int Ci, int H, int W,
                               int Co, int tensor_core_dgrad, cudaStream_t s) {
-  {
+  // TF32 mode, conv2, thousands of images: the tensor-core weight gradient is the faster one (518 vs 588 us at 10 000
+  // images, 60 vs 53 us at 1 024: profiles/layer_bench_r2.json); for conv1 the pooled-grid FFMA kernel wins 2.3x
+  if (tensor_core_dgrad && Ci == 6 && H == 14 && W == 14 && Co == 16 && N >= 4096) {
+    const int rc = launch_tc_conv_wgrad(x, y, idx, dy, dw, db, N, Ci, H, W, Co, s);
+    if (rc) return rc;
+  } else {
     // enough (o, c, batch chunk) CTAs for two waves; small batches keep one chunk and the fixed summation order
     int chunks = N >= 64 ? (2 * 148 + Co * Ci - 1) / (Co * Ci) : 1;
     if (chunks > N / 8) chunks = N / 8 > 0 ? N / 8 : 1;

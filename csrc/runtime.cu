@@ -60,6 +60,8 @@ int launch_softmax_xent(const float*, const long long*, float*, float*, int, int
 int launch_sgd_momentum(float*, const float*, float*, int, float, float, int, float, cudaStream_t);
 int launch_tc_conv_relu_pool_fwd(const float*, const float*, const float*, float*, unsigned char*, int, int, int, int,
                                  int, cudaStream_t);
+int launch_tc_conv_wgrad(const float*, const float*, const unsigned char*, const float*, float*, float*, int, int, int, int,
+                         int, cudaStream_t);
 int launch_tc_gemm_probe(const float*, const float*, float*, int, cudaStream_t);
 int launch_tc_linear_fwd(const float*, const float*, const float*, float*, int, int, int, int, cudaStream_t);
 int launch_tc_lab(const float*, int, const float*, int, unsigned long long, unsigned long long, unsigned int, int, int,
@@ -338,6 +340,11 @@ int dnnb200_conv_relu_pool_bwd_tc(const float* x, const float* w, const float* y
                                   float* dx, float* dw, float* db, int N, int Ci, int H, int W, int Co, void* stream) {
   DNN_ARG_CHECK(N > 0 && Ci > 0 && Co > 0, "conv_relu_pool_bwd_tc: bad shape");
   return launch_conv_relu_pool_bwd(x, w, y, idx, dy, dx, dw, db, N, Ci, H, W, Co, 1, (cudaStream_t)stream);
+}
+int dnnb200_tc_conv_wgrad(const float* x, const float* y, const uint8_t* idx, const float* dy, float* dw, float* db, int N,
+                          int Ci, int H, int W, int Co, void* stream) {
+  DNN_ARG_CHECK(N > 0 && x && y && idx && dy && dw && db, "tc_conv_wgrad: bad arguments");
+  return launch_tc_conv_wgrad(x, y, idx, dy, dw, db, N, Ci, H, W, Co, (cudaStream_t)stream);
 }
 int dnnb200_tc_conv_relu_pool_fwd(const float* x, const float* w, const float* b, float* y, uint8_t* idx, int N,
                                   int Ci, int H, int W, int Co, void* stream) {

@@ -164,26 +164,23 @@ tc_conv_relu_pool_fwd_kernel(const float* __restrict__ x, const float* __restric
         mbar_expect_tx(&bar_img, C::STAGE_FLOATS * 4);
         bulk_g2s(stage, x + (size_t)(img + gridDim.x) * C::STAGE_FLOATS, C::STAGE_FLOATS * 4, &bar_img);
       }
-      const uint32_t a0 = smem_u32(planes), b0 = smem_u32(sB);
+      // Issue loop kept to the bone (bench/tc_mma_rate.py: an MMA of this shape costs its issuing thread 64 cycles when
+      // the thread does nothing else, 90+ with descriptor arithmetic in between): the two descriptor bases are built
+      // once, every tap offset is a compile-time constant, per MMA two 64-bit adds remain.
+      const uint64_t b0 = smem_desc_nosw(smem_u32(sB), 128, (uint32_t)(2 * C::NMMA) * 128);
+      const uint64_t a_in = smem_desc_nosw(smem_u32(planes), C::G == 1 ? 16u : (uint32_t)C::kPlaneBytes, 128);
+      const uint64_t a_x = smem_desc_nosw(smem_u32(planes), (uint32_t)(C::WIN - 4) * 16, 128);   // (G == 1) taps 2j, 2j+1 in different kernel rows
 #pragma unroll 1
       for (int t = 0; t < C::TILES; ++t) {
-#pragma unroll 1
+        const uint64_t at = (uint64_t)(t * 128);
+#pragma unroll
         for (int j = 0; j < C::NMMA; ++j) {
-          uint32_t a_start, lbo;
-          if (C::G == 1) {            // K-chunks = taps 2j and 2j+1 of the single plane
-            const int t0 = 2 * j, t1 = 2 * j + 1;
-            const int off0 = (t0 / 5) * C::WIN + (t0 % 5);
-            const int off1 = t1 < 25 ? (t1 / 5) * C::WIN + (t1 % 5) : off0 + 1;   // chunk 25 does not exist: B is zero there
-            a_start = a0 + (uint32_t)(t * 128 + off0) * 16;
-            lbo = (uint32_t)(off1 - off0) * 16;
-          } else {                    // K-chunks = the two channel groups of tap j
-            const int off0 = (j / 5) * C::WIN + (j % 5);
-            a_start = a0 + (uint32_t)(t * 128 + off0) * 16;
-            lbo = (uint32_t)C::kPlaneBytes;
-          }
-          const uint64_t ad = smem_desc_nosw(a_start, lbo, 128);
-          const uint64_t bd = smem_desc_nosw(b0 + (uint32_t)(2 * j) * 128, 128, (uint32_t)(2 * C::NMMA) * 128);
-          mma_tf32(tmem + (uint32_t)t * 16, ad, bd, kIdesc, j > 0);
+          // G == 1: K-chunks = taps 2j and 2j+1 of the single plane (chunk 25 does not exist: B is zero there);
+          // G == 2: K-chunks = the two channel groups of tap j, a plane apart
+          const int tap0 = C::G == 1 ? 2 * j : j;
+          const int off0 = (tap0 / 5) * C::WIN + (tap0 % 5);
+          const bool cross = C::G == 1 && (tap0 % 5) == 4 && tap0 + 1 < 25;
+          mma_tf32(tmem + (uint32_t)t * 16, (cross ? a_x : a_in) + at + (uint64_t)off0, b0 + (uint64_t)(16 * j), kIdesc, j > 0);
         }
       }
       mma_commit(&bar_mma);
@@ -295,18 +292,19 @@ tc_conv2_dgrad_kernel(const float* __restrict__ w, const float* __restrict__ y, 
     fence_proxy_async();
     __syncthreads();
     if (tid == 0) {
-      const uint32_t a0 = smem_u32(planes), b0 = smem_u32(sB);
+      // (lean issue loop: descriptor bases once, compile-time offsets, two 64-bit adds per MMA -- see the forward kernel)
+      const uint64_t a0 = smem_desc_nosw(smem_u32(planes), (uint32_t)C::kPlaneBytes, 128);
+      const uint64_t b0 = smem_desc_nosw(smem_u32(sB), 128, 100 * 128);
 #pragma unroll 1
-      for (int t = 0; t < C::TILES; ++t)
-#pragma unroll 1
+      for (int t = 0; t < C::TILES; ++t) {
+        const uint64_t at = (uint64_t)(t * 128);
+#pragma unroll
         for (int j = 0; j < C::NMMA; ++j) {
           const int tap = j >> 1, gp = (j & 1) * 2;   // this MMA: planes gp and gp+1 of tap
-          const int off = (tap / 5) * C::WP + (tap % 5);
-          const uint64_t ad = smem_desc_nosw(a0 + (uint32_t)(gp * C::kPlaneBytes) + (uint32_t)(t * 128 + off) * 16,
-                                             (uint32_t)C::kPlaneBytes, 128);
-          const uint64_t bd = smem_desc_nosw(b0 + (uint32_t)(2 * j) * 128, 128, 100 * 128);
-          mma_tf32(tmem + (uint32_t)t * 16, ad, bd, kIdesc, j > 0);
+          const int off = (tap / 5) * C::WP + (tap % 5) + gp * C::PLANE_PIX;
+          mma_tf32(tmem + (uint32_t)t * 16, a0 + at + (uint64_t)off, b0 + (uint64_t)(16 * j), kIdesc, j > 0);
         }
+      }
       mma_commit(&bar_mma);
     }
     mbar_wait(&bar_mma, phase);

@@ -184,6 +184,15 @@ def conv_relu_pool_bwd(x, w, y, idx, dy, dx, dw, db, tensor_cores: bool = False)
                                           N, Ci, H, W, w.shape[0], _stream()))
 
 
+def tc_conv_wgrad(x, y, idx, dy, dw, db) -> None:
+    """Tensor-core (tcgen05, TF32) weight/bias gradient of conv_relu_pool for the CNN's two conv shapes
+    (csrc/tc_conv_wgrad.cu). The measured alternative to the pooled-grid FFMA kernel inside conv_relu_pool_bwd."""
+    lib = require()
+    N, Ci, H, W = x.shape
+    _check(lib.dnnb200_tc_conv_wgrad(_p(_f32(x, "x")), _p(_f32(y, "y")), _p(idx), _p(_f32(dy, "dy")), _p(_f32(dw, "dw")),
+                                     _p(_f32(db, "db")), N, Ci, H, W, dw.shape[0], _stream()))
+
+
 def linear_fwd(x, w, b, y, relu: bool) -> None:
     lib = require()
     N, K = x.shape

@@ -45,6 +45,12 @@ int dnnb200_conv_relu_pool_bwd(const float* x, const float* w, const float* y, c
 int dnnb200_conv_relu_pool_bwd_tc(const float* x, const float* w, const float* y, const uint8_t* idx,
                                   const float* dy, float* dx, float* dw, float* db,
                                   int N, int Ci, int H, int W, int Co, void* stream);
+/* weight and bias gradient of conv5x5 + ReLU + maxpool2x2 on the tensor cores (tcgen05.mma kind::tf32): the reduction
+ * runs over output pixels, so the transposed im2col operand is gathered into shared memory block by block and the
+ * accumulators stay in tensor memory over all images of a CTA (csrc/tc_conv_wgrad.cu). dw, db are overwritten.
+ * Only the CNN's two conv shapes. (reference: convolution_backward of data_parallelism_train.py:198) */
+int dnnb200_tc_conv_wgrad(const float* x, const float* y, const uint8_t* idx, const float* dy, float* dw, float* db, int N,
+                          int Ci, int H, int W, int Co, void* stream);
 /* the same forward on the tensor cores: implicit GEMM, tcgen05.mma kind::tf32 with TMEM accumulators,
  * the shared-memory descriptor performs the im2col (csrc/tc_conv.cu). TF32 operands, fp32 accumulate.
  * Instantiated for the two conv layers of the CNN: (Ci,H,W,Co) = (3,32,32,6) and (6,14,14,16). */

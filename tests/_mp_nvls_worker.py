@@ -1,4 +1,5 @@
 """Worker for the NVLS test: all-reduce the same random vectors with the one-shot and the NVLS variant."""
+import os
 import sys
 from pathlib import Path
 
@@ -12,6 +13,7 @@ from distributed_neural_network_b200.trainer import TrainConfig, Trainer  # noqa
 
 def main():
     out_dir = sys.argv[1]
+    os.makedirs(out_dir, exist_ok=True)   # every rank writes its result here; nobody may rely on another rank's mkdir
     tr = Trainer(TrainConfig(device="cuda", synthetic=True, quiet=True, sync_mode="step-allreduce", seed=3,
                              peer_timeout_s=20.0, log_dir=out_dir + "/log"))
     res = {"rank": tr.rank, "nvls": tr.nvls_ok}

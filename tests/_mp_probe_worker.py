@@ -1,4 +1,5 @@
 """Worker for the 128-byte-line probe: ranks pair up (0-1, 2-3, ...) and play ping-pong over NVLink."""
+import os
 import sys
 from pathlib import Path
 
@@ -11,6 +12,7 @@ from distributed_neural_network_b200.trainer import TrainConfig, Trainer  # noqa
 
 def main():
     out_dir, iters, n_ctas = sys.argv[1], int(sys.argv[2]), int(sys.argv[3])
+    os.makedirs(out_dir, exist_ok=True)   # every rank writes its result here; nobody may rely on another rank's mkdir
     tr = Trainer(TrainConfig(device="cuda", synthetic=True, quiet=True, sync_mode="step-allreduce", seed=3,
                              peer_timeout_s=20.0, log_dir=out_dir + "/log", calibrate_exchange=False))
     res = {"rank": tr.rank, "world": tr.world}

@@ -13,6 +13,7 @@ from distributed_neural_network_b200.trainer import TrainConfig, Trainer  # noqa
 
 def main():
     out_dir, mode = sys.argv[1], sys.argv[2]
+    os.makedirs(out_dir, exist_ok=True)   # every rank writes its result here; nobody may rely on another rank's mkdir
     kw = json.loads(sys.argv[3]) if len(sys.argv) > 3 else {}
     cfg = TrainConfig(device=kw.pop("device", "cpu"), synthetic=True, quiet=True, sync_mode=mode,
                       log_dir=out_dir + "/log", **kw)

@@ -172,3 +172,35 @@ def test_mn_major_tf32_operand_address_function():
                       idesc(128, 16, 1, 0), 16)
     torch.cuda.synchronize()
     assert float(D[:, :8].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("shape", [(3, 32, 6), (6, 14, 16)])
+@pytest.mark.parametrize("N", [1, 16, 300, 1111])
+def test_tc_conv_weight_gradient(N, shape):
+    """Tensor-core weight/bias gradient of conv+ReLU+pool (transposed im2col gathered into shared memory, reduction
+    over pixels on tcgen05, accumulators kept in tensor memory over all images of a CTA) against PyTorch autograd.
+    Forward and argmax come from the exact fp32 kernel, so the two sides route every gradient to the same pixel and
+    only the TF32 rounding of the operands separates them."""
+    Ci, H, Co = shape
+    torch.manual_seed(17 * N + Ci)
+    x = torch.randn(N, Ci, H, H)
+    w = (torch.randn(Co, Ci, 5, 5) * (Ci * 25) ** -0.5).requires_grad_(True)
+    b = (torch.randn(Co) * 0.1).requires_grad_(True)
+    out = F.max_pool2d(F.relu(F.conv2d(x, w, b)), 2, 2)
+    gy = torch.randn_like(out)
+    out.backward(gy)
+    xg, wg, bg = x.cuda(), w.detach().cuda(), b.detach().cuda()
+    Hp = (H - 4) // 2
+    y = torch.empty(N, Co, Hp, Hp, device="cuda")
+    idx = torch.empty(N, Co, Hp, Hp, dtype=torch.uint8, device="cuda")
+    native.conv_relu_pool_fwd(xg, wg, bg, y, idx)
+    dw = torch.full((Co, Ci, 5, 5), float("nan"), device="cuda")
+    db = torch.full((Co,), float("nan"), device="cuda")
+    native.tc_conv_wgrad(xg, y, idx, gy.cuda().contiguous(), dw, db)
+    torch.cuda.synchronize()
+    assert _rel(dw, w.grad) < 3e-3, _rel(dw, w.grad)
+    assert _rel(db, b.grad) < 2e-3, _rel(db, b.grad)
+    # and it agrees with the FFMA kernel it is the alternative to
+    dw2, db2 = torch.empty_like(dw), torch.empty_like(db)
+    native.conv_relu_pool_bwd(xg, wg, y, idx, gy.cuda().contiguous(), None, dw2, db2)
+    assert _rel(dw, dw2) < 3e-3
