@@ -749,12 +749,13 @@ int dnnb200_engine_train_host(dnnb200_engine* e, const float* h_x, const int64_t
   // images and one for the labels (every step's inputs are still copied, inside the call, just not one DMA
   // descriptor per step), and the cross-stream events (inputs ready / slots free) are recorded once per group, so
   // that inside a group nothing sits between the kernels in the stream and their programmatic dependent launches
-  // overlap. The FIRST group of a call is short: the GPU starts on step 0 after two steps' worth of PCIe time
-  // instead of eight, which is most of the fixed cost of a short call.
+  // overlap. A call ramps up: its groups hold 1, 2, 4, then 8 steps, so the GPU starts on step 0 after ONE step's
+  // worth of PCIe time and every later copy (16 us per step of batch 16) is shorter than the kernels of the group
+  // before it (17-24 us per step) -- most of the fixed cost of a short call.
   constexpr int G = dnnb200_engine::kGroup;
   const bool may_chain = !stream_capturing(s);   // same rule as train_device: a captured counter value would be stale
   for (int t0 = 0; t0 < nsteps;) {
-    const int cap = t0 == 0 ? 2 : G;
+    const int cap = t0 + 1 < G ? t0 + 1 : G;   // groups of 1, 2, 4, 8, 8, ...: each group's copy hides under the previous group's kernels
     const int n = nsteps - t0 < cap ? nsteps - t0 : cap;
     const int gslot = (int)((e->ring_uses / G) % (R / G));        // group index in the ring
     if (e->ring_uses >= (unsigned long long)R) DNN_CUDA_CHECK(cudaStreamWaitEvent(e->copy_stream, e->slot_free[gslot], 0));
