@@ -329,6 +329,10 @@ def run_ours(args) -> int:
             "dtype": ("tf32 tensor-core operands for conv1/conv2 forward and the conv2 data gradient (tcgen05, fp32 "
                       "accumulate); FC layers, weight gradients, softmax, SGD and master weights fp32"
                       if eng.precision == "tf32" and cs > 1 else
+                      "fp32 (FFMA, fp32 accumulate, fp32 master weights) except the conv2 data gradient, which runs on "
+                      "the tensor cores (tcgen05, TF32 operands, fp32 accumulate): forward, loss and all gradients but "
+                      "conv1's are the fp32 ones"
+                      if eng.precision == "tf32-dgrad" and cs > 1 else
                       "fp32 (FFMA, fp32 accumulate, fp32 master weights; reference is fp32)"),
             "data": "synthetic CIFAR-10-shaped (3x32x32 in [-1,1], 10 classes), random-init weights",
             "config": {"model": "models/model.py Network (LeNet-5 style CNN, 62006 params)",
@@ -474,7 +478,7 @@ def main() -> int:
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--exchange", choices=["auto", "one-shot", "one-shot-128", "two-shot", "nvls"], default="auto",
                     help="gradient exchange variant (auto: every usable variant is timed at start-up, the fastest runs)")
-    ap.add_argument("--precision", choices=["tf32", "fp32"], default=None,
+    ap.add_argument("--precision", choices=["fp32", "tf32", "tf32-dgrad"], default=None,
                     help="conv stages of the fused step: fp32 = FFMA (default, measured faster), tf32 = tcgen05 tensor cores")
     ap.add_argument("--ref-max-steps", type=int, default=400)
     ap.add_argument("--ref-timeout", type=float, default=1500.0)

@@ -42,11 +42,13 @@ constexpr int kXCh = 32 * kXRow + 8;       //   kernel rows of a wgrad gather fa
 // stage barriers: one mbarrier per all-gather, completed by the st.async traffic itself
 enum { kBarP1 = 0, kBarP2, kBarH1, kBarH2, kBarD1, kBarG2, kBarW1, kNumStageBars };
 
-template <bool kTC>
+// kMode: 0 = fp32 FFMA throughout; 1 = conv1, conv2 and the conv2 data gradient on tcgen05 (TF32 operands);
+//        2 = fp32 FFMA forward and weight gradients, ONLY the conv2 data gradient on tcgen05
+template <int kMode>
 struct CLSmemT;
 
 template <>
-struct __align__(16) CLSmemT<false> {
+struct __align__(16) CLSmemT<0> {
   alignas(16) float xd[kImgNumel];    // image as it is in global memory (ONE 12 KB TMA bulk copy)
   alignas(16) float x[3 * kXCh];      // image, CHW with padded rows (re-laid out by the threads)
   alignas(16) float cw[kConvPrefix];  // conv1.weight | conv1.bias | conv2.weight | conv2.bias exactly as in the flat
@@ -91,7 +93,7 @@ constexpr uint32_t kTmemC2 = 64, kTmemDg = 96;
 enum { kTBarC1 = 0, kTBarC2, kTBarDg, kNumTcBars };
 
 template <>
-struct __align__(128) CLSmemT<true> {
+struct __align__(128) CLSmemT<1> {
   alignas(128) float xpl[kXPlanePix * 4];        // image, NHWC4 (x, y, z, 0) per pixel, row pitch kXPitch: conv1 A operand
                                                  //   and the conv1 weight gradient's gather
   alignas(128) float dpl[4 * kDPlanePix * 4];    // dL/d(conv2 output), 4 planes of 4 channels, zero-padded 18x18: dgrad A
@@ -118,6 +120,36 @@ struct __align__(128) CLSmemT<true> {
   alignas(8) unsigned long long sbar[kNumStageBars];
   alignas(8) unsigned long long tbar[kNumTcBars];      // tcgen05.commit targets
   alignas(8) unsigned long long pbar;                  // bulk copy of sb2 | sbd (packed operands from global memory)
+  uint32_t tmem_slot;
+};
+
+// fp32 layout with the data gradient's tensor-core operands in place of its FFMA buffers (dc2p, w2d)
+template <>
+struct __align__(128) CLSmemT<2> {
+  alignas(128) float dpl[4 * kDPlanePix * 4];    // dL/d(conv2 output), 4 planes of 4 channels, zero-padded 18x18: dgrad A
+  alignas(128) float sbd[2 * kBdChunks * 32];    // conv2.weight flipped and transposed for the data gradient (B operand)
+  alignas(16) float xd[kImgNumel];    // image as it is in global memory (ONE 12 KB TMA bulk copy)
+  alignas(16) float x[3 * kXCh];      // image, CHW with padded rows (re-laid out by the threads)
+  alignas(16) float cw[kConvPrefix];  // conv1.weight | conv1.bias | conv2.weight | conv2.bias exactly as in the flat
+                                      // parameter vector (offsets kOffW1, kOffB1, kOffW2, kOffB2): one TMA bulk copy
+  alignas(16) float p1[1176 + 8];
+  alignas(16) float p2[400];
+  alignas(16) float h1[120];
+  alignas(16) float h2[88];
+  alignas(16) float logits[16];
+  alignas(16) float d3[16];
+  alignas(16) float d2[88];
+  alignas(16) float d1[120];
+  alignas(16) float g2[400];
+  alignas(16) float g1[1176 + 8];
+  alignas(16) int idx1[1176 + 8];     // 2-bit argmax of the pooling windows (one word each: st.async granularity)
+  alignas(16) int idx2[400];
+  alignas(16) int poff[196];          // (2*ph)*kXRow + 2*pw of pooled pixel q
+  alignas(8) unsigned long long mbar;                  // image bulk copies
+  alignas(8) unsigned long long cbar;                  // conv weights bulk copy (once per launch)
+  alignas(8) unsigned long long sbar[kNumStageBars];   // all-gather completion
+  alignas(8) unsigned long long tbar[kNumTcBars];      // tcgen05.commit target (only kTBarDg is used)
+  alignas(8) unsigned long long pbar;                  // bulk copy of sbd (packed operand from global memory)
   uint32_t tmem_slot;
 };
 
@@ -338,9 +370,9 @@ struct FCSmem {
   alignas(16) float rx_g2[CS * kFlat];  // partial dL/dp2
   alignas(8) unsigned long long wbar;   // weight prefetch
 };
-template <bool kTC>
+template <int kMode>
 __host__ __device__ constexpr size_t fc_off() {
-  return (sizeof(CLSmemT<kTC>) + 127) & ~(size_t)127;
+  return (sizeof(CLSmemT<kMode>) + 127) & ~(size_t)127;
 }
 // conv1 weight-gradient partials of the CTAs of a cluster, collected by CTA 0 (row d = CTA d: 450 weights + 6 biases)
 constexpr int kW1Row = 456;
@@ -348,29 +380,35 @@ constexpr int kW1Row = 456;
 // 5*no*150 live together; every other use (conv2 forward partials, conv1 wgrad partials, CS<4 FC splits) is smaller
 // (tensor-core instantiation: the data gradient and the conv2 forward need no partials, only the two weight
 // gradients do -- 5*no*150 and 5*450+30 floats; clusters below 4 still split the FC data gradients through it)
-template <int CS, bool kTC = false>
+template <int CS, int kMode = 0>
 struct W1Rx {
   static constexpr int kNq = (196 + CS - 1) / CS, kNo = (16 + CS - 1) / CS;
-  static constexpr int kRed0 = kTC ? (5 * kNo * 150 > 2304 ? 5 * kNo * 150 : 2304) : 96 * kNq + 5 * kNo * 150;
-  static constexpr int kRedMin = (kTC && CS >= 4) ? 0 : 6400;
+  static constexpr int kWg = 5 * kNo * 150 > 2304 ? 5 * kNo * 150 : 2304;        // the two weight gradients' partials
+  static constexpr int kC2 = kNo * 600;                                          // FFMA conv2 forward partials
+  static constexpr int kRed0 = kMode == 1 ? kWg : (kMode == 2 ? (kWg > kC2 ? kWg : kC2) : 96 * kNq + 5 * kNo * 150);
+  static constexpr int kRedMin = (kMode != 0 && CS >= 4) ? 0 : 6400;
   static constexpr int kRed = kRed0 > kRedMin ? kRed0 : kRedMin;
   alignas(16) float red[kRed];
   alignas(16) float rx[CS * kW1Row];
 };
-template <int CS, bool kTC = false>
+template <int CS, int kMode = 0>
 __host__ __device__ constexpr size_t w1rx_offset() {
-  return CS >= 4 ? ((fc_off<kTC>() + sizeof(FCSmem<CS>) + 127) & ~(size_t)127) : fc_off<kTC>();
+  return CS >= 4 ? ((fc_off<kMode>() + sizeof(FCSmem<CS>) + 127) & ~(size_t)127) : fc_off<kMode>();
 }
-template <int CS, bool kTC = false>
+template <int CS, int kMode = 0>
 __host__ __device__ constexpr size_t cluster_smem_bytes() {
-  return w1rx_offset<CS, kTC>() + sizeof(W1Rx<CS, kTC>);
+  return w1rx_offset<CS, kMode>() + sizeof(W1Rx<CS, kMode>);
 }
 static_assert(cluster_smem_bytes<4>() <= 227 * 1024 && cluster_smem_bytes<2>() <= 227 * 1024 &&
               cluster_smem_bytes<8>() <= 227 * 1024, "shared memory budget");
-static_assert(cluster_smem_bytes<2, true>() <= 227 * 1024 && cluster_smem_bytes<3, true>() <= 227 * 1024 &&
-              cluster_smem_bytes<4, true>() <= 227 * 1024 && cluster_smem_bytes<5, true>() <= 227 * 1024 &&
-              cluster_smem_bytes<6, true>() <= 227 * 1024 && cluster_smem_bytes<7, true>() <= 227 * 1024 &&
-              cluster_smem_bytes<8, true>() <= 227 * 1024, "shared memory budget (tensor-core instantiation)");
+static_assert(cluster_smem_bytes<2, 1>() <= 227 * 1024 && cluster_smem_bytes<3, 1>() <= 227 * 1024 &&
+              cluster_smem_bytes<4, 1>() <= 227 * 1024 && cluster_smem_bytes<5, 1>() <= 227 * 1024 &&
+              cluster_smem_bytes<6, 1>() <= 227 * 1024 && cluster_smem_bytes<7, 1>() <= 227 * 1024 &&
+              cluster_smem_bytes<8, 1>() <= 227 * 1024, "shared memory budget (tensor-core instantiation)");
+static_assert(cluster_smem_bytes<2, 2>() <= 227 * 1024 && cluster_smem_bytes<3, 2>() <= 227 * 1024 &&
+              cluster_smem_bytes<4, 2>() <= 227 * 1024 && cluster_smem_bytes<5, 2>() <= 227 * 1024 &&
+              cluster_smem_bytes<6, 2>() <= 227 * 1024 && cluster_smem_bytes<7, 2>() <= 227 * 1024 &&
+              cluster_smem_bytes<8, 2>() <= 227 * 1024, "shared memory budget (tensor-core data gradient only)");
 
 // rows [m0, m1) of y = act(b + W . in) with the rows in shared memory (wsm[0] is row m0)
 template <int CS, int K, bool kRelu>
@@ -446,7 +484,7 @@ __device__ __forceinline__ void tc_issue_taps(uint32_t d_tmem, uint64_t a0, uint
 #ifndef DNN_F_MAXNREG
 #define DNN_F_MAXNREG 0
 #endif
-template <int CS, bool kTC>
+template <int CS, int kMode>
 #if DNN_F_MAXNREG > 0
 __global__ void __maxnreg__(DNN_F_MAXNREG)
 #else
@@ -460,9 +498,11 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
                        const float* __restrict__ packed) {
   static_assert(CS >= 2 && CS <= 8, "the one-CTA case is fused_step.cu's fwd_bwd_kernel");
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  using SM = CLSmemT<kTC>;
+  constexpr bool kTC = kMode == 1;    // conv1, conv2 forward on tcgen05 (and the layouts that go with it)
+  constexpr bool kTCD = kMode != 0;   // conv2 data gradient on tcgen05
+  using SM = CLSmemT<kMode>;
   SM& s = *reinterpret_cast<SM*>(smem_raw);
-  constexpr size_t kFcOff = fc_off<kTC>();
+  constexpr size_t kFcOff = fc_off<kMode>();
   cg::cluster_group cluster = cg::this_cluster();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (trace != nullptr && tid == 0) trace[blockIdx.x * 32 + 14] = (long long)globaltimer_ns();
@@ -475,9 +515,9 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
   FCSmem<kPre ? CS : 4>& f = *reinterpret_cast<FCSmem<kPre ? CS : 4>*>(smem_raw + kFcOff);
   constexpr uint32_t kRxD1 = (uint32_t)(kFcOff + offsetof(FCSmem<kPre ? CS : 4>, rx_d1));
   constexpr uint32_t kRxG2 = (uint32_t)(kFcOff + offsetof(FCSmem<kPre ? CS : 4>, rx_g2));
-  using Tail = W1Rx<CS, kTC>;
-  Tail& tail = *reinterpret_cast<Tail*>(smem_raw + w1rx_offset<CS, kTC>());
-  constexpr uint32_t kRxW1 = (uint32_t)(w1rx_offset<CS, kTC>() + offsetof(Tail, rx));
+  using Tail = W1Rx<CS, kMode>;
+  Tail& tail = *reinterpret_cast<Tail*>(smem_raw + w1rx_offset<CS, kMode>());
+  constexpr uint32_t kRxW1 = (uint32_t)(w1rx_offset<CS, kMode>() + offsetof(Tail, rx));
   const float* rx_w1 = tail.rx;
   float* const sred = tail.red;
 
@@ -491,8 +531,8 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
 #pragma unroll
     for (int i = 0; i < kNumStageBars; ++i) cl_mbar_init(&s.sbar[i], 1);
     if (kPre) cl_mbar_init(&f.wbar, 1);
-    if constexpr (kTC) {   // one arrival per issuing thread: conv1 one per tile of mine, conv2 and the data gradient two
-      cl_mbar_init(&s.tbar[kTBarC1], (8 - r + CS - 1) / CS);
+    if constexpr (kTCD) {   // one arrival per issuing thread: conv1 one per tile of mine, conv2 and the data gradient two
+      cl_mbar_init(&s.tbar[kTBarC1], kTC ? (8 - r + CS - 1) / CS : 1);
       cl_mbar_init(&s.tbar[kTBarC2], 2);
       cl_mbar_init(&s.tbar[kTBarDg], 2);
       cl_mbar_init(&s.pbar, 1);
@@ -518,9 +558,14 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     for (int i = tid; i < 2 * kP1PlanePix; i += kCLThreads) reinterpret_cast<float4*>(s.p1n)[i] = z;
     static_assert(offsetof(SM, sb2) == offsetof(SM, sb1) + sizeof(s.sb1) &&
                   offsetof(SM, sbd) == offsetof(SM, sb2) + sizeof(s.sb2), "B operands are zeroed as one block");
+  } else if constexpr (kTCD) {
+    if (packed == nullptr) {   // the data gradient's B operand is packed in this kernel: zero its padding beforehand
+      for (int i = tid; i < (int)sizeof(s.sbd) / 16; i += kCLThreads)
+        reinterpret_cast<float4*>(s.sbd)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
   }
   __syncthreads();
-  if constexpr (kTC) {
+  if constexpr (kTCD) {
     // (allocation takes a few hundred cycles: warp 1 does it while the others go on to the image and the dependency
     // wait; the address is picked up after the block barrier at the top of the image loop)
     if (warp == 1) {
@@ -560,7 +605,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
   };
   // dense dL/d(conv2 output), zero-padded: rewritten (scattered into) for every image, so zeroed for every image
   auto zero_grad_plane = [&]() {
-    if constexpr (kTC) {
+    if constexpr (kTCD) {
       const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
       for (int i = tid; i < 4 * kDPlanePix; i += kCLThreads) reinterpret_cast<float4*>(s.dpl)[i] = z;
     } else {
@@ -607,6 +652,12 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     } else {
       cl_mbar_expect_tx(&s.cbar, kConvPrefix * 4);
       cl_bulk_g2s(s.cw, params, kConvPrefix * 4, &s.cbar);
+      if constexpr (kTCD) {
+        if (packed != nullptr) {   // the data gradient's B operand, ready-made; needed two thirds into the kernel
+          cl_mbar_expect_tx(&s.pbar, (uint32_t)sizeof(s.sbd));
+          cl_bulk_g2s(s.sbd, packed + kPackBd, (uint32_t)sizeof(s.sbd), &s.pbar);
+        }
+      }
     }
     if (kPre) {
       const int a0 = r * kF1 / CS, a1 = (r + 1) * kF1 / CS, c0 = r * kF2 / CS, c1 = (r + 1) * kF2 / CS;
@@ -658,7 +709,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     }
     cl_mbar_wait(&s.cbar, 0);      // conv weights landed (first image; complete ever after)
     __syncthreads();
-    if constexpr (kTC) {
+    if constexpr (kTCD) {
       tc::tc_fence_after();
       tmem = s.tmem_slot;
     }
@@ -908,12 +959,25 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
           push_all<CS>(R, CL_OFF(idx1) + 4u * oi, CL_BAR(kBarP1), (uint32_t)bi);
         }
       }
-      if (first_img) {  // conv2 weights in data-gradient layout [(o,tap)][c8]: built once, off the critical path
-        for (int ot = tid; ot < 400; ot += kCLThreads) {
-          const int o = ot / 25, t = ot - o * 25;
-          const float* src = s.cw + kOffW2 + o * 150 + t;
-          reinterpret_cast<float4*>(s.w2d)[ot * 2] = make_float4(src[0], src[25], src[50], src[75]);
-          reinterpret_cast<float4*>(s.w2d)[ot * 2 + 1] = make_float4(src[100], src[125], 0.f, 0.f);
+      if constexpr (!kTCD) {
+        if (first_img) {  // conv2 weights in data-gradient layout [(o,tap)][c8]: built once, off the critical path
+          for (int ot = tid; ot < 400; ot += kCLThreads) {
+            const int o = ot / 25, t = ot - o * 25;
+            const float* src = s.cw + kOffW2 + o * 150 + t;
+            reinterpret_cast<float4*>(s.w2d)[ot * 2] = make_float4(src[0], src[25], src[50], src[75]);
+            reinterpret_cast<float4*>(s.w2d)[ot * 2 + 1] = make_float4(src[100], src[125], 0.f, 0.f);
+          }
+        }
+      } else {
+        if (first_img && packed == nullptr) {
+          // no ready-made operand (first step of an engine call): pack the data gradient's B operand here, off the
+          // critical path -- n = input channel, K-chunk = 4*(flipped tap) + o/4, component o%4; a warp writes the 32
+          // consecutive floats of one chunk
+          for (int u = warp; u < 100; u += kCLThreads / 32) {
+            const int tp = u >> 2, og = u & 3, ch = lane >> 2, o = og * 4 + (lane & 3);
+            if (ch < 6) s.sbd[(4 * tp + og) * 32 + lane] = s.cw[kOffW2 + (o * 6 + ch) * 25 + (24 - tp)];
+          }
+          tc::fence_proxy_async();   // (a block barrier follows long before the data gradient reads it)
         }
       }
       CL_TRACE(3);
@@ -1083,7 +1147,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     if (tid < 400) {  // scatter the pooled gradient to its argmax position (maxpool backward)
       const int o = tid / 25, pp = tid - o * 25, ph = pp / 5, pw = pp - ph * 5;
       const int id = s.idx2[tid];
-      if constexpr (kTC) {
+      if constexpr (kTCD) {
         s.dpl[(((o >> 2) * kDPlanePix) + (2 * ph + (id >> 1) + 4) * kDPitch + (2 * pw + (id & 1) + 4)) * 4 + (o & 3)] = s.g2[tid];
         tc::fence_proxy_async();
       } else {
@@ -1097,16 +1161,17 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     // first, the weight-gradient items fill the remaining threads, and only two block barriers are needed.
     {
       const int no = o1 - o0;
-      const int n_dg = kTC ? 0 : nq * 16;   // data gradient: (o, pixel) -> 6 channel sums (kTC: on the tensor core instead)
+      const int n_dg = kTCD ? 0 : nq * 16;  // data gradient: (o, pixel) -> 6 channel sums (kTCD: on the tensor core instead)
       const int n_wg = no * 30 * 5;         // weight gradient: (pixel row, o, c, kh) -> 5 taps
       float* red_dg = sred;                            // [16*6][nq]
-      float* red_wg = kTC ? sred : sred + 96 * nq;     // [5][no*150]
-      // kTC: dX[c][ih][iw] = sum_{o,a,b} dCp[o][ih+a][iw+b] W[o][c][4-a][4-b] as ONE 128-row tile of the implicit GEMM
+      float* red_wg = kTCD ? sred : sred + 96 * nq;    // [5][no*150]
+      // kTCD: dX[c][ih][iw] = sum_{o,a,b} dCp[o][ih+a][iw+b] W[o][c][4-a][4-b] as ONE 128-row tile of the implicit GEMM
       // over the zero-padded gradient planes: GEMM row m = ih*18 + iw, my pixel rows start at row dg_m0 of the plane
       // (clamped so that the tile ends inside the plane; any cluster size's pixel range spans fewer than 128 rows).
       const int dg_m0 = min((q0 / 14) * kDPitch, 128);
-      if constexpr (kTC) {
+      if constexpr (kTCD) {
         if (lane == 0 && warp < 2) {   // two issuing threads, 25 MMAs each, into two accumulators (added in the epilogue)
+          if (packed != nullptr) cl_mbar_wait(&s.pbar, 0);   // the B operand has landed (long ago; stays complete)
           tc::tc_fence_after();
           constexpr uint32_t kIdesc = tc::idesc_tf32(128, 16);
           // K-chunks of MMA j = two of the four channel planes of tap j/2: planes 0,1 for even j, 2,3 for odd j
@@ -1119,12 +1184,12 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
           if (warp == 0) CL_TRACE(21);
         }
       }
-      // (kTC: warps 0 and 1 hold the two issuing threads; their other lanes would only start on weight-gradient
+      // (kTCD: warps 0 and 1 hold the two issuing threads; their other lanes would only start on weight-gradient
       // items once the issue loop is through, so the items go to warps 2..15)
-      for (int item = kTC ? tid - 64 : tid; item < n_dg + n_wg; item += kTC ? kCLThreads - 64 : kCLThreads) {
+      for (int item = kTCD ? tid - 64 : tid; item < n_dg + n_wg; item += kTCD ? kCLThreads - 64 : kCLThreads) {
         if (item < 0) break;
         if (item < n_dg) {
-         if constexpr (!kTC) {
+         if constexpr (!kTCD) {
           const int o = item / nq, ql = item - o * nq, q = q0 + ql;
           const int ih = q / 14, iw = q - ih * 14;
           float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -1170,7 +1235,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       }
       __syncthreads();
       CL_TRACE(11);
-      if constexpr (kTC) {
+      if constexpr (kTCD) {
         cl_mbar_wait(&s.tbar[kTBarDg], phase);
         tc::tc_fence_after();
         if (warp < 4) {   // TMEM lane = GEMM row: dL/dp1 for my pixels, masked by ReLU (stays in this CTA)
@@ -1183,18 +1248,22 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
           if (iw < 14 && q >= q0 && q < q1) {
 #pragma unroll
             for (int c = 0; c < 6; ++c) {
-              const uint32_t pbits = __float_as_uint(s.p1n[(((c >> 2) * kP1PlanePix) + q) * 4 + (c & 3)]);
-              s.g1[c * 196 + q] = (pbits & ~3u) != 0u ? v[c] : 0.f;   // p1 > 0, ignoring the argmax bits
+              if constexpr (kTC) {
+                const uint32_t pbits = __float_as_uint(s.p1n[(((c >> 2) * kP1PlanePix) + q) * 4 + (c & 3)]);
+                s.g1[c * 196 + q] = (pbits & ~3u) != 0u ? v[c] : 0.f;   // p1 > 0, ignoring the argmax bits
+              } else {
+                s.g1[c * 196 + q] = s.p1[c * 196 + q] > 0.f ? v[c] : 0.f;
+              }
             }
           }
         }
         tc::tc_fence_before();
       }
       float* dst = part2 + (size_t)img * (kConvPrefix - kOffW2);
-      const int n_g1 = kTC ? 0 : nq * 6, n_w2 = no * 150;
+      const int n_g1 = kTCD ? 0 : nq * 6, n_w2 = no * 150;
       for (int t = tid; t < n_g1 + n_w2 + no; t += kCLThreads) {
         if (t < n_g1) {                    // dL/dp1 for my pixels, masked by ReLU (stays in this CTA)
-         if constexpr (!kTC) {
+         if constexpr (!kTCD) {
           const int c = t / nq, ql = t - c * nq;
           float v = 0.f;
 #pragma unroll
@@ -1296,21 +1365,21 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       load_image(img + n_clusters);
     }
   }
-  if constexpr (kTC) {
+  if constexpr (kTCD) {
     tc::tc_fence_before();
     __syncthreads();
     if (warp == 1) tc::tmem_free<kTmemCols>(tmem);
   }
 }
 
-template <int CS, bool kTC>
+template <int CS, int kMode>
 static int launch_cluster_t(const float* params, const float* x, const long long* labels, float* saved, float* part1,
                             float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
                             long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
                             const float* packed, cudaStream_t stream) {
   static PerDeviceOnce attr_set;
-  auto kern = fwd_bwd_cluster_kernel<CS, kTC>;
-  const size_t smem = cluster_smem_bytes<CS, kTC>();
+  auto kern = fwd_bwd_cluster_kernel<CS, kMode>;
+  const size_t smem = cluster_smem_bytes<CS, kMode>();
   if (int rc = ensure_max_dynamic_smem(attr_set, kern, smem)) return rc;
   const int n_clusters = B < max_clusters ? B : max_clusters;
   cudaLaunchConfig_t cfg = {};
@@ -1332,7 +1401,7 @@ static int launch_cluster_t(const float* params, const float* x, const long long
   const float inv_batch = 1.f / (float)B;
   DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, params, x, labels, saved, part1, part2, img_loss, img_correct, B,
                                     inv_batch, trace, CS >= 4 ? ready_ctr : nullptr, ready_expect,
-                                    kTC ? packed : nullptr));
+                                    kMode != 0 ? packed : nullptr));
   return kOk;
 }
 
@@ -1346,12 +1415,12 @@ int pick_cluster_size(int B, int num_sms) {
 }
 
 // how many clusters of CS CTAs of this kernel the device can hold at once
-template <int CS, bool kTC>
+template <int CS, int kMode>
 static int max_active_clusters_t() {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(CS * 64);
   cfg.blockDim = dim3(kCLThreads);
-  cfg.dynamicSmemBytes = cluster_smem_bytes<CS, kTC>();
+  cfg.dynamicSmemBytes = cluster_smem_bytes<CS, kMode>();
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CS;
@@ -1360,39 +1429,39 @@ static int max_active_clusters_t() {
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   int n = 0;
-  cudaFuncSetAttribute(fwd_bwd_cluster_kernel<CS, kTC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                       (int)cluster_smem_bytes<CS, kTC>());
-  if (cudaOccupancyMaxActiveClusters(&n, fwd_bwd_cluster_kernel<CS, kTC>, &cfg) != cudaSuccess) {
+  cudaFuncSetAttribute(fwd_bwd_cluster_kernel<CS, kMode>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                       (int)cluster_smem_bytes<CS, kMode>());
+  if (cudaOccupancyMaxActiveClusters(&n, fwd_bwd_cluster_kernel<CS, kMode>, &cfg) != cudaSuccess) {
     cudaGetLastError();
     return 0;
   }
   return n;
 }
-template <bool kTC>
+template <int kMode>
 static int max_active_clusters_p(int cs) {
   switch (cs) {
-    case 2: return max_active_clusters_t<2, kTC>();
-    case 3: return max_active_clusters_t<3, kTC>();
-    case 4: return max_active_clusters_t<4, kTC>();
-    case 5: return max_active_clusters_t<5, kTC>();
-    case 6: return max_active_clusters_t<6, kTC>();
-    case 7: return max_active_clusters_t<7, kTC>();
-    case 8: return max_active_clusters_t<8, kTC>();
+    case 2: return max_active_clusters_t<2, kMode>();
+    case 3: return max_active_clusters_t<3, kMode>();
+    case 4: return max_active_clusters_t<4, kMode>();
+    case 5: return max_active_clusters_t<5, kMode>();
+    case 6: return max_active_clusters_t<6, kMode>();
+    case 7: return max_active_clusters_t<7, kMode>();
+    case 8: return max_active_clusters_t<8, kMode>();
     default: return 0;
   }
 }
-int max_active_clusters(int cs, bool tensor_cores) {
-  return tensor_cores ? max_active_clusters_p<true>(cs) : max_active_clusters_p<false>(cs);
+int max_active_clusters(int cs, int mode) {
+  return mode == 1 ? max_active_clusters_p<1>(cs) : (mode == 2 ? max_active_clusters_p<2>(cs) : max_active_clusters_p<0>(cs));
 }
 
-template <bool kTC>
+template <int kMode>
 static int launch_cluster_p(int cs, const float* params, const float* x, const long long* labels, float* saved,
                             float* part1, float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
                             long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
                             const float* packed, cudaStream_t stream) {
 #define DNN_CL_CASE(N)                                                                                              \
   case N:                                                                                                           \
-    return launch_cluster_t<N, kTC>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, max_clusters, \
+    return launch_cluster_t<N, kMode>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, max_clusters, \
                                     trace, ready_ctr, ready_expect, packed, stream);
   switch (cs) {
     DNN_CL_CASE(8) DNN_CL_CASE(7) DNN_CL_CASE(6) DNN_CL_CASE(5) DNN_CL_CASE(4) DNN_CL_CASE(3) DNN_CL_CASE(2)
@@ -1401,16 +1470,17 @@ static int launch_cluster_p(int cs, const float* params, const float* x, const l
 #undef DNN_CL_CASE
 }
 
-// tensor_cores: conv1/conv2 forward and the conv2 data gradient on tcgen05 (TF32 operands, fp32 accumulate);
-// false: everything fp32 FFMA (the parity path, bit-comparable in structure with the one-CTA kernel)
-int launch_fwd_bwd_cluster(int cs, bool tensor_cores, const float* params, const float* x, const long long* labels,
+// mode 0: everything fp32 FFMA (the parity path, bit-comparable in structure with the one-CTA kernel); 1: conv1/conv2
+// forward and the conv2 data gradient on tcgen05 (TF32 operands, fp32 accumulate); 2: only the conv2 data gradient
+int launch_fwd_bwd_cluster(int cs, int mode, const float* params, const float* x, const long long* labels,
                            float* saved, float* part1, float* part2, float* img_loss, int* img_correct, int B,
                            int max_clusters, long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
                            const float* packed, cudaStream_t stream) {
-  return tensor_cores ? launch_cluster_p<true>(cs, params, x, labels, saved, part1, part2, img_loss, img_correct, B,
-                                               max_clusters, trace, ready_ctr, ready_expect, packed, stream)
-                      : launch_cluster_p<false>(cs, params, x, labels, saved, part1, part2, img_loss, img_correct, B,
-                                                max_clusters, trace, ready_ctr, ready_expect, nullptr, stream);
+#define DNN_CL_MODE(M)                                                                                             \
+  launch_cluster_p<M>(cs, params, x, labels, saved, part1, part2, img_loss, img_correct, B, max_clusters, trace, \
+                      ready_ctr, ready_expect, M != 0 ? packed : nullptr, stream)
+  return mode == 1 ? DNN_CL_MODE(1) : (mode == 2 ? DNN_CL_MODE(2) : DNN_CL_MODE(0));
+#undef DNN_CL_MODE
 }
 
 }  // namespace dnnb200

@@ -35,11 +35,11 @@ void set_last_error(const char* fmt, ...) {
 int launch_fwd_bwd(bool train, const float* params, const float* x, const long long* labels, float* saved,
                    float* part1, float* part2, float* img_loss, int* img_correct, float* logits_out, int B,
                    int max_ctas, cudaStream_t stream);
-int launch_fwd_bwd_cluster(int cs, bool tensor_cores, const float* params, const float* x, const long long* labels,
+int launch_fwd_bwd_cluster(int cs, int mode, const float* params, const float* x, const long long* labels,
                            float* saved, float* part1, float* part2, float* img_loss, int* img_correct, int B,
                            int max_clusters, long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
                            const float* packed, cudaStream_t stream);
-int max_active_clusters(int cs, bool tensor_cores);
+int max_active_clusters(int cs, int mode);
 int launch_pingpong(const RankCtx* d_ctx, int peer, int iters, unsigned int base_seq, long long* d_out_ns,
                     cudaStream_t stream);
 int launch_ll128_probe(const RankCtx* d_ctx, int peer, int iters, int n_ctas, unsigned int base_seq,
@@ -117,8 +117,9 @@ struct dnnb200_engine {
   int debug_flags = 0;             // OR-ed into the update kernel's flags (bit 1: no early launch of the successor)
   int forced_cluster = 0;          // 0 = pick per batch size
   int max_clusters[9] = {};        // resident clusters of the fwd/bwd kernel per cluster size (index = CS), for `tf32`
-  int max_clusters_p[2][9] = {};   // the same for both precisions ([0] fp32 FFMA, [1] TF32 tensor cores)
-  int tf32 = 0;                    // conv stages of the clustered kernel: 0 fp32 FFMA (default), 1 tcgen05 (TF32 operands)
+  int max_clusters_p[3][9] = {};   // the same per precision mode
+  int tf32 = 0;                    // conv stages of the clustered kernel: 0 fp32 FFMA, 1 all three GEMM-shaped conv stages on
+                                   // tcgen05 (TF32 operands), 2 fp32 FFMA except the conv2 data gradient (tcgen05)
   int* img_correct = nullptr;
   float* eval_loss = nullptr;
   int* eval_correct = nullptr;
@@ -273,7 +274,7 @@ static int fwd_bwd_any(dnnb200_engine* e, const float* x, const long long* y, in
   if (cs == 1)
     return launch_fwd_bwd(true, e->params, x, y, e->saved, e->part1, e->part2, e->img_loss, e->img_correct, nullptr,
                           B, e->num_sms, s);
-  return launch_fwd_bwd_cluster(cs, e->tf32 != 0, e->params, x, y, e->saved, e->part1, e->part2, e->img_loss, e->img_correct, B,
+  return launch_fwd_bwd_cluster(cs, e->tf32, e->params, x, y, e->saved, e->part1, e->part2, e->img_loss, e->img_correct, B,
                                 e->max_clusters[cs] > 0 ? e->max_clusters[cs] : 1, e->trace,
                                 chained && !(e->debug_flags & 8) ? &e->ctl->updates_done : nullptr, e->updates_launched,
                                 // ready-made operands are only trusted when the previous operation on the stream was this
@@ -463,8 +464,7 @@ static int engine_fill(dnnb200_engine* e, float* params, float* momentum, float*
   DNN_CUDA_CHECK(cudaMalloc(&e->part2, (size_t)max_batch * (kConvPrefix - kOffW2) * sizeof(float)));
   DNN_CUDA_CHECK(cudaMemset(e->part2, 0, (size_t)max_batch * (kConvPrefix - kOffW2) * sizeof(float)));
   for (int cs = 2; cs <= 8; ++cs) {
-    e->max_clusters_p[0][cs] = max_active_clusters(cs, false);
-    e->max_clusters_p[1][cs] = max_active_clusters(cs, true);
+    for (int m = 0; m < 3; ++m) e->max_clusters_p[m][cs] = max_active_clusters(cs, m);
     e->max_clusters[cs] = e->max_clusters_p[e->tf32][cs];
   }
   DNN_CUDA_CHECK(cudaMemset(e->saved, 0, (size_t)max_batch * kSavStride * sizeof(float)));
@@ -616,7 +616,8 @@ int dnnb200_engine_set_cluster_size(dnnb200_engine* e, int cs) {
 
 int dnnb200_engine_set_precision(dnnb200_engine* e, int tf32) {
   DNN_ARG_CHECK(e, "null engine");
-  DNN_ARG_CHECK(tf32 == 0 || tf32 == 1, "precision must be 0 (fp32 FFMA) or 1 (TF32 tensor cores)");
+  DNN_ARG_CHECK(tf32 >= 0 && tf32 <= 2,
+                "precision must be 0 (fp32 FFMA), 1 (TF32 tensor cores) or 2 (fp32 with the conv2 data gradient on tensor cores)");
   e->tf32 = tf32;
   for (int cs = 2; cs <= 8; ++cs) e->max_clusters[cs] = e->max_clusters_p[tf32][cs];
   if (e->forced_cluster > 1 && e->max_clusters[e->forced_cluster] <= 0) e->forced_cluster = 0;

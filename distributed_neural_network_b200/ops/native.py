@@ -61,10 +61,13 @@ class Ctl(C.Structure):
 _default_precision = os.environ.get("DNNB200_PRECISION", "fp32")
 
 
+PRECISIONS = {"fp32": 0, "tf32": 1, "tf32-dgrad": 2}
+
+
 def set_default_precision(p: str) -> None:
     global _default_precision
-    if p not in ("tf32", "fp32"):
-        raise ValueError("precision must be 'tf32' or 'fp32'")
+    if p not in PRECISIONS:
+        raise ValueError(f"precision must be one of {sorted(PRECISIONS)}")
     _default_precision = p
 
 
@@ -336,11 +339,12 @@ class Engine:
         _check(require().dnnb200_engine_set_divisor(self._h, C.c_uint(divisor), _stream()))
 
     def set_precision(self, precision: str) -> None:
-        """"tf32": conv1/conv2 forward and the conv2 data gradient of the clustered step kernel run as implicit GEMMs
-        on the tensor cores (tcgen05, TF32 operands, fp32 accumulation); "fp32": FFMA throughout."""
-        if precision not in ("tf32", "fp32"):
-            raise ValueError("precision must be 'tf32' or 'fp32'")
-        _check(require().dnnb200_engine_set_precision(self._h, 1 if precision == "tf32" else 0))
+        """"fp32": FFMA throughout. "tf32": conv1/conv2 forward and the conv2 data gradient of the clustered step kernel
+        run as implicit GEMMs on the tensor cores (tcgen05, TF32 operands, fp32 accumulation). "tf32-dgrad": only the
+        conv2 data gradient does -- forward, loss and every gradient but conv1's stay bit-for-bit the fp32 ones."""
+        if precision not in PRECISIONS:
+            raise ValueError(f"precision must be one of {sorted(PRECISIONS)}")
+        _check(require().dnnb200_engine_set_precision(self._h, PRECISIONS[precision]))
         self.precision = precision
 
     def zero_momentum(self) -> None:

@@ -50,7 +50,7 @@ def add_new_flags(p: argparse.ArgumentParser, sync_default: str) -> None:
     g.add_argument("--allreduce-variant", default="auto", choices=["auto", "one-shot", "one-shot-128", "two-shot", "nvls"],
                    help="gradient exchange: one-shot push, two-shot (owner-reduce + broadcast), chosen by world size, or "
                         "(parameter averaging only) nvls = in-switch reduction over NVLink multicast")
-    g.add_argument("--precision", default=None, choices=["tf32", "fp32"],
+    g.add_argument("--precision", default=None, choices=["fp32", "tf32", "tf32-dgrad"],
                    help="convolution stages of the fused GPU step: fp32 = FFMA throughout (default: parity with PyTorch "
                         "fp32, and measured faster at this model's GEMM sizes), tf32 = tcgen05 tensor cores")
     g.add_argument("--neptune", action="store_true", help="log to Neptune (needs NEPTUNE_API_TOKEN in the environment)")

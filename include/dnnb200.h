@@ -157,6 +157,8 @@ int dnnb200_engine_cluster_info(const dnnb200_engine* e, int B, int* chosen, int
  * fp32 to 2e-5 and that measures faster at batch 16 (profiles/step_tc_ab_v1.md).
  * Everything else (FC layers, weight gradients, softmax, SGD, master weights) is fp32 either way. Batches that
  * run the one-CTA-per-image kernel (cluster size 1) are always fp32. */
+/* 2 = fp32 FFMA everywhere except the conv2 data gradient, which runs on the tensor cores (TF32 operands): the forward
+ * pass, the loss and every gradient except conv1.weight / conv1.bias are bit-for-bit those of mode 0. */
 int dnnb200_engine_set_precision(dnnb200_engine* e, int tf32);
 /* development aid: d_trace[cta*16 + k] receives the SM clock at stage boundary k of the clustered
  * forward/backward kernel (NULL switches it off) */

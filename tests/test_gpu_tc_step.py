@@ -187,3 +187,53 @@ def test_tc_multi_image_loop_and_chained_steps():
         cos, err = _cos_err(gtc, g32)
         assert cos > 0.998 and err < 6e-2, (cs, cos, err)
         e32.close(); etc.close()
+
+
+@pytest.mark.parametrize("cs", [2, 4, 5, 6, 8])
+def test_dgrad_only_mode_changes_nothing_but_the_conv1_gradient(cs):
+    """precision "tf32-dgrad": the conv2 data gradient is the only thing on the tensor cores. Forward, loss, FC and
+    conv2 gradients must be BIT-identical to the fp32 kernel (nothing that feeds them is rounded); conv1's weight and
+    bias gradient, which sit behind the data gradient, agree to TF32 rounding (no pooling decision can flip)."""
+    torch.manual_seed(40 + cs)
+    B = 16
+    model = Network().cuda()
+    x = torch.randn(B, 3, 32, 32, device="cuda")
+    y = torch.randint(0, 10, (B,), device="cuda")
+    e32, emx = _engine(model, B, "fp32", cs=cs), _engine(model, B, "tf32-dgrad", cs=cs)
+    g32 = torch.zeros(L.FLAT_NUMEL, device="cuda")
+    gmx = torch.full((L.FLAT_NUMEL,), float("nan"), device="cuda")
+    l32 = e32.grad_only(x, y, g32)
+    lmx = emx.grad_only(x, y, gmx)
+    lmx2 = emx.grad_only(x, y, gmx)          # and again: operand buffers and tensor memory are reusable
+    assert l32 == lmx == lmx2
+    v3, vm = L.views(g32), L.views(gmx)
+    for name in L.PARAM_SHAPES:
+        if name.startswith("conv1"):
+            cos, err = _cos_err(vm[name], v3[name])
+            assert err < 3e-3 and cos > 0.99999, (name, cos, err)
+        else:
+            assert torch.equal(vm[name], v3[name]), name
+    assert gmx[~L.real_mask("cuda")].abs().sum().item() == 0.0
+    e32.close(); emx.close()
+
+
+def test_dgrad_only_mode_trains_like_fp32_with_chained_steps():
+    """Chained steps fetch the data gradient's B operand ready-made from the update kernel; the first step of a call
+    packs it in the kernel. Both must see the CURRENT weights: 60 steps in one call vs the fp32 engine."""
+    torch.manual_seed(5)
+    base = Network()
+    B, steps = 16, 60
+    xs = torch.randn(steps, B, 3, 32, 32, device="cuda")
+    ys = torch.randint(0, 10, (steps, B), device="cuda")
+    out = {}
+    for prec in ("fp32", "tf32-dgrad"):
+        m = copy.deepcopy(base).cuda()
+        eng = _engine(m, B, prec, lr=0.01, mu=0.9)
+        eng.train_device(xs[:30], ys[:30])
+        eng.train_device(xs[30:], ys[30:])
+        torch.cuda.synchronize()
+        out[prec] = (m.flat_params.detach().clone(), eng.read_ctl().loss_sum / steps)
+        eng.close()
+    rel = ((out["tf32-dgrad"][0] - out["fp32"][0]).norm() / out["fp32"][0].norm()).item()
+    assert rel < 1e-2, rel   # (measured 2e-3: sixty chaotic steps amplify the 1e-3 rounding of one gradient)
+    assert abs(out["tf32-dgrad"][1] - out["fp32"][1]) < 5e-3
