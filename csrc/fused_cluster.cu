@@ -559,10 +559,10 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     static_assert(offsetof(SM, sb2) == offsetof(SM, sb1) + sizeof(s.sb1) &&
                   offsetof(SM, sbd) == offsetof(SM, sb2) + sizeof(s.sb2), "B operands are zeroed as one block");
   } else if constexpr (kTCD) {
-    if (packed == nullptr) {   // the data gradient's B operand is packed in this kernel: zero its padding beforehand
-      for (int i = tid; i < (int)sizeof(s.sbd) / 16; i += kCLThreads)
-        reinterpret_cast<float4*>(s.sbd)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
+    // rows 8..15 of the data gradient's B operand never hold a weight (always zeroed here); rows 0..7 arrive ready-made
+    // or, when this kernel packs them itself, need their padding (channels 6, 7) zeroed too
+    for (int i = tid + (packed != nullptr ? (int)sizeof(s.sbd) / 32 : 0); i < (int)sizeof(s.sbd) / 16; i += kCLThreads)
+      reinterpret_cast<float4*>(s.sbd)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   __syncthreads();
   if constexpr (kTCD) {
@@ -652,12 +652,6 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
     } else {
       cl_mbar_expect_tx(&s.cbar, kConvPrefix * 4);
       cl_bulk_g2s(s.cw, params, kConvPrefix * 4, &s.cbar);
-      if constexpr (kTCD) {
-        if (packed != nullptr) {   // the data gradient's B operand, ready-made; needed two thirds into the kernel
-          cl_mbar_expect_tx(&s.pbar, (uint32_t)sizeof(s.sbd));
-          cl_bulk_g2s(s.sbd, packed + kPackBd, (uint32_t)sizeof(s.sbd), &s.pbar);
-        }
-      }
     }
     if (kPre) {
       const int a0 = r * kF1 / CS, a1 = (r + 1) * kF1 / CS, c0 = r * kF2 / CS, c1 = (r + 1) * kF2 / CS;
@@ -669,6 +663,14 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       cl_bulk_g2s(f.bf1, params + kOffF1B, kF1 * 4, &f.wbar);
       cl_bulk_g2s(f.bf2, params + kOffF2B, kF2 * 4, &f.wbar);
       cl_bulk_g2s(f.bf3, params + kOffF3B, 48, &f.wbar);  // 10 biases + 2 floats of the (zero) alignment gap
+    }
+    if constexpr (kTCD && !kTC) {
+      if (packed != nullptr) {
+        // the data gradient's B operand, ready-made: needed two thirds into the kernel, so it is fetched behind
+        // everything the forward pass waits for; only rows 0..7 hold weights (six input channels), rows 8..15 were zeroed
+        cl_mbar_expect_tx(&s.pbar, (uint32_t)sizeof(s.sbd) / 2);
+        cl_bulk_g2s(s.sbd, packed + kPackBd, (uint32_t)sizeof(s.sbd) / 2, &s.pbar);
+      }
     }
   }
 
@@ -1286,6 +1288,11 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       }
     }
     __syncthreads();
+    if constexpr (kTCD && !kTC) {
+      // tensor memory is not touched again after the last image's data gradient: give it back here instead of behind
+      // the kernel's last stage (the tcgen05.ld of every warp precede the block barrier above)
+      if (img + n_clusters >= B && warp == 1) tc::tmem_free<kTmemCols>(tmem);
+    }
 
     CL_TRACE(12);
     // ================= conv1 weight gradient over my pooled pixels (partial) =================
@@ -1365,7 +1372,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       load_image(img + n_clusters);
     }
   }
-  if constexpr (kTCD) {
+  if constexpr (kTC) {
     tc::tc_fence_before();
     __syncthreads();
     if (warp == 1) tc::tmem_free<kTmemCols>(tmem);
