@@ -356,7 +356,7 @@ def run_ours(args) -> int:
                     "ms_per_step": round(e2e_max * 1e3 / K, 6),
                     "how": "Engine.train_host: every step's images+labels are copied from pinned host memory inside the "
                            "region (cudaMemcpyAsync on a copy stream into a 32-slot device ring, the steps of a group of "
-                           "<= 8 sharing one copy), 2 kernels per step, and the update kernel stores each step's mean "
+                           "<= 16 sharing one copy), 2 kernels per step, and the update kernel stores each step's mean "
                            "loss into the caller's pinned host buffer (device->host over PCIe); wall clock with "
                            "synchronize on both sides, max over ranks",
                     "mean_loss_read_back": round(max(s["loss"] for s in stats), 4)},

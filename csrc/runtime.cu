@@ -137,7 +137,8 @@ struct dnnb200_engine {
   int num_sms = 148;
   // host-fed ring
   static constexpr int kRing = 32;   // device input slots
-  static constexpr int kGroup = 8;   // steps per event group (stream events break the kernels' programmatic overlap)
+  static constexpr int kGroup = 16;  // steps per event group (stream events break the kernels' programmatic overlap and
+                                     // the chaining of steps, so groups are long; two regions of the ring alternate)
   cudaStream_t copy_stream = nullptr, d2h_stream = nullptr;
   cudaEvent_t slot_ready[kRing] = {}, slot_free[kRing] = {}, step_done[kRing] = {};
   float* ring_x = nullptr;        // [kRing / kGroup] group regions of kGroup * max_batch images; a call packs its steps at its own batch size
@@ -750,13 +751,13 @@ int dnnb200_engine_train_host(dnnb200_engine* e, const float* h_x, const int64_t
   // images and one for the labels (every step's inputs are still copied, inside the call, just not one DMA
   // descriptor per step), and the cross-stream events (inputs ready / slots free) are recorded once per group, so
   // that inside a group nothing sits between the kernels in the stream and their programmatic dependent launches
-  // overlap. A call ramps up: its groups hold 1, 2, 4, then 8 steps, so the GPU starts on step 0 after ONE step's
-  // worth of PCIe time and every later copy (16 us per step of batch 16) is shorter than the kernels of the group
-  // before it (17-24 us per step) -- most of the fixed cost of a short call.
+  // overlap. The first group of a call holds 4 steps, the others 16: the GPU starts on step 0 after four steps' worth
+  // of PCIe time (4 us per step of batch 16), every later copy hides under the kernels of the group before it, and a
+  // 20-step call has one group boundary (each boundary costs the first step of the next group its chaining).
   constexpr int G = dnnb200_engine::kGroup;
   const bool may_chain = !stream_capturing(s);   // same rule as train_device: a captured counter value would be stale
   for (int t0 = 0; t0 < nsteps;) {
-    const int cap = t0 + 1 < G ? t0 + 1 : G;   // groups of 1, 2, 4, 8, 8, ...: each group's copy hides under the previous group's kernels
+    const int cap = t0 == 0 ? 4 : G;   // a short first group (the GPU starts after 4 steps' worth of PCIe time), then full ones
     const int n = nsteps - t0 < cap ? nsteps - t0 : cap;
     const int gslot = (int)((e->ring_uses / G) % (R / G));        // group index in the ring
     if (e->ring_uses >= (unsigned long long)R) DNN_CUDA_CHECK(cudaStreamWaitEvent(e->copy_stream, e->slot_free[gslot], 0));

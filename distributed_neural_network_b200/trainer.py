@@ -208,7 +208,7 @@ class Trainer:
         """Exchange variants this run may use. The one-shot forms tolerate ranks leaving mid-epoch (leave markers);
         two-shot has static slice ownership and the NVSwitch adds EVERY member of the multicast group, so both need
         a membership that cannot change (no drop-mode failure drill, every rank a stepping trainer for NVLS)."""
-        names = ["one-shot", "one-shot-128"]
+        names = ["one-shot"] + (["one-shot-128"] if self.world <= 8 else [])   # (the 128-byte-line form parks 7 peers' lines)
         if not self._can_drop():
             names.append("two-shot")
             if self.nvls_ok and len(self.membership.active) == self.world:
@@ -226,9 +226,9 @@ class Trainer:
             return native.variant_id(v if v in usable else "one-shot")
         if self.exchange_choice in usable:
             return native.variant_id(self.exchange_choice)
-        # not measured (calibration switched off): one hop while the 128-byte lines keep the traffic below the
-        # link time of the other ranks, measured winner of profiles/exchange_table_n*.json
-        return native.variant_id("one-shot-128")
+        # not measured (calibration switched off): the variant that tolerates ranks leaving and wins up to 4 GPUs
+        # (profiles/exchange_table_n*.json); two-shot wins at 8 but needs a static membership
+        return native.variant_id("one-shot")
 
     def _exchange_two_shot(self) -> bool:
         return self._exchange_variant() == 1
@@ -240,9 +240,12 @@ class Trainer:
             if not self.nvls_ok:
                 raise RuntimeError("--allreduce-variant nvls: NVLink multicast is not available to this job")
             return 2
-        if v == "auto":
-            return native.variant_id(self.exchange_choice) if self.exchange_choice in ("one-shot", "one-shot-128",
-                                                                                       "two-shot") else 3
+        if v == "auto":   # the measured winner of the fused exchange where there is one; else by world size (round-1 table)
+            if self.exchange_choice in ("one-shot", "one-shot-128", "two-shot"):
+                return native.variant_id(self.exchange_choice)
+            return 1 if self.world >= 6 else 0
+        if v == "one-shot-128" and self.world > 8:
+            return 0
         return native.variant_id(v)
 
     @torch.no_grad()

@@ -180,7 +180,7 @@ int dnnb200_engine_step(dnnb200_engine* e, const float* x, const int64_t* y, int
  * no per-step Python (the whole dataset fits in HBM many times over) */
 int dnnb200_engine_train_device(dnnb200_engine* e, const float* x, const int64_t* y, int B, int nsteps, void* stream);
 /* nsteps steps fed from PINNED host memory: every step's inputs are copied host->device inside the call (32-slot
- * device ring on a copy stream; the steps of a group -- 1, 2, 4, then 8 per group within a call -- share one copy for
+ * device ring on a copy stream; the steps of a group -- 4 in the first group of a call, then 16 -- share one copy for
  * their images and one for their labels and one pair of events) and run through the two kernels; the update kernel writes
  * the step's mean loss straight into h_losses[t] (pinned host memory, 4 bytes device->host per
  * step). Returns after everything is enqueued; the caller synchronises `stream` before reading
