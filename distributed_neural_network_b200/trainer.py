@@ -75,6 +75,10 @@ class TrainConfig:
     precision: Optional[str] = None        # conv stages of the fused step: fp32 (FFMA; parity with PyTorch fp32 and, at
                                            # these GEMM sizes, the faster one) | tf32 (tcgen05 tensor cores);
                                            # None = native.default_precision()
+    step_path: str = "fused"               # fused: the two-kernel step engine (default) | autograd: Network.forward +
+                                           # loss.backward() through the layer kernels, gradients averaged bucket by
+                                           # bucket on a side stream while backward runs (large batches per GPU)
+    overlap_exchange: bool = True          # autograd path: False = all-reduce after backward (A/B switch)
     exchange_timing: bool = True           # per-epoch "allreduce_us" in the JSONL (the reference books its
                                            # mpi_communication_time_children, data_parallelism_train.py:209-213)
     peer_timeout_s: float = 30.0
@@ -85,6 +89,8 @@ class TrainConfig:
     def __post_init__(self):
         if self.sync_mode not in ("step-allreduce", "epoch-average", "replication", "none"):
             raise ValueError(f"unknown sync mode {self.sync_mode!r}")
+        if self.step_path not in ("fused", "autograd"):
+            raise ValueError(f"unknown step path {self.step_path!r}")
         self.lr, self.momentum = float(self.lr), float(self.momentum)   # the reference forgets the casts (Q5)
         self.batch_size, self.epochs = int(self.batch_size), int(self.epochs)
 
@@ -149,6 +155,7 @@ class Trainer:
         self.nvls_ok = False
         self._nvls_probed = False
         self._utrace: Optional[torch.Tensor] = None
+        self._averager = None                           # autograd path: per-bucket exchange overlapped with backward
         self.last_exchange_us: Optional[float] = None  # median exposed exchange per step over the epoch's last steps
         self.exchange_choice: Optional[str] = None     # measured winner (calibrate_exchange)
         self.exchange_table: Dict = {}
@@ -364,9 +371,50 @@ class Trainer:
         if cfg.sync_mode in ("epoch-average", "replication"):
             self.momentum.zero_()      # the reference builds a new optimizer every epoch (:187)
             self.first_step = True
+        if cfg.step_path == "autograd":
+            return self._train_epoch_autograd(shard, B, local_sgd, drop_at)
         if self.engine is not None:
             return self._train_epoch_cuda(shard, B, local_sgd, drop_at)
         return self._train_epoch_cpu(shard, B, local_sgd, drop_at)
+
+    def _train_epoch_autograd(self, shard, B, local_sgd, drop_at) -> Tuple[float, int]:
+        """The layer-at-a-time step: forward and backward through the autograd ops (layer kernels on CUDA), the
+        gradient averaged bucket by bucket on a side stream while backward is still running
+        (parallel/bucketed.py), one SGD-momentum kernel over the flat vector. Same arithmetic as the reference's
+        loop body (data_parallelism_train.py:195-203) with the exchange moved from the epoch boundary into the step."""
+        if drop_at is not None:
+            raise ValueError("the drop-mode failure drill runs on the fused step path (leave markers live in its exchange)")
+        from .parallel.bucketed import BucketedGradientAverager
+
+        model, cfg = self.model, self.cfg
+        model.train()
+        avg = None
+        if not local_sgd and self.world > 1:
+            if self.engine is not None:
+                self._align_sequence()
+                self._apply_membership()
+            if self._averager is None:
+                self._averager = BucketedGradientAverager(
+                    model, len(self.membership.active), engine=self.engine, allreduce_fn=self.comm.allreduce_sum_,
+                    variant=self._standalone_variant() if self.engine is not None else "one-shot",
+                    overlap=cfg.overlap_exchange)
+            avg = self._averager
+        total = torch.zeros((), device=self.device)
+        nb = 0
+        for x, y in D.batches(shard, B, shuffle=True, generator=self.gen):
+            model.zero_grad()
+            loss = Fn.cross_entropy(model(x), y)
+            if avg is not None:
+                avg.arm()
+            loss.backward()
+            if avg is not None:
+                avg.finish()
+            Fn.sgd_momentum_(model.flat_params.data, model.flat_grads, self.momentum, cfg.lr, cfg.momentum, self.first_step)
+            self.first_step = False
+            total += loss.detach()
+            nb += 1
+        self.steps_this_epoch = nb
+        return float(total), nb
 
     def _train_epoch_cuda(self, shard, B, local_sgd, drop_at) -> Tuple[float, int]:
         eng = self.engine

@@ -50,6 +50,9 @@ def add_new_flags(p: argparse.ArgumentParser, sync_default: str) -> None:
     g.add_argument("--allreduce-variant", default="auto", choices=["auto", "one-shot", "one-shot-128", "two-shot", "nvls"],
                    help="gradient exchange: one-shot push, two-shot (owner-reduce + broadcast), chosen by world size, or "
                         "(parameter averaging only) nvls = in-switch reduction over NVLink multicast")
+    g.add_argument("--step-path", default="fused", choices=["fused", "autograd"],
+                   help="fused: the two-kernel step engine; autograd: layer kernels through torch autograd with the "
+                        "gradient exchanged per bucket on a side stream while backward runs (large batches)")
     g.add_argument("--precision", default=None, choices=["fp32", "tf32", "tf32-dgrad"],
                    help="convolution stages of the fused GPU step: fp32 = FFMA throughout (default: parity with PyTorch "
                         "fp32, and measured faster at this model's GEMM sizes), tf32 = tcgen05 tensor cores")
@@ -67,4 +70,4 @@ def config_from_args(a: argparse.Namespace) -> TrainConfig:
         device=a.device, data_root=a.data_root, synthetic=True if a.synthetic else None,
         train_size=a.train_size, test_size=a.test_size, seed=a.seed, log_dir=a.log_dir, jsonl=a.jsonl,
         save=a.save, resume=a.resume, input_pipeline=a.input_pipeline, allreduce_variant=a.allreduce_variant,
-        neptune=a.neptune, quiet=a.quiet, precision=a.precision)
+        neptune=a.neptune, quiet=a.quiet, precision=a.precision, step_path=a.step_path)

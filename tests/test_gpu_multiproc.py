@@ -177,3 +177,20 @@ def test_second_device_in_one_process():
             eng.close()
     assert torch.allclose(got[0][0], got[1][0], rtol=0, atol=0) and got[0][1:3] == got[1][1:3]
     assert torch.equal(got[0][3], got[1][3])
+
+
+@needs2
+def test_ipc_autograd_step_path_with_bucketed_overlap(tmp_path):
+    """--step-path autograd on GPUs: layer kernels through autograd, the gradient averaged bucket by bucket over peer
+    memory on a side stream while backward runs. Replicas must stay bit-identical, with and without the overlap, and
+    the two runs must agree (the exchange is the same arithmetic in the same order either way)."""
+    n = min(torch.cuda.device_count(), 8)
+    kw = dict(train_size=256 * n, test_size=32, epochs=2, batch_size=64, lr=0.05, seed=13, step_path="autograd")
+    a = _launch(n, tmp_path / "overlap", "step-allreduce", **kw)
+    b = _launch(n, tmp_path / "after", "step-allreduce", overlap_exchange=False, **kw)
+    for r in range(1, n):
+        assert torch.equal(a[0]["flat"], a[r]["flat"]) and torch.equal(b[0]["flat"], b[r]["flat"])
+    # (large-batch layer kernels add their batch chunks with atomics, so two RUNS agree to round-off, not to the bit)
+    rel = ((a[0]["flat"] - b[0]["flat"]).norm() / b[0]["flat"].norm()).item()
+    assert rel < 1e-4, rel
+    assert a[0]["history"][-1]["train_loss"] < a[0]["history"][0]["train_loss"] + 0.05

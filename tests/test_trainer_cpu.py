@@ -232,3 +232,41 @@ def test_mpi4py_control_plane_world2_equals_gloo(tmp_path):
     assert (probe.parent / "provider.0").read_text() == "mpi4py" and (probe.parent / "provider.1").read_text() == "mpi4py"
     assert torch.equal(mpi[0]["flat"], mpi[1]["flat"])
     assert torch.equal(mpi[0]["flat"], gloo[0]["flat"]), "the control plane must not change the numbers"
+
+
+def test_buckets_cover_the_flat_vector_and_leave_in_backward_order():
+    """The three gradient buckets tile the flat vector, and autograd finishes them in the order fc2+fc3, fc1, conv --
+    so the first two exchanges can run while the convolution backward is still computing."""
+    from distributed_neural_network_b200.ops import flat as L
+    from distributed_neural_network_b200.parallel.bucketed import BUCKETS, BucketedGradientAverager
+
+    spans = sorted((lo, hi) for _, lo, hi, _ in BUCKETS)
+    assert spans[0][0] == 0 and spans[-1][1] == L.FLAT_NUMEL
+    assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+    assert sorted(n for _, _, _, names in BUCKETS for n in names) == sorted(L.PARAM_SHAPES)
+    torch.manual_seed(0)
+    model = Network()
+    seen = []
+    avg = BucketedGradientAverager(model, world=2, allreduce_fn=lambda t: seen.append(t.numel()) or t.mul_(2.0))
+    x, y = torch.randn(8, 3, 32, 32), torch.randint(0, 10, (8,))
+    ref = copy.deepcopy(model)
+    ref.zero_grad()
+    F.cross_entropy(ref(x), y).backward()
+    model.zero_grad()
+    avg.arm()
+    F.cross_entropy(model(x), y).backward()
+    assert avg.launched == ["fc2+fc3", "fc1", "conv"]          # all three left DURING backward, in this order
+    avg.finish()
+    assert seen == [hi - lo for _, lo, hi, _ in BUCKETS]
+    assert torch.allclose(model.flat_grads, ref.flat_grads)    # "sum" of two identical ranks / 2 = the gradient
+    avg.close()
+
+
+def test_autograd_step_path_world2_equals_fused_semantics(tmp_path):
+    """--step-path autograd (layer ops through autograd, per-bucket exchange) trains the same model as the
+    step-allreduce reference semantics: world 2 x batch 8 == the CPU run of the default path."""
+    kw = dict(train_size=128, test_size=32, epochs=1, batch_size=8, lr=0.05, seed=11)
+    a = _launch(2, tmp_path / "fused", "step-allreduce", **kw)
+    b = _launch(2, tmp_path / "autograd", "step-allreduce", step_path="autograd", **kw)
+    assert torch.equal(b[0]["flat"], b[1]["flat"])
+    assert torch.allclose(a[0]["flat"], b[0]["flat"], atol=2e-6)
