@@ -109,20 +109,27 @@ class ClockSampler:
             self._t.join()
 
     def nvlink_kib(self):
-        """(transmitted, received) KiB over all NVLinks of this GPU since the driver loaded (payload counters), or None."""
+        """(transmitted, received) KiB over all NVLinks of this GPU since the driver loaded (payload counters), or None
+        where NVML does not expose them (self.nvlink_note says what it answered)."""
         if not self.ok:
             return None
+        nv = self._nv
+        ids = (nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX)
         try:
-            nv = self._nv
-            vals = nv.nvmlDeviceGetFieldValues(self._h, [(nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, 0xffffffff),
-                                                         (nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, 0xffffffff)])
-            out = []
-            for v in vals:
-                if v.nvmlReturn != 0:
+            vals = nv.nvmlDeviceGetFieldValues(self._h, [(ids[0], 0xffffffff), (ids[1], 0xffffffff)])   # all links
+            if all(v.nvmlReturn == 0 for v in vals):
+                return tuple(int(v.value.ullVal) for v in vals)
+            tot = [0, 0]
+            for link in range(18):                                                                       # link by link
+                vals = nv.nvmlDeviceGetFieldValues(self._h, [(ids[0], link), (ids[1], link)])
+                if any(v.nvmlReturn != 0 for v in vals):
+                    self.nvlink_note = f"NVML field NVLINK_THROUGHPUT_DATA: return code {vals[0].nvmlReturn} (link {link})"
                     return None
-                out.append(int(v.value.ullVal))
-            return tuple(out)
-        except Exception:
+                tot[0] += int(vals[0].value.ullVal)
+                tot[1] += int(vals[1].value.ullVal)
+            return tuple(tot)
+        except Exception as e:
+            self.nvlink_note = f"NVML NVLink counters: {e}"
             return None
 
     def window(self, t_lo: float, t_hi: float, t_timed: float = None):
@@ -286,7 +293,8 @@ def run_ours(args) -> int:
                "mean_us": float(wait.mean()), "steps": n_tr,
                # what the NVLink counters of this GPU saw per step during the traced pass (payload bytes, all links)
                "nvlink_tx_bytes_per_step": (nvl1[0] - nvl0[0]) * 1024 / (A + n_tr) if nvl0 and nvl1 else None,
-               "nvlink_rx_bytes_per_step": (nvl1[1] - nvl0[1]) * 1024 / (A + n_tr) if nvl0 and nvl1 else None}
+               "nvlink_rx_bytes_per_step": (nvl1[1] - nvl0[1]) * 1024 / (A + n_tr) if nvl0 and nvl1 else None,
+               "nvlink_note": getattr(clk, "nvlink_note", None)}
         comm.barrier()
 
     stats = comm.allgather({"ms": ms, "e2e_s": e2e_s, "launches": launches, "clk": clk.summary(),
@@ -315,7 +323,8 @@ def run_ours(args) -> int:
                                  "per_rank_median_us": [round(x["median_us"], 3) for x in xs],
                                  "nvlink_counters_bytes_per_step_per_gpu": {
                                      "tx": xs[0]["nvlink_tx_bytes_per_step"], "rx": xs[0]["nvlink_rx_bytes_per_step"],
-                                     "note": "NVML NVLINK_THROUGHPUT_DATA_TX/RX of rank 0's GPU over the traced pass "
+                                     "note": xs[0].get("nvlink_note") or
+                                             "NVML NVLINK_THROUGHPUT_DATA_TX/RX of rank 0's GPU over the traced pass "
                                              "(KiB granularity), to set against bytes_per_direction_per_gpu"}}}
         out = {
             "metric": METRIC, "value": round(value, 1), "unit": "images/s", "n_gpus": world, "steps": K,
