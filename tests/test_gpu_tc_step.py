@@ -237,3 +237,29 @@ def test_dgrad_only_mode_trains_like_fp32_with_chained_steps():
     rel = ((out["tf32-dgrad"][0] - out["fp32"][0]).norm() / out["fp32"][0].norm()).item()
     assert rel < 1e-2, rel   # (measured 2e-3: sixty chaotic steps amplify the 1e-3 rounding of one gradient)
     assert abs(out["tf32-dgrad"][1] - out["fp32"][1]) < 5e-3
+
+
+@pytest.mark.parametrize("prec", ["tf32", "tf32-dgrad"])
+def test_ready_made_operands_equal_the_ones_packed_in_the_kernel(prec):
+    """A chained step fetches its tensor-core B operands from the image the update kernel keeps in global memory; an
+    unchained step (every `step()` call) packs them from the weights inside the kernel. Same numbers, same arithmetic:
+    thirty steps taken either way must give the same bits. (A stale or misplaced entry in the packed image would
+    show after the first update.)"""
+    torch.manual_seed(21)
+    base = Network()
+    B, steps = 16, 30
+    xs = torch.randn(steps, B, 3, 32, 32, device="cuda")
+    ys = torch.randint(0, 10, (steps, B), device="cuda")
+    out = []
+    for chained in (True, False):
+        m = copy.deepcopy(base).cuda()
+        eng = _engine(m, B, prec, lr=0.05, mu=0.9)
+        if chained:
+            eng.train_device(xs, ys)
+        else:
+            for t in range(steps):
+                eng.step(xs[t], ys[t])
+        torch.cuda.synchronize()
+        out.append(m.flat_params.detach().clone())
+        eng.close()
+    assert torch.equal(out[0], out[1])
