@@ -32,6 +32,8 @@ def payload(rank, step, s):
 
 
 class World:
+    early_leave_lookup = False   # round 2: markers are also read at the START of a step (update kernel, before its wait)
+
     def __init__(self, W, steps, leave_at):
         self.W, self.steps = W, steps
         self.leave_at = leave_at                       # rank -> first step (0-based) it does not take part in
@@ -54,17 +56,27 @@ def rank_program(w: World, r: int):
                     yield
             return
         parity = seq & 1
+        # 0. (round 2) look the leave markers up early -- a racy read: a marker that lands later is found by the waiters
+        #    below, once, the slow way. A rank whose marker covers this step is not pushed to and not waited for.
+        gone = set()
+        if w.early_leave_lookup:
+            for q in range(W):
+                if q != r:
+                    L = w.leave[r][q]
+                    yield
+                    if L != 0 and seq >= L:
+                        gone.add(q)
         # 1. push all lines of this step to every peer (a departed peer keeps its memory mapped: harmless)
         for s in range(S):
             for p in range(W):
-                if p == r:
+                if p == r or p in gone:
                     continue
                 w.recv[p][parity][r][s] = (payload(r, step, s), seq)
                 yield
         # 2. per slice: poll my own receive area until every peer's line carries seq, or the peer has left
         for s in range(S):
-            got, absent = {}, set()
-            pending = [q for q in range(W) if q != r]
+            got, absent = {}, set(gone)
+            pending = [q for q in range(W) if q != r and q not in gone]
             while pending:
                 for q in list(pending):
                     val, sq = w.recv[r][parity][q][s]
@@ -95,9 +107,10 @@ def rank_program(w: World, r: int):
     return
 
 
-def run(W, steps, leave_at, seed):
+def run(W, steps, leave_at, seed, early_leave_lookup=False):
     rng = random.Random(seed)
     w = World(W, steps, leave_at)
+    w.early_leave_lookup = early_leave_lookup
     progs = {r: rank_program(w, r) for r in range(W)}
     budget = 2_000_000
     while progs:
@@ -139,6 +152,18 @@ def test_ranks_leaving_mid_run_survivors_agree(W):
         leavers = rng.sample(range(W), k=rng.randint(1, W - 1))
         leave_at = {r: rng.randint(1, 5) for r in leavers}
         check(run(W, steps=7, leave_at=leave_at, seed=1000 + seed))
+
+
+@pytest.mark.parametrize("W", [3, 4, 8])
+def test_early_leave_lookup_keeps_survivors_in_agreement(W):
+    """Round 2: the update kernel reads the leave markers before its dependency wait, so survivors skip a departed rank
+    from the first instruction instead of polling for it in every step. The early read races with the marker's
+    arrival; whoever misses it falls back to the waiters' check. Everybody must still agree on every step."""
+    rng = random.Random(50 + W)
+    for seed in range(80):
+        leavers = rng.sample(range(W), k=rng.randint(1, W - 1))
+        leave_at = {r: rng.randint(1, 5) for r in leavers}
+        check(run(W, steps=7, leave_at=leave_at, seed=3000 + seed, early_leave_lookup=True))
 
 
 def rank_program_two_shot(w: World, r: int):
