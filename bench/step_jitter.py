@@ -39,9 +39,18 @@ def main():
     extra = int(os.environ.get("DNN_DEBUG_FLAGS", "0"))   # 8: forward/backward waits for grid completion (no counter)
     eng.set_debug_flags(4 | extra)
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    host = os.environ.get("DNN_HOST")                     # the host-fed path (per-step inputs from pinned memory) instead
+    if host:
+        hx, hy = dx.cpu().pin_memory(), dy.cpu().pin_memory()
+        eng.train_host(hx, hy, None)
+        torch.cuda.synchronize()
+        tr.comm.barrier()
     a.record()
     for _ in range(32):                 # 2048 steps; the ring keeps the last 1024
-        eng.train_device(dx, dy)
+        if host:
+            eng.train_host(hx, hy, None)
+        else:
+            eng.train_device(dx, dy)
     b.record()
     torch.cuda.synchronize()
     eng.set_debug_flags(0)
@@ -63,6 +72,12 @@ def main():
           f"p90 {np.percentile(period, 90):.2f} | compute mean {comp.mean():.2f} std {comp.std():.2f} p90 "
           f"{np.percentile(comp, 90):.2f} | exchange mean {wait.mean():.2f} p50 {np.median(wait):.2f} p90 "
           f"{np.percentile(wait, 90):.2f}", flush=True)
+    if host:   # where do the slow steps sit inside a 64-step call (groups of 4, 16, 16, 16, 12 steps)?
+        pos = (np.arange(len(period)) + 1 + (int(eng.read_ctl().step) - len(xd))) % 64
+        by = [float(np.mean(period[pos == k])) for k in range(64)]
+        print(f"rank {tr.rank}/{world} host-fed: period p50 {np.median(period):.2f} p90 {np.percentile(period, 90):.2f} p99 "
+              f"{np.percentile(period, 99):.2f} max {period.max():.1f}; mean period by position in the call: " +
+              " ".join(f"{v:.0f}" for v in by), flush=True)
     sgd, fen, end = rows[:, 4], rows[:, 5], rows[:, 6]
     print(f"rank {tr.rank}/{world}: first update CTA enters -> dependency passed {np.mean(dep - rows[:, 3]) / 1e3:.2f}, -> local "
           f"gradients done {np.mean(grad - dep) / 1e3:.2f} (per-slice mean {np.mean(u[:, :, 2] - u[:, :, 1]) / 1e3:.2f}); "

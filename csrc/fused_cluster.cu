@@ -495,7 +495,7 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
                        float* __restrict__ part1, float* __restrict__ part2, float* __restrict__ img_loss,
                        int* __restrict__ img_correct, int B, float inv_batch, long long* __restrict__ trace,
                        const unsigned int* __restrict__ ready_ctr, unsigned int ready_expect,
-                       const float* __restrict__ packed) {
+                       const float* __restrict__ packed, const unsigned int* __restrict__ in_flag, unsigned int in_expect) {
   static_assert(CS >= 2 && CS <= 8, "the one-CTA case is fused_step.cu's fwd_bwd_kernel");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr bool kTC = kMode == 1;    // conv1, conv2 forward on tcgen05 (and the layouts that go with it)
@@ -612,6 +612,13 @@ fwd_bwd_cluster_kernel(const float* __restrict__ params, const float* __restrict
       for (int i = tid; i < 16 * 18 * 18; i += kCLThreads) s.dc2p[i] = 0.f;
     }
   };
+  // Host-fed steps: the batch is copied in by the copy engine on ANOTHER stream, and instead of a stream event in front
+  // of this kernel (which would end the programmatic overlap with its predecessor and the chaining of steps) the copy
+  // stream writes a sequence number behind the data; the one thread that fetches images waits for it here.
+  if (in_flag != nullptr && tid == 0) {
+    while ((int)(ld_acquire_sys(in_flag) - in_expect) < 0) {}
+    asm volatile("fence.proxy.async;" ::: "memory");   // the bulk copies below read through the async proxy
+  }
   load_image(img);   // the input batch does not depend on the previous kernel of the stream,
   if (img < B) {     // ... so the first image is landed AND re-laid out before the dependency is even looked at
     cl_mbar_wait(&s.mbar, phase);
@@ -1383,7 +1390,7 @@ template <int CS, int kMode>
 static int launch_cluster_t(const float* params, const float* x, const long long* labels, float* saved, float* part1,
                             float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
                             long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
-                            const float* packed, cudaStream_t stream) {
+                            const float* packed, const unsigned int* in_flag, unsigned int in_expect, cudaStream_t stream) {
   static PerDeviceOnce attr_set;
   auto kern = fwd_bwd_cluster_kernel<CS, kMode>;
   const size_t smem = cluster_smem_bytes<CS, kMode>();
@@ -1408,7 +1415,7 @@ static int launch_cluster_t(const float* params, const float* x, const long long
   const float inv_batch = 1.f / (float)B;
   DNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, params, x, labels, saved, part1, part2, img_loss, img_correct, B,
                                     inv_batch, trace, CS >= 4 ? ready_ctr : nullptr, ready_expect,
-                                    kMode != 0 ? packed : nullptr));
+                                    kMode != 0 ? packed : nullptr, in_flag, in_expect));
   return kOk;
 }
 
@@ -1465,11 +1472,11 @@ template <int kMode>
 static int launch_cluster_p(int cs, const float* params, const float* x, const long long* labels, float* saved,
                             float* part1, float* part2, float* img_loss, int* img_correct, int B, int max_clusters,
                             long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
-                            const float* packed, cudaStream_t stream) {
+                            const float* packed, const unsigned int* in_flag, unsigned int in_expect, cudaStream_t stream) {
 #define DNN_CL_CASE(N)                                                                                              \
   case N:                                                                                                           \
     return launch_cluster_t<N, kMode>(params, x, labels, saved, part1, part2, img_loss, img_correct, B, max_clusters, \
-                                    trace, ready_ctr, ready_expect, packed, stream);
+                                    trace, ready_ctr, ready_expect, packed, in_flag, in_expect, stream);
   switch (cs) {
     DNN_CL_CASE(8) DNN_CL_CASE(7) DNN_CL_CASE(6) DNN_CL_CASE(5) DNN_CL_CASE(4) DNN_CL_CASE(3) DNN_CL_CASE(2)
     default: set_last_error("cluster size %d not supported", cs); return kErrArg;
@@ -1482,10 +1489,11 @@ static int launch_cluster_p(int cs, const float* params, const float* x, const l
 int launch_fwd_bwd_cluster(int cs, int mode, const float* params, const float* x, const long long* labels,
                            float* saved, float* part1, float* part2, float* img_loss, int* img_correct, int B,
                            int max_clusters, long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
-                           const float* packed, cudaStream_t stream) {
+                           const float* packed, const unsigned int* in_flag, unsigned int in_expect,
+                           cudaStream_t stream) {
 #define DNN_CL_MODE(M)                                                                                             \
   launch_cluster_p<M>(cs, params, x, labels, saved, part1, part2, img_loss, img_correct, B, max_clusters, trace, \
-                      ready_ctr, ready_expect, M != 0 ? packed : nullptr, stream)
+                      ready_ctr, ready_expect, M != 0 ? packed : nullptr, in_flag, in_expect, stream)
   return mode == 1 ? DNN_CL_MODE(1) : (mode == 2 ? DNN_CL_MODE(2) : DNN_CL_MODE(0));
 #undef DNN_CL_MODE
 }

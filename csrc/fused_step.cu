@@ -758,6 +758,9 @@ update_kernel(const RankCtx* __restrict__ ctxs, int B, int n_part1, int loss_slo
       // Every CTA fenced its stores before it bumped ctas_done, and this CTA has observed all the bumps; the
       // release also orders the two stores above (one fence on this path, not three).
       st_release_gpu(&ctl->updates_done, ctl_snap.updates_done + 1u);
+      // the same number for the HOST (a 4-byte store over PCIe, nobody waits for it here): everything this step read
+      // -- its input slot included -- has been consumed
+      if (cx.host_progress != nullptr) *reinterpret_cast<volatile unsigned int*>(cx.host_progress) = ctl_snap.updates_done + 1u;
     }
   }
 }

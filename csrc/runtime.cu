@@ -38,7 +38,7 @@ int launch_fwd_bwd(bool train, const float* params, const float* x, const long l
 int launch_fwd_bwd_cluster(int cs, int mode, const float* params, const float* x, const long long* labels,
                            float* saved, float* part1, float* part2, float* img_loss, int* img_correct, int B,
                            int max_clusters, long long* trace, const unsigned int* ready_ctr, unsigned int ready_expect,
-                           const float* packed, cudaStream_t stream);
+                           const float* packed, const unsigned int* in_flag, unsigned int in_expect, cudaStream_t stream);
 int max_active_clusters(int cs, int mode);
 int launch_pingpong(const RankCtx* d_ctx, int peer, int iters, unsigned int base_seq, long long* d_out_ns,
                     cudaStream_t stream);
@@ -145,6 +145,15 @@ struct dnnb200_engine {
   long long* ring_y = nullptr;    // [kRing][max_batch]
   bool ring_ready = false;
   unsigned long long ring_uses = 0;
+  // event-free variant of the host-fed path (clustered kernel): "inputs landed" flags written by the copy stream,
+  // "region free" known from a progress word the update kernel stores to pinned host memory
+  unsigned int* d_in_flags = nullptr;            // [kRing / kGroup] device words
+  unsigned int* h_flag_vals = nullptr;           // pinned: sources of the 4-byte flag copies (a ring of 64)
+  volatile unsigned int* h_progress = nullptr;   // pinned, written by the update kernel (RankCtx::host_progress)
+  unsigned int flag_seq = 0;
+  unsigned int region_busy_until[kRing / kGroup] = {};   // updates_launched after the last step that reads the region
+  bool region_used[kRing / kGroup] = {};
+  int last_host_path = -1;                       // 1: the event-free variant ran last, 0: the event variant
   unsigned int pingpong_seq = 1000;
 };
 
@@ -220,8 +229,15 @@ static void free_ring(dnnb200_engine* e) {   // tolerates a ring that was only p
   }
   cudaFree(e->ring_x);
   cudaFree(e->ring_y);
+  cudaFree(e->d_in_flags);
+  if (e->h_flag_vals) cudaFreeHost(e->h_flag_vals);
+  if (e->h_progress) cudaFreeHost(const_cast<unsigned int*>(e->h_progress));
   e->ring_x = nullptr;
   e->ring_y = nullptr;
+  e->d_in_flags = nullptr;
+  e->h_flag_vals = nullptr;
+  e->h_progress = nullptr;
+  e->h_ctx.host_progress = nullptr;
   if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
   if (e->d2h_stream) cudaStreamDestroy(e->d2h_stream);
   e->copy_stream = e->d2h_stream = nullptr;
@@ -240,7 +256,16 @@ static int create_ring(dnnb200_engine* e) {
   // in the ring, so a whole group of steps is moved by one copy for the images and one for the labels
   DNN_CUDA_CHECK(cudaMalloc(&e->ring_x, (size_t)dnnb200_engine::kRing * e->max_batch * kImgNumel * sizeof(float)));
   DNN_CUDA_CHECK(cudaMalloc(&e->ring_y, (size_t)dnnb200_engine::kRing * e->max_batch * sizeof(long long)));
-  return kOk;
+  constexpr int kRegions = dnnb200_engine::kRing / dnnb200_engine::kGroup;
+  DNN_CUDA_CHECK(cudaMalloc(&e->d_in_flags, kRegions * sizeof(unsigned int)));
+  DNN_CUDA_CHECK(cudaMemset(e->d_in_flags, 0, kRegions * sizeof(unsigned int)));
+  DNN_CUDA_CHECK(cudaMallocHost(&e->h_flag_vals, 64 * sizeof(unsigned int)));
+  unsigned int* prog = nullptr;
+  DNN_CUDA_CHECK(cudaHostAlloc(&prog, sizeof(unsigned int), cudaHostAllocMapped));
+  *prog = e->updates_launched;
+  e->h_progress = prog;
+  DNN_CUDA_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&e->h_ctx.host_progress), prog, 0));
+  return push_ctx(e, nullptr);   // (synchronises: happens once, when the host-fed path is first used)
 }
 
 static int ensure_ring(dnnb200_engine* e) {
@@ -269,7 +294,7 @@ static int cluster_size_for(const dnnb200_engine* e, int B) {
 // nothing else came between (inner iterations of the multi-step calls). Only then may the kernel wait on the
 // update counter instead of on the completion of the previous grid (fused_cluster.cu).
 static int fwd_bwd_any(dnnb200_engine* e, const float* x, const long long* y, int B, cudaStream_t s, int* n_part1,
-                       bool chained = false) {
+                       bool chained = false, const unsigned int* in_flag = nullptr, unsigned int in_expect = 0u) {
   const int cs = cluster_size_for(e, B);
   *n_part1 = B;  // clusters reduce their conv1 partials to one row per image before they write them
   if (cs == 1)
@@ -281,7 +306,7 @@ static int fwd_bwd_any(dnnb200_engine* e, const float* x, const long long* y, in
                                 // ready-made operands are only trusted when the previous operation on the stream was this
                                 // engine's own update kernel (which wrote them together with the parameters): the host
                                 // may change the parameters between calls
-                                chained && !(e->debug_flags & 128) ? e->packed : nullptr, s);
+                                chained && !(e->debug_flags & 128) ? e->packed : nullptr, in_flag, in_expect, s);
 }
 
 // The counter value a chained step waits for is a kernel ARGUMENT: baked into a CUDA graph it would be stale on
@@ -734,6 +759,58 @@ int dnnb200_engine_grad_only(dnnb200_engine* e, const float* x, const int64_t* y
   return push_ctx(e, s);
 }
 
+// Host-fed steps without a single stream event on the compute stream. A group's inputs go out on the copy stream
+// (images, labels, then a 4-byte sequence number into the region's flag word); the first forward/backward kernel that
+// reads the region waits for that number itself (fused_cluster.cu), so every step of the call stays chained to its
+// predecessor and programmatic dependent launch is never interrupted. (With an event pair per group, the two steps
+// after every group boundary took 28 and 47 us instead of 22 at four GPUs -- bench/step_jitter.py with DNN_HOST=1 --
+// and a boundary on ANY rank stalls all of them.) A region is overwritten only when the update kernel of the last
+// step that read it has reported in through the pinned progress word, so the call runs at most two groups ahead of
+// the GPU: it returns when everything is enqueued, which for long calls is shortly before the end.
+static int train_host_flags(dnnb200_engine* e, const float* h_x, const long long* h_y, int B, int nsteps, float* d_losses,
+                            cudaStream_t s) {
+  constexpr int G = dnnb200_engine::kGroup, kRegions = dnnb200_engine::kRing / dnnb200_engine::kGroup;
+  const size_t xb = (size_t)B * kImgNumel * sizeof(float), yb = (size_t)B * sizeof(long long);
+  for (int t0 = 0; t0 < nsteps;) {
+    const int cap = t0 == 0 ? 4 : G;   // a short first group (the GPU starts after 4 steps' worth of PCIe time), then full ones
+    const int n = nsteps - t0 < cap ? nsteps - t0 : cap;
+    const int region = (int)((e->ring_uses / G) % kRegions);
+    if (e->region_used[region]) {      // its last readers must be through (they were enqueued two groups ago)
+      const unsigned int need = e->region_busy_until[region];
+      unsigned long long spins = 0;
+      while ((int)(*e->h_progress - need) < 0) {
+        if ((++spins & 0xfffffull) == 0 && cudaStreamQuery(s) == cudaSuccess) break;   // everything has run: also fine
+      }
+    }
+    float* gx = e->ring_x + (size_t)region * G * e->max_batch * kImgNumel;
+    long long* gy = e->ring_y + (size_t)region * G * e->max_batch;
+    const unsigned int seq = ++e->flag_seq;
+    unsigned int* src = e->h_flag_vals + (seq & 63u);
+    *src = seq;
+    DNN_CUDA_CHECK(cudaMemcpyAsync(gx, h_x + (size_t)t0 * B * kImgNumel, (size_t)n * xb, cudaMemcpyHostToDevice, e->copy_stream));
+    DNN_CUDA_CHECK(cudaMemcpyAsync(gy, h_y + (size_t)t0 * B, (size_t)n * yb, cudaMemcpyHostToDevice, e->copy_stream));
+    DNN_CUDA_CHECK(cudaMemcpyAsync(e->d_in_flags + region, src, sizeof(unsigned int), cudaMemcpyHostToDevice, e->copy_stream));
+    for (int k = 0; k < n; ++k) {
+      const int t = t0 + k;
+      int n_part1 = B;
+      int rc = fwd_bwd_any(e, gx + (size_t)k * B * kImgNumel, gy + (size_t)k * B, B, s, &n_part1, /*chained=*/t > 0,
+                           e->d_in_flags + region, seq);
+      if (rc) return rc;
+      const int lslot = (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask);
+      rc = launch_update(e->d_ctx, 1, B, n_part1, lslot, e->debug_flags | peers_flag(e), d_losses ? d_losses + t : nullptr, s);
+      if (rc) return rc;
+      e->updates_launched += 1u;
+      e->launches += 2;
+      e->steps_launched += 1;
+    }
+    e->region_busy_until[region] = e->updates_launched;
+    e->region_used[region] = true;
+    e->ring_uses += G;
+    t0 += n;
+  }
+  return kOk;
+}
+
 int dnnb200_engine_train_host(dnnb200_engine* e, const float* h_x, const int64_t* h_y, int B, int nsteps,
                               float* h_losses, void* stream) {
   DNN_ARG_CHECK(e && h_x && h_y, "engine_train_host: null argument");
@@ -747,6 +824,17 @@ int dnnb200_engine_train_host(dnnb200_engine* e, const float* h_x, const int64_t
   // pinned host memory is addressable from the device (unified addressing): resolve the device view once
   float* d_losses = nullptr;
   if (h_losses) DNN_CUDA_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&d_losses), h_losses, 0));
+  // The clustered kernel can wait for its inputs itself: no stream events (train_host_flags above). The one-CTA kernel
+  // of large batches, and calls recorded by a stream capture (the host must not wait inside one), keep the events.
+  const int use_flags = (cluster_size_for(e, B) > 1 && !stream_capturing(s) && !(e->debug_flags & 256)) ? 1 : 0;
+  if (e->last_host_path >= 0 && e->last_host_path != use_flags) {   // the two variants guard the ring differently
+    DNN_CUDA_CHECK(cudaStreamSynchronize(s));
+    DNN_CUDA_CHECK(cudaStreamSynchronize(e->copy_stream));
+    for (bool& u : e->region_used) u = false;
+    e->ring_uses = 0;
+  }
+  e->last_host_path = use_flags;
+  if (use_flags) return train_host_flags(e, h_x, (const long long*)h_y, B, nsteps, d_losses, s);
   // Steps are enqueued in groups of up to kGroup: the inputs of a group's steps travel in one H2D copy for the
   // images and one for the labels (every step's inputs are still copied, inside the call, just not one DMA
   // descriptor per step), and the cross-stream events (inputs ready / slots free) are recorded once per group, so

@@ -69,6 +69,8 @@ struct RankCtx {
   float* nvls_mc;         //   and the MULTICAST address of the same buffer on all ranks (nullptr: not available)
   long long* trace;       // development aid: update-kernel timestamps (globaltimer ns), nullptr in production
   float* packed;          // [kPackNumel] conv weights as tensor-core B operands (layout.h), refreshed with every update
+  unsigned int* host_progress;   // pinned host word (device view) that receives StepCtl::updates_done after every update
+                                 // kernel: how the host-fed path knows, without a stream event, that a ring region is free
   float* recv[kMaxWorld];          // recv[p]  = rank p's receive area as mapped in THIS process
   unsigned int* flags[kMaxWorld];  // flags[p] = rank p's flag area as mapped in THIS process
 };

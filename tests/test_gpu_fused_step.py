@@ -168,3 +168,30 @@ def test_network_autograd_path_on_gpu():
     gpu.zero_grad()                                  # default: TF32 tensor-core conv forward
     Fn.cross_entropy(gpu(x.cuda()), y.cuda()).backward()
     assert _rel(gpu.flat_grads, g_ref) < 2e-2
+
+
+def test_train_host_long_runs_reuse_the_ring_without_events():
+    """The host-fed path of the clustered kernel uses no stream event: the copy stream writes a sequence number behind
+    each group's inputs, the kernel that reads the group waits for it, and a ring region is reused once the update
+    kernel of its last reader has reported in through a pinned progress word. 150 steps cross the two regions many
+    times; several calls in a row, a call with another batch size (other packing of the region), a batch that runs
+    the one-CTA kernel (event variant) in between, and the host buffer being overwritten right after each call's
+    synchronize: the weights must be exactly those of the device-resident path."""
+    torch.manual_seed(17)
+    base = Network()
+    a, b = copy.deepcopy(base).cuda(), copy.deepcopy(base).cuda()
+    ea = native.Engine(a.flat_params, torch.zeros(L.FLAT_NUMEL, device="cuda"), None, 256, 0.01, 0.9)
+    eb = native.Engine(b.flat_params, torch.zeros(L.FLAT_NUMEL, device="cuda"), None, 256, 0.01, 0.9)
+    for steps, B in ((150, 16), (3, 16), (37, 8), (2, 256), (41, 16)):
+        hx = torch.randn(steps, B, 3, 32, 32).pin_memory()
+        hy = torch.randint(0, 10, (steps, B)).pin_memory()
+        hl = torch.full((steps,), float("nan")).pin_memory()
+        dx, dy = hx.cuda(), hy.cuda()
+        ea.train_host(hx, hy, hl)
+        eb.train_device(dx, dy)
+        torch.cuda.synchronize()
+        hx.fill_(123.0)                       # the call is over: its host buffers belong to the caller again
+        assert torch.isfinite(hl).all() and (hl > 0).all()
+        assert torch.equal(a.flat_params, b.flat_params), (steps, B)
+    assert ea.read_ctl().step == eb.read_ctl().step == 150 + 3 + 37 + 2 + 41
+    ea.close(); eb.close()
