@@ -190,6 +190,8 @@ def run_ours(args) -> int:
                       allreduce_variant=args.exchange, precision=args.precision)
     trainer = Trainer(cfg)            # public API: model + engine + peer group + control plane
     eng, comm = trainer.engine, trainer.comm
+    if os.environ.get("DNN_DEBUG_FLAGS_BENCH"):           # engine A/B switches (include/dnnb200.h), development only
+        eng.set_debug_flags(int(os.environ["DNN_DEBUG_FLAGS_BENCH"]))
     dev = trainer.device
     variant = trainer._exchange_variant() if world > 1 else 0
     variant_name = {0: "one-shot push, 16-byte LL lines (value, seq, value, seq)",

@@ -10,6 +10,7 @@
 #include <stdarg.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <new>
@@ -151,8 +152,10 @@ struct dnnb200_engine {
   unsigned int* h_flag_vals = nullptr;           // pinned: sources of the 4-byte flag copies (a ring of 64)
   volatile unsigned int* h_progress = nullptr;   // pinned, written by the update kernel (RankCtx::host_progress)
   unsigned int flag_seq = 0;
-  unsigned int region_busy_until[kRing / kGroup] = {};   // updates_launched after the last step that reads the region
-  bool region_used[kRing / kGroup] = {};
+  unsigned int region_busy_until[kRing] = {};    // updates_launched after the last step that reads the region
+  bool region_used[kRing] = {};
+  int flag_group = 2;                            // steps per group of the event-free variant (kRing / flag_group regions)
+  unsigned long long flag_uses = 0;              // groups handed out by the event-free variant
   int last_host_path = -1;                       // 1: the event-free variant ran last, 0: the event variant
   unsigned int pingpong_seq = 1000;
 };
@@ -256,9 +259,13 @@ static int create_ring(dnnb200_engine* e) {
   // in the ring, so a whole group of steps is moved by one copy for the images and one for the labels
   DNN_CUDA_CHECK(cudaMalloc(&e->ring_x, (size_t)dnnb200_engine::kRing * e->max_batch * kImgNumel * sizeof(float)));
   DNN_CUDA_CHECK(cudaMalloc(&e->ring_y, (size_t)dnnb200_engine::kRing * e->max_batch * sizeof(long long)));
-  constexpr int kRegions = dnnb200_engine::kRing / dnnb200_engine::kGroup;
+  constexpr int kRegions = dnnb200_engine::kRing;   // (one flag word per slot: any group size divides the ring)
   DNN_CUDA_CHECK(cudaMalloc(&e->d_in_flags, kRegions * sizeof(unsigned int)));
   DNN_CUDA_CHECK(cudaMemset(e->d_in_flags, 0, kRegions * sizeof(unsigned int)));
+  if (const char* g = getenv("DNN_HOST_GROUP")) {   // development: steps per group of the event-free host-fed path
+    const int v = atoi(g);
+    if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) e->flag_group = v;
+  }
   DNN_CUDA_CHECK(cudaMallocHost(&e->h_flag_vals, 64 * sizeof(unsigned int)));
   unsigned int* prog = nullptr;
   DNN_CUDA_CHECK(cudaHostAlloc(&prog, sizeof(unsigned int), cudaHostAllocMapped));
@@ -769,12 +776,15 @@ int dnnb200_engine_grad_only(dnnb200_engine* e, const float* x, const int64_t* y
 // the GPU: it returns when everything is enqueued, which for long calls is shortly before the end.
 static int train_host_flags(dnnb200_engine* e, const float* h_x, const long long* h_y, int B, int nsteps, float* d_losses,
                             cudaStream_t s) {
-  constexpr int G = dnnb200_engine::kGroup, kRegions = dnnb200_engine::kRing / dnnb200_engine::kGroup;
+  // Groups are SMALL here (a boundary costs nothing): a 3 MB copy burst per 16 steps delays the GPU's fetch of the
+  // kernel launches that share PCIe with it by tens of microseconds, and at N GPUs a late launch on any rank stalls
+  // all of them. Measured at 4 GPUs, us per step host-fed vs device-resident 21.75: groups of 16 steps 23.67, of 4
+  // 21.80, of 2 21.80, of 1 21.89; 20-step calls 27.3 / 26.2 / 24.8 / 26.1 (profiles/host_fed_groups_n4.txt).
+  const int G = e->flag_group, kRegions = dnnb200_engine::kRing / G;
   const size_t xb = (size_t)B * kImgNumel * sizeof(float), yb = (size_t)B * sizeof(long long);
   for (int t0 = 0; t0 < nsteps;) {
-    const int cap = t0 == 0 ? 4 : G;   // a short first group (the GPU starts after 4 steps' worth of PCIe time), then full ones
-    const int n = nsteps - t0 < cap ? nsteps - t0 : cap;
-    const int region = (int)((e->ring_uses / G) % kRegions);
+    const int n = nsteps - t0 < G ? nsteps - t0 : G;
+    const int region = (int)(e->flag_uses % (unsigned long long)kRegions);
     if (e->region_used[region]) {      // its last readers must be through (they were enqueued two groups ago)
       const unsigned int need = e->region_busy_until[region];
       unsigned long long spins = 0;
@@ -793,8 +803,9 @@ static int train_host_flags(dnnb200_engine* e, const float* h_x, const long long
     for (int k = 0; k < n; ++k) {
       const int t = t0 + k;
       int n_part1 = B;
+      // (only the group's first kernel has to look at the flag: the steps behind it are ordered after it)
       int rc = fwd_bwd_any(e, gx + (size_t)k * B * kImgNumel, gy + (size_t)k * B, B, s, &n_part1, /*chained=*/t > 0,
-                           e->d_in_flags + region, seq);
+                           k == 0 ? e->d_in_flags + region : nullptr, seq);
       if (rc) return rc;
       const int lslot = (int)(e->steps_launched & (unsigned long long)e->loss_ring_mask);
       rc = launch_update(e->d_ctx, 1, B, n_part1, lslot, e->debug_flags | peers_flag(e), d_losses ? d_losses + t : nullptr, s);
@@ -805,7 +816,7 @@ static int train_host_flags(dnnb200_engine* e, const float* h_x, const long long
     }
     e->region_busy_until[region] = e->updates_launched;
     e->region_used[region] = true;
-    e->ring_uses += G;
+    e->flag_uses += 1;
     t0 += n;
   }
   return kOk;
@@ -832,6 +843,7 @@ int dnnb200_engine_train_host(dnnb200_engine* e, const float* h_x, const int64_t
     DNN_CUDA_CHECK(cudaStreamSynchronize(e->copy_stream));
     for (bool& u : e->region_used) u = false;
     e->ring_uses = 0;
+    e->flag_uses = 0;
   }
   e->last_host_path = use_flags;
   if (use_flags) return train_host_flags(e, h_x, (const long long*)h_y, B, nsteps, d_losses, s);

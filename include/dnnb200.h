@@ -170,7 +170,9 @@ int dnnb200_engine_set_update_trace(dnnb200_engine* e, long long* d_trace);
 /* development aid / A-B switches, OR-ed: 2 = the update kernel does not trigger the early launch of the next
  * kernel; 4 = the update trace is a ring over the last 1024 steps; 8 = chained steps wait for the completion of
  * the previous update GRID instead of its update counter; 32 = with peers, use the unconstrained update kernel
- * instead of the one that fits three CTAs per SM */
+ * instead of the one that fits three CTAs per SM; 128 = chained steps of the tensor-core
+ * instantiations pack their B operands in the kernel instead of fetching them ready-made; 256 = the host-fed path
+ * uses the event variant even with the clustered kernel */
 int dnnb200_engine_set_debug_flags(dnnb200_engine* e, int flags);
 
 /* one optimizer step on a device-resident batch: fwd/bwd kernel + update kernel
@@ -179,12 +181,15 @@ int dnnb200_engine_step(dnnb200_engine* e, const float* x, const int64_t* y, int
 /* nsteps steps over device-resident batches x[nsteps][B][3][32][32], y[nsteps][B]: one native loop,
  * no per-step Python (the whole dataset fits in HBM many times over) */
 int dnnb200_engine_train_device(dnnb200_engine* e, const float* x, const int64_t* y, int B, int nsteps, void* stream);
-/* nsteps steps fed from PINNED host memory: every step's inputs are copied host->device inside the call (32-slot
- * device ring on a copy stream; the steps of a group -- 4 in the first group of a call, then 16 -- share one copy for
- * their images and one for their labels and one pair of events) and run through the two kernels; the update kernel writes
- * the step's mean loss straight into h_losses[t] (pinned host memory, 4 bytes device->host per
- * step). Returns after everything is enqueued; the caller synchronises `stream` before reading
- * h_losses. */
+/* nsteps steps fed from PINNED host memory: every step's inputs are copied host->device inside the call (copy stream,
+ * 32-slot device ring) and run through the two kernels; the update kernel writes the step's mean loss straight into
+ * h_losses[t] (pinned host memory, 4 bytes device->host per step). With the clustered kernel (batches up to a few
+ * dozen images) there is no stream event anywhere: the copy stream writes a sequence number behind every two steps'
+ * inputs, the kernel that reads them waits for it, and a ring region is overwritten once the update kernel of its
+ * last reader has reported in through a pinned progress word -- so the call runs at most 32 steps ahead of the GPU
+ * and returns when everything is enqueued. Larger batches (one-CTA kernel) and calls under stream capture use an
+ * event pair per group of 16 steps instead. The caller synchronises `stream` before reading h_losses or reusing the
+ * host buffers. */
 int dnnb200_engine_train_host(dnnb200_engine* e, const float* h_x, const int64_t* h_y, int B, int nsteps,
                               float* h_losses, void* stream);
 /* forward only over N device-resident images; h_out2 = {mean over batches of the batch-mean
