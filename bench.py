@@ -367,10 +367,11 @@ def run_ours(args) -> int:
                     "h2d_bytes_per_step": B * 3 * 32 * 32 * 4 + B * 8, "d2h_bytes_per_step": 4,
                     "ms_per_step": round(e2e_max * 1e3 / K, 6),
                     "how": "Engine.train_host: every step's images+labels are copied from pinned host memory inside the "
-                           "region (cudaMemcpyAsync on a copy stream into a 32-slot device ring, the steps of a group of "
-                           "<= 16 sharing one copy), 2 kernels per step, and the update kernel stores each step's mean "
-                           "loss into the caller's pinned host buffer (device->host over PCIe); wall clock with "
-                           "synchronize on both sides, max over ranks",
+                           "region (cudaMemcpyAsync on a copy stream into a 32-slot device ring, two steps per copy; the "
+                           "kernels wait for a sequence number the copy stream writes behind the data, no stream events), "
+                           "2 kernels per step, and the update kernel stores each step's mean loss into the caller's "
+                           "pinned host buffer (device->host over PCIe); wall clock with synchronize on both sides, "
+                           "max over ranks",
                     "mean_loss_read_back": round(max(s["loss"] for s in stats), 4)},
             "gpu_launches": int(sum(s["launches"] for s in stats) // world),
             "gpu_launches_note": "kernels of libdnnb200.so per rank inside the device-timed region "
