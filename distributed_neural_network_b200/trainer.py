@@ -423,6 +423,7 @@ class Trainer:
         eng = self.engine
         self._apply_membership(local_only=local_sgd)
         eng.reset_loss()
+        pinned = None
         steps = len(shard) // B
         x, y, tail_xy = D.epoch_tensor(shard, B, shuffle=True, generator=self.gen)
         run_steps = steps if drop_at is None else min(steps, drop_at)
@@ -432,7 +433,10 @@ class Trainer:
         if self.cfg.input_pipeline == "host":
             # per-step H2D copies from pinned memory through the engine's 32-slot ring
             if run_steps:
-                eng.train_host(x[:run_steps].pin_memory(), y[:run_steps].pin_memory(), None)
+                # (kept alive until the synchronising read of the control block below: train_host returns while the
+                # last copies are still in flight, and the copy stream is not one PyTorch's pinned allocator knows)
+                pinned = (x[:run_steps].pin_memory(), y[:run_steps].pin_memory())
+                eng.train_host(pinned[0], pinned[1], None)
         elif run_steps:
             if run_steps > n_tail:
                 eng.train_device(x[:run_steps - n_tail], y[:run_steps - n_tail])
@@ -456,6 +460,7 @@ class Trainer:
             eng.leave()
             self.dropped = True
         ctl = eng.read_ctl()
+        pinned = None
         if ctl.status & 1:
             self._log(f"[rank {self.rank}] peers timed out during the epoch: mask 0x{(ctl.status >> 8) & 0xffff:x}")
             self.saw_timeout = True
