@@ -301,9 +301,10 @@ int launch_tc_conv_wgrad(const float* x, const float* y, const unsigned char* id
 int launch_conv_relu_pool_bwd(const float* x, const float* w, const float* y, const unsigned char* idx,
                               const float* dy, float* dx, float* dw, float* db, int N, int Ci, int H, int W,
                               int Co, int tensor_core_dgrad, cudaStream_t s) {
-  // TF32 mode, conv2, thousands of images: the tensor-core weight gradient is the faster one (518 vs 588 us at 10 000
-  // images, 60 vs 53 us at 1 024: profiles/layer_bench_r2.json); for conv1 the pooled-grid FFMA kernel wins 2.3x
-  if (tensor_core_dgrad && Ci == 6 && H == 14 && W == 14 && Co == 16 && N >= 4096) {
+  // TF32 mode, conv2, from a thousand images on: the tensor-core weight gradient is the faster one (189 vs 585 us at
+  // 10 000 images, 33 vs 54 us at 1 024, 14 vs 11 us at 16: profiles/layer_bench_r2.json); for conv1 the two tie at
+  // 10 000 images (999 vs 932 us) and the pooled-grid FFMA kernel wins below
+  if (tensor_core_dgrad && Ci == 6 && H == 14 && W == 14 && Co == 16 && N >= 1024) {
     const int rc = launch_tc_conv_wgrad(x, y, idx, dy, dw, db, N, Ci, H, W, Co, s);
     if (rc) return rc;
   } else {

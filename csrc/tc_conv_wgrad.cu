@@ -18,10 +18,11 @@
 // once, at the end. Persistent CTAs over the batch, the next image arrives by TMA bulk copy while the last block of
 // the current one is multiplied.
 //
-// What it costs is in profiles/layer_bench_r2.json: the gather writes as many elements per image as the pooled-grid
-// FFMA kernel (layers.cu) executes multiply-adds, and every K=8 slab of pixels costs a 47..64-cycle MMA whatever N is
-// (bench/tc_mma_rate.py), so for this model's 6 and 16 output channels the FFMA kernel stays the default; this one is
-// the measured alternative (`conv_relu_pool_bwd(..., tensor_cores=2)`).
+// What it costs is in profiles/layer_bench_r2.json (10 000 images): conv2 189 us against 585 us for the pooled-grid FFMA
+// kernel of layers.cu and 540 us for cuDNN given the dense gradient; conv1 999 us against 932 and 1 890. The autograd
+// path uses it for conv2 from 1 024 images on (layers.cu: launch_conv_relu_pool_bwd); `native.tc_conv_wgrad` calls it
+// directly. For conv1 the gather writes as many elements per image as the FFMA kernel executes multiply-adds and every
+// K=8 slab of pixels costs a 47..64-cycle MMA whatever N is (bench/tc_mma_rate.py), so the two tie.
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -92,34 +93,40 @@ tc_conv_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ y, c
       const int k0 = blk * C::KB_PIX;
 #pragma unroll 1
       for (int t = 0; t < C::TILES; ++t) {
-        // ---- A block of tile t: a warp writes the 32 floats of one (chunk, row group) at a time ----
-        for (int it = warp; it < C::KB_CH * C::GROUPS; it += 8) {
-          const int q = it / C::GROUPS, g = it - q * C::GROUPS;
-          const int m = g * 8 + (lane >> 2), k = k0 + q * 4 + (lane & 3);
-          float v = 0.f;
-          if (k < C::P) {
-            if (m < C::MT) {
-              const int cl = m / 25, tap = m - cl * 25, c = t * 3 + cl;
-              const int oh = k / C::WOUT, ow = k - oh * C::WOUT;
-              if (c < CI) v = stage[(c * HIN + oh + tap / 5) * C::WIN + ow + tap % 5];
-            } else if (m == C::MT && t == 0) {
-              v = 1.f;
+        // ---- A block of tile t. A thread keeps ONE row m = (c, kh, kw) for the whole kernel (its base address in the
+        // image is computed once) and walks that row's K-chunks, three threads per row: four pixels per item, one
+        // 16-byte store. (The first version did the index arithmetic per element: ncu showed the kernel bound by the
+        // issue slots of this gather -- 57-69 % busy, tensor pipe 1.5 % -- not by its MMAs.)
+        if (tid < 3 * C::GROUPS * 8) {
+          const int m = tid % (C::GROUPS * 8), q0 = tid / (C::GROUPS * 8);
+          const int cl = m / 25, tap = m - cl * 25, c = t * 3 + cl;
+          const bool real = m < C::MT && c < CI, ones = m == C::MT && t == 0;
+          const float* src = stage + (c * HIN + tap / 5) * C::WIN + tap % 5;   // (only dereferenced for real rows)
+          for (int q = q0; q < C::KB_CH; q += 3) {
+            float v[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int k = k0 + q * 4 + e, oh = k / C::WOUT, ow = k - oh * C::WOUT;
+              v[e] = k < C::P ? (real ? src[oh * C::WIN + ow] : (ones ? 1.f : 0.f)) : 0.f;
             }
+            *reinterpret_cast<float4*>(sA + (q * 16 + (m >> 3)) * 32 + (m & 7) * 4) = make_float4(v[0], v[1], v[2], v[3]);
           }
-          sA[(q * 16 + g) * 32 + lane] = v;
         }
         if (t == 0) {
           // ---- B block (shared by the tiles): dC of these pixels, from the pooled gradient and the argmax ----
-          for (int it = warp; it < C::KB_CH * C::NG; it += 8) {
-            const int q = it / C::NG, g = it - q * C::NG;
-            const int o = g * 8 + (lane >> 2), k = k0 + q * 4 + (lane & 3);
-            float v = 0.f;
-            if (k < C::P && o < CO) {
-              const int oh = k / C::WOUT, ow = k - oh * C::WOUT;
-              const int pi = (o * C::HP + (oh >> 1)) * C::HP + (ow >> 1);
-              if ((int)__ldg(ib + pi) == (oh & 1) * 2 + (ow & 1) && __ldg(yb + pi) > 0.f) v = __ldg(dyb + pi);
+          for (int it = tid; it < C::KB_CH * C::NG * 8; it += 256) {
+            const int q = it / (C::NG * 8), o = it - q * (C::NG * 8);
+            float v[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int k = k0 + q * 4 + e, oh = k / C::WOUT, ow = k - oh * C::WOUT;
+              v[e] = 0.f;
+              if (k < C::P && o < CO) {
+                const int pi = (o * C::HP + (oh >> 1)) * C::HP + (ow >> 1);
+                if ((int)__ldg(ib + pi) == (oh & 1) * 2 + (ow & 1) && __ldg(yb + pi) > 0.f) v[e] = __ldg(dyb + pi);
+              }
             }
-            sB[(q * 2 + g) * 32 + lane] = v;
+            *reinterpret_cast<float4*>(sB + (q * 2 + (o >> 3)) * 32 + (o & 7) * 4) = make_float4(v[0], v[1], v[2], v[3]);
           }
         }
         fence_proxy_async();   // operands were written with st.shared; the tensor core reads through the async proxy
