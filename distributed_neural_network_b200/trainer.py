@@ -78,10 +78,10 @@ class TrainConfig:
     step_path: str = "fused"               # fused: the two-kernel step engine (default) | autograd: Network.forward +
                                            # loss.backward() through the layer kernels, gradients averaged bucket by
                                            # bucket on a side stream while backward runs (large batches per GPU)
-    overlap_exchange: Optional[bool] = None  # autograd path: exchange buckets while backward runs (True), after it (False),
-                                           # or by batch size (None: from 2048 images per GPU, where the step is GPU-bound
-                                           # and the overlap measures faster; below, the hooks' host work costs more
-                                           # than the exchange it hides -- profiles/autograd_overlap_n2.json)
+    overlap_exchange: Optional[bool] = None  # autograd path: exchange buckets while backward runs (True) or after it
+                                           # (False, and None). Off unless asked for: the overlap won only at 2 GPUs with
+                                           # 4096 images each (1161 vs 1171 us) and lost everywhere else, at 8 GPUs at
+                                           # every size -- profiles/autograd_overlap_n{2,8}.json
     exchange_timing: bool = True           # per-epoch "allreduce_us" in the JSONL (the reference books its
                                            # mpi_communication_time_children, data_parallelism_train.py:209-213)
     peer_timeout_s: float = 30.0
@@ -400,7 +400,7 @@ class Trainer:
                 self._averager = BucketedGradientAverager(
                     model, len(self.membership.active), engine=self.engine, allreduce_fn=self.comm.allreduce_sum_,
                     variant=self._standalone_variant() if self.engine is not None else "one-shot",
-                    overlap=cfg.overlap_exchange if cfg.overlap_exchange is not None else B >= 2048)
+                    overlap=bool(cfg.overlap_exchange))
             avg = self._averager
         total = torch.zeros((), device=self.device)
         nb = 0

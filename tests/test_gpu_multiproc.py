@@ -186,7 +186,7 @@ def test_ipc_autograd_step_path_with_bucketed_overlap(tmp_path):
     the two runs must agree (the exchange is the same arithmetic in the same order either way)."""
     n = min(torch.cuda.device_count(), 8)
     kw = dict(train_size=256 * n, test_size=32, epochs=2, batch_size=64, lr=0.05, seed=13, step_path="autograd")
-    a = _launch(n, tmp_path / "overlap", "step-allreduce", **kw)
+    a = _launch(n, tmp_path / "overlap", "step-allreduce", overlap_exchange=True, **kw)
     b = _launch(n, tmp_path / "after", "step-allreduce", overlap_exchange=False, **kw)
     for r in range(1, n):
         assert torch.equal(a[0]["flat"], a[r]["flat"]) and torch.equal(b[0]["flat"], b[r]["flat"])
