@@ -462,6 +462,13 @@ int dnnb200_group_connect_local(dnnb200_group** groups, int n) {
         DNN_CUDA_CHECK(cudaDeviceCanAccessPeer(&can, groups[a]->device, groups[b]->device));
         DNN_ARG_CHECK(can, "group_connect_local: device %d cannot access device %d", groups[a]->device,
                       groups[b]->device);
+        int cur = 0;
+        DNN_CUDA_CHECK(cudaGetDevice(&cur));
+        DNN_CUDA_CHECK(cudaSetDevice(groups[a]->device));
+        const cudaError_t pe = cudaDeviceEnablePeerAccess(groups[b]->device, 0);
+        cudaSetDevice(cur);
+        if (pe == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+        else DNN_CUDA_CHECK(pe);
       }
       groups[a]->peer_base[b] = groups[b]->base;
     }
@@ -924,6 +931,35 @@ int dnnb200_engine_allreduce(dnnb200_engine* e, const float* in, float* out, int
   int rc = launch_allreduce(e->d_ctx, 1, ins, outs, n, mode, two_shot, (cudaStream_t)stream);
   if (rc) return rc;
   e->launches += 1;
+  return kOk;
+}
+
+int dnnb200_engine_allreduce_timed(dnnb200_engine* e, const float* in, float* out, int n, int two_shot, int iters,
+                                   double* h_us_per_call, void* stream) {
+  DNN_ARG_CHECK(e && in && out && h_us_per_call && iters >= 1, "engine_allreduce_timed: bad argument");
+  cudaStream_t s = (cudaStream_t)stream;
+  // Launched from here, not from an interpreter: 2-3 us of host work per launch against >= 8 us per kernel, so the
+  // stream never runs dry and the events bracket device time. The first calls align the ranks (the collective is
+  // its own barrier) and are not timed.
+  for (int i = 0; i < 8; ++i) {
+    const int rc = dnnb200_engine_allreduce(e, in, out, n, 0, two_shot, stream);
+    if (rc) return rc;
+  }
+  cudaEvent_t e0, e1;
+  DNN_CUDA_CHECK(cudaEventCreate(&e0));
+  DNN_CUDA_CHECK(cudaEventCreate(&e1));
+  int rc = kOk;
+  cudaEventRecord(e0, s);
+  for (int i = 0; i < iters && rc == kOk; ++i) rc = dnnb200_engine_allreduce(e, in, out, n, 0, two_shot, stream);
+  cudaEventRecord(e1, s);
+  const cudaError_t se = cudaEventSynchronize(e1);
+  float ms = 0.f;
+  if (se == cudaSuccess) cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (rc) return rc;
+  DNN_CUDA_CHECK(se);
+  *h_us_per_call = (double)ms * 1e3 / iters;
   return kOk;
 }
 

@@ -266,6 +266,50 @@ def sgd_momentum(p, g, buf, lr: float, mu: float, first_step: bool, scale: float
 # ---------------------------------------------------------------------------
 # peer group
 # ---------------------------------------------------------------------------
+def share_fd(rank: int, world: int, name: str, word: int = 0, fd: int = -1, timeout_s: float = 30.0):
+    """Rank 0 hands (word, file descriptor) to every other rank on this host over an abstract Unix socket named after
+    ``name`` (SCM_RIGHTS); returns (word, fd) -- on ranks > 0 a duplicate of the descriptor, theirs to close."""
+    w, f = C.c_ulonglong(word), C.c_int(fd)
+    _check(require().dnnb200_share_fd(rank, world, name.encode(), C.byref(w), C.byref(f), int(timeout_s * 1000)))
+    return int(w.value), int(f.value)
+
+
+def nvls_supported(device_index: int) -> bool:
+    lib = _load()
+    return bool(lib is not None and torch.cuda.is_available() and lib.dnnb200_nvls_supported(device_index))
+
+
+class NvlsGroup:
+    """NVLink multicast group (csrc/nvls_group.cu): ``NvlsGroup(...)`` on every rank, a barrier, ``map()`` on every
+    rank, a barrier, then ``local_ptr`` / ``multicast_ptr`` are this rank's and the all-GPU view of one zero-filled
+    symmetric buffer. ``name`` must be the same on all ranks and unique to the job."""
+
+    def __init__(self, rank: int, world: int, device_index: int, nbytes: int, name: str, timeout_s: float = 30.0):
+        self._h = C.c_void_p()
+        self.local_ptr = self.multicast_ptr = 0
+        self.nbytes = 0
+        _check(require().dnnb200_nvls_open(C.byref(self._h), rank, world, device_index, C.c_size_t(nbytes),
+                                           name.encode(), int(timeout_s * 1000)))
+
+    def map(self):
+        loc, mc, nb = C.c_void_p(), C.c_void_p(), C.c_size_t()
+        _check(require().dnnb200_nvls_map(self._h, C.byref(loc), C.byref(mc), C.byref(nb)))
+        self.local_ptr, self.multicast_ptr, self.nbytes = int(loc.value), int(mc.value), int(nb.value)
+        return self.local_ptr, self.multicast_ptr
+
+    def close(self) -> None:
+        if self._h:
+            require().dnnb200_nvls_close(self._h)
+            self._h = C.c_void_p()
+            self.local_ptr = self.multicast_ptr = 0
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class Group:
     """This rank's receive/flag area plus the mapped areas of its peers."""
 
@@ -435,6 +479,14 @@ class Engine:
         _check(require().dnnb200_engine_allreduce(self._h, _p(inp), _p(out), inp.numel(), mode, variant_id(two_shot),
                                                   _stream()))
 
+    def allreduce_timed(self, inp: torch.Tensor, out: torch.Tensor, variant, iters: int = 200) -> float:
+        """Device-timed microseconds per stand-alone mean all-reduce (a burst enqueued from C). Collective."""
+        _f32(inp, "in")
+        us = C.c_double()
+        _check(require().dnnb200_engine_allreduce_timed(self._h, _p(inp), _p(out), inp.numel(), variant_id(variant),
+                                                        iters, C.byref(us), _stream()))
+        return float(us.value)
+
     def ll128_probe(self, peer: int, iters: int = 2000, n_ctas: int = 32):
         """Ping-pong of 128-byte lines with rank ``peer`` (which must call it too): returns (torn words -- must be 0,
         microseconds per round trip, gave_up)."""
@@ -442,11 +494,18 @@ class Engine:
         _check(require().dnnb200_engine_ll128_probe(self._h, peer, iters, n_ctas, out, _stream()))
         return int(out[0]), float(out[1]) / 1e3 / iters, bool(out[2])
 
-    def attach_nvls(self, local_buf: torch.Tensor, multicast_ptr: int) -> None:
-        _f32(local_buf, "local_buf")
-        assert local_buf.numel() >= NVLS_FLOATS
-        self._nvls_buf = local_buf
-        _check(require().dnnb200_engine_attach_nvls(self._h, _p(local_buf), C.c_void_p(multicast_ptr)))
+    def attach_nvls(self, local_buf, multicast_ptr: int) -> None:
+        """``local_buf``: this rank's view of the symmetric buffer (an ``NvlsGroup`` after ``map()``, or a float32
+        CUDA tensor of at least NVLS_FLOATS elements); ``multicast_ptr`` the all-GPU view of the same bytes."""
+        if isinstance(local_buf, NvlsGroup):
+            assert local_buf.nbytes >= NVLS_FLOATS * 4 and local_buf.local_ptr
+            ptr = C.c_void_p(local_buf.local_ptr)
+        else:
+            _f32(local_buf, "local_buf")
+            assert local_buf.numel() >= NVLS_FLOATS
+            ptr = _p(local_buf)
+        self._nvls_buf = local_buf              # keeps the mapping alive as long as the engine may use it
+        _check(require().dnnb200_engine_attach_nvls(self._h, ptr, C.c_void_p(multicast_ptr)))
 
     def leave(self) -> None:
         _check(require().dnnb200_engine_leave(self._h, _stream()))

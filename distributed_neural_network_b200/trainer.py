@@ -172,7 +172,7 @@ class Trainer:
                 self.engine.attach_group(self.group)
                 self._apply_membership()
                 # NVLS (in-switch reduction) where the host exposes NVLink multicast; all ranks or nobody
-                made = nvls.try_create(self.device)
+                made = nvls.try_create(self.device, self.comm)
                 if all(self.comm.allgather(made is not None)):
                     self.nvls_buf, self.nvls_mc = made
                     self.engine.attach_nvls(self.nvls_buf, self.nvls_mc)
@@ -735,7 +735,10 @@ class Trainer:
             self.engine.close()
             self.engine = None
         if self.group is not None:
-            self.comm.barrier()
+            self.comm.barrier()                 # nobody stores into a peer's (or the multicast) mapping any more
+            if getattr(self, "nvls_buf", None) is not None:
+                self.nvls_buf.close()
+                self.nvls_buf = None
             self.group.close()
             self.group = None
         try:

@@ -229,11 +229,36 @@ int dnnb200_batch_grad_noalloc(const float* params, const float* x, const int64_
 int dnnb200_engine_allreduce(dnnb200_engine* e, const float* in, float* out, int n, int mode, int two_shot,
                              void* stream);
 
+/* `iters` back-to-back mean all-reduces (after 8 untimed ones) between two events on `stream`, enqueued from C so
+ * that the stream never runs dry: device time per call in microseconds. Collective; synchronises. */
+int dnnb200_engine_allreduce_timed(dnnb200_engine* e, const float* in, float* out, int n, int two_shot, int iters,
+                                   double* h_us_per_call, void* stream);
+
 /* NVLS: give the engine a symmetric buffer of DNNB200_NVLS_FLOATS floats that every rank allocated and mapped
- * into one NVLink multicast object (e.g. with torch.distributed._symmetric_memory): `local_buf` is this rank's
+ * into one NVLink multicast object (dnnb200_nvls_open / dnnb200_nvls_map below): `local_buf` is this rank's
  * copy, `multicast_buf` the multicast address. The buffer must be zero-initialised. */
 #define DNNB200_NVLS_FLOATS (2 * DNNB200_FLAT_NUMEL + 2 * 16 * 128)
 int dnnb200_engine_attach_nvls(dnnb200_engine* e, float* local_buf, float* multicast_buf);
+
+/* ---- NVLink multicast group (csrc/nvls_group.cu): the symmetric buffer for dnnb200_engine_attach_nvls, made with the
+ * CUDA virtual-memory and multicast driver calls; rank 0 hands the multicast object to the other processes as a file
+ * descriptor over an abstract Unix socket named after `name` (SCM_RIGHTS), which must be unique to the job.
+ *   every rank: dnnb200_nvls_open(...)           -> creates / imports the object, adds this rank's device
+ *   BARRIER of the caller's control plane        (memory may only be bound once every device is in)
+ *   every rank: dnnb200_nvls_map(...)            -> allocates, binds, maps; `local` is zero-filled
+ *   BARRIER before the first use                 (a multicast store to a member that has not bound yet is lost)
+ * All ranks must pass the same `bytes` (rounded up to the granularity the driver recommends; `*bytes_out`).
+ * Errors: DNNB200 code 3 when the driver or device has no multicast support, 4 when a rank did not show up within
+ * `timeout_ms`. dnnb200_nvls_close unmaps and releases; detach the engine (or destroy it) first. */
+typedef struct dnnb200_nvls dnnb200_nvls;
+int dnnb200_nvls_supported(int device);
+int dnnb200_nvls_open(dnnb200_nvls** out, int rank, int world, int device, size_t bytes, const char* name,
+                      int timeout_ms);
+int dnnb200_nvls_map(dnnb200_nvls* g, float** local, float** multicast, size_t* bytes_out);
+int dnnb200_nvls_close(dnnb200_nvls* g);
+/* the rendezvous underneath, usable on its own: rank 0 passes (*word, *fd) to every other rank of the same host, which
+ * receive a duplicate of the descriptor in *fd (theirs to close) and the word in *word. */
+int dnnb200_share_fd(int rank, int world, const char* name, unsigned long long* word, int* fd, int timeout_ms);
 
 /* latency probe: `iters` round trips of one 16-byte LL line with rank `peer` (which must make the matching call);
  * returns the one-way store->visible latency over peer memory in microseconds. Synchronises. */

@@ -16,7 +16,10 @@ def main():
     os.makedirs(out_dir, exist_ok=True)   # every rank writes its result here; nobody may rely on another rank's mkdir
     tr = Trainer(TrainConfig(device="cuda", synthetic=True, quiet=True, sync_mode="step-allreduce", seed=3,
                              peer_timeout_s=20.0, log_dir=out_dir + "/log"))
-    res = {"rank": tr.rank, "nvls": tr.nvls_ok}
+    from distributed_neural_network_b200.parallel import nvls
+    res = {"rank": tr.rank, "nvls": tr.nvls_ok, "why_not": nvls.last_error}
+    if not tr.nvls_ok:
+        print(f"[rank {tr.rank}] NVLS group not created: {nvls.last_error or 'another rank failed'}", flush=True)
     if tr.nvls_ok:
         eng = tr.engine
         g = torch.Generator().manual_seed(100 + tr.rank)

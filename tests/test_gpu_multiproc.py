@@ -1,6 +1,7 @@
 """Real multi-process, multi-GPU path: CUDA-IPC peer group + fused exchange, one process per GPU.
 Needs at least 2 GPUs (`gpurun --gpus 2`); ranks sharing ONE GPU must never spin on each other."""
 import json
+import os
 import sys
 from pathlib import Path
 
@@ -69,7 +70,7 @@ def test_nvls_in_switch_allreduce_matches_peer_memory_variant(tmp_path):
     assert rc == 0
     res = [torch.load(f"{tmp_path}/rank{r}.pt", weights_only=False) for r in range(n)]
     if not all(r["nvls"] for r in res):
-        pytest.skip("NVLink multicast is not exposed on this host")
+        pytest.skip("NVLink multicast is not exposed on this host: " + "; ".join(sorted({r["why_not"] for r in res})))
     assert all(r["status"] == 0 for r in res)
     for key in res[0]["outs"]:
         nelem = int(key.split("_")[0])
@@ -194,3 +195,78 @@ def test_ipc_autograd_step_path_with_bucketed_overlap(tmp_path):
     rel = ((a[0]["flat"] - b[0]["flat"]).norm() / b[0]["flat"].norm()).item()
     assert rel < 1e-4, rel
     assert a[0]["history"][-1]["train_loss"] < a[0]["history"][0]["train_loss"] + 0.05
+
+
+@needs2
+def test_native_nvls_group_two_devices_in_one_process():
+    """csrc/nvls_group.cu directly: two threads stand in for two ranks (devices 0 and 1), rank 0 creates the multicast
+    object and hands it over as a file descriptor, both bind and map; then the in-switch all-reduce through that mapping
+    must equal the one-shot push variant and the mean computed on the host."""
+    import threading
+    import time
+
+    from distributed_neural_network_b200.ops import flat as L
+    from distributed_neural_network_b200.ops import native
+
+    world = 2
+    if not all(native.nvls_supported(d) for d in range(world)):
+        pytest.skip("NVLink multicast is not exposed on this host")
+    groups, engines = [], []
+    for d in range(world):
+        with torch.cuda.device(d):
+            groups.append(native.Group(d, world))
+    native.Group.connect_local(groups)
+    for d in range(world):
+        with torch.cuda.device(d):
+            p = torch.zeros(L.FLAT_NUMEL, device=f"cuda:{d}")
+            e = native.Engine(p, torch.zeros_like(p), None, 16, 0.01, 0.9, precision="fp32")
+            e.attach_group(groups[d])
+            e.set_membership((1 << world) - 1, timeout_ns=5_000_000_000)
+            torch.cuda.synchronize(d)
+            engines.append(e)
+    name = f"test-{os.getpid()}-{time.time_ns():x}"
+    gen = torch.Generator().manual_seed(77)
+    xs = [torch.randn(L.FLAT_NUMEL, generator=gen) for _ in range(world)]
+    bar = threading.Barrier(world)
+    out, errs, made = {}, [], {}
+
+    def run(r):
+        try:
+            with torch.cuda.device(r):
+                g = native.NvlsGroup(r, world, r, native.NVLS_FLOATS * 4, name, 20.0)
+                made[r] = g
+                bar.wait(30)                       # every device has been added
+                g.map()
+                bar.wait(30)                       # every rank has bound its memory
+                assert g.nbytes >= native.NVLS_FLOATS * 4 and g.local_ptr and g.multicast_ptr
+                engines[r].attach_nvls(g, g.multicast_ptr)
+                x = xs[r].cuda(r)
+                y_one, y_nvls = torch.zeros_like(x), torch.zeros_like(x)
+                for _ in range(3):                 # both parities, flag reuse
+                    engines[r].allreduce(x, y_one, mode=0, two_shot="one-shot")
+                    engines[r].allreduce(x, y_nvls, mode=0, two_shot="nvls")
+                torch.cuda.synchronize(r)
+                out[r] = (y_one.cpu(), y_nvls.cpu(), int(engines[r].read_ctl().status))
+                bar.wait(30)
+        except Exception as e:                     # noqa: BLE001 -- reported below, the other thread must not wait
+            errs.append((r, repr(e)))
+            bar.abort()
+
+    threads = [threading.Thread(target=run, args=(r,)) for r in range(world)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(120)
+    for e in engines:
+        e.close()
+    for g in made.values():
+        g.close()
+    for g in groups:
+        g.close()
+    assert not errs, errs
+    want = torch.stack([x.double() for x in xs]).mean(0)
+    for r in range(world):
+        y_one, y_nvls, status = out[r]
+        assert status == 0
+        assert (y_one.double() - want).abs().max() < 1e-6 and (y_nvls.double() - want).abs().max() < 1e-6
+    assert torch.equal(out[0][1], out[1][1]), "NVLS result differs between ranks"

@@ -270,3 +270,24 @@ def test_autograd_step_path_world2_equals_fused_semantics(tmp_path):
     b = _launch(2, tmp_path / "autograd", "step-allreduce", step_path="autograd", **kw)
     assert torch.equal(b[0]["flat"], b[1]["flat"])
     assert torch.allclose(a[0]["flat"], b[0]["flat"], atol=2e-6)
+
+
+def test_share_fd_hands_a_descriptor_from_rank0_to_every_process(tmp_path):
+    """The rendezvous under the NVLS group (csrc/nvls_group.cu): SCM_RIGHTS over an abstract Unix socket. The clients
+    start BEFORE the server here, so the connect retry is exercised too; a missing rank must end in a timeout error."""
+    import time as _time
+    from distributed_neural_network_b200.ops import native
+    if not native.available():
+        pytest.skip("native runtime not built")
+    secret = tmp_path / "secret.txt"
+    secret.write_text("handed over by the kernel")
+    name = f"t-{os.getpid()}-{_time.time_ns():x}"
+    worker = str(Path(__file__).parent / "_mp_sharefd_worker.py")
+    procs = [subprocess.Popen([sys.executable, worker, str(r), "3", name, str(secret), str(tmp_path)]) for r in (2, 1)]
+    _time.sleep(0.3)
+    procs.append(subprocess.Popen([sys.executable, worker, "0", "3", name, str(secret), str(tmp_path)]))
+    assert [p.wait(timeout=120) for p in procs] == [0, 0, 0]
+    for r in range(3):
+        assert (tmp_path / f"rank{r}.txt").read_text() == "c0ffee True handed over by the kernel"
+    with pytest.raises(RuntimeError, match="did not get the descriptor"):
+        native.share_fd(1, 2, name + "-nobody", timeout_s=0.2)
