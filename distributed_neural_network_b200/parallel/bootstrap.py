@@ -44,6 +44,10 @@ def discover() -> Tuple[int, int, int]:
     return rank, world, (local if local is not None else rank)
 
 
+class PeerLost(RuntimeError):
+    """A control-plane collective could not complete: some rank is gone (process died, host unreachable)."""
+
+
 class Comm:
     """Control-plane communicator: object all-gather / broadcast, barrier, CPU tensor all-reduce."""
 
@@ -101,10 +105,16 @@ class _MpiComm(Comm):
 class _TorchComm(Comm):
     provider = "torch.distributed"
 
-    def __init__(self, rank: int, world: int, local_rank: int, timeout_s: float = 600.0):
+    def __init__(self, rank: int, world: int, local_rank: int, timeout_s: Optional[float] = None):
         import torch
         import torch.distributed as dist
 
+        # How long a control-plane collective waits for a rank that has really died (not the simulated failures, which
+        # keep answering): the reference waits for ever in MPI recv (data_parallelism_train.py:118,135); here the
+        # survivors get a PeerLost error after DNNB200_COMM_TIMEOUT_S (default 600 s) instead of hanging.
+        if timeout_s is None:
+            timeout_s = float(os.environ.get("DNNB200_COMM_TIMEOUT_S", "600"))
+        self.timeout_s = timeout_s
         self._dist = dist
         self.rank, self.world, self.local_rank = rank, world, local_rank
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -116,26 +126,34 @@ class _TorchComm(Comm):
             dist.init_process_group(backend=backend, init_method="env://", rank=rank, world_size=world,
                                     timeout=datetime.timedelta(seconds=timeout_s))
         # object traffic always goes over gloo: it must work with ranks that have left the GPU group
-        self._cpu_group = dist.new_group(backend="gloo") if dist.get_backend() != "gloo" else dist.group.WORLD
+        self._cpu_group = (dist.new_group(backend="gloo", timeout=datetime.timedelta(seconds=timeout_s))
+                           if dist.get_backend() != "gloo" else dist.group.WORLD)
+
+    def _guard(self, what: str, fn):
+        try:
+            return fn()
+        except RuntimeError as e:        # DistBackendError and gloo's own errors are RuntimeErrors
+            raise PeerLost(f"control plane: {what} on rank {self.rank} of {self.world} failed or timed out after "
+                           f"{self.timeout_s:.0f} s -- a rank has died or hangs ({str(e).splitlines()[0][:200]})") from e
 
     def barrier(self):
-        self._dist.barrier(group=self._cpu_group)
+        self._guard("barrier", lambda: self._dist.barrier(group=self._cpu_group))
 
     def allgather(self, obj):
         out: List[Any] = [None] * self.world
-        self._dist.all_gather_object(out, obj, group=self._cpu_group)
+        self._guard("all-gather", lambda: self._dist.all_gather_object(out, obj, group=self._cpu_group))
         return out
 
     def bcast(self, obj, root=0):
         box = [obj]
-        self._dist.broadcast_object_list(box, src=root, group=self._cpu_group)
+        self._guard("broadcast", lambda: self._dist.broadcast_object_list(box, src=root, group=self._cpu_group))
         return box[0]
 
     def allreduce_sum_(self, t):
         if t.is_cuda:
-            self._dist.all_reduce(t)
+            self._guard("all-reduce", lambda: self._dist.all_reduce(t))
         else:
-            self._dist.all_reduce(t, group=self._cpu_group)
+            self._guard("all-reduce", lambda: self._dist.all_reduce(t, group=self._cpu_group))
         return t
 
     def close(self):

@@ -618,6 +618,26 @@ class Trainer:
 
     # ------------------------------------------------------------------ the whole run
     def fit(self, shard: Optional[D.TensorDataset] = None, test: Optional[D.TensorDataset] = None) -> List[Dict]:
+        """Trains ``cfg.epochs`` epochs. A rank that is really gone (process dead, not the simulated failure) ends the
+        job on the survivors with ``bootstrap.PeerLost`` instead of the reference's endless recv
+        (data_parallelism_train.py:118,135); with ``cfg.save`` set each survivor first writes what it has to
+        ``<save>.peerlost.rank<r>`` (epoch = last completed one), which ``--resume`` accepts."""
+        try:
+            return self._fit(shard, test)
+        except bootstrap.PeerLost as e:
+            self._log(f"Process {self.rank}: {e}")
+            if self.cfg.save:
+                done = self.history[-1]["epoch"] if self.history else self.start_epoch - 1
+                path = f"{self.cfg.save}.peerlost.rank{self.rank}"
+                try:
+                    self._sync()
+                    ckpt.save(path, self.model, self.momentum, epoch=done, membership_epoch=self.membership.epoch)
+                    self._log(f"Process {self.rank}: state after epoch {done} saved to {path}")
+                except Exception as save_err:  # noqa: BLE001 -- the PeerLost is what the caller must see
+                    self._log(f"Process {self.rank}: could not save {path}: {save_err}")
+            raise
+
+    def _fit(self, shard: Optional[D.TensorDataset] = None, test: Optional[D.TensorDataset] = None) -> List[Dict]:
         cfg = self.cfg
         if shard is None and test is None:
             shard, test = self.load_data()

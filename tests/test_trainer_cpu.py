@@ -291,3 +291,45 @@ def test_share_fd_hands_a_descriptor_from_rank0_to_every_process(tmp_path):
         assert (tmp_path / f"rank{r}.txt").read_text() == "c0ffee True handed over by the kernel"
     with pytest.raises(RuntimeError, match="did not get the descriptor"):
         native.share_fd(1, 2, name + "-nobody", timeout_s=0.2)
+
+
+def test_a_rank_that_really_dies_ends_in_peer_lost_not_in_a_hang(tmp_path):
+    """the reference blocks for ever in recv when a process is gone. Here the control plane's collectives
+    carry a timeout (DNNB200_COMM_TIMEOUT_S) and surface PeerLost on the survivors."""
+    from distributed_neural_network_b200.parallel import launch
+    out = tmp_path / "verdict.txt"
+    rc = launch.spawn(2, [sys.executable, str(Path(__file__).parent / "_mp_peerlost_worker.py"), str(out)],
+                      env_extra={"DNNB200_COMM_TIMEOUT_S": "5", "CUDA_VISIBLE_DEVICES": ""}, gpus=0)
+    assert rc == 0
+    verdict = out.read_text()
+    assert verdict.startswith("PeerLost after"), verdict
+    assert float(verdict.split()[2].rstrip("s:")) < 30.0, verdict
+
+
+def test_fit_saves_what_it_has_when_a_peer_is_lost(tmp_path):
+    """Trainer.fit on PeerLost: emergency checkpoint named after the rank, epoch = last completed, error re-raised;
+    the file resumes like any other checkpoint."""
+    save = str(tmp_path / "ck.pt")
+    cfg = TrainConfig(device="cpu", synthetic=True, train_size=64, test_size=32, epochs=3, batch_size=16, quiet=True,
+                      sync_mode="none", seed=2, save=save, log_dir=str(tmp_path / "log"))
+    tr = Trainer(cfg)
+    calls = {"n": 0}
+    real = tr.comm.allgather
+
+    def flaky(obj):
+        calls["n"] += 1
+        if len(tr.history) == 1 and isinstance(obj, tuple):      # the loss bookkeeping of the SECOND epoch
+            raise bootstrap.PeerLost("control plane: all-gather failed (test)")
+        return real(obj)
+
+    tr.comm.allgather = flaky
+    with pytest.raises(bootstrap.PeerLost):
+        tr.fit()
+    lost = Path(save + ".peerlost.rank0")
+    assert lost.exists() and len(tr.history) == 1
+    after = tr.model.flat_params.detach().clone()
+    tr.close()
+    tr2 = Trainer(TrainConfig(device="cpu", synthetic=True, train_size=64, test_size=32, epochs=3, batch_size=16,
+                              quiet=True, sync_mode="none", seed=2, resume=str(lost), log_dir=str(tmp_path / "log2")))
+    assert tr2.start_epoch == 1 and torch.equal(tr2.model.flat_params.detach(), after)
+    tr2.close()
