@@ -9,3 +9,5 @@ do
     "$MPIEXEC" -n $np python data_parallelism_train.py --nb-proc $np --batch-size $bs "$@"
   done
 done
+# the two tables of the reference's project report (process sweep, batch-size sweep) from the files just written
+python -m distributed_neural_network_b200.utils.report "${LOG_DIR:-log}" --topology symmetric

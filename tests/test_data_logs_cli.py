@@ -137,3 +137,42 @@ def test_checkpoint_is_reference_format_and_resumes_exactly(tmp_path, reference_
     m2, mom2 = Network(), torch.zeros(L.FLAT_NUMEL)
     meta = ckpt.load(path, m2, mom2)
     assert meta["epoch"] == 3 and torch.equal(m2.flat_params, m.flat_params) and torch.equal(mom2, mom)
+
+
+def test_sweep_report_reproduces_the_reference_tables(tmp_path):
+    """utils/report.py on timing files with the reference's committed values (log_epochs25_proc{3,8}_*, bs{1,64}_...proc4,
+    SURVEY section 6.2): same derived throughput, the un-prefixed and the bs16_ run of 4 processes kept apart."""
+    from distributed_neural_network_b200.utils import report
+
+    def put(name, a, b, c, labels):
+        (tmp_path / name).write_text("".join(f"{lab}: {v}\n" for lab, v in zip(labels, (a, b, c))))
+
+    ch = ("Train data loading time", "Time spent on training", "Time spent on children communication")
+    pa = ("Eval data loading time", "Time spent on evaluation", "Time spent on parent communication and param sync")
+    put("log_epochs25_proc3_children.txt", 4.27, 316.52, 0.161, ch)
+    put("log_epochs25_proc3_parent.txt", 1.94, 56.45, 0.179, pa)
+    put("log_epochs25_proc8_children.txt", 18.52, 1566.32, 0.694, ch)
+    put("log_epochs25_proc8_parent.txt", 7.75, 58.00, 0.778, pa)
+    put("log_epochs25_proc4_children.txt", 6.19, 734.60, 0.235, ch)
+    put("log_epochs25_proc4_parent.txt", 2.57, 56.74, 0.255, pa)
+    put("bs16_log_epochs25_proc4_children.txt", 6.31, 701.82, 0.240, ch)
+    put("bs16_log_epochs25_proc4_parent.txt", 2.54, 56.69, 0.227, pa)
+    put("bs1_log_epochs25_proc4_children.txt", 6.07, 1167.29, 0.166, ch)
+    put("bs1_log_epochs25_proc4_parent.txt", 2.57, 158.62, 0.282, pa)
+    (tmp_path / "notes.txt").write_text("not a timing file\n")
+    rows = report.read_logs(str(tmp_path))
+    assert len(rows) == 5
+    for r in rows.values():
+        report.derive(r, 50000, "reference")
+    t1, t2 = report.tables(rows)
+    assert [r.nb_proc for r in t1] == [3, 4, 8] and not t1[1].bs_in_name
+    assert round(t1[0].img_per_s_aggregate) == 3949 and round(t1[2].img_per_s_aggregate) == 798
+    assert round(t1[0].comm_ms_per_epoch_child, 1) == 6.4 and round(t1[2].comm_ms_per_epoch_parent, 1) == 31.1
+    assert abs(t1[0].total_s - (316.52 + 56.45 + 4.27 + 1.94)) < 1e-9
+    assert list(t2) == [4] and [r.batch_size for r in t2[4]] == [1, 16] and t2[4][1].bs_in_name
+    assert round(t2[4][0].img_per_s_aggregate) == 1071 and round(t2[4][1].img_per_s_aggregate) == 1781
+    sym = report.derive(report.RunRow(nb_proc=8, batch_size=16, epochs=5, train_s=10.0), 50000, "symmetric")
+    assert sym.images_per_trainer_epoch == 6250 and round(sym.img_per_s_aggregate) == 25000
+    text = report.render(str(tmp_path))
+    assert "Table 1" in text and "Table 2" in text and "| 3 | 316.52 | 56.45 |" in text
+    assert report.main([str(tmp_path), "--json"]) == 0
