@@ -9,6 +9,7 @@ a per-epoch JSONL of this framework lies next to them, accuracy, loss and the de
 
     python -m distributed_neural_network_b200.utils.report log/            # markdown on stdout
     python -m distributed_neural_network_b200.utils.report log/ --json     # the rows as JSON
+    python -m distributed_neural_network_b200.utils.report log/ --svg curves.svg   # + accuracy / loss curves (Fig. 1 / 2)
 
 Shard sizes follow the topology that wrote the files: ``--topology reference`` (rank 0 does not train, P-1 shards of
 ``train_size // (P-1)`` images, reference :49-53) or ``symmetric`` (all P ranks train ``train_size // P``; the default
@@ -175,13 +176,87 @@ def render(log_dir: str, train_size: int = 50000, topology: str = "reference") -
     return "\n".join(parts)
 
 
+# ---------------------------------------------------------------------------
+# Figures 1 / 2 of the reference's report: validation accuracy and loss per epoch. No plotting package on the box,
+# so the curves are written as a small stand-alone SVG.
+# ---------------------------------------------------------------------------
+_COLOURS = ("#1f77b4", "#d62728", "#2ca02c", "#9467bd", "#ff7f0e", "#8c564b", "#17becf", "#7f7f7f")
+
+
+def read_curves(paths: List[str]) -> Dict[str, List[dict]]:
+    """{label: per-epoch records} of the given JSONL files (label = file name without the extension)."""
+    curves: Dict[str, List[dict]] = {}
+    for path in paths:
+        recs = []
+        with open(path) as f:
+            for line in f:
+                line = line.strip()
+                if line:
+                    rec = json.loads(line)
+                    if "epoch" in rec:
+                        recs.append(rec)
+        if recs:
+            curves[os.path.splitext(os.path.basename(path))[0]] = sorted(recs, key=lambda r: r["epoch"])
+    return curves
+
+
+def _panel(x0: float, y0: float, w: float, h: float, title: str, series: Dict[str, List[Tuple[float, float]]]) -> List[str]:
+    pts = [p for s in series.values() for p in s]
+    if not pts:
+        return []
+    xmin, xmax = min(p[0] for p in pts), max(p[0] for p in pts)
+    ymin, ymax = min(p[1] for p in pts), max(p[1] for p in pts)
+    if xmax == xmin:
+        xmax = xmin + 1
+    if ymax == ymin:
+        ymax = ymin + 1
+    pad = 0.05 * (ymax - ymin)
+    ymin, ymax = ymin - pad, ymax + pad
+    sx = lambda x: x0 + (x - xmin) / (xmax - xmin) * w          # noqa: E731
+    sy = lambda y: y0 + h - (y - ymin) / (ymax - ymin) * h      # noqa: E731
+    out = [f'<rect x="{x0:.1f}" y="{y0:.1f}" width="{w:.1f}" height="{h:.1f}" fill="none" stroke="#444"/>',
+           f'<text x="{x0 + w / 2:.1f}" y="{y0 - 8:.1f}" text-anchor="middle" font-size="13">{title}</text>']
+    for k in range(5):
+        yv = ymin + (ymax - ymin) * k / 4
+        out.append(f'<line x1="{x0:.1f}" y1="{sy(yv):.1f}" x2="{x0 + w:.1f}" y2="{sy(yv):.1f}" stroke="#ddd"/>')
+        out.append(f'<text x="{x0 - 6:.1f}" y="{sy(yv) + 4:.1f}" text-anchor="end" font-size="10">{yv:.3g}</text>')
+    for xv in sorted({int(round(xmin + (xmax - xmin) * k / 4)) for k in range(5)}):
+        out.append(f'<text x="{sx(xv):.1f}" y="{y0 + h + 14:.1f}" text-anchor="middle" font-size="10">{xv}</text>')
+    out.append(f'<text x="{x0 + w / 2:.1f}" y="{y0 + h + 30:.1f}" text-anchor="middle" font-size="11">epoch</text>')
+    for i, (label, s) in enumerate(series.items()):
+        colour = _COLOURS[i % len(_COLOURS)]
+        path = " ".join(f"{sx(x):.1f},{sy(y):.1f}" for x, y in s)
+        out.append(f'<polyline points="{path}" fill="none" stroke="{colour}" stroke-width="1.8"/>')
+        out.append(f'<text x="{x0 + 8:.1f}" y="{y0 + 16 + 14 * i:.1f}" font-size="11" fill="{colour}">{label}</text>')
+    return out
+
+
+def curves_svg(curves: Dict[str, List[dict]]) -> str:
+    """Validation accuracy (left) and validation + training loss (right) against the epoch, one line per run."""
+    acc = {k: [(r["epoch"], r["val_acc"]) for r in v if r.get("val_acc") is not None] for k, v in curves.items()}
+    loss: Dict[str, List[Tuple[float, float]]] = {}
+    for k, v in curves.items():
+        loss[f"{k} val"] = [(r["epoch"], r["val_loss"]) for r in v if r.get("val_loss") is not None]
+        loss[f"{k} train"] = [(r["epoch"], r["train_loss"]) for r in v if r.get("train_loss") is not None]
+    body = _panel(60, 40, 380, 260, "validation accuracy (%)", {k: s for k, s in acc.items() if s})
+    body += _panel(520, 40, 380, 260, "loss", {k: s for k, s in loss.items() if s})
+    return ('<svg xmlns="http://www.w3.org/2000/svg" width="940" height="350" font-family="sans-serif">'
+            '<rect width="100%" height="100%" fill="white"/>' + "".join(body) + "</svg>\n")
+
+
 def main(argv: Optional[List[str]] = None) -> int:
     ap = argparse.ArgumentParser(description=__doc__.split("\n\n")[0])
     ap.add_argument("log_dir")
     ap.add_argument("--train-size", type=int, default=50000)
     ap.add_argument("--topology", choices=("reference", "symmetric"), default="reference")
     ap.add_argument("--json", action="store_true", help="print the rows as JSON instead of markdown")
+    ap.add_argument("--svg", metavar="FILE", help="also write accuracy / loss curves of every *.jsonl in log_dir (the "
+                                                  "report's Fig. 1 / 2) to FILE")
     a = ap.parse_args(argv)
+    if a.svg:
+        curves = read_curves([os.path.join(a.log_dir, n) for n in sorted(os.listdir(a.log_dir)) if n.endswith(".jsonl")])
+        with open(a.svg, "w") as f:
+            f.write(curves_svg(curves))
     if a.json:
         rows = read_logs(a.log_dir)
         for r in rows.values():

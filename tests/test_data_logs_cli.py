@@ -176,3 +176,23 @@ def test_sweep_report_reproduces_the_reference_tables(tmp_path):
     text = report.render(str(tmp_path))
     assert "Table 1" in text and "Table 2" in text and "| 3 | 316.52 | 56.45 |" in text
     assert report.main([str(tmp_path), "--json"]) == 0
+
+
+def test_report_writes_accuracy_and_loss_curves_as_svg(tmp_path):
+    """The report's Fig. 1 / 2 from the per-epoch JSONL, as a stand-alone SVG (no plotting package on the box)."""
+    import json
+    import xml.dom.minidom
+
+    from distributed_neural_network_b200.utils import report
+    for name, shift in (("dp4_bs16", 0.0), ("dp8_bs16", 3.0)):
+        with open(tmp_path / f"{name}.jsonl", "w") as f:
+            for e in range(6):
+                f.write(json.dumps({"epoch": e, "train_loss": 2.3 - 0.2 * e, "val_loss": 2.2 - 0.18 * e,
+                                    "val_acc": 10 + 9 * e - shift}) + "\n")
+    curves = report.read_curves(sorted(str(p) for p in tmp_path.glob("*.jsonl")))
+    assert list(curves) == ["dp4_bs16", "dp8_bs16"] and len(curves["dp4_bs16"]) == 6
+    out = tmp_path / "curves.svg"
+    assert report.main([str(tmp_path), "--svg", str(out)]) == 0
+    doc = xml.dom.minidom.parse(str(out))
+    assert len(doc.getElementsByTagName("polyline")) == 2 + 4        # accuracy per run; val + train loss per run
+    assert "validation accuracy" in out.read_text()
