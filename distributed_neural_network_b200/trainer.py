@@ -157,6 +157,7 @@ class Trainer:
         self.first_step = True
         self.nvls_ok = False
         self._nvls_probed = False
+        self.ll128_ok = False                           # 128-byte lines arrive whole on this job's links (probed below)
         self._utrace: Optional[torch.Tensor] = None
         self._averager = None                           # autograd path: per-bucket exchange overlapped with backward
         self.last_exchange_us: Optional[float] = None  # median exposed exchange per step over the epoch's last steps
@@ -179,6 +180,7 @@ class Trainer:
                     self.nvls_ok = True
                 self._nvls_probed = True
                 self._apply_membership()
+                self.ll128_ok = self._probe_ll128()
         self.failure = FailureSimulator(cfg.failure_probability, cfg.failure_duration, cfg.failure_mode, cfg.seed,
                                         self.rank)
         self.dropped = False
@@ -214,11 +216,27 @@ class Trainer:
     def _can_drop(self) -> bool:
         return self.cfg.failure_mode == "drop" and self.cfg.failure_probability > 0
 
+    def _probe_ll128(self, iters: int = 300, n_ctas: int = 8) -> bool:
+        """The one-shot-128 exchange relies on a warp-wide 128-byte store becoming visible in a peer's memory as a
+        unit (31 values + 1 flag word; tests/test_protocol_model.py shows what goes wrong otherwise). Ranks pair up
+        (0-1, 2-3, ...) and play ping-pong with such lines; one torn line anywhere, or a pair that did not finish,
+        and the variant is not offered to this job. Collective."""
+        ok = self.world <= 8
+        peer = self.rank ^ 1
+        self.comm.barrier()
+        if ok and peer < self.world:
+            try:
+                torn, _, gave_up = self.engine.ll128_probe(peer, iters=iters, n_ctas=n_ctas)
+                ok = torn == 0 and not gave_up
+            except RuntimeError:
+                ok = False
+        return all(self.comm.allgather(ok))
+
     def _usable_variants(self) -> List[str]:
         """Exchange variants this run may use. The one-shot forms tolerate ranks leaving mid-epoch (leave markers);
         two-shot has static slice ownership and the NVSwitch adds EVERY member of the multicast group, so both need
         a membership that cannot change (no drop-mode failure drill, every rank a stepping trainer for NVLS)."""
-        names = ["one-shot"] + (["one-shot-128"] if self.world <= 8 else [])   # (the 128-byte-line form parks 7 peers' lines)
+        names = ["one-shot"] + (["one-shot-128"] if self.world <= 8 and self.ll128_ok else [])   # (parks 7 peers' lines)
         if not self._can_drop():
             names.append("two-shot")
             if self.nvls_ok and len(self.membership.active) == self.world:

@@ -22,7 +22,8 @@ def main():
         Path(os.environ["DNNB200_PROVIDER_PROBE"] + f".{tr.rank}").write_text(tr.comm.provider)
     hist = tr.fit()
     torch.save({"flat": tr.model.flat_params.detach().cpu(), "history": hist, "rank": tr.rank,
-                "timers": tr.timers.__dict__, "exchange_table": tr.exchange_table}, f"{out_dir}/rank{tr.rank}.pt")
+                "timers": tr.timers.__dict__, "exchange_table": tr.exchange_table,
+                "ll128_ok": tr.ll128_ok, "variant": tr._exchange_variant() if tr.world > 1 else 0}, f"{out_dir}/rank{tr.rank}.pt")
     tr.close()
     tr.comm.close()
 

@@ -121,6 +121,8 @@ def test_ipc_one_shot_128_trains_the_same_bits_as_one_shot(tmp_path):
     b = _launch(n, tmp_path / "ll128", "step-allreduce", allreduce_variant="one-shot-128", **kw)
     for r in range(n):
         assert torch.equal(a[0]["flat"], b[r]["flat"])
+        # ... and the second run really used the 128-byte lines: the start-up probe found them whole on these links
+        assert b[r]["ll128_ok"] and b[r]["variant"] == 3 and a[r]["variant"] == 0
 
 
 @needs2

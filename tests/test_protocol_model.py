@@ -333,3 +333,92 @@ def test_chained_step_model_fails_without_the_counter_wait():
         except AssertionError:
             failures += 1
     assert failures > 0
+
+
+# ---------------------------------------------------------------------------------------------------------
+# One-shot with 128-byte lines (exchange.cuh, variant 3): a line is 31 values and ONE flag word, written by one
+# warp-wide store and read by one warp-wide load. What the variant assumes of the hardware is that such a store
+# becomes visible in the peer's memory as a unit (tests/test_gpu_multiproc.py::test_ll128_lines_are_never_torn hammers
+# exactly that over NVLink). The model states the assumption and shows what breaks without it.
+# ---------------------------------------------------------------------------------------------------------
+LINE_VALUES = 3        # values per line in the model (31 in the kernel)
+
+
+def rank_program_lines(w, r, atomic_lines, rng):
+    """recv128[p][parity][src][line] = [v0, .., v_{n-1}, flag]; jobs (line, peer) are polled in any order."""
+    W = w.W
+    for step in range(w.steps):
+        seq = step + 1
+        parity = seq & 1
+        for line in range(S):
+            words = [payload(r, step, line) + 0.1 * k for k in range(LINE_VALUES)] + [seq]
+            for p in range(W):
+                if p == r:
+                    continue
+                dst = w.recv128[p][parity][r][line]
+                if atomic_lines:
+                    dst[:] = words
+                    yield
+                else:                                   # a fabric that delivers the words of a line one by one, any order
+                    for k in rng.sample(range(len(words)), len(words)):
+                        dst[k] = words[k]
+                        yield
+        jobs = [(line, q) for line in range(S) for q in range(W) if q != r]
+        got = {}
+        while jobs:
+            for job in list(jobs):
+                line, q = job
+                snap = list(w.recv128[r][parity][q][line])      # one warp-wide load: a snapshot of the whole line
+                yield
+                if snap[-1] == seq:
+                    got[job] = snap[:-1]
+                    jobs.remove(job)
+        for line in range(S):
+            for k in range(LINE_VALUES):
+                total = 0.0
+                for q in range(W):                              # rank order, own contribution at its position
+                    total += payload(r, step, line) + 0.1 * k if q == r else got[(line, q)][k]
+                w.results[(r, step, line, k)] = total
+
+
+def _run_lines(W, steps, seed, atomic_lines):
+    rng = random.Random(seed)
+    w = World(W, steps, {})
+    w.recv128 = [[[[[0.0] * LINE_VALUES + [0] for _ in range(S)] for _ in range(W)] for _ in range(2)] for _ in range(W)]
+    progs = {r: rank_program_lines(w, r, atomic_lines, rng) for r in range(W)}
+    budget = 2_000_000
+    while progs:
+        r = rng.choice(list(progs))
+        for _ in range(rng.choice((1, 1, 2, 5, 40))):
+            try:
+                next(progs[r])
+            except StopIteration:
+                del progs[r]
+                break
+            budget -= 1
+            assert budget > 0, "livelock"
+    for step in range(steps):
+        for line in range(S):
+            for k in range(LINE_VALUES):
+                want = sum(payload(q, step, line) + 0.1 * k for q in range(W))
+                for r in range(W):
+                    assert abs(w.results[(r, step, line, k)] - want) < 1e-9, (r, step, line, k)
+
+
+@pytest.mark.parametrize("W", [2, 4, 8])
+def test_128_byte_lines_with_one_flag_word_agree_when_lines_arrive_whole(W):
+    for seed in range(40):
+        _run_lines(W, steps=5, seed=seed, atomic_lines=True)
+
+
+def test_128_byte_lines_need_lines_that_arrive_whole():
+    """Negative control: if the words of a line could arrive separately, a reader that sees this step's flag word may
+    still see last-but-one step's values next to it -- the sums go wrong. This is why the variant is only enabled
+    after the probe kernel has found no torn line on the actual links."""
+    broken = 0
+    for seed in range(40):
+        try:
+            _run_lines(3, steps=6, seed=seed, atomic_lines=False)
+        except AssertionError:
+            broken += 1
+    assert broken > 0
