@@ -333,3 +333,86 @@ def test_fit_saves_what_it_has_when_a_peer_is_lost(tmp_path):
                               quiet=True, sync_mode="none", seed=2, resume=str(lost), log_dir=str(tmp_path / "log2")))
     assert tr2.start_epoch == 1 and torch.equal(tr2.model.flat_params.detach(), after)
     tr2.close()
+
+
+class _ThreadComm:
+    """Control plane for ranks that are threads of this process (tests of collective choreography)."""
+
+    def __init__(self, rank, world, shared):
+        self.rank, self.world, self.local_rank, self._s = rank, world, rank, shared
+
+    def allgather(self, obj):
+        s = self._s
+        s["slots"][self.rank] = obj
+        s["bar"].wait(30)
+        out = list(s["slots"])
+        s["bar"].wait(30)
+        return out
+
+    def bcast(self, obj, root=0):
+        return self.allgather(obj)[root]
+
+    def barrier(self):
+        self.allgather(None)
+
+
+def _run_nvls_choreography(monkeypatch, world, hosts, fail_open=(), fail_map=()):
+    import threading
+
+    from distributed_neural_network_b200.ops import native
+    from distributed_neural_network_b200.parallel import nvls
+    events, lock = [], threading.Lock()
+
+    class FakeGroup:
+        def __init__(self, rank, world_, idx, nbytes, name, timeout_s):
+            if rank in fail_open:
+                raise RuntimeError(f"open failed on {rank}")
+            self.rank, self.name, self.multicast_ptr, self.nbytes = rank, name, 0, nbytes
+            with lock:
+                events.append(("open", rank))
+
+        def map(self):
+            if self.rank in fail_map:
+                raise RuntimeError(f"map failed on {self.rank}")
+            with lock:
+                events.append(("map", self.rank))
+            self.multicast_ptr = 0xABC000
+            return 0x123000, self.multicast_ptr
+
+        def close(self):
+            with lock:
+                events.append(("close", self.rank))
+
+    monkeypatch.setattr(native, "NvlsGroup", FakeGroup)
+    monkeypatch.setattr(native, "nvls_supported", lambda idx: True)
+    shared = {"slots": [None] * world, "bar": threading.Barrier(world)}
+    names = iter(hosts)
+    host_of = {r: next(names) for r in range(world)}
+    monkeypatch.setattr(nvls.socket, "gethostname", lambda: host_of[int(threading.current_thread().name)])
+    out = {}
+
+    def run(r):
+        out[r] = nvls.try_create(torch.device("cuda", r), _ThreadComm(r, world, shared))
+
+    ts = [threading.Thread(target=run, args=(r,), name=str(r)) for r in range(world)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(60)
+    return out, events
+
+
+def test_nvls_group_is_made_by_all_ranks_or_by_nobody(monkeypatch):
+    """parallel/nvls.py: every rank opens, THEN every rank maps (the driver refuses to bind before all devices are in);
+    one failure anywhere and every rank closes what it has and reports 'no NVLS'; ranks on two hosts do not even try."""
+    out, ev = _run_nvls_choreography(monkeypatch, 4, ["a"] * 4)
+    assert all(o is not None and o[1] == 0xABC000 for o in out.values())
+    assert len({o[0].name for o in out.values()}) == 1                         # one job-unique name, from rank 0
+    assert max(i for i, e in enumerate(ev) if e[0] == "open") < min(i for i, e in enumerate(ev) if e[0] == "map")
+    out, ev = _run_nvls_choreography(monkeypatch, 4, ["a"] * 4, fail_open={2})
+    assert all(o is None for o in out.values())
+    assert sorted(e for e in ev if e[0] == "close") == [("close", 0), ("close", 1), ("close", 3)] and not [e for e in ev if e[0] == "map"]
+    out, ev = _run_nvls_choreography(monkeypatch, 3, ["a"] * 3, fail_map={0})
+    assert all(o is None for o in out.values()) and sorted(e for e in ev if e[0] == "close") == [("close", r) for r in range(3)]
+    out, ev = _run_nvls_choreography(monkeypatch, 2, ["a", "b"])
+    assert all(o is None for o in out.values()) and ev == []
