@@ -25,7 +25,7 @@ from ..ops import native
 last_error: str = ""      # why the last try_create on this rank returned None ("" = it did not, or another rank failed)
 
 
-def try_create(device: torch.device, comm, timeout_s: float = 30.0) -> Optional[Tuple["native.NvlsGroup", int]]:
+def try_create(device: torch.device, comm, timeout_s: float = 10.0) -> Optional[Tuple["native.NvlsGroup", int]]:
     """(group, multicast pointer) or None. Collective: every rank of ``comm`` must call it."""
     global last_error
     last_error = ""
