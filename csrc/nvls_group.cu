@@ -98,6 +98,20 @@ const DriverApi& driver() {
     }                                                                                                   \
   } while (0)
 
+// The calls below work on the group's device and leave the caller's current device as they found it.
+struct DeviceScope {
+  int prev = -1;
+  explicit DeviceScope(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { prev = -1; cudaGetLastError(); }
+    if (prev != dev) cudaSetDevice(dev);
+  }
+  ~DeviceScope() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+  DeviceScope(const DeviceScope&) = delete;
+  DeviceScope& operator=(const DeviceScope&) = delete;
+};
+
 int64_t now_ms() {
   timespec ts;
   clock_gettime(CLOCK_MONOTONIC, &ts);
@@ -248,7 +262,10 @@ int dnnb200_nvls_supported(int device) {
   if (!d.ok) return 0;
   CUdevice dev;
   int v = 0;
-  if (cudaSetDevice(device) != cudaSuccess || cudaFree(nullptr) != cudaSuccess) { cudaGetLastError(); return 0; }
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) { cudaGetLastError(); return 0; }
+  DeviceScope scope(device);
+  if (cudaFree(nullptr) != cudaSuccess) { cudaGetLastError(); return 0; }
   if (d.DeviceGet(&dev, device) != CUDA_SUCCESS) return 0;
   if (d.DeviceGetAttribute(&v, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, dev) != CUDA_SUCCESS) return 0;
   return v != 0;
@@ -261,7 +278,10 @@ int dnnb200_nvls_open(dnnb200_nvls** out, int rank, int world, int device, size_
   *out = nullptr;
   const DriverApi& d = driver();
   if (!d.ok) { set_last_error("nvls_open: this driver has no cuMulticast* entry points"); return kErrState; }
-  DNN_CUDA_CHECK(cudaSetDevice(device));
+  int count = 0;
+  DNN_CUDA_CHECK(cudaGetDeviceCount(&count));
+  DNN_ARG_CHECK(device >= 0 && device < count, "nvls_open: no device %d", device);
+  DeviceScope scope(device);
   DNN_CUDA_CHECK(cudaFree(nullptr));                       // make sure the primary context exists and is current
   dnnb200_nvls* g = new dnnb200_nvls;
   g->rank = rank; g->world = world; g->device = device;
@@ -328,7 +348,7 @@ int dnnb200_nvls_map(dnnb200_nvls* g, float** local, float** multicast, size_t* 
   DNN_ARG_CHECK(g && local && multicast, "nvls_map: null argument");
   DNN_ARG_CHECK(g->have_mc && !g->bound, "nvls_map: group is not open, or already mapped");
   const DriverApi& d = driver();
-  DNN_CUDA_CHECK(cudaSetDevice(g->device));
+  DeviceScope scope(g->device);
   CUmemAllocationProp ap;
   memset(&ap, 0, sizeof(ap));
   ap.type = CU_MEM_ALLOCATION_TYPE_PINNED;
@@ -364,7 +384,7 @@ int dnnb200_nvls_close(dnnb200_nvls* g) {
   if (!g) return kOk;
   const DriverApi& d = driver();
   if (d.ok) {
-    cudaSetDevice(g->device);
+    DeviceScope scope(g->device);
     cudaDeviceSynchronize();
     if (g->mc_mapped) d.MemUnmap(g->mc_va, g->bytes);
     if (g->mc_va) d.MemAddressFree(g->mc_va, g->bytes);
