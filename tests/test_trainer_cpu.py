@@ -416,3 +416,66 @@ def test_nvls_group_is_made_by_all_ranks_or_by_nobody(monkeypatch):
     assert all(o is None for o in out.values()) and sorted(e for e in ev if e[0] == "close") == [("close", r) for r in range(3)]
     out, ev = _run_nvls_choreography(monkeypatch, 2, ["a", "b"])
     assert all(o is None for o in out.values()) and ev == []
+
+
+def test_exchange_variants_offered_depend_on_probes_and_on_the_failure_mode():
+    """Trainer._usable_variants / _exchange_variant / _probe_ll128 without a GPU: the 128-byte lines need a passed probe
+    on EVERY rank, two-shot and NVLS a membership that cannot change, a forced variant that is not usable falls back to
+    the one that always is."""
+    from types import SimpleNamespace
+
+    from distributed_neural_network_b200.ops import native
+    from distributed_neural_network_b200.parallel.membership import Membership
+
+    def make(world=4, ll128=True, nvls=True, mode="sleep", p=0.0, variant="auto", choice=None, active=None):
+        t = Trainer.__new__(Trainer)
+        t.world, t.rank, t.ll128_ok, t.nvls_ok, t._nvls_probed = world, 0, ll128, nvls, True
+        t.cfg = TrainConfig(failure_mode=mode, failure_probability=p, allreduce_variant=variant)
+        t.membership = Membership(world, active=set(active if active is not None else range(world)))
+        t.exchange_choice = choice
+        return t
+
+    assert make()._usable_variants() == ["one-shot", "one-shot-128", "two-shot", "nvls"]
+    assert make(ll128=False)._usable_variants() == ["one-shot", "two-shot", "nvls"]
+    assert make(nvls=False)._usable_variants() == ["one-shot", "one-shot-128", "two-shot"]
+    assert make(active=[1, 2, 3])._usable_variants() == ["one-shot", "one-shot-128", "two-shot"]     # a non-stepping parent
+    assert make(mode="drop", p=0.1)._usable_variants() == ["one-shot", "one-shot-128"]                # ranks may leave
+    assert make(world=9)._usable_variants()[:2] == ["one-shot", "two-shot"]
+    assert make(choice="two-shot")._exchange_variant() == native.variant_id("two-shot")
+    assert make(choice="two-shot", mode="drop", p=0.1)._exchange_variant() == native.variant_id("one-shot")
+    assert make(variant="one-shot-128", ll128=False)._exchange_variant() == native.variant_id("one-shot")
+    assert make(variant="one-shot-128")._exchange_variant() == 3
+    with pytest.raises(RuntimeError, match="multicast is not available"):
+        make(variant="nvls", nvls=False)._exchange_variant()
+
+    # the probe: pairs 0-1, 2-3; the odd rank out has no partner and passes; one torn line anywhere fails everybody
+    class Comm:
+        def __init__(self, verdicts):
+            self.verdicts = verdicts
+
+        def barrier(self):
+            pass
+
+        def allgather(self, ok):
+            return [ok] + self.verdicts
+
+    def probe(rank, world, result, others):
+        t = Trainer.__new__(Trainer)
+        t.world, t.rank, t.comm = world, rank, Comm(others)
+        calls = []
+
+        def ll128_probe(peer, iters, n_ctas):
+            calls.append(peer)
+            if isinstance(result, Exception):
+                raise result
+            return result
+        t.engine = SimpleNamespace(ll128_probe=ll128_probe)
+        return t._probe_ll128(), calls
+
+    assert probe(2, 4, (0, 3.1, False), [True] * 3) == (True, [3])
+    assert probe(0, 4, (5, 3.1, False), [True] * 3) == (False, [1])            # torn lines
+    assert probe(0, 4, (0, 3.1, True), [True] * 3) == (False, [1])             # the pair did not finish
+    assert probe(0, 4, RuntimeError("launch failed"), [True] * 3) == (False, [1])
+    assert probe(2, 3, (0, 3.1, False), [True] * 2) == (True, [])              # rank 2 of 3 has no partner
+    assert probe(0, 2, (0, 3.1, False), [False]) == (False, [1])               # the OTHER pair saw a torn line
+    assert probe(0, 16, (0, 3.1, False), [True] * 15) == (False, [])           # the variant parks at most 7 peers' lines
