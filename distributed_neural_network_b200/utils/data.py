@@ -12,7 +12,8 @@ B200-first differences: the whole dataset is materialised ONCE as two tensors
 host memory), batches are index views, and no DataLoader worker processes, pickling or
 per-sample transforms sit on the step path. There is no network on the build or the GPU
 box, so ``download=True`` is never attempted: real CIFAR-10 is used when
-``<root>/cifar-10-batches-py`` exists, otherwise a deterministic synthetic set of the
+``<root>/cifar-10-batches-py`` exists (or the binary version ``cifar-10-batches-bin``, or the
+undecompressed ``cifar-10-python.tar.gz``), otherwise a deterministic synthetic set of the
 same shape stands in (and the caller is told).
 """
 from __future__ import annotations
@@ -26,6 +27,8 @@ import numpy as np
 import torch
 
 CIFAR_DIR = "cifar-10-batches-py"
+CIFAR_BIN_DIR = "cifar-10-batches-bin"          # the dataset's "binary version"
+CIFAR_TARBALL = "cifar-10-python.tar.gz"        # what the reference's download leaves in ./data
 TRAIN_SIZE, TEST_SIZE = 50_000, 10_000
 
 
@@ -135,10 +138,47 @@ def _load_cifar_batches(root: str, train: bool) -> Optional[Tuple[np.ndarray, np
     return x, np.asarray(ys, dtype=np.int64)
 
 
+def _load_cifar_binary(root: str, train: bool) -> Optional[Tuple[np.ndarray, np.ndarray]]:
+    """The "binary version" of the dataset (``cifar-10-batches-bin``): records of 1 label byte + 3072 bytes CHW."""
+    d = os.path.join(root, CIFAR_BIN_DIR)
+    names = [f"data_batch_{i}.bin" for i in range(1, 6)] if train else ["test_batch.bin"]
+    if not all(os.path.exists(os.path.join(d, n)) for n in names):
+        return None
+    recs = [np.fromfile(os.path.join(d, n), dtype=np.uint8) for n in names]
+    for n, r in zip(names, recs):
+        if r.size == 0 or r.size % 3073 != 0:
+            raise ValueError(f"{os.path.join(d, n)}: size {r.size} is not a multiple of the 3073-byte record")
+    rec = np.concatenate(recs).reshape(-1, 3073)
+    x = rec[:, 1:].reshape(-1, 3, 32, 32).transpose(0, 2, 3, 1)     # NHWC uint8, as the pickled batches are held
+    return np.ascontiguousarray(x), rec[:, 0].astype(np.int64)
+
+
+def _load_cifar_tarball(root: str, train: bool) -> Optional[Tuple[np.ndarray, np.ndarray]]:
+    """``cifar-10-python.tar.gz`` as torchvision leaves it next to the extracted directory: read in place."""
+    path = os.path.join(root, CIFAR_TARBALL)
+    if not os.path.exists(path):
+        return None
+    import tarfile
+
+    names = [f"data_batch_{i}" for i in range(1, 6)] if train else ["test_batch"]
+    xs: List[np.ndarray] = []
+    ys: List[int] = []
+    with tarfile.open(path, "r:*") as tar:
+        members = {os.path.basename(m.name): m for m in tar.getmembers() if m.isfile()}
+        if not all(n in members for n in names):
+            return None
+        for n in names:
+            entry = pickle.load(tar.extractfile(members[n]), encoding="latin1")
+            xs.append(entry["data"])
+            ys.extend(entry.get("labels", entry.get("fine_labels")))
+    x = np.vstack(xs).reshape(-1, 3, 32, 32).transpose(0, 2, 3, 1)
+    return x, np.asarray(ys, dtype=np.int64)
+
+
 def cifar10(root: str = "./data", train: bool = True, allow_synthetic: bool = True,
             synthetic_size: Optional[int] = None, verbose: bool = True) -> TensorDataset:
     """CIFAR-10 as tensors; synthetic stand-in of the same shape when the files are absent."""
-    got = _load_cifar_batches(root, train)
+    got = _load_cifar_batches(root, train) or _load_cifar_binary(root, train) or _load_cifar_tarball(root, train)
     if got is not None:
         x, y = got
         return TensorDataset(transform(x), torch.from_numpy(y), "cifar10")

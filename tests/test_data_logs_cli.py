@@ -196,3 +196,45 @@ def test_report_writes_accuracy_and_loss_curves_as_svg(tmp_path):
     doc = xml.dom.minidom.parse(str(out))
     assert len(doc.getElementsByTagName("polyline")) == 2 + 4        # accuracy per run; val + train loss per run
     assert "validation accuracy" in out.read_text()
+
+
+def test_cifar_readers_agree_on_pickled_binary_and_tarball_layouts(tmp_path):
+    """The three on-disk forms a user may have (extracted python batches as the reference's torchvision download leaves
+    them, the dataset's binary version, the undecompressed tarball) must give the same tensors, in [-1, 1], NCHW."""
+    import pickle
+    import tarfile
+
+    import numpy as np
+
+    rng = np.random.default_rng(0)
+    per = 4
+    data = [rng.integers(0, 256, size=(per, 3072), dtype=np.uint8) for _ in range(6)]      # 5 train files + test
+    labels = [rng.integers(0, 10, size=per).tolist() for _ in range(6)]
+    names = [f"data_batch_{i}" for i in range(1, 6)] + ["test_batch"]
+
+    py_root, bin_root, tar_root = tmp_path / "py", tmp_path / "bin", tmp_path / "tar"
+    (py_root / D.CIFAR_DIR).mkdir(parents=True)
+    (bin_root / D.CIFAR_BIN_DIR).mkdir(parents=True)
+    tar_root.mkdir()
+    for n, x, y in zip(names, data, labels):
+        with open(py_root / D.CIFAR_DIR / n, "wb") as f:
+            pickle.dump({"data": x, "labels": y}, f)
+        rec = np.concatenate([np.asarray(y, dtype=np.uint8)[:, None], x], axis=1)
+        rec.tofile(bin_root / D.CIFAR_BIN_DIR / f"{n}.bin")
+    with tarfile.open(tar_root / D.CIFAR_TARBALL, "w:gz") as tar:
+        tar.add(py_root / D.CIFAR_DIR, arcname=D.CIFAR_DIR)
+
+    for train, n_img in ((True, 5 * per), (False, per)):
+        got = [D.cifar10(str(r), train=train, allow_synthetic=False) for r in (py_root, bin_root, tar_root)]
+        for ds in got:
+            assert ds.source == "cifar10" and ds.images.shape == (n_img, 3, 32, 32) and ds.images.dtype == torch.float32
+            assert ds.labels.dtype == torch.int64 and float(ds.images.min()) >= -1.0 and float(ds.images.max()) <= 1.0
+        assert torch.equal(got[0].images, got[1].images) and torch.equal(got[0].images, got[2].images)
+        assert torch.equal(got[0].labels, got[1].labels) and torch.equal(got[0].labels, got[2].labels)
+    want = torch.from_numpy(data[0][0].reshape(3, 32, 32).astype(np.float32)) / 255.0 * 2 - 1
+    assert torch.allclose(D.cifar10(str(bin_root), train=True, allow_synthetic=False).images[0], want, atol=1e-6)
+    (bin_root / D.CIFAR_BIN_DIR / "test_batch.bin").write_bytes(b"\\0" * 100)
+    with pytest.raises(ValueError, match="3073-byte record"):
+        D.cifar10(str(bin_root), train=False, allow_synthetic=False)
+    with pytest.raises(FileNotFoundError):
+        D.cifar10(str(tmp_path / "nothing"), train=True, allow_synthetic=False)
