@@ -77,13 +77,30 @@ def spawn(n: int, cmd: List[str], env_extra=None, gpus: int | None = None) -> in
 
 def main(argv=None) -> int:
     ap = argparse.ArgumentParser(prog="mpiexec", description=__doc__, formatter_class=argparse.RawTextHelpFormatter)
-    ap.add_argument("-n", "-np", "--np", dest="n", type=int, required=True, help="number of processes")
+    ap.add_argument("-n", "-np", "--np", "-c", dest="n", type=int, required=True, help="number of processes")
+    # what people have in their Open MPI / MPICH command lines; accepted so that those lines keep working
+    ap.add_argument("--oversubscribe", "--allow-run-as-root", "--use-hwthread-cpus", "--report-bindings",
+                    "--tag-output", dest="_ignored", action="store_true", help="accepted, no effect (one node, one spawner)")
+    ap.add_argument("--bind-to", "--map-by", "--rank-by", dest="_ignored_1", metavar="X",
+                    help="accepted with its value, no effect")
+    ap.add_argument("--mca", dest="_ignored_2", nargs=2, action="append", metavar=("KEY", "VALUE"),
+                    help="accepted with its two values, no effect")
+    ap.add_argument("-x", dest="export", action="append", default=[], metavar="VAR[=VALUE]",
+                    help="Open MPI: export VAR (with VALUE, or its current value) to the processes")
+    ap.add_argument("-genv", "-env", dest="genv", action="append", nargs=2, default=[], metavar=("VAR", "VALUE"),
+                    help="MPICH: set VAR=VALUE for the processes")
     ap.add_argument("cmd", nargs=argparse.REMAINDER, help="program and its arguments")
     a = ap.parse_args(argv)
     cmd = a.cmd[1:] if a.cmd and a.cmd[0] == "--" else a.cmd
     if not cmd:
         ap.error("no command given")
-    return spawn(a.n, cmd)
+    env_extra = {}
+    for item in a.export:
+        name, eq, value = item.partition("=")
+        env_extra[name] = value if eq else os.environ.get(name, "")
+    for name, value in a.genv:
+        env_extra[name] = value
+    return spawn(a.n, cmd, env_extra=env_extra or None)
 
 
 if __name__ == "__main__":

@@ -479,3 +479,18 @@ def test_exchange_variants_offered_depend_on_probes_and_on_the_failure_mode():
     assert probe(2, 3, (0, 3.1, False), [True] * 2) == (True, [])              # rank 2 of 3 has no partner
     assert probe(0, 2, (0, 3.1, False), [False]) == (False, [1])               # the OTHER pair saw a torn line
     assert probe(0, 16, (0, 3.1, False), [True] * 15) == (False, [])           # the variant parks at most 7 peers' lines
+
+
+def test_mpiexec_front_end_accepts_the_usual_open_mpi_and_mpich_options():
+    """Command lines written for a real mpiexec keep working: placement options are accepted and ignored, `-x` and
+    `-genv` reach the processes' environment, every process gets its rank."""
+    code = "import os; print('rank', os.environ['RANK'], os.environ['WORLD_SIZE'], os.environ['FOO'], os.environ['BAZ'], os.environ['HOME_COPY'])"
+    env = dict(os.environ, HOME_COPY="from-parent")
+    out = subprocess.run([str(ROOT / "bin" / "mpiexec"), "--oversubscribe", "--allow-run-as-root", "--bind-to", "none",
+                          "--map-by", "slot", "--mca", "btl", "self,vader", "-x", "FOO=bar", "-x", "HOME_COPY",
+                          "-genv", "BAZ", "7", "-np", "3", sys.executable, "-c", code],
+                         capture_output=True, text=True, cwd=ROOT, timeout=120, env=env)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert sorted(out.stdout.split("\n")[:3]) == [f"rank {r} 3 bar 7 from-parent" for r in range(3)]
+    bad = subprocess.run([str(ROOT / "bin" / "mpiexec"), "-n", "2"], capture_output=True, text=True, cwd=ROOT, timeout=60)
+    assert bad.returncode != 0 and "no command given" in bad.stderr
